@@ -1,0 +1,122 @@
+/*
+ * szb200.h -- C-ABI of the CUDA shim under the drop-in API of include/sz.h, plus the device-pointer
+ * variants of the public calls.  extern "C", plain pointers and sizes only (no torch / C++ types).
+ *
+ * Layering (mirrors the reference's L3 -> L2/L1/L0 split):
+ *   sz_host.c (C)            SZ_Init / SZ_compress_args / SZ_decompress ...   == reference sz/src/sz.c, conf.c
+ *        |  calls
+ *   szb200_* below (this file; implemented in szb_shim.cu)                     == reference sz_float.c / sz_double.c /
+ *        |  launches                                                              szd_float.c / szd_double.c / Huffman.c
+ *   hand-written sm_100a kernels
+ *
+ * Each entry point cites the reference interface it replaces.  All functions return SZ_SCES (0) on success
+ * and a negative SZ_* code on failure; none of them falls back to the CPU.
+ */
+#ifndef SZB200_H
+#define SZB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* one blocked-regression job == one call of
+ *   SZ_compress_{float,double}_{2D,3D}_MDQ_nonblocked_with_blocked_regression  (ref: sz/src/sz_float.c:5516, :6527;
+ *   sz/src/sz_double.c:4900, :5904) or of the matching decompressDataSeries_* (ref: sz/src/szd_float.c:3141, :3483). */
+typedef struct szb200_job {
+    int dtype;                      /* SZ_FLOAT (0) or SZ_DOUBLE (1) */
+    int dim;                        /* 2 or 3 (a 4D array is flattened to (r4*r3, r2, r1) by the caller, ref: sz_float.c:3010) */
+    size_t n0, n1, n2;              /* slow -> fast.  dim == 2: (n1, n2) = (r2, r1) and n0 = 1 */
+    double eb;                      /* realPrecision as computed by getRealPrecision_* (ref: dataCompression.c:288-332) */
+    unsigned int max_quant_intervals;     /* <= 65536 */
+    unsigned int quantization_intervals;  /* 0: optimise (optQuantMode = 1); else fixed, even */
+    int sampleDistance;             /* >= 2 */
+    float predThreshold;
+} szb200_job;
+
+/* by-products of one job (the reference's HAVE_WRITESTATS counters, ref: sz/include/sz_stats.h:21-47) + stage timings */
+typedef struct szb200_stats {
+    unsigned int intervals;
+    int use_mean;
+    double mean;
+    size_t num_blocks, reg_count, total_unpred;
+    unsigned int tree_bytes, node_count;
+    size_t type_bits_bytes;         /* Huffman payload of the quantisation codes */
+    size_t body_bytes;              /* everything after the 4+MD-byte header */
+    float ms_total;                 /* device time of the whole job (CUDA events) */
+    float ms_stage[16];             /* per stage, see szb200_stage_name() */
+    unsigned int launches;          /* kernels launched by this job */
+} szb200_stats;
+
+const char *szb200_stage_name(int i);
+
+/* device management: one context (stream + grow-only workspace) per device and host thread */
+int szb200_device_count(void);
+int szb200_set_device(int device);
+const char *szb200_last_error(void);
+/* release the workspace of the current device's context */
+void szb200_release(void);
+
+/* H2D staging for the host-pointer API: copies into the context's input buffer, returns the device pointer
+ * (valid until the next call on this context).  NULL on failure. */
+void *szb200_stage_input(const void *host_ptr, size_t bytes);
+
+/* device staging buffer of the context for the host-pointer decompress call (valid until the next call) */
+void *szb200_output_buffer(size_t bytes);
+
+/* replaces computeRangeSize_float/_double (ref: sz/src/dataCompression.c:102-119, :149-166).
+ * d_data is a DEVICE pointer.  vmin / vmax are the first-occurrence minimum and maximum (bit pattern preserved). */
+int szb200_range(int dtype, const void *d_data, size_t n, double *vmin, double *vmax);
+
+/* replaces the body of SZ_compress_*_MDQ_nonblocked_with_blocked_regression (see szb200_job) from the element-count
+ * field onwards (offset 4+MD): writes [N:8][block_size:4][eb:T][intervals:4]...[type bits].
+ * d_data: DEVICE pointer to the original array.  dst: destination of the body (device pointer if dst_on_device). */
+int szb200_compress_blocked(const szb200_job *job, const void *d_data, void *dst, int dst_on_device,
+                            size_t dst_capacity, size_t *body_size, szb200_stats *stats);
+/* upper bound of the body size for a job (the reference's calloc size, ref: sz_float.c:7394) */
+size_t szb200_body_capacity(const szb200_job *job);
+
+/* replaces decompressDataSeries_*_nonblocked_with_blocked_regression (ref: szd_float.c:3141, :3483; szd_double.c:2974,
+ * :3316).  body: the stream from the block_size field onwards (i.e. tdps->raBytes, ref: TightDataPointStorageF.c:121).
+ * d_out: DEVICE pointer to N elements. */
+int szb200_decompress_blocked(const szb200_job *job, const void *body, size_t body_len, int body_on_device,
+                              void *d_out, szb200_stats *stats);
+
+/* replaces the big-endian copy loops of SZ_compress_args_*_StoreOriData (ref: sz_float.c:526-559) and of the
+ * isLossless branch of SZ_decompress_args_* (ref: szd_float.c:106-119): element-wise byte swap on the device */
+int szb200_swap_copy(int dtype, const void *src, int src_on_device, void *dst, int dst_on_device, size_t n);
+/* constant stream decode (ref: TightDataPointStorageF.c:590-629 / getSnapshotData_*): fill n elements */
+int szb200_fill(int dtype, double value, void *d_out, size_t n);
+/* protectValueRange clamp (ref: szd_float.c:161-176) */
+int szb200_clamp(int dtype, void *d_out, size_t n, double vmin, double vmax);
+/* plain copies through the context's stream */
+int szb200_copy(void *dst, const void *src, size_t bytes, int kind /*0 h2d, 1 d2h, 2 d2d*/);
+int szb200_sync(void);
+/* CUDA stream of the current context as an opaque handle (cudaStream_t) -- lets a caller order its own work */
+void *szb200_stream(void);
+
+/* ---- device-pointer variants of the public API (same semantics as SZ_compress_args / SZ_decompress_args,
+ * ref: sz/src/sz.c:294, :584, but data and stream live in device memory; implemented in sz_host.c) ---- */
+size_t szb200_compress_bound(int dataType, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+int szb200_compress_args_device(int dataType, const void *d_data, void *d_stream, size_t stream_capacity, size_t *outSize,
+                                int errBoundMode, double absErrBound, double relBoundRatio,
+                                size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+int szb200_decompress_device(int dataType, const void *d_stream, size_t byteLength, void *d_out,
+                             size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+/* statistics of the most recent job on this context */
+int szb200_last_stats(szb200_stats *out);
+
+/* ---- debug / parity triage: copy intermediates of the most recent compress job to host memory ----------
+ * which: 0 reg_params [ncoef][num_blocks] (T)   1 indicator [num_blocks] (u8, 1 = Lorenzo)
+ *        2 coeff_last [ncoef][num_blocks] (T)   3 type codes [N] (u16, block-major)
+ *        4 recon field [N] (T, raster)           5 coeff_type [ncoef][num_blocks] (u16, first reg_count valid)
+ *        6 code histogram [2*intervals] (u32)
+ * returns the number of bytes copied (<= cap) or a negative code */
+long long szb200_debug_fetch(int which, void *host_dst, size_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

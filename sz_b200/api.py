@@ -1,0 +1,196 @@
+"""ctypes binding of libSZ_b200.so.  Mirrors the reference's operator interface for this path
+(SZ_Init / SZ_compress_args / SZ_decompress, ref: sz/include/sz.h:253-334) plus the device-pointer variants
+declared in include/szb200.h.  numpy arrays are HOST buffers; torch CUDA tensors are DEVICE buffers."""
+import ctypes as C
+import os
+import tempfile
+
+import numpy as np
+
+SZ_FLOAT, SZ_DOUBLE = 0, 1
+ABS, REL, ABS_AND_REL, ABS_OR_REL = 0, 1, 2, 3
+_MODE_NAMES = {ABS: "ABS", REL: "REL", ABS_AND_REL: "ABS_AND_REL", ABS_OR_REL: "ABS_OR_REL"}
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libSZ_b200.so")
+
+
+class SZError(RuntimeError):
+    pass
+
+
+class Stats(C.Structure):
+    _fields_ = [("intervals", C.c_uint), ("use_mean", C.c_int), ("mean", C.c_double), ("num_blocks", C.c_size_t), ("reg_count", C.c_size_t),
+                ("total_unpred", C.c_size_t), ("tree_bytes", C.c_uint), ("node_count", C.c_uint), ("type_bits_bytes", C.c_size_t),
+                ("body_bytes", C.c_size_t), ("ms_total", C.c_float), ("ms_stage", C.c_float * 16), ("launches", C.c_uint)]
+
+    def as_dict(self):
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "ms_stage"}
+        d["ms_stage"] = {n: self.ms_stage[i] for i, n in enumerate(stage_names()) if n}
+        return d
+
+
+_lib = None
+
+
+def lib():
+    """Load libSZ_b200.so (built in-tree by `__graft_entry__.build()` / `make -C sz_b200/csrc`). Fails loudly if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SZError("libSZ_b200.so not built: run `python -c 'import __graft_entry__ as g; g.build()'` (no CPU fallback exists)")
+    L = C.CDLL(LIB_PATH)
+    sz = C.c_size_t
+    L.SZ_Init.argtypes = [C.c_char_p]; L.SZ_Init.restype = C.c_int
+    L.SZ_Finalize.argtypes = []; L.SZ_Finalize.restype = None
+    L.SZ_compress_args.argtypes = [C.c_int, C.c_void_p, C.POINTER(sz), C.c_int, C.c_double, C.c_double, C.c_double] + [sz] * 5
+    L.SZ_compress_args.restype = C.c_void_p
+    L.SZ_decompress.argtypes = [C.c_int, C.c_void_p, sz] + [sz] * 5; L.SZ_decompress.restype = C.c_void_p
+    L.SZ_decompress_args.argtypes = [C.c_int, C.c_void_p, sz, C.c_void_p] + [sz] * 5; L.SZ_decompress_args.restype = sz
+    L.szb200_compress_bound.argtypes = [C.c_int] + [sz] * 5; L.szb200_compress_bound.restype = sz
+    L.szb200_compress_args_device.argtypes = [C.c_int, C.c_void_p, C.c_void_p, sz, C.POINTER(sz), C.c_int, C.c_double, C.c_double] + [sz] * 5
+    L.szb200_compress_args_device.restype = C.c_int
+    L.szb200_decompress_device.argtypes = [C.c_int, C.c_void_p, sz, C.c_void_p] + [sz] * 5; L.szb200_decompress_device.restype = C.c_int
+    L.szb200_last_stats.argtypes = [C.POINTER(Stats)]; L.szb200_last_stats.restype = C.c_int
+    L.szb200_last_error.argtypes = []; L.szb200_last_error.restype = C.c_char_p
+    L.szb200_stage_name.argtypes = [C.c_int]; L.szb200_stage_name.restype = C.c_char_p
+    L.szb200_set_device.argtypes = [C.c_int]; L.szb200_set_device.restype = C.c_int
+    L.szb200_device_count.argtypes = []; L.szb200_device_count.restype = C.c_int
+    L.szb200_debug_fetch.argtypes = [C.c_int, C.c_void_p, sz]; L.szb200_debug_fetch.restype = C.c_longlong
+    L.szb200_release.argtypes = []; L.szb200_release.restype = None
+    L.szb200_sync.argtypes = []; L.szb200_sync.restype = C.c_int
+    L.szb200_stream.argtypes = []; L.szb200_stream.restype = C.c_void_p
+    L.szb200_range.argtypes = [C.c_int, C.c_void_p, sz, C.POINTER(C.c_double), C.POINTER(C.c_double)]; L.szb200_range.restype = C.c_int
+    _lib = L
+    return L
+
+
+_libc = C.CDLL(None)
+_libc.free.argtypes = [C.c_void_p]
+
+
+def stage_names():
+    L = lib()
+    return [L.szb200_stage_name(i).decode() for i in range(16)]
+
+
+def _dims5(shape):
+    r = list(reversed(shape)) + [0] * (5 - len(shape))
+    return r[4], r[3], r[2], r[1], r[0]
+
+
+def _code(dtype):
+    dt = np.dtype(dtype)
+    if dt == np.float32:
+        return SZ_FLOAT
+    if dt == np.float64:
+        return SZ_DOUBLE
+    raise SZError("only float32 / float64 are on this path (got %s)" % dt)
+
+
+_DEFAULT_CFG = dict(max_quant_intervals=65536, quantization_intervals=0, sampleDistance=100, predThreshold=0.99, szMode="SZ_BEST_SPEED",
+                    protectValueRange="NO", withLinearRegression="YES", errorBoundMode="ABS", absErrBound=1e-4, relBoundRatio=1e-4)
+
+
+def init(cfg=None, path=None):
+    """SZ_Init with an sz.config written from `cfg` (same keys as the reference's example/sz.config), or with `path`."""
+    L = lib()
+    if path is not None:
+        rc = L.SZ_Init(path.encode())
+    else:
+        c = dict(_DEFAULT_CFG)
+        c.update(cfg or {})
+        fd, p = tempfile.mkstemp(suffix=".config")
+        os.close(fd)
+        try:
+            with open(p, "w") as f:
+                f.write("[ENV]\ndataEndianType = LITTLE_ENDIAN_DATA\nsol_name = SZ\n[PARAMETER]\n")
+                for k in ("withLinearRegression", "protectValueRange", "sampleDistance", "quantization_intervals", "max_quant_intervals", "szMode", "errorBoundMode"):
+                    f.write("%s = %s\n" % (k, c[k]))
+                f.write("predThreshold = %r\nabsErrBound = %r\nrelBoundRatio = %r\n" % (c["predThreshold"], float(c["absErrBound"]), float(c["relBoundRatio"])))
+            rc = L.SZ_Init(p.encode())
+        finally:
+            os.unlink(p)
+    if rc != 0:
+        raise SZError("SZ_Init failed (rc=%d)" % rc)
+
+
+def finalize():
+    lib().SZ_Finalize()
+
+
+def set_device(dev):
+    if lib().szb200_set_device(int(dev)) != 0:
+        raise SZError(lib().szb200_last_error().decode())
+
+
+def compress(a, mode, abs_eb=0.0, rel=0.0):
+    """SZ_compress_args on a HOST numpy array -> bytes (H2D, kernels, D2H all inside the call)."""
+    L = lib()
+    a = np.ascontiguousarray(a)
+    n = C.c_size_t(0)
+    p = L.SZ_compress_args(_code(a.dtype), a.ctypes.data, C.byref(n), int(mode), float(abs_eb), float(rel), 0.0, *_dims5(a.shape))
+    if not p:
+        raise SZError("SZ_compress_args failed: %s" % L.szb200_last_error().decode())
+    out = C.string_at(p, n.value)
+    _libc.free(p)
+    return out
+
+
+def decompress(stream, dtype, shape):
+    """SZ_decompress of a HOST byte stream -> numpy array."""
+    L = lib()
+    dt = np.dtype(dtype)
+    buf = np.frombuffer(stream, dtype=np.uint8)
+    p = L.SZ_decompress(_code(dt), buf.ctypes.data, buf.size, *_dims5(shape))
+    if not p:
+        raise SZError("SZ_decompress failed: %s" % L.szb200_last_error().decode())
+    n = int(np.prod(shape))
+    out = np.frombuffer(C.string_at(p, n * dt.itemsize), dtype=dt).reshape(shape).copy()
+    _libc.free(p)
+    return out
+
+
+def compress_bound(dtype, shape):
+    return int(lib().szb200_compress_bound(_code(dtype), *_dims5(shape)))
+
+
+def compress_device(x, out, mode, abs_eb=0.0, rel=0.0):
+    """Device-resident compress: x is a contiguous torch CUDA tensor (float32/float64), out a uint8 CUDA tensor of at least
+    compress_bound() bytes.  Returns the stream length."""
+    import torch
+    assert x.is_cuda and out.is_cuda and x.is_contiguous() and out.dtype == torch.uint8
+    code = SZ_FLOAT if x.dtype == torch.float32 else SZ_DOUBLE
+    n = C.c_size_t(0)
+    L = lib()
+    rc = L.szb200_compress_args_device(code, x.data_ptr(), out.data_ptr(), out.numel(), C.byref(n), int(mode), float(abs_eb), float(rel), *_dims5(tuple(x.shape)))
+    if rc != 0:
+        raise SZError("szb200_compress_args_device rc=%d: %s" % (rc, L.szb200_last_error().decode()))
+    return n.value
+
+
+def decompress_device(stream, nbytes, out):
+    """Device-resident decompress: stream is a uint8 CUDA tensor, out a contiguous CUDA tensor of the original shape/dtype."""
+    import torch
+    assert stream.is_cuda and out.is_cuda and out.is_contiguous()
+    code = SZ_FLOAT if out.dtype == torch.float32 else SZ_DOUBLE
+    L = lib()
+    rc = L.szb200_decompress_device(code, stream.data_ptr(), int(nbytes), out.data_ptr(), *_dims5(tuple(out.shape)))
+    if rc != 0:
+        raise SZError("szb200_decompress_device rc=%d: %s" % (rc, L.szb200_last_error().decode()))
+    return out
+
+
+def last_stats():
+    s = Stats()
+    if lib().szb200_last_stats(C.byref(s)) != 0:
+        return None
+    return s
+
+
+def debug_fetch(which, dtype, count):
+    buf = np.zeros(count, dtype=dtype)
+    n = lib().szb200_debug_fetch(which, buf.ctypes.data, buf.nbytes)
+    if n < 0:
+        raise SZError("debug_fetch(%d) failed" % which)
+    return buf[: n // buf.itemsize]

@@ -1,0 +1,438 @@
+// szb_huffman.cuh -- quant-code histogram, exact SZ Huffman tree (heap emulation), code table + tree serialisation,
+// encode (per-chunk bit lengths + prefix sum + bit scatter) and the marker-less parallel decode.
+// ref: sz/src/Huffman.c:17-185 (tree), :122-157 (codes), :205-308 (encode), :310-343 (decode), :443-585 (serialise),
+//      :656-788 (reconstruct); call sites sz/src/sz_float.c:7379-7471.
+#pragma once
+#include "szb_common.cuh"
+
+namespace szb {
+
+// =====================================================================================================================
+// Block-major <-> raster index iterator.  The reference emits type[] / unpredictable data "block-major": blocks in
+// (b0,b1,b2) raster order, points inside a block in (ii,jj,kk) raster order (ref: sz_float.c:7064, :7359).  Our code
+// array lives in RASTER order (the wavefront kernels want coalesced rows), so the encoder/decoder walk block-major
+// order and translate to raster addresses incrementally.
+// =====================================================================================================================
+struct BMIter {
+    uint32_t b0, b1, b2, ii, jj, kk, sx, sy, sz;
+    uint64_t raster;
+    __device__ __forceinline__ static void split_div(uint64_t &rem, uint64_t unit, const Axis &a, uint32_t &b, uint32_t &edge) {
+        uint64_t cut = (uint64_t)a.split * a.early * unit;
+        if (rem < cut) { uint64_t u = (uint64_t)a.early * unit; b = (uint32_t)(rem / u); rem -= (uint64_t)b * u; edge = a.early; }
+        else { uint64_t r2 = rem - cut; uint64_t u = (uint64_t)a.late * unit; uint32_t bb = (uint32_t)(r2 / u); rem = r2 - (uint64_t)bb * u; b = a.split + bb; edge = a.late; }
+    }
+    __device__ __forceinline__ void set_raster(const Geom &g) {
+        raster = ((uint64_t)(g.ax[0].off(b0) + ii) * g.ax[1].n + (g.ax[1].off(b1) + jj)) * g.ax[2].n + g.ax[2].off(b2) + kk;
+    }
+    __device__ __forceinline__ void init(const Geom &g, uint64_t p) {
+        uint64_t rem = p;
+        split_div(rem, g.s0, g.ax[0], b0, sx);
+        split_div(rem, (uint64_t)sx * g.ax[2].n, g.ax[1], b1, sy);
+        split_div(rem, (uint64_t)sx * sy, g.ax[2], b2, sz);
+        uint64_t plane = (uint64_t)sy * sz;
+        ii = (uint32_t)(rem / plane); rem -= (uint64_t)ii * plane;
+        jj = (uint32_t)(rem / sz); kk = (uint32_t)(rem - (uint64_t)jj * sz);
+        set_raster(g);
+    }
+    __device__ __forceinline__ void next(const Geom &g) {
+        kk++; raster++;
+        if (kk == sz) {
+            kk = 0; jj++; raster += g.ax[2].n - sz;
+            if (jj == sy) {
+                jj = 0; ii++; raster += g.s0 - (uint64_t)sy * g.ax[2].n;
+                if (ii == sx) {
+                    ii = 0; b2++;
+                    if (b2 == g.ax[2].nb) { b2 = 0; b1++; if (b1 == g.ax[1].nb) { b1 = 0; b0++; } }
+                    if (b0 < g.ax[0].nb) { sx = g.ax[0].edge(b0); sy = g.ax[1].edge(b1); sz = g.ax[2].edge(b2); set_raster(g); }
+                }
+            }
+        }
+    }
+};
+
+// =====================================================================================================================
+// histogram of u16 symbols (order-independent): shared-memory privatisation when the bin count fits, 128-bit loads
+// =====================================================================================================================
+__global__ void __launch_bounds__(512) hist_kernel(const uint16_t *__restrict__ s, uint64_t n, uint32_t nbins, uint32_t *g_hist, int use_smem) {
+    extern __shared__ uint32_t s_hist[];
+    if (use_smem) { for (uint32_t i = threadIdx.x; i < nbins; i += blockDim.x) s_hist[i] = 0; __syncthreads(); }
+    uint32_t *h = use_smem ? s_hist : g_hist;
+    uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (uint64_t)gridDim.x * blockDim.x;
+    uint64_t head = ((16 - ((uintptr_t)s & 15)) & 15) / 2; if (head > n) head = n;
+    if (tid < head) atomicAdd(&h[s[tid]], 1u);
+    const uint4 *sv = reinterpret_cast<const uint4 *>(s + head);
+    uint64_t nvec = (n - head) / 8;
+    for (uint64_t i = tid; i < nvec; i += nthreads) {
+        uint4 v = __ldg(sv + i);
+        uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) { atomicAdd(&h[w[q] & 0xffffu], 1u); atomicAdd(&h[w[q] >> 16], 1u); }
+    }
+    uint64_t tail0 = head + nvec * 8;
+    if (tail0 + tid < n) atomicAdd(&h[s[tail0 + tid]], 1u);
+    if (use_smem) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < nbins; i += blockDim.x) { uint32_t v = s_hist[i]; if (v) atomicAdd(&g_hist[i], v); }
+    }
+}
+
+// =====================================================================================================================
+// Huffman tree build: EXACT emulation of the reference's binary-heap construction, one CTA per tree.
+//   leaves inserted in increasing symbol order; merge step as gcc compiles Huffman.c:181: b = qremove(), a = qremove(),
+//   parent.left = a, parent.right = b.  The heap holds (freq, node, subtree size) entries in shared memory when it fits
+//   (global-memory fallback otherwise); the serial part is done by thread 0, the code assignment and the pre-order
+//   serialisation (pad_tree_*, Huffman.c:443-501) are breadth-first over the finished tree with the whole CTA.
+// =====================================================================================================================
+struct HuffTreeDesc {           // per-tree I/O, all pointers to global memory
+    const uint32_t *hist;       // [nbins]
+    uint32_t nbins;             // stateNum (symbols are < nbins)
+    // workspace, capacity 2*max_leaves nodes
+    uint32_t *n_left, *n_right, *n_sizeL, *n_sym;   // internal: left/right/size of left subtree; leaf: symbol in n_sym, left=right=0xffffffff
+    uint32_t *n_pre;            // pre-order index
+    uint64_t *n_code;           // right-aligned code bits
+    uint8_t *n_len;
+    uint32_t *frontier;         // [2][capacity]
+    uint32_t *heap_g;           // global fallback heap: [3][capacity]
+    // outputs
+    uint64_t *code;             // [nbins] right-aligned bits
+    uint8_t *clen;              // [nbins]
+    unsigned char *tree_bytes;  // serialised tree
+    uint32_t *out;              // [0]=treeByteSize [1]=nodeCount [2]=leaves [3]=error(1 = code longer than 64 bits)
+    uint32_t capacity;          // node capacity
+};
+
+struct HeapView { uint32_t *f, *n, *s; };
+
+__device__ __forceinline__ void heap_insert(HeapView h, int &qend, uint32_t freq, uint32_t node, uint32_t size) {
+    int j, i = qend++;
+    while ((j = i >> 1)) {                                     // ref: Huffman.c:76-85
+        uint32_t fj = h.f[j];
+        if (fj <= freq) break;
+        h.f[i] = fj; h.n[i] = h.n[j]; h.s[i] = h.s[j]; i = j;
+    }
+    h.f[i] = freq; h.n[i] = node; h.s[i] = size;
+}
+__device__ __forceinline__ void heap_remove(HeapView h, int &qend, uint32_t &freq, uint32_t &node, uint32_t &size) {
+    freq = h.f[1]; node = h.n[1]; size = h.s[1];               // ref: Huffman.c:87-114
+    qend--;
+    uint32_t mf = h.f[qend], mn = h.n[qend], ms = h.s[qend];   // element moved to the root, kept in registers ("hole" form of the swaps)
+    int i = 1, l;
+    while ((l = i << 1) < qend) {
+        uint32_t fl = h.f[l];
+        if (l + 1 < qend) { uint32_t fr = h.f[l + 1]; if (fr < fl) { l++; fl = fr; } }
+        if (mf > fl) { h.f[i] = fl; h.n[i] = h.n[l]; h.s[i] = h.s[l]; i = l; }
+        else break;
+    }
+    h.f[i] = mf; h.n[i] = mn; h.s[i] = ms;
+}
+
+__global__ void __launch_bounds__(1024) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
+    extern __shared__ uint32_t s_heap[];
+    const HuffTreeDesc D = descs[blockIdx.x];
+    __shared__ uint32_t s_root, s_leaves, s_cnt[2], s_err;
+    const int t = threadIdx.x;
+    // ---- leaves in increasing symbol order: parallel count, serial insert ----
+    if (t == 0) {
+        uint32_t leaves = 0;
+        for (uint32_t i = 0; i < D.nbins; i++) if (D.hist[i]) leaves++;
+        s_leaves = leaves; s_err = 0;
+        HeapView h;
+        if (leaves + 2 <= smem_heap_capacity) { h.f = s_heap; h.n = s_heap + smem_heap_capacity; h.s = s_heap + 2 * smem_heap_capacity; }
+        else { h.f = D.heap_g; h.n = D.heap_g + D.capacity; h.s = D.heap_g + 2 * D.capacity; }
+        int qend = 1;
+        uint32_t nn = 0;
+        for (uint32_t i = 0; i < D.nbins; i++) {
+            uint32_t f = D.hist[i];
+            if (f) { D.n_left[nn] = 0xffffffffu; D.n_right[nn] = 0xffffffffu; D.n_sizeL[nn] = 0; D.n_sym[nn] = i; heap_insert(h, qend, f, nn, 1u); nn++; }
+        }
+        while (qend > 2) {
+            uint32_t fb, nb_, sb, fa, na, sa;
+            heap_remove(h, qend, fb, nb_, sb);     // first removed -> right
+            heap_remove(h, qend, fa, na, sa);      // second removed -> left
+            D.n_left[nn] = na; D.n_right[nn] = nb_; D.n_sizeL[nn] = sa; D.n_sym[nn] = 0;
+            heap_insert(h, qend, fa + fb, nn, sa + sb + 1u);
+            nn++;
+        }
+        s_root = (leaves > 0) ? h.n[1] : 0;
+    }
+    __syncthreads();
+    const uint32_t leaves = s_leaves;
+    const uint32_t nodeCount = leaves ? 2 * leaves - 1 : 0;
+    for (uint32_t i = t; i < D.nbins; i += blockDim.x) { D.code[i] = 0; D.clen[i] = 0; }
+    if (leaves == 0) { if (t == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = 0; D.out[3] = 0; } return; }
+    // ---- serialised layout (ref: Huffman.c:503-585): [endian:1][L: w*n][R: w*n][C: 4*n][t: n], native endian ----
+    const uint32_t w = nodeCount <= 256 ? 1u : (nodeCount <= 65536 ? 2u : 4u);
+    unsigned char *tb = D.tree_bytes;
+    unsigned char *pl = tb + 1, *pr = pl + (size_t)w * nodeCount, *pc = pr + (size_t)w * nodeCount, *pt = pc + (size_t)4 * nodeCount;
+    auto put_w = [&](unsigned char *base, uint32_t idx, uint32_t v) {
+        if (w == 1) base[idx] = (unsigned char)v;
+        else if (w == 2) { base[2 * idx] = (unsigned char)v; base[2 * idx + 1] = (unsigned char)(v >> 8); }
+        else { base[4 * idx] = (unsigned char)v; base[4 * idx + 1] = (unsigned char)(v >> 8); base[4 * idx + 2] = (unsigned char)(v >> 16); base[4 * idx + 3] = (unsigned char)(v >> 24); }
+    };
+    // ---- breadth-first: pre-order index + code per node ----
+    uint32_t *fr0 = D.frontier, *fr1 = D.frontier + D.capacity;
+    if (t == 0) { tb[0] = 0; fr0[0] = s_root; D.n_pre[s_root] = 0; D.n_code[s_root] = 0; D.n_len[s_root] = 0; s_cnt[0] = 1; s_cnt[1] = 0; }
+    __syncthreads();
+    int cur = 0;
+    for (int depth = 0; depth < 70; depth++) {
+        uint32_t cnt = s_cnt[cur];
+        if (cnt == 0) break;
+        uint32_t *fin = cur ? fr1 : fr0, *fout = cur ? fr0 : fr1;
+        for (uint32_t q = t; q < cnt; q += blockDim.x) {
+            uint32_t n = fin[q];
+            uint32_t pre = D.n_pre[n]; uint64_t code = D.n_code[n]; uint32_t len = D.n_len[n];
+            uint32_t l = D.n_left[n], r = D.n_right[n];
+            if (l == 0xffffffffu) {            // leaf
+                uint32_t sym = D.n_sym[n];
+                put_w(pl, pre, 0); put_w(pr, pre, 0);
+                pc[4 * pre] = (unsigned char)sym; pc[4 * pre + 1] = (unsigned char)(sym >> 8); pc[4 * pre + 2] = (unsigned char)(sym >> 16); pc[4 * pre + 3] = (unsigned char)(sym >> 24);
+                pt[pre] = 1;
+                if (len > 64) s_err = 1;
+                D.code[sym] = code; D.clen[sym] = (uint8_t)len;
+            } else {
+                uint32_t pre_l = pre + 1, pre_r = pre + 1 + D.n_sizeL[n];
+                put_w(pl, pre, pre_l); put_w(pr, pre, pre_r);
+                pc[4 * pre] = 0; pc[4 * pre + 1] = 0; pc[4 * pre + 2] = 0; pc[4 * pre + 3] = 0;
+                pt[pre] = 0;
+                D.n_pre[l] = pre_l; D.n_pre[r] = pre_r;
+                D.n_code[l] = code << 1; D.n_code[r] = (code << 1) | 1ULL;
+                D.n_len[l] = (uint8_t)(len + 1); D.n_len[r] = (uint8_t)(len + 1);
+                uint32_t o = atomicAdd(&s_cnt[cur ^ 1], 2u);
+                fout[o] = l; fout[o + 1] = r;
+            }
+        }
+        __syncthreads();
+        if (t == 0) s_cnt[cur] = 0;
+        cur ^= 1;
+        __syncthreads();
+    }
+    if (t == 0) { D.out[0] = 1 + 2 * w * nodeCount + 4 * nodeCount + nodeCount; D.out[1] = nodeCount; D.out[2] = leaves; D.out[3] = s_err | (s_cnt[cur] ? 1u : 0u); }
+}
+
+// =====================================================================================================================
+// encode: pass 1 = bit length + zero-code count per CTA chunk; pass 2 = bit scatter at absolute bit offsets and
+// block-major scatter of the unpredictable values.  BLOCKMAJOR = walk block-major order over a raster code array
+// (main type array); otherwise the symbol array is linear (coefficient codes).
+// =====================================================================================================================
+constexpr int ENC_THREADS = 256;
+constexpr int ENC_PER_THREAD = 16;
+constexpr int ENC_CHUNK = ENC_THREADS * ENC_PER_THREAD;
+
+template <bool BLOCKMAJOR>
+__global__ void __launch_bounds__(ENC_THREADS) enc_len_kernel(const uint16_t *__restrict__ s, uint64_t n, Geom g, const uint8_t *__restrict__ clen,
+                                                              uint32_t *chunk_bits, uint32_t *chunk_zeros) {
+    const uint64_t p0 = ((uint64_t)blockIdx.x * ENC_THREADS + threadIdx.x) * ENC_PER_THREAD;
+    uint32_t bits = 0, zeros = 0;
+    if (p0 < n) {
+        BMIter it;
+        if (BLOCKMAJOR) it.init(g, p0);
+        const int cnt = (int)min((uint64_t)ENC_PER_THREAD, n - p0);
+        for (int q = 0; q < cnt; q++) {
+            uint32_t sym = BLOCKMAJOR ? s[it.raster] : s[p0 + q];
+            bits += clen[sym];
+            zeros += (sym == 0);
+            if (BLOCKMAJOR) it.next(g);
+        }
+    }
+    __shared__ uint32_t sb[ENC_THREADS / 32], sz_[ENC_THREADS / 32];
+    for (int o = 16; o > 0; o >>= 1) { bits += __shfl_xor_sync(0xffffffffu, bits, o); zeros += __shfl_xor_sync(0xffffffffu, zeros, o); }
+    if ((threadIdx.x & 31) == 0) { sb[threadIdx.x >> 5] = bits; sz_[threadIdx.x >> 5] = zeros; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t b = 0, z = 0;
+        for (int i = 0; i < ENC_THREADS / 32; i++) { b += sb[i]; z += sz_[i]; }
+        chunk_bits[blockIdx.x] = b; chunk_zeros[blockIdx.x] = z;
+    }
+}
+
+template <typename T, bool BLOCKMAJOR>
+__global__ void __launch_bounds__(ENC_THREADS) enc_write_kernel(const uint16_t *__restrict__ s, uint64_t n, Geom g,
+                                                                const uint64_t *__restrict__ code, const uint8_t *__restrict__ clen,
+                                                                const unsigned long long *__restrict__ chunk_bit_off,
+                                                                const unsigned long long *__restrict__ chunk_zero_off,
+                                                                uint32_t *out_words /*zeroed, 4-byte aligned*/,
+                                                                const T *__restrict__ x, T *unpred_out) {
+    const uint64_t p0 = ((uint64_t)blockIdx.x * ENC_THREADS + threadIdx.x) * ENC_PER_THREAD;
+    uint32_t syms[ENC_PER_THREAD];
+    uint64_t rast0 = 0;
+    uint32_t bits = 0, zeros = 0;
+    int cnt = 0;
+    BMIter it0;
+    if (p0 < n) {
+        BMIter it;
+        if (BLOCKMAJOR) { it.init(g, p0); it0 = it; rast0 = it.raster; }
+        cnt = (int)min((uint64_t)ENC_PER_THREAD, n - p0);
+#pragma unroll
+        for (int q = 0; q < ENC_PER_THREAD; q++) {
+            if (q < cnt) {
+                uint32_t sym = BLOCKMAJOR ? s[it.raster] : s[p0 + q];
+                syms[q] = sym; bits += clen[sym]; zeros += (sym == 0);
+                if (BLOCKMAJOR) it.next(g);
+            } else syms[q] = 0;
+        }
+    }
+    (void)rast0;
+    // CTA-wide exclusive prefix of (bits, zeros)
+    __shared__ uint32_t wb[ENC_THREADS / 32], wz[ENC_THREADS / 32];
+    uint32_t ib = bits, iz = zeros;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t a = __shfl_up_sync(0xffffffffu, ib, o), b = __shfl_up_sync(0xffffffffu, iz, o);
+        if (lane >= o) { ib += a; iz += b; }
+    }
+    if (lane == 31) { wb[wid] = ib; wz[wid] = iz; }
+    __syncthreads();
+    uint32_t pb = 0, pz = 0;
+    for (int i = 0; i < wid; i++) { pb += wb[i]; pz += wz[i]; }
+    if (cnt == 0) return;
+    uint64_t pos = chunk_bit_off[blockIdx.x] + pb + (ib - bits);
+    uint64_t zr = chunk_zero_off[blockIdx.x] + pz + (iz - zeros);
+    // bit scatter: MSB-first stream, 32-bit big-endian words, atomicOr on shared boundary words
+    uint64_t widx = pos >> 5;
+    uint32_t fill = (uint32_t)(pos & 31), cur = 0;
+    BMIter it = it0;
+#pragma unroll
+    for (int q = 0; q < ENC_PER_THREAD; q++) {
+        if (q < cnt) {
+            uint32_t sym = syms[q];
+            uint32_t len = clen[sym];
+            uint64_t cb = code[sym];
+            while (len > 0) {
+                uint32_t take = min(32u - fill, len);
+                uint32_t piece = (uint32_t)((cb >> (len - take)) & ((take == 32) ? 0xffffffffULL : ((1ULL << take) - 1ULL)));
+                cur |= piece << (32 - fill - take);
+                fill += take; len -= take;
+                if (fill == 32) { atomicOr(out_words + widx, bswap32(cur)); widx++; cur = 0; fill = 0; }
+            }
+            if (unpred_out && sym == 0) { unpred_out[zr++] = BLOCKMAJOR ? x[it.raster] : x[p0 + q]; }
+            if (BLOCKMAJOR) it.next(g);
+        }
+    }
+    if (fill > 0 && cur != 0) atomicOr(out_words + widx, bswap32(cur));
+}
+
+// =====================================================================================================================
+// decode.  The stream carries no chunk index (ref: Huffman.c:310-343 is a bit-serial walk), so the decoder is
+// self-synchronising: every thread owns a fixed-size sub-sequence of the bit stream; it first decodes speculatively
+// from the sub-sequence start, then repeatedly restarts from the position where its predecessor's last codeword ended
+// until no start position changes any more (Jacobi iteration; after m rounds the first m+1 sub-sequences are exact,
+// a fixed point is therefore the exact serial decode).  Counts are prefix-summed and a final pass writes symbols.
+// =====================================================================================================================
+constexpr int DEC_SUB_BITS = 256;
+
+// unpack the serialised tree (arbitrary byte alignment) into u32 child arrays; leaf <=> t != 0
+__global__ void dec_tree_unpack_kernel(const unsigned char *__restrict__ tb, uint32_t nodeCount, uint32_t *L, uint32_t *R, uint32_t *C, uint8_t *leaf) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nodeCount) return;
+    const uint32_t w = nodeCount <= 256 ? 1u : (nodeCount <= 65536 ? 2u : 4u);
+    const unsigned char *pl = tb + 1, *pr = pl + (size_t)w * nodeCount, *pc = pr + (size_t)w * nodeCount, *pt = pc + (size_t)4 * nodeCount;
+    uint32_t l = 0, r = 0;
+    for (uint32_t b = 0; b < w; b++) { l |= (uint32_t)pl[(size_t)w * i + b] << (8 * b); r |= (uint32_t)pr[(size_t)w * i + b] << (8 * b); }
+    uint32_t c = (uint32_t)pc[4 * (size_t)i] | ((uint32_t)pc[4 * (size_t)i + 1] << 8) | ((uint32_t)pc[4 * (size_t)i + 2] << 16) | ((uint32_t)pc[4 * (size_t)i + 3] << 24);
+    L[i] = l < nodeCount ? l : 0; R[i] = r < nodeCount ? r : 0; C[i] = c; leaf[i] = pt[i] ? 1 : 0;
+}
+
+struct DecTree { const uint32_t *L, *R, *C; const uint8_t *leaf; uint32_t nodeCount; };
+
+__device__ __forceinline__ uint32_t dec_bit(const uint32_t *__restrict__ words, uint64_t pos) {
+    uint32_t wv = bswap32(__ldg(words + (pos >> 5)));
+    return (wv >> (31 - (uint32_t)(pos & 31))) & 1u;
+}
+
+// one Jacobi round.  start_used[s] = start position used by the most recent decode of sub-sequence s (init ~0).
+__global__ void __launch_bounds__(256) dec_sync_kernel(const uint32_t *__restrict__ words, uint64_t total_bits, uint64_t nsub, DecTree tr,
+                                                       const unsigned long long *__restrict__ end_prev, unsigned long long *end_cur,
+                                                       unsigned long long *start_used, uint32_t *count, uint32_t *zcount,
+                                                       int first_round, unsigned int *changed) {
+    uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (sidx >= nsub) return;
+    uint64_t lo = sidx * DEC_SUB_BITS, hi = lo + DEC_SUB_BITS;
+    uint64_t start = (sidx == 0) ? 0 : (first_round ? lo : end_prev[sidx - 1]);
+    if (!first_round && start == start_used[sidx]) { end_cur[sidx] = end_prev[sidx]; return; }
+    uint64_t pos = start;
+    uint32_t cnt = 0, zc = 0;
+    const uint64_t limit = total_bits + 64;
+    while (pos < hi && pos < limit) {
+        uint32_t node = 0;
+        do {
+            uint32_t bit = dec_bit(words, pos); pos++;
+            node = bit ? tr.R[node] : tr.L[node];
+        } while (!tr.leaf[node] && node != 0 && pos < limit + 128);
+        cnt++; zc += (tr.C[node] == 0);
+    }
+    start_used[sidx] = start; end_cur[sidx] = pos; count[sidx] = cnt; zcount[sidx] = zc;
+    *changed = 1u;
+}
+
+// final pass: decode each sub-sequence again and write symbols (block-major index = sym_off[s] + m).
+// BLOCKMAJOR: scatter into the raster code array and pre-place unpredictable values into the output field.
+template <typename T, bool BLOCKMAJOR>
+__global__ void __launch_bounds__(256) dec_write_kernel(const uint32_t *__restrict__ words, uint64_t total_bits, uint64_t nsub, DecTree tr,
+                                                        const unsigned long long *__restrict__ start_used,
+                                                        const unsigned long long *__restrict__ sym_off, const unsigned long long *__restrict__ zero_off,
+                                                        uint64_t n, Geom g, uint16_t *codes_out, const T *__restrict__ unpred, uint64_t unpred_count, T *field_out) {
+    uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (sidx >= nsub) return;
+    uint64_t p = sym_off[sidx];
+    if (p >= n) return;
+    uint64_t zr = zero_off ? zero_off[sidx] : 0;
+    uint64_t hi = (sidx + 1) * DEC_SUB_BITS, pos = start_used[sidx];
+    const uint64_t limit = total_bits + 64;
+    BMIter it;
+    if (BLOCKMAJOR) it.init(g, p);
+    while (pos < hi && pos < limit && p < n) {
+        uint32_t node = 0;
+        do {
+            uint32_t bit = dec_bit(words, pos); pos++;
+            node = bit ? tr.R[node] : tr.L[node];
+        } while (!tr.leaf[node] && node != 0 && pos < limit + 128);
+        uint32_t sym = tr.C[node];
+        if (BLOCKMAJOR) {
+            codes_out[it.raster] = (uint16_t)sym;
+            if (sym == 0 && field_out) { if (zr < unpred_count) field_out[it.raster] = unpred[zr]; zr++; }
+            it.next(g);
+        } else codes_out[p] = (uint16_t)sym;
+        p++;
+    }
+}
+
+// single-leaf tree: every symbol is the root's symbol and the payload is empty (ref: Huffman.c:316-321)
+__global__ void fill_u16_kernel(uint16_t *out, uint64_t n, uint16_t v) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) out[i] = v;
+}
+
+// coefficient chain decode (S1, decoder side; ref: szd_float.c:5809-5819): pure add chain per coefficient lane
+template <typename T>
+__global__ void __launch_bounds__(32) coeff_chain_decode_kernel(const uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, uint32_t nb, uint32_t reg_count, int ncoef,
+                                                                const uint32_t *__restrict__ reg_list, T p0, T p1, T p2, T p3, int r0_, int r1_, int r2_, int r3_,
+                                                                const T *__restrict__ cu0, const T *__restrict__ cu1, const T *__restrict__ cu2, const T *__restrict__ cu3,
+                                                                T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
+    const int e = threadIdx.x;
+    if (e >= ncoef) return;
+    const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
+    const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
+    const T *cu = e == 0 ? cu0 : e == 1 ? cu1 : e == 2 ? cu2 : cu3;
+    T last = (T)0;
+    uint32_t ui = 0;
+    for (uint32_t r = 0; r < reg_count; r++) {
+        int tcode = coeff_type[(size_t)e * nb + r];
+        if (tcode != 0) { T dq = (T)(2 * (tcode - rad)); T v = dq * prec; last = last + v; }
+        else last = cu[ui++];
+        coeff_last[(size_t)e * nb + reg_list[r]] = last;
+    }
+}
+
+// indicator bits (MSB-first, 1 = Lorenzo; ref: TypeManager.c:47-71) <-> byte-per-block array
+__global__ void indicator_pack_kernel(const unsigned char *__restrict__ ind, uint32_t nb, unsigned char *out) {
+    uint32_t byte = blockIdx.x * blockDim.x + threadIdx.x;
+    if (byte >= (nb + 7) / 8) return;
+    unsigned int v = 0;
+    for (int j = 0; j < 8; j++) { uint32_t b = byte * 8 + j; if (b < nb && ind[b] == 1) v |= 1u << (7 - j); }
+    out[byte] = (unsigned char)v;
+}
+__global__ void indicator_unpack_kernel(const unsigned char *__restrict__ in, uint32_t nb, unsigned char *ind) {
+    uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < nb) ind[b] = (in[b >> 3] >> (7 - (b & 7))) & 1;
+}
+
+}  // namespace szb

@@ -1,0 +1,859 @@
+// szb_shim.cu -- the C-ABI shim (include/szb200.h): per-device context (stream + grow-only workspace), kernel
+// launch sequences for one blocked-regression job, stream-section assembly.  No CPU fallback anywhere: every stage of
+// the hot path is a kernel from szb_stage1.cuh / szb_wavefront.cuh / szb_huffman.cuh.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -lineinfo -Xcompiler -ffp-contract=off ...
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/szb200.h"
+#include "szb_common.cuh"
+#include "szb_huffman.cuh"
+#include "szb_stage1.cuh"
+#include "szb_wavefront.cuh"
+
+using namespace szb;
+
+#define SZ_SCES 0
+#define SZ_NSCS -1
+#define SZ_DERR -4
+#define SZ_MERR -5
+
+static thread_local char g_err[512] = "";
+static void set_err(const char *fmt, ...) __attribute__((format(printf, 1, 2)));
+static void set_err(const char *fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+}
+#define CU(call)                                                                                              \
+    do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { set_err("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); return SZ_NSCS; } } while (0)
+#define KCHECK()                                                                                              \
+    do { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_err("%s:%d kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return SZ_NSCS; } c.launches++; } while (0)
+
+enum Stage { ST_OPT = 0, ST_MEAN, ST_FIT, ST_CHAIN, ST_WAVE, ST_HIST, ST_TREE, ST_ENC, ST_EMIT, ST_PARSE, ST_DECODE, ST_DCHAIN, ST_RECON, ST_COUNT };
+static const char *k_stage_names[16] = {"opt_intervals", "use_mean_mean", "fit_select", "coeff_chain", "wavefront_quant", "histogram", "huffman_tree",
+                                        "encode", "emit", "d_parse", "d_huffman_decode", "d_coeff_chain", "d_wavefront_recon", "", "", ""};
+extern "C" const char *szb200_stage_name(int i) { return (i >= 0 && i < 16) ? k_stage_names[i] : ""; }
+
+// ---------------------------------------------------------------------------------------------------------------------
+struct Buf { void *p = nullptr; size_t cap = 0; };
+
+struct Ctx {
+    int dev = -1;
+    cudaStream_t stream = nullptr;
+    std::map<std::string, Buf> bufs;
+    void *pinned = nullptr; size_t pinned_cap = 0;
+    cudaEvent_t ev[ST_COUNT + 2];
+    bool ev_ok = false;
+    unsigned int launches = 0;
+    int sm_count = 148;
+    size_t smem_optin = 0;
+    szb200_stats last; bool have_last = false;
+    // debug bookkeeping of the last compress job
+    Geom dbg_g; int dbg_dtype = -1; unsigned int dbg_intervals = 0; size_t dbg_reg_count = 0;
+    // cached sample-position table
+    std::vector<uint64_t> pos_cache; size_t pos_key[4] = {0, 0, 0, 0};
+
+    int init(int d) {
+        dev = d;
+        CU(cudaSetDevice(d));
+        CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        for (auto &e : ev) CU(cudaEventCreate(&e));
+        ev_ok = true;
+        cudaDeviceProp pr; CU(cudaGetDeviceProperties(&pr, d));
+        sm_count = pr.multiProcessorCount; smem_optin = pr.sharedMemPerBlockOptin;
+        return 0;
+    }
+    void *get(const char *name, size_t bytes) {
+        Buf &b = bufs[name];
+        if (b.cap < bytes) {
+            if (b.p) cudaFree(b.p);
+            size_t want = bytes + bytes / 8 + 256;
+            if (cudaMalloc(&b.p, want) != cudaSuccess) { b.p = nullptr; b.cap = 0; set_err("cudaMalloc(%zu) for %s failed", want, name); return nullptr; }
+            b.cap = want;
+        }
+        return b.p;
+    }
+    void *pin(size_t bytes) {
+        if (pinned_cap < bytes) {
+            if (pinned) cudaFreeHost(pinned);
+            if (cudaMallocHost(&pinned, bytes + 4096) != cudaSuccess) { pinned = nullptr; pinned_cap = 0; return nullptr; }
+            pinned_cap = bytes + 4096;
+        }
+        return pinned;
+    }
+    void release() {
+        for (auto &kv : bufs) if (kv.second.p) cudaFree(kv.second.p);
+        bufs.clear();
+        if (pinned) { cudaFreeHost(pinned); pinned = nullptr; pinned_cap = 0; }
+    }
+};
+
+static std::mutex g_mu;
+static std::map<int, Ctx *> g_ctx;
+
+static Ctx *ctx() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess) { set_err("no CUDA device: %s", cudaGetErrorString(cudaGetLastError())); return nullptr; }
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_ctx.find(d);
+    if (it != g_ctx.end()) return it->second;
+    Ctx *c = new Ctx();
+    if (c->init(d) != 0) { delete c; return nullptr; }
+    g_ctx[d] = c;
+    return c;
+}
+
+extern "C" int szb200_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
+extern "C" int szb200_set_device(int device) { CU(cudaSetDevice(device)); return ctx() ? 0 : SZ_NSCS; }
+extern "C" const char *szb200_last_error(void) { return g_err; }
+extern "C" void szb200_release(void) { Ctx *c = ctx(); if (c) { cudaStreamSynchronize(c->stream); c->release(); } }
+extern "C" void *szb200_stream(void) { Ctx *c = ctx(); return c ? (void *)c->stream : nullptr; }
+extern "C" int szb200_sync(void) { Ctx *c = ctx(); if (!c) return SZ_NSCS; CU(cudaStreamSynchronize(c->stream)); return 0; }
+extern "C" int szb200_last_stats(szb200_stats *out) { Ctx *c = ctx(); if (!c || !c->have_last) return SZ_NSCS; *out = c->last; return 0; }
+
+extern "C" void *szb200_stage_input(const void *host_ptr, size_t bytes) {
+    Ctx *c = ctx(); if (!c) return nullptr;
+    void *d = c->get("in_stage", bytes); if (!d) return nullptr;
+    if (cudaMemcpyAsync(d, host_ptr, bytes, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { set_err("H2D failed"); return nullptr; }
+    return d;
+}
+
+extern "C" void *szb200_output_buffer(size_t bytes) { Ctx *c = ctx(); return c ? c->get("out_stage", bytes) : nullptr; }
+
+extern "C" int szb200_copy(void *dst, const void *src, size_t bytes, int kind) {
+    Ctx *c = ctx(); if (!c) return SZ_NSCS;
+    cudaMemcpyKind k = kind == 0 ? cudaMemcpyHostToDevice : kind == 1 ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    CU(cudaMemcpyAsync(dst, src, bytes, k, c->stream));
+    if (kind != 2) CU(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// K1
+template <typename T>
+static int range_impl(Ctx &c, const T *d, size_t n, double *vmin, double *vmax) {
+    int grid = c.sm_count * 4;
+    size_t need = ((n * sizeof(T)) / 16 + 511) / 512; if ((size_t)grid > need) grid = (int)(need ? need : 1);
+    MinMax<T> *part = (MinMax<T> *)c.get("mm_part", sizeof(MinMax<T>) * (size_t)(c.sm_count * 4 + 1) + 64);
+    if (!part) return SZ_NSCS;
+    MinMax<T> *res = part + c.sm_count * 4;
+    unsigned int *done = (unsigned int *)c.get("mm_done", 64); if (!done) return SZ_NSCS;
+    CU(cudaMemsetAsync(done, 0, 64, c.stream));
+    range_kernel<T><<<grid, 512, 0, c.stream>>>(d, (uint64_t)n, part, done, res); KCHECK();
+    MinMax<T> h;
+    CU(cudaMemcpyAsync(&h, res, sizeof(h), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    // sign of zero: the reference keeps the FIRST occurrence among equal values (ref: dataCompression.c:108-113)
+    T ext[2] = {h.mn, h.mx};
+    for (int q = 0; q < 2; q++) {
+        if (ext[q] == (T)0) {
+            unsigned long long *idx = (unsigned long long *)done;
+            CU(cudaMemsetAsync(idx, 0xff, 8, c.stream));
+            first_equal_kernel<T><<<c.sm_count * 2, 256, 0, c.stream>>>(d, (uint64_t)n, (T)0, idx); KCHECK();
+            unsigned long long hi = 0;
+            CU(cudaMemcpyAsync(&hi, idx, 8, cudaMemcpyDeviceToHost, c.stream));
+            CU(cudaStreamSynchronize(c.stream));
+            if (hi != ~0ULL) { CU(cudaMemcpyAsync(&ext[q], d + hi, sizeof(T), cudaMemcpyDeviceToHost, c.stream)); CU(cudaStreamSynchronize(c.stream)); }
+            CU(cudaMemsetAsync(done, 0, 64, c.stream));
+        }
+    }
+    *vmin = (double)ext[0]; *vmax = (double)ext[1];
+    return 0;
+}
+
+extern "C" int szb200_range(int dtype, const void *d_data, size_t n, double *vmin, double *vmax) {
+    Ctx *c = ctx(); if (!c) return SZ_NSCS;
+    if (n == 0) { set_err("empty input"); return SZ_NSCS; }
+    return dtype == 0 ? range_impl<float>(*c, (const float *)d_data, n, vmin, vmax) : range_impl<double>(*c, (const double *)d_data, n, vmin, vmax);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host-side helpers (scalar arithmetic of the reference that is not data-parallel)
+static unsigned int round_up_pow2(unsigned int base) {   // ref: conf.c:35-46
+    base -= 1; base |= base >> 1; base |= base >> 2; base |= base >> 4; base |= base >> 8; base |= base >> 16; return base + 1;
+}
+
+// positions of the sampling-mean walk (ref: sz_float.c:6400-6420 3D; :5409-5418 2D) -- shape-only, cached
+static void sample_positions(Ctx &c, const Geom &g, std::vector<uint64_t> &out) {
+    size_t key[4] = {(size_t)g.dim, g.ax[0].n, g.ax[1].n, g.ax[2].n};
+    if (memcmp(key, c.pos_key, sizeof(key)) == 0 && !c.pos_cache.empty()) { out = c.pos_cache; return; }
+    out.clear();
+    const uint64_t len = g.N;
+    const uint64_t md = (uint64_t)(int)sqrt((double)len);
+    if (g.dim == 2) { for (uint64_t p = 0; p < len; p += md) out.push_back(p); }
+    else {
+        const uint64_t r3 = g.ax[2].n, r23 = (uint64_t)g.ax[1].n * g.ax[2].n;
+        uint64_t pos = 0, oc = 0, oc2 = 0;
+        while (pos < len) {
+            out.push_back(pos);
+            pos += md; oc += md; oc2 += md;
+            if (oc >= r3) { oc = 0; pos -= 1; }
+            if (oc2 >= r23) { oc2 = 0; pos -= 1; }
+        }
+    }
+    c.pos_cache = out; memcpy(c.pos_key, key, sizeof(key));
+}
+
+// number of sample ROWS the interval-optimiser walk visits before its first address >= N
+static uint64_t opt_row_limit(const Geom &g, uint32_t sd) {
+    const uint64_t N = g.N, n1 = g.ax[1].n, n2 = g.ax[2].n, s0 = n1 * n2;
+    if (g.dim == 3) {
+        const uint64_t n0 = g.ax[0].n;
+        if (n0 < 2 || n1 < 2) return 0;
+        uint64_t total = (n0 - 1) * (n1 - 1);
+        // rows whose first sample could spill past N: only those within (sd + s0) elements of the end
+        uint64_t safe_i = 1;
+        if (N > (uint64_t)sd + 2 * s0) safe_i = (N - sd - s0) / s0;        // rows with i < safe_i cannot reach N
+        if (safe_i < 1) safe_i = 1;
+        uint64_t r = (safe_i - 1) * (n1 - 1);
+        for (; r < total; r++) {
+            uint64_t i = 1 + r / (n1 - 1), j = 1 + r % (n1 - 1);
+            int64_t c0 = (r == 0) ? (int64_t)sd - 2 : (int64_t)(sd - (uint32_t)((i + j) % sd));
+            if (i * s0 + j * n2 + (uint64_t)c0 >= N) return r;
+        }
+        return total;
+    } else {
+        if (n1 < 2) return 0;
+        uint64_t total = n1 - 1;
+        uint64_t r = 0;
+        if (N > (uint64_t)sd + 2 * n2) { uint64_t safe_i = (N - sd - n2) / n2; if (safe_i > 1) r = safe_i - 1; }
+        for (; r < total; r++) {
+            uint64_t i = 1 + r;
+            int64_t c0 = (r == 0) ? (int64_t)sd - 1 : (int64_t)(sd - (uint32_t)(i % sd));
+            if (i * n2 + (uint64_t)c0 >= N) return r;
+        }
+        return total;
+    }
+}
+
+// anti-diagonal pencil order for the wavefront ticket dispenser
+static void pencil_order(uint32_t A, uint32_t B, std::vector<uint32_t> &order) {
+    order.clear(); order.reserve((size_t)A * B);
+    for (uint32_t d = 0; d + 1 < A + B; d++) {
+        uint32_t a_lo = d >= B ? d - B + 1 : 0, a_hi = d < A ? d : A - 1;
+        for (uint32_t a = a_lo; a <= a_hi; a++) order.push_back(a * B + (d - a));
+    }
+}
+
+static void put_be32(unsigned char *b, uint32_t v) { b[0] = v >> 24; b[1] = v >> 16; b[2] = v >> 8; b[3] = v; }
+static void put_be64(unsigned char *b, uint64_t v) { for (int i = 0; i < 8; i++) b[i] = (unsigned char)(v >> (56 - 8 * i)); }
+static uint32_t get_be32(const unsigned char *b) { return ((uint32_t)b[0] << 24) | ((uint32_t)b[1] << 16) | ((uint32_t)b[2] << 8) | b[3]; }
+static uint64_t get_be64(const unsigned char *b) { uint64_t v = 0; for (int i = 0; i < 8; i++) v = (v << 8) | b[i]; return v; }
+template <typename T> static void put_beT(unsigned char *b, T v) {
+    if (sizeof(T) == 4) { uint32_t u; memcpy(&u, &v, 4); put_be32(b, u); } else { uint64_t u; memcpy(&u, &v, 8); put_be64(b, u); }
+}
+template <typename T> static T get_beT(const unsigned char *b) {
+    T v; if (sizeof(T) == 4) { uint32_t u = get_be32(b); memcpy(&v, &u, 4); } else { uint64_t u = get_be64(b); memcpy(&v, &u, 8); } return v;
+}
+
+// stream assembly: a list of pieces, each either host bytes (copied into a pinned arena first) or a device section
+struct Piece { bool dev; size_t off_or_ptr; const void *dptr; size_t len; };
+struct Emitter {
+    std::vector<unsigned char> host; std::vector<Piece> pieces; size_t total = 0;
+    unsigned char *h(size_t n) { size_t o = host.size(); host.resize(o + n); pieces.push_back({false, o, nullptr, n}); total += n; return host.data() + o; }
+    void d(const void *p, size_t n) { if (n) { pieces.push_back({true, 0, p, n}); total += n; } }
+};
+
+static int emit_all(Ctx &c, Emitter &E, void *dst, int dst_on_device) {
+    unsigned char *out = (unsigned char *)dst;
+    unsigned char *arena = nullptr;
+    if (dst_on_device) { arena = (unsigned char *)c.pin(E.host.size() + 16); if (!arena) { set_err("pinned alloc failed"); return SZ_NSCS; } memcpy(arena, E.host.data(), E.host.size()); }
+    size_t o = 0;
+    for (auto &p : E.pieces) {
+        if (!p.dev) {
+            if (dst_on_device) CU(cudaMemcpyAsync(out + o, arena + p.off_or_ptr, p.len, cudaMemcpyHostToDevice, c.stream));
+            else memcpy(out + o, E.host.data() + p.off_or_ptr, p.len);
+        } else {
+            CU(cudaMemcpyAsync(out + o, p.dptr, p.len, dst_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c.stream));
+        }
+        o += p.len;
+    }
+    CU(cudaStreamSynchronize(c.stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+struct TreeWs {              // device workspace + descriptor for one Huffman tree
+    HuffTreeDesc d; uint32_t *hist;
+};
+
+static int tree_ws(Ctx &c, int idx, uint32_t nbins, TreeWs &w) {
+    char name[32]; snprintf(name, sizeof(name), "tree%d", idx);
+    const uint32_t cap = 2 * nbins + 2;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    size_t o_hist = take(4ull * nbins), o_left = take(4ull * cap), o_right = take(4ull * cap), o_sizeL = take(4ull * cap), o_sym = take(4ull * cap),
+           o_pre = take(4ull * cap), o_code_n = take(8ull * cap), o_len_n = take(cap), o_front = take(8ull * cap), o_heap = take(12ull * cap),
+           o_code = take(8ull * nbins), o_clen = take(nbins), o_tree = take(16 + 13ull * cap), o_out = take(64);
+    unsigned char *base = (unsigned char *)c.get(name, off); if (!base) return SZ_NSCS;
+    w.hist = (uint32_t *)(base + o_hist);
+    w.d.hist = w.hist; w.d.nbins = nbins; w.d.capacity = cap;
+    w.d.n_left = (uint32_t *)(base + o_left); w.d.n_right = (uint32_t *)(base + o_right); w.d.n_sizeL = (uint32_t *)(base + o_sizeL); w.d.n_sym = (uint32_t *)(base + o_sym);
+    w.d.n_pre = (uint32_t *)(base + o_pre); w.d.n_code = (uint64_t *)(base + o_code_n); w.d.n_len = (uint8_t *)(base + o_len_n);
+    w.d.frontier = (uint32_t *)(base + o_front); w.d.heap_g = (uint32_t *)(base + o_heap);
+    w.d.code = (uint64_t *)(base + o_code); w.d.clen = (uint8_t *)(base + o_clen); w.d.tree_bytes = base + o_tree; w.d.out = (uint32_t *)(base + o_out);
+    return 0;
+}
+
+static int launch_hist(Ctx &c, const uint16_t *s, uint64_t n, uint32_t nbins, uint32_t *hist) {
+    CU(cudaMemsetAsync(hist, 0, 4ull * nbins, c.stream));
+    if (n == 0) return 0;
+    int use_smem = nbins <= 16384;
+    size_t sm = use_smem ? 4ull * nbins : 0;
+    if (sm > 48 * 1024) CU(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    uint64_t want = (n / 8 + 511) / 512; int grid = (int)std::min<uint64_t>(std::max<uint64_t>(want, 1), (uint64_t)c.sm_count * 4);
+    hist_kernel<<<grid, 512, sm, c.stream>>>(s, n, nbins, hist, use_smem); KCHECK();
+    return 0;
+}
+
+template <typename T, int DIM>
+static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, int cap, const unsigned char *indicator, const T *x, uint16_t *codes,
+                            T *recon, const T *coeff_last, T eb, T recip, T mean, int write_all) {
+    constexpr int PI = Pencil<DIM>::PI, PJ = Pencil<DIM>::PJ;
+    WfParams P; memset(&P, 0, sizeof(P));
+    P.g = g; P.cap = cap; P.radius = cap / 2; P.cap_l = cap - 2; P.use_mean = use_mean;
+    P.pencils_a = (g.ax[0].n + PI - 1) / PI; P.pencils_b = (g.ax[1].n + PJ - 1) / PJ; P.num_pencils = P.pencils_a * P.pencils_b;
+    std::vector<uint32_t> order; pencil_order(P.pencils_a, P.pencils_b, order);
+    uint32_t *d_order = (uint32_t *)c.get("wf_order", 4ull * P.num_pencils); if (!d_order) return SZ_NSCS;
+    int *d_flags = (int *)c.get("wf_flags", 4ull * P.num_pencils + 64); if (!d_flags) return SZ_NSCS;
+    unsigned int *d_misc = (unsigned int *)c.get("wf_misc", 64); if (!d_misc) return SZ_NSCS;
+    // pageable source: the runtime stages it before returning, so `order` may die at scope exit
+    CU(cudaMemcpyAsync(d_order, order.data(), 4ull * P.num_pencils, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemsetAsync(d_flags, 0, 4ull * P.num_pencils, c.stream));
+    CU(cudaMemsetAsync(d_misc, 0, 64, c.stream));
+    P.order = d_order; P.flags = d_flags; P.ticket = d_misc; P.err = (int *)(d_misc + 4); P.indicator = indicator; P.write_all_recon = write_all;
+    const size_t per_warp = wf_smem_per_warp<T>(DIM);
+    int warps = sizeof(T) == 4 ? 4 : 2;
+    while (warps > 1 && per_warp * warps > c.smem_optin) warps--;
+    const size_t smem = per_warp * warps;
+    int ctas_per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (c.smem_optin + 1024) / (smem + 1024)));
+    uint32_t need_ctas = (P.num_pencils + warps - 1) / warps;
+    int grid = (int)std::min<uint32_t>(need_ctas, (uint32_t)(c.sm_count * ctas_per_sm));
+    auto run = [&](auto kern) -> int {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, warps * 32, smem, c.stream>>>(P, x, codes, recon, coeff_last, eb, recip, mean); KCHECK();
+        return 0;
+    };
+    int rc;
+    if (decomp) rc = use_mean ? run(wavefront_kernel<T, DIM, true, true>) : run(wavefront_kernel<T, DIM, false, true>);
+    else rc = use_mean ? run(wavefront_kernel<T, DIM, true, false>) : run(wavefront_kernel<T, DIM, false, false>);
+    if (rc) return rc;
+    return 0;
+}
+
+static int check_wf_err(Ctx &c) {
+    unsigned int *d_misc = (unsigned int *)c.get("wf_misc", 64);
+    int e = 0;
+    CU(cudaMemcpyAsync(&e, d_misc + 4, 4, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    if (e) { set_err("wavefront kernel: dependency wait timed out (internal error)"); return SZ_NSCS; }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" size_t szb200_body_capacity(const szb200_job *job) {
+    Geom g = make_geom(job->dim, job->n0, job->n1, job->n2);
+    size_t st = job->dtype == 0 ? 4 : 8;
+    // mirrors the reference's calloc (ref: sz_float.c:7394) plus slack for the coefficient trees
+    return 8 + 4 + st + 12 + 5ull * (16 + 13ull * 2 * 65536) + 1 + st + g.num_blocks * (4 * 4 + 2 + 2 + st) + 8 + g.N * st + g.N * 4 + 4096;
+}
+
+template <typename T>
+static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst, int dst_on_device, size_t dst_cap, size_t *body_size, szb200_stats *stats) {
+    const Geom g = make_geom(job.dim, job.n0, job.n1, job.n2);
+    const int ncoef = g.ncoef;
+    const uint32_t nb = g.num_blocks;
+    const uint64_t N = g.N;
+    if (N >= (1ull << 32)) { set_err("arrays of 2^32 or more elements must be cut into slabs (N=%llu)", (unsigned long long)N); return SZ_DERR; }
+    if (job.max_quant_intervals > 65536 || job.quantization_intervals > 65536) { set_err("more than 65536 quantization intervals is not supported"); return SZ_NSCS; }
+    if (job.sampleDistance < 2) { set_err("sampleDistance must be >= 2"); return SZ_NSCS; }
+    c.launches = 0;
+    int evi = 0;
+    CU(cudaEventRecord(c.ev[evi++], c.stream));
+    float ms_stage[16]; memset(ms_stage, 0, sizeof(ms_stage));
+    int stage_of_ev[ST_COUNT + 2];
+    auto mark = [&](int st) -> int { stage_of_ev[evi] = st; CU(cudaEventRecord(c.ev[evi++], c.stream)); return 0; };
+
+    const T eb = (T)job.eb;                      // float path: the kernels see the narrowed value (ref: sz_float.c:6527 signature)
+    const double ebw = (double)eb;
+    const T recip_eb = (T)1 / eb;
+    unsigned int intervals;
+    int use_mean = 0;
+    T mean = (T)0;
+    const uint32_t maxRangeRadius = job.max_quant_intervals / 2;
+
+    // ---- interval optimiser (ref: sz_float.c:6647-6655) ----
+    T dense_pos = (T)0;
+    if (job.quantization_intervals == 0) {
+        std::vector<uint64_t> pos; sample_positions(c, g, pos);
+        const uint32_t cnt = (uint32_t)pos.size();
+        uint64_t *d_pos = (uint64_t *)c.get("opt_pos", 8ull * cnt + 8); T *d_vals = (T *)c.get("opt_vals", sizeof(T) * (size_t)cnt + 64);
+        unsigned char *ob = (unsigned char *)c.get("opt_misc", 4ull * 32768 + 4ull * 8192 + 256);
+        if (!d_pos || !d_vals || !ob) return SZ_NSCS;
+        uint32_t *d_int = (uint32_t *)ob, *d_freq = d_int + 32768; OptAccum *d_acc = (OptAccum *)(d_freq + 8192);
+        OptOut *d_out = (OptOut *)((unsigned char *)d_acc + 64); T *d_mean = (T *)((unsigned char *)d_acc + 128);
+        void *pin = c.pin(8ull * cnt + 64); if (!pin) return SZ_NSCS;
+        memcpy(pin, pos.data(), 8ull * cnt);
+        CU(cudaMemcpyAsync(d_pos, pin, 8ull * cnt, cudaMemcpyHostToDevice, c.stream));
+        CU(cudaMemsetAsync(ob, 0, 4ull * 32768 + 4ull * 8192 + 256, c.stream));
+        sample_mean_kernel<T><<<1, 1024, 0, c.stream>>>(d_x, d_pos, cnt, d_vals, d_mean); KCHECK();
+        const uint64_t rows = opt_row_limit(g, (uint32_t)job.sampleDistance);
+        if (rows > 0) {
+            int grid = (int)std::min<uint64_t>((rows + 255) / 256, (uint64_t)c.sm_count * 8);
+            if (job.dim == 3) opt_sample_kernel<T, 3><<<grid, 256, 0, c.stream>>>(d_x, g, (uint32_t)job.sampleDistance, rows, d_mean, ebw, maxRangeRadius, d_int, d_freq, d_acc);
+            else opt_sample_kernel<T, 2><<<grid, 256, 0, c.stream>>>(d_x, g, (uint32_t)job.sampleDistance, rows, d_mean, ebw, maxRangeRadius, d_int, d_freq, d_acc);
+            KCHECK();
+        }
+        opt_finish_kernel<T><<<1, 1024, 0, c.stream>>>(d_int, d_freq, d_acc, d_mean, maxRangeRadius, job.predThreshold, d_out); KCHECK();
+        OptOut ho;
+        CU(cudaMemcpyAsync(&ho, d_out, sizeof(ho), cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        // scalar tail of optimize_intervals_* (ref: sz_float.c:6486-6520)
+        unsigned int acc = 2 * (ho.first_index + 1);
+        unsigned int p2 = round_up_pow2(acc); if (p2 < 32) p2 = 32;
+        intervals = p2;
+        const T smean = (T)ho.mean;
+        const T max_freq = (T)((double)ho.hits * 1.0 / (double)ho.samples);
+        dense_pos = (T)((double)smean + ebw * (double)(long long)((long long)ho.max_index + 1 - 4096));
+        const T mean_freq = (T)((double)ho.max_sum * 1.0 / (double)ho.samples);
+        if ((double)mean_freq > 0.5 || mean_freq > max_freq) use_mean = 1;
+        if (job.dim == 2) use_mean = 0;             // ref: sz_float.c:5615
+    } else intervals = job.quantization_intervals;
+    if (mark(ST_OPT)) return SZ_NSCS;
+
+    if (use_mean) {                                 // ref: sz_float.c:6657-6669
+        T *d_m = (T *)c.get("mean_out", 64); if (!d_m) return SZ_NSCS;
+        mean_kernel<T><<<1, 1024, 0, c.stream>>>(d_x, N, dense_pos, eb, d_m); KCHECK();
+        CU(cudaMemcpyAsync(&mean, d_m, sizeof(T), cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+    }
+    if (mark(ST_MEAN)) return SZ_NSCS;
+
+    // ---- precisions (ref: sz_float.c:6639-6645, 2D :5608-5612) and noise (:6697 / :5674) ----
+    T prec[4] = {0, 0, 0, 0};
+    {
+        const T rel = (job.dim == 3) ? (T)0.025 : (T)(0.15 / 3);
+        const T t = rel * eb;
+        if (job.dim == 3) { prec[0] = t / (T)g.ax[0].late; prec[1] = t / (T)g.ax[1].late; prec[2] = t / (T)g.ax[2].late; prec[3] = t; }
+        else { prec[0] = t / (T)g.ax[1].late; prec[1] = t / (T)g.ax[2].late; prec[2] = t; }
+    }
+    const T noise = (job.dim == 3) ? (T)((double)eb * 1.22) : (T)((double)eb * 0.81);
+
+    // ---- fit + selection ----
+    T *d_reg = (T *)c.get("reg", sizeof(T) * 4ull * nb), *d_regc = (T *)c.get("reg_c", sizeof(T) * 4ull * nb), *d_clast = (T *)c.get("coeff_last", sizeof(T) * 4ull * nb),
+      *d_cunp = (T *)c.get("coeff_unpred", sizeof(T) * 4ull * nb);
+    uint16_t *d_ctype = (uint16_t *)c.get("coeff_type", 2ull * 4 * nb + 64);
+    unsigned char *d_ind = (unsigned char *)c.get("indicator", nb + 64);
+    uint32_t *d_flags = (uint32_t *)c.get("reg_flags", 4ull * nb + 64), *d_list = (uint32_t *)c.get("reg_list", 4ull * nb + 64);
+    unsigned long long *d_rank = (unsigned long long *)c.get("reg_rank", 8ull * nb + 64);
+    unsigned long long *d_tot = (unsigned long long *)c.get("totals", 256);
+    if (!d_reg || !d_regc || !d_clast || !d_cunp || !d_ctype || !d_ind || !d_flags || !d_list || !d_rank || !d_tot) return SZ_NSCS;
+    {
+        int grid = (nb + 127) / 128;
+        if (job.dim == 3) fit_select_kernel<T, 3><<<grid, 128, 0, c.stream>>>(d_x, g, noise, use_mean, mean, d_reg, d_ind);
+        else fit_select_kernel<T, 2><<<grid, 128, 0, c.stream>>>(d_x, g, noise, use_mean, mean, d_reg, d_ind);
+        KCHECK();
+        reg_flag_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_flags); KCHECK();
+        scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_flags, nb, d_rank, d_tot); KCHECK();
+    }
+    unsigned long long reg_count_ll = 0;
+    CU(cudaMemcpyAsync(&reg_count_ll, d_tot, 8, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    const uint32_t reg_count = (uint32_t)reg_count_ll;
+    if (mark(ST_FIT)) return SZ_NSCS;
+
+    // ---- coefficient chain ----
+    ChainOut *d_chain = (ChainOut *)c.get("chain_out", 64); if (!d_chain) return SZ_NSCS;
+    CU(cudaMemsetAsync(d_chain, 0, 64, c.stream));
+    if (reg_count > 0) {
+        reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, ncoef, d_reg, d_regc, d_list); KCHECK();
+        const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
+        coeff_chain_kernel<T><<<1, 32, 0, c.stream>>>(d_regc, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
+    }
+    if (mark(ST_CHAIN)) return SZ_NSCS;
+
+    // ---- wavefront predict + quantise ----
+    uint16_t *d_codes = (uint16_t *)c.get("codes", 2ull * N + 64);
+    T *d_recon = (T *)c.get("recon", sizeof(T) * N + 64);
+    if (!d_codes || !d_recon) return SZ_NSCS;
+    const int write_all = getenv("SZB200_DEBUG_RECON") ? 1 : 0;
+    {
+        int rc = (job.dim == 3) ? launch_wavefront<T, 3>(c, g, false, use_mean, (int)intervals, d_ind, d_x, d_codes, d_recon, d_clast, eb, recip_eb, mean, write_all)
+                                : launch_wavefront<T, 2>(c, g, false, use_mean, (int)intervals, d_ind, d_x, d_codes, d_recon, d_clast, eb, recip_eb, mean, write_all);
+        if (rc) return rc;
+    }
+    if (mark(ST_WAVE)) return SZ_NSCS;
+
+    // ---- histograms ----
+    TreeWs tw[5];
+    if (tree_ws(c, 0, intervals, tw[0])) return SZ_NSCS;
+    if (launch_hist(c, d_codes, N, intervals, tw[0].hist)) return SZ_NSCS;
+    const int ntrees = 1 + (reg_count > 0 ? ncoef : 0);
+    for (int e = 0; e < ntrees - 1; e++) {
+        if (tree_ws(c, 1 + e, 65536, tw[1 + e])) return SZ_NSCS;
+        if (launch_hist(c, d_ctype + (size_t)e * nb, reg_count, 65536, tw[1 + e].hist)) return SZ_NSCS;
+    }
+    if (mark(ST_HIST)) return SZ_NSCS;
+
+    // ---- Huffman trees (one CTA each) ----
+    HuffTreeDesc *d_desc = (HuffTreeDesc *)c.get("tree_desc", sizeof(HuffTreeDesc) * 8); if (!d_desc) return SZ_NSCS;
+    {
+        HuffTreeDesc hd[8];
+        for (int i = 0; i < ntrees; i++) hd[i] = tw[i].d;
+        CU(cudaMemcpyAsync(d_desc, hd, sizeof(HuffTreeDesc) * ntrees, cudaMemcpyHostToDevice, c.stream));   // pageable: staged before return
+        uint32_t heap_cap = (uint32_t)((c.smem_optin - 1024) / 12);
+        size_t sm = 12ull * heap_cap;
+        CU(cudaFuncSetAttribute(huff_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        huff_build_kernel<<<ntrees, 1024, sm, c.stream>>>(d_desc, heap_cap); KCHECK();
+    }
+    if (mark(ST_TREE)) return SZ_NSCS;
+
+    // ---- encode pass 1: chunk bit lengths (+ zero counts for the main array), prefix sums ----
+    const uint64_t nchunk_main = (N + ENC_CHUNK - 1) / ENC_CHUNK, nchunk_c = reg_count ? ((uint64_t)reg_count + ENC_CHUNK - 1) / ENC_CHUNK : 0;
+    const uint64_t nch_all = nchunk_main + 4 * nchunk_c + 8;
+    uint32_t *d_cb = (uint32_t *)c.get("enc_cb", 4 * nch_all), *d_cz = (uint32_t *)c.get("enc_cz", 4 * nch_all);
+    unsigned long long *d_cbo = (unsigned long long *)c.get("enc_cbo", 8 * nch_all), *d_czo = (unsigned long long *)c.get("enc_czo", 8 * nch_all);
+    if (!d_cb || !d_cz || !d_cbo || !d_czo) return SZ_NSCS;
+    enc_len_kernel<true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.clen, d_cb, d_cz); KCHECK();
+    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cb, nchunk_main, d_cbo, d_tot + 1); KCHECK();
+    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cz, nchunk_main, d_czo, d_tot + 2); KCHECK();
+    for (int e = 0; e < ntrees - 1; e++) {
+        const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
+        enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
+        scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cb + o, nchunk_c, d_cbo + o, d_tot + 3 + e); KCHECK();
+    }
+    // read back sizes
+    unsigned long long h_tot[8]; uint32_t h_tree[5][4]; ChainOut h_chain;
+    CU(cudaMemcpyAsync(h_tot, d_tot, sizeof(h_tot), cudaMemcpyDeviceToHost, c.stream));
+    for (int i = 0; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 16, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    if (check_wf_err(c)) return SZ_NSCS;
+    for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err("Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
+    const uint64_t main_bits = h_tot[1], total_unpred = h_tot[2];
+    const uint64_t main_bytes = (main_bits + 7) / 8;
+    uint64_t cbytes[4] = {0, 0, 0, 0};
+    for (int e = 0; e < ntrees - 1; e++) cbytes[e] = (h_tot[3 + e] + 7) / 8;
+
+    // ---- encode pass 2 ----
+    uint32_t *d_bits = (uint32_t *)c.get("enc_bits", main_bytes + 64);
+    T *d_unp = (T *)c.get("unpred", sizeof(T) * (total_unpred + 8));
+    if (!d_bits || !d_unp) return SZ_NSCS;
+    CU(cudaMemsetAsync(d_bits, 0, main_bytes + 64, c.stream));
+    enc_write_kernel<T, true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.code, tw[0].d.clen, d_cbo, d_czo, d_bits, d_x, d_unp); KCHECK();
+    uint32_t *d_cbits[4] = {nullptr, nullptr, nullptr, nullptr};
+    for (int e = 0; e < ntrees - 1; e++) {
+        char name[32]; snprintf(name, sizeof(name), "enc_cbits%d", e);
+        d_cbits[e] = (uint32_t *)c.get(name, cbytes[e] + 64); if (!d_cbits[e]) return SZ_NSCS;
+        CU(cudaMemsetAsync(d_cbits[e], 0, cbytes[e] + 64, c.stream));
+        const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
+        enc_write_kernel<T, false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.code, tw[1 + e].d.clen, d_cbo + o, d_czo + o,
+                                                                                      d_cbits[e], (const T *)nullptr, (T *)nullptr); KCHECK();
+    }
+    unsigned char *d_indbits = (unsigned char *)c.get("ind_bits", (nb + 7) / 8 + 64); if (!d_indbits) return SZ_NSCS;
+    indicator_pack_kernel<<<((nb + 7) / 8 + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_indbits); KCHECK();
+    if (mark(ST_ENC)) return SZ_NSCS;
+
+    // ---- stream body (SURVEY.md Appendix A from offset 4+MD; ref: sz_float.c:7392-7489) ----
+    Emitter E;
+    { unsigned char *p = E.h(8 + 4 + sizeof(T) + 12);
+      put_be64(p, N); p += 8; put_be32(p, job.dim == 3 ? 6 : 16); p += 4; put_beT<T>(p, eb); p += sizeof(T);
+      put_be32(p, intervals); p += 4; put_be32(p, h_tree[0][0]); p += 4; put_be32(p, h_tree[0][1]); }
+    E.d(tw[0].d.tree_bytes, h_tree[0][0]);
+    { unsigned char *p = E.h(1 + sizeof(T)); p[0] = (unsigned char)use_mean; memcpy(p + 1, &mean, sizeof(T)); }
+    E.d(d_indbits, (nb + 7) / 8);
+    for (int e = 0; e < ntrees - 1; e++) {
+        { unsigned char *p = E.h(sizeof(T) + 12); put_beT<T>(p, prec[e]); p += sizeof(T); put_be32(p, 32768); p += 4; put_be32(p, h_tree[1 + e][0]); p += 4; put_be32(p, h_tree[1 + e][1]); }
+        E.d(tw[1 + e].d.tree_bytes, h_tree[1 + e][0]);
+        { unsigned char *p = E.h(8); put_be64(p, cbytes[e]); }
+        E.d(d_cbits[e], cbytes[e]);
+        { unsigned char *p = E.h(4); put_be32(p, h_chain.unpred_count[e]); }
+        E.d(d_cunp + (size_t)e * nb, sizeof(T) * (size_t)h_chain.unpred_count[e]);
+    }
+    { unsigned char *p = E.h(8); uint64_t tu = total_unpred; memcpy(p, &tu, 8); }
+    E.d(d_unp, sizeof(T) * total_unpred);
+    E.d(d_bits, main_bytes);
+    if (E.total > dst_cap) { set_err("stream body (%zu bytes) exceeds the destination capacity (%zu)", E.total, dst_cap); return SZ_NSCS; }
+    if (emit_all(c, E, dst, dst_on_device)) return SZ_NSCS;
+    *body_size = E.total;
+    if (mark(ST_EMIT)) return SZ_NSCS;
+    CU(cudaStreamSynchronize(c.stream));
+
+    szb200_stats st; memset(&st, 0, sizeof(st));
+    st.intervals = intervals; st.use_mean = use_mean; st.mean = (double)mean; st.num_blocks = nb; st.reg_count = reg_count; st.total_unpred = total_unpred;
+    st.tree_bytes = h_tree[0][0]; st.node_count = h_tree[0][1]; st.type_bits_bytes = main_bytes; st.body_bytes = E.total; st.launches = c.launches;
+    for (int i = 1; i < evi; i++) { float ms = 0; cudaEventElapsedTime(&ms, c.ev[i - 1], c.ev[i]); st.ms_stage[stage_of_ev[i]] += ms; }
+    cudaEventElapsedTime(&st.ms_total, c.ev[0], c.ev[evi - 1]);
+    c.last = st; c.have_last = true;
+    c.dbg_g = g; c.dbg_dtype = job.dtype; c.dbg_intervals = intervals; c.dbg_reg_count = reg_count;
+    if (stats) *stats = st;
+    return 0;
+}
+
+extern "C" int szb200_compress_blocked(const szb200_job *job, const void *d_data, void *dst, int dst_on_device, size_t dst_capacity, size_t *body_size, szb200_stats *stats) {
+    Ctx *c = ctx(); if (!c) return SZ_NSCS;
+    if (job->dim != 2 && job->dim != 3) { set_err("dim must be 2 or 3"); return SZ_DERR; }
+    if (job->dtype == 0) return compress_impl<float>(*c, *job, (const float *)d_data, dst, dst_on_device, dst_capacity, body_size, stats);
+    if (job->dtype == 1) return compress_impl<double>(*c, *job, (const double *)d_data, dst, dst_on_device, dst_capacity, body_size, stats);
+    set_err("dtype must be SZ_FLOAT or SZ_DOUBLE"); return SZ_NSCS;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// decode one Huffman-coded symbol array.  tree bytes + payload are device pointers into the (aligned copy of the) stream.
+template <typename T, bool BLOCKMAJOR>
+static int huff_decode(Ctx &c, int slot, const unsigned char *d_tree, uint32_t nodeCount, const unsigned char *d_payload, uint64_t payload_bytes,
+                       uint64_t nsym, const Geom &g, uint16_t *d_out, const T *d_unpred, uint64_t unpred_count, T *d_field) {
+    char nm[48];
+    snprintf(nm, sizeof(nm), "dec_tree%d", slot);
+    unsigned char *tb = (unsigned char *)c.get(nm, 16ull * nodeCount + 1024); if (!tb) return SZ_NSCS;
+    uint32_t *L = (uint32_t *)tb, *R = L + nodeCount, *C = R + nodeCount; uint8_t *leaf = (uint8_t *)(C + nodeCount);
+    dec_tree_unpack_kernel<<<(nodeCount + 255) / 256, 256, 0, c.stream>>>(d_tree, nodeCount, L, R, C, leaf); KCHECK();
+    // single-leaf tree: constant symbol array, empty payload
+    uint8_t root_leaf = 0; uint32_t root_sym = 0;
+    CU(cudaMemcpyAsync(&root_leaf, leaf, 1, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaMemcpyAsync(&root_sym, C, 4, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    if (root_leaf) {
+        if (BLOCKMAJOR && root_sym == 0) { set_err("all-unpredictable stream with a single-leaf tree is not supported"); return SZ_NSCS; }
+        fill_u16_kernel<<<c.sm_count * 4, 256, 0, c.stream>>>(d_out, nsym, (uint16_t)root_sym); KCHECK();
+        return 0;
+    }
+    // aligned, zero-padded copy of the payload
+    snprintf(nm, sizeof(nm), "dec_words%d", slot);
+    const uint64_t total_bits = payload_bytes * 8;
+    const size_t wbytes = ((payload_bytes + 3) & ~(size_t)3) + 256;
+    uint32_t *words = (uint32_t *)c.get(nm, wbytes); if (!words) return SZ_NSCS;
+    CU(cudaMemsetAsync((unsigned char *)words + (payload_bytes & ~(size_t)3), 0, wbytes - (payload_bytes & ~(size_t)3), c.stream));
+    CU(cudaMemcpyAsync(words, d_payload, payload_bytes, cudaMemcpyDeviceToDevice, c.stream));
+    const uint64_t nsub = (total_bits + DEC_SUB_BITS - 1) / DEC_SUB_BITS;
+    if (nsub == 0) { set_err("empty Huffman payload for %llu symbols", (unsigned long long)nsym); return SZ_NSCS; }
+    snprintf(nm, sizeof(nm), "dec_sub%d", slot);
+    const size_t per = 8 * 5 + 4 * 2;
+    unsigned char *sb = (unsigned char *)c.get(nm, per * (nsub + 8) + 256); if (!sb) return SZ_NSCS;
+    unsigned long long *endA = (unsigned long long *)sb, *endB = endA + nsub + 1, *start_used = endB + nsub + 1, *sym_off = start_used + nsub + 1, *zero_off = sym_off + nsub + 1;
+    uint32_t *count = (uint32_t *)(zero_off + nsub + 1), *zcount = count + nsub + 1;
+    unsigned int *d_changed = (unsigned int *)c.get("dec_changed", 64); if (!d_changed) return SZ_NSCS;
+    DecTree tr{L, R, C, leaf, nodeCount};
+    const unsigned grid = (unsigned)((nsub + 255) / 256);
+    unsigned long long *ep = endA, *ec = endB;
+    for (int round = 0;; round++) {
+        CU(cudaMemsetAsync(d_changed, 0, 4, c.stream));
+        dec_sync_kernel<<<grid, 256, 0, c.stream>>>(words, total_bits, nsub, tr, ep, ec, start_used, count, zcount, round == 0 ? 1 : 0, d_changed); KCHECK();
+        std::swap(ep, ec);
+        if (round == 0) continue;
+        unsigned int ch = 0;
+        CU(cudaMemcpyAsync(&ch, d_changed, 4, cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        if (!ch) break;
+        if (round > (int)nsub + 2) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
+    }
+    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(count, nsub, sym_off, nullptr); KCHECK();
+    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(zcount, nsub, zero_off, nullptr); KCHECK();
+    dec_write_kernel<T, BLOCKMAJOR><<<grid, 256, 0, c.stream>>>(words, total_bits, nsub, tr, start_used, sym_off, zero_off, nsym, g, d_out, d_unpred, unpred_count, d_field); KCHECK();
+    return 0;
+}
+
+template <typename T>
+static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size_t body_len, int body_on_device, T *d_out, szb200_stats *stats) {
+    const Geom g = make_geom(job.dim, job.n0, job.n1, job.n2);
+    const int ncoef = g.ncoef; const uint32_t nb = g.num_blocks; const uint64_t N = g.N;
+    if (N >= (1ull << 32)) { set_err("arrays of 2^32 or more elements must be cut into slabs"); return SZ_DERR; }
+    c.launches = 0;
+    int evi = 0; int stage_of_ev[ST_COUNT + 2];
+    CU(cudaEventRecord(c.ev[evi++], c.stream));
+    auto mark = [&](int st) -> int { stage_of_ev[evi] = st; CU(cudaEventRecord(c.ev[evi++], c.stream)); return 0; };
+    // ---- device copy of the body (aligned), host copy of its parseable head ----
+    unsigned char *d_body = (unsigned char *)c.get("dec_body", body_len + 256); if (!d_body) return SZ_NSCS;
+    CU(cudaMemcpyAsync(d_body, body, body_len, body_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c.stream));
+    std::vector<unsigned char> hostcopy;
+    const unsigned char *hb;
+    if (body_on_device) {
+        // everything except the two big tails (unpredictable data, type bits) is parsed on the host: fetch lazily grown prefix
+        size_t want = std::min<size_t>(body_len, (size_t)(64 + 5 * (16 + 13ull * 2 * 65536) + (nb + 7) / 8 + 4ull * 4 * nb * 2 + 4096));
+        hostcopy.resize(want);
+        CU(cudaMemcpyAsync(hostcopy.data(), d_body, want, cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        hb = hostcopy.data();
+    } else hb = (const unsigned char *)body;
+    const size_t hlen = body_on_device ? hostcopy.size() : body_len;
+    size_t o = 0;
+    auto need = [&](size_t n) -> bool { return o + n <= hlen; };
+    if (!need(4 + sizeof(T) + 12)) { set_err("truncated stream"); return SZ_NSCS; }
+    const uint32_t B = get_be32(hb + o); o += 4;
+    if (B != (uint32_t)(job.dim == 3 ? 6 : 16)) { set_err("unexpected block size %u in stream", B); return SZ_NSCS; }
+    const T eb = get_beT<T>(hb + o); o += sizeof(T);
+    const uint32_t intervals = get_be32(hb + o); o += 4;
+    const uint32_t tree_size = get_be32(hb + o); o += 4;
+    const uint32_t nodeCount = get_be32(hb + o); o += 4;
+    if (intervals > 65536 || nodeCount == 0 || nodeCount > 2 * 65536) { set_err("unsupported stream: intervals=%u nodeCount=%u", intervals, nodeCount); return SZ_NSCS; }
+    const size_t o_tree = o; o += tree_size;
+    if (!need(1 + sizeof(T))) { set_err("truncated stream"); return SZ_NSCS; }
+    const int use_mean = hb[o]; o += 1;
+    T mean; memcpy(&mean, hb + o, sizeof(T)); o += sizeof(T);
+    const size_t o_ind = o; const size_t ind_bytes = (nb - 1) / 8 + 1; o += ind_bytes;
+    if (!need(0)) { set_err("truncated stream"); return SZ_NSCS; }
+    uint32_t reg_count = 0;
+    for (uint32_t b = 0; b < nb; b++) if (!((hb[o_ind + (b >> 3)] >> (7 - (b & 7))) & 1)) reg_count++;
+    T prec[4] = {0, 0, 0, 0}; int crad[4] = {0, 0, 0, 0}; size_t o_ctree[4], o_cbits[4], o_cunp[4]; uint32_t cnode[4], ctree_size[4], cunp_cnt[4]; uint64_t cbits_bytes[4];
+    if (reg_count > 0) {
+        for (int e = 0; e < ncoef; e++) {
+            if (!need(sizeof(T) + 12)) { set_err("truncated stream"); return SZ_NSCS; }
+            prec[e] = get_beT<T>(hb + o); o += sizeof(T);
+            crad[e] = (int)get_be32(hb + o); o += 4;
+            ctree_size[e] = get_be32(hb + o); o += 4;
+            cnode[e] = get_be32(hb + o); o += 4;
+            o_ctree[e] = o; o += ctree_size[e];
+            if (!need(8)) { set_err("truncated stream"); return SZ_NSCS; }
+            cbits_bytes[e] = get_be64(hb + o); o += 8;
+            o_cbits[e] = o; o += cbits_bytes[e];
+            if (!need(4)) { set_err("truncated stream"); return SZ_NSCS; }
+            cunp_cnt[e] = get_be32(hb + o); o += 4;
+            o_cunp[e] = o; o += (size_t)cunp_cnt[e] * sizeof(T);
+            if (crad[e] != 32768 || cnode[e] == 0 || cnode[e] > 2 * 65536) { set_err("unsupported coefficient section"); return SZ_NSCS; }
+        }
+    }
+    if (!need(8)) { set_err("truncated stream"); return SZ_NSCS; }
+    uint64_t total_unpred; memcpy(&total_unpred, hb + o, 8); o += 8;
+    const size_t o_unp = o; o += total_unpred * sizeof(T);
+    if (o > body_len) { set_err("truncated stream"); return SZ_NSCS; }
+    const size_t o_bits = o; const uint64_t main_bytes = body_len - o;
+    if (mark(ST_PARSE)) return SZ_NSCS;
+
+    // ---- aligned copies of the T-typed sections ----
+    T *d_unp = (T *)c.get("dec_unpred", sizeof(T) * (total_unpred + 8)); if (!d_unp) return SZ_NSCS;
+    if (total_unpred) CU(cudaMemcpyAsync(d_unp, d_body + o_unp, sizeof(T) * total_unpred, cudaMemcpyDeviceToDevice, c.stream));
+    unsigned char *d_ind = (unsigned char *)c.get("indicator", nb + 64); if (!d_ind) return SZ_NSCS;
+    indicator_unpack_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_body + o_ind, nb, d_ind); KCHECK();
+
+    // ---- Huffman decode: main codes -> raster code array (+ unpredictable values pre-placed in the output) ----
+    uint16_t *d_codes = (uint16_t *)c.get("codes", 2ull * N + 64); if (!d_codes) return SZ_NSCS;
+    if (huff_decode<T, true>(c, 0, d_body + o_tree, nodeCount, d_body + o_bits, main_bytes, N, g, d_codes, d_unp, total_unpred, d_out)) return SZ_NSCS;
+    T *d_clast = (T *)c.get("coeff_last", sizeof(T) * 4ull * nb); if (!d_clast) return SZ_NSCS;
+    uint16_t *d_ctype = (uint16_t *)c.get("coeff_type", 2ull * 4 * nb + 64); if (!d_ctype) return SZ_NSCS;
+    if (reg_count > 0) {
+        for (int e = 0; e < ncoef; e++)
+            if (huff_decode<T, false>(c, 1 + e, d_body + o_ctree[e], cnode[e], d_body + o_cbits[e], cbits_bytes[e], reg_count, g, d_ctype + (size_t)e * nb, (const T *)nullptr, 0, (T *)nullptr)) return SZ_NSCS;
+    }
+    if (mark(ST_DECODE)) return SZ_NSCS;
+
+    // ---- coefficient chain ----
+    if (reg_count > 0) {
+        uint32_t *d_flags = (uint32_t *)c.get("reg_flags", 4ull * nb + 64), *d_list = (uint32_t *)c.get("reg_list", 4ull * nb + 64);
+        unsigned long long *d_rank = (unsigned long long *)c.get("reg_rank", 8ull * nb + 64);
+        T *d_cu = (T *)c.get("coeff_unpred", sizeof(T) * 4ull * nb);
+        T *d_dummy = (T *)c.get("reg", sizeof(T) * 4ull * nb), *d_dummy2 = (T *)c.get("reg_c", sizeof(T) * 4ull * nb);
+        if (!d_flags || !d_list || !d_rank || !d_cu || !d_dummy || !d_dummy2) return SZ_NSCS;
+        reg_flag_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_flags); KCHECK();
+        scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_flags, nb, d_rank, nullptr); KCHECK();
+        reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, 0, d_dummy, d_dummy2, d_list); KCHECK();
+        for (int e = 0; e < ncoef; e++) if (cunp_cnt[e]) CU(cudaMemcpyAsync(d_cu + (size_t)e * nb, d_body + o_cunp[e], sizeof(T) * cunp_cnt[e], cudaMemcpyDeviceToDevice, c.stream));
+        coeff_chain_decode_kernel<T><<<1, 32, 0, c.stream>>>(d_ctype, nb, reg_count, ncoef, d_list, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3],
+                                                             d_cu, d_cu + nb, d_cu + 2ull * nb, d_cu + 3ull * nb, d_clast); KCHECK();
+    }
+    if (mark(ST_DCHAIN)) return SZ_NSCS;
+
+    // ---- wavefront reconstruction ----
+    {
+        const T recip = (T)1 / eb;
+        int rc = (job.dim == 3) ? launch_wavefront<T, 3>(c, g, true, use_mean, (int)intervals, d_ind, (const T *)nullptr, d_codes, d_out, d_clast, eb, recip, mean, 0)
+                                : launch_wavefront<T, 2>(c, g, true, use_mean, (int)intervals, d_ind, (const T *)nullptr, d_codes, d_out, d_clast, eb, recip, mean, 0);
+        if (rc) return rc;
+    }
+    if (mark(ST_RECON)) return SZ_NSCS;
+    if (check_wf_err(c)) return SZ_NSCS;
+    szb200_stats st; memset(&st, 0, sizeof(st));
+    st.intervals = intervals; st.use_mean = use_mean; st.mean = (double)mean; st.num_blocks = nb; st.reg_count = reg_count; st.total_unpred = total_unpred;
+    st.tree_bytes = tree_size; st.node_count = nodeCount; st.type_bits_bytes = main_bytes; st.body_bytes = body_len; st.launches = c.launches;
+    for (int i = 1; i < evi; i++) { float ms = 0; cudaEventElapsedTime(&ms, c.ev[i - 1], c.ev[i]); st.ms_stage[stage_of_ev[i]] += ms; }
+    cudaEventElapsedTime(&st.ms_total, c.ev[0], c.ev[evi - 1]);
+    c.last = st; c.have_last = true;
+    if (stats) *stats = st;
+    return 0;
+}
+
+extern "C" int szb200_decompress_blocked(const szb200_job *job, const void *body, size_t body_len, int body_on_device, void *d_out, szb200_stats *stats) {
+    Ctx *c = ctx(); if (!c) return SZ_NSCS;
+    if (job->dim != 2 && job->dim != 3) { set_err("dim must be 2 or 3"); return SZ_DERR; }
+    if (job->dtype == 0) return decompress_impl<float>(*c, *job, body, body_len, body_on_device, (float *)d_out, stats);
+    if (job->dtype == 1) return decompress_impl<double>(*c, *job, body, body_len, body_on_device, (double *)d_out, stats);
+    set_err("dtype must be SZ_FLOAT or SZ_DOUBLE"); return SZ_NSCS;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// small element-wise kernels for the constant / lossless containers and protectValueRange
+template <typename U> __global__ void swap_copy_kernel(const unsigned char *__restrict__ src, unsigned char *__restrict__ dst, uint64_t n) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        unsigned char b[sizeof(U)];
+#pragma unroll
+        for (int q = 0; q < (int)sizeof(U); q++) b[q] = src[i * sizeof(U) + q];
+#pragma unroll
+        for (int q = 0; q < (int)sizeof(U); q++) dst[i * sizeof(U) + q] = b[sizeof(U) - 1 - q];
+    }
+}
+template <typename T> __global__ void fill_kernel(T *out, uint64_t n, T v) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) out[i] = v;
+}
+template <typename T> __global__ void clamp_kernel(T *out, uint64_t n, T mn, T mx) {     // ref: szd_float.c:161-176
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        T v = out[i];
+        if (v <= mx && v >= mn) continue;
+        if (v < mn) out[i] = mn; else if (v > mx) out[i] = mx;
+    }
+}
+
+extern "C" int szb200_swap_copy(int dtype, const void *src, int src_on_device, void *dst, int dst_on_device, size_t n) {
+    Ctx *cp = ctx(); if (!cp) return SZ_NSCS; Ctx &c = *cp;
+    const size_t es = dtype == 0 ? 4 : 8, bytes = n * es;
+    const unsigned char *s = (const unsigned char *)src; unsigned char *d = (unsigned char *)dst;
+    if (!src_on_device) { unsigned char *t = (unsigned char *)c.get("swap_in", bytes + 64); if (!t) return SZ_NSCS; CU(cudaMemcpyAsync(t, src, bytes, cudaMemcpyHostToDevice, c.stream)); s = t; }
+    if (!dst_on_device) { d = (unsigned char *)c.get("swap_out", bytes + 64); if (!d) return SZ_NSCS; }
+    if (dtype == 0) swap_copy_kernel<uint32_t><<<c.sm_count * 8, 256, 0, c.stream>>>(s, d, n); else swap_copy_kernel<uint64_t><<<c.sm_count * 8, 256, 0, c.stream>>>(s, d, n);
+    KCHECK();
+    if (!dst_on_device) CU(cudaMemcpyAsync(dst, d, bytes, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    return 0;
+}
+extern "C" int szb200_fill(int dtype, double value, void *d_out, size_t n) {
+    Ctx *cp = ctx(); if (!cp) return SZ_NSCS; Ctx &c = *cp;
+    if (dtype == 0) fill_kernel<float><<<c.sm_count * 8, 256, 0, c.stream>>>((float *)d_out, n, (float)value); else fill_kernel<double><<<c.sm_count * 8, 256, 0, c.stream>>>((double *)d_out, n, value);
+    KCHECK(); CU(cudaStreamSynchronize(c.stream)); return 0;
+}
+extern "C" int szb200_clamp(int dtype, void *d_out, size_t n, double vmin, double vmax) {
+    Ctx *cp = ctx(); if (!cp) return SZ_NSCS; Ctx &c = *cp;
+    if (dtype == 0) clamp_kernel<float><<<c.sm_count * 8, 256, 0, c.stream>>>((float *)d_out, n, (float)vmin, (float)vmax);
+    else clamp_kernel<double><<<c.sm_count * 8, 256, 0, c.stream>>>((double *)d_out, n, vmin, vmax);
+    KCHECK(); CU(cudaStreamSynchronize(c.stream)); return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" long long szb200_debug_fetch(int which, void *host_dst, size_t cap) {
+    Ctx *cp = ctx(); if (!cp) return SZ_NSCS; Ctx &c = *cp;
+    if (c.dbg_dtype < 0) return SZ_NSCS;
+    const size_t ts = c.dbg_dtype == 0 ? 4 : 8; const Geom &g = c.dbg_g; const size_t nb = g.num_blocks;
+    const char *name = nullptr; size_t bytes = 0;
+    switch (which) {
+        case 0: name = "reg"; bytes = ts * g.ncoef * nb; break;
+        case 1: name = "indicator"; bytes = nb; break;
+        case 2: name = "coeff_last"; bytes = ts * g.ncoef * nb; break;
+        case 3: name = "codes"; bytes = 2 * g.N; break;
+        case 4: name = "recon"; bytes = ts * g.N; break;
+        case 5: name = "coeff_type"; bytes = 2 * g.ncoef * nb; break;
+        case 6: name = "tree0"; bytes = 4ull * c.dbg_intervals; break;
+        default: return SZ_NSCS;
+    }
+    auto it = c.bufs.find(name); if (it == c.bufs.end() || !it->second.p) return SZ_NSCS;
+    if (bytes > cap) bytes = cap;
+    CU(cudaMemcpyAsync(host_dst, it->second.p, bytes, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    return (long long)bytes;
+}

@@ -208,7 +208,7 @@ class Oracle:
     @staticmethod
     def _trace_to_dict(tr, dt):
         d = {k: getattr(tr, k) for k, _ in szo_trace._fields_ if not k.startswith(("reg_params", "indicator", "coeff_", "type", "unpred", "recon"))}
-        if tr.kind != 0:
+        if tr.kind not in (0, 2):
             return d
         ncoef = 4 if tr.dim == 3 else 3
         nb, rc, N = tr.num_blocks, tr.reg_count, tr.N
