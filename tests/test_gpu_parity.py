@@ -1,0 +1,180 @@
+"""GPU parity tests (run on the B200 box: python -m pytest tests -m gpu).  Every call goes through the C-ABI of
+libSZ_b200.so (SZ_Init / SZ_compress_args / SZ_decompress and the szb200_* device-pointer variants); the oracle and the
+golden digests are only the checkers.  Bar: bit-exact streams and bit-exact reconstructions."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import cases
+import szref
+
+pytestmark = pytest.mark.gpu
+
+GOLD = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "streams.json")))
+
+
+@pytest.fixture(scope="module")
+def sz():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import sz_b200
+    assert os.path.exists(sz_b200.LIB_PATH), "libSZ_b200.so missing: the CUDA extension must be built in-tree (no fallback)"
+    sz_b200.set_device(0)
+    return sz_b200
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return szref.Oracle()
+
+
+def _norm(stream, kind):
+    return stream if kind != "constant" else stream[:19] + b"\0" + stream[20:]
+
+
+@pytest.mark.parametrize("case", cases.CASES, ids=cases.CASE_IDS)
+def test_stream_and_reconstruction_match_reference_digests(sz, case):
+    name, g, mode, ab, rl, extra = case
+    a = g()
+    gold = GOLD[name]
+    sz.init(cases.make_cfg(mode, ab, rl, extra))
+    s = sz.compress(a, mode, ab, rl)
+    assert len(s) == gold["size"]
+    assert hashlib.md5(_norm(s, gold["kind"])).hexdigest() == gold["md5"], "GPU stream differs from the reference stream"
+    rec = sz.decompress(s, a.dtype, a.shape)
+    if gold["dec_md5"] is not None:
+        assert hashlib.md5(rec.tobytes()).hexdigest() == gold["dec_md5"], "GPU reconstruction differs from the reference's"
+    else:
+        assert np.array_equal(rec, a)
+    sz.finalize()
+
+
+@pytest.mark.parametrize("case", cases.CASES[::4], ids=cases.CASE_IDS[::4])
+def test_cross_decode_with_oracle(sz, orc, case):
+    """oracle decodes the GPU stream; GPU decodes the oracle stream; identical bits; every point within the bound."""
+    name, g, mode, ab, rl, extra = case
+    a = g()
+    cfg = cases.make_cfg(mode, ab, rl, extra)
+    sz.init(cfg)
+    orc.init(cfg)
+    s_gpu = sz.compress(a, mode, ab, rl)
+    s_orc, tr = orc.compress(a, mode, ab, rl, trace=True)
+    d1 = orc.decompress(s_gpu, a.dtype, a.shape)
+    d2 = sz.decompress(s_orc, a.dtype, a.shape)
+    assert d1.tobytes() == d2.tobytes()
+    if tr["kind"] == 0:
+        assert np.max(np.abs(d2.astype(np.float64) - a.astype(np.float64))) <= tr["eb"]
+    sz.finalize()
+
+
+@pytest.mark.skipif(not szref.have_ref(), reason="compiled reference (oracle/_ref) not present")
+@pytest.mark.parametrize("case", cases.CASES[1::5], ids=cases.CASE_IDS[1::5])
+def test_live_reference_decodes_gpu_stream(sz, case):
+    name, g, mode, ab, rl, extra = case
+    a = g()
+    if a.size <= 20:
+        pytest.skip("the reference cannot decode its own headerless N<=20 streams")
+    cfg = cases.make_cfg(mode, ab, rl, extra)
+    ref = szref.SZLib(szref.REF_SO)
+    ref.init(cfg)
+    sz.init(cfg)
+    s_gpu = sz.compress(a, mode, ab, rl)
+    s_ref = ref.compress(a, mode, ab, rl)
+    assert _norm(s_gpu, GOLD[name]["kind"]) == _norm(s_ref, GOLD[name]["kind"])
+    d_ref = ref.decompress(s_gpu, a.dtype, a.shape)
+    d_gpu = sz.decompress(s_ref, a.dtype, a.shape)
+    assert d_ref.tobytes() == d_gpu.tobytes()
+    ref.finalize()
+    sz.finalize()
+
+
+BIG = [
+    # BASELINE.json config shapes, at sizes the oracle finishes in seconds
+    ("cfg2_nyx_256c_rel", lambda: szref.smooth_field((256, 256, 256), np.float32, span=4 * np.pi), szref.REL, 1e-4, 1e-3),
+    ("cfg3_isabel_100x500x500_abs", lambda: szref.smooth_field((100, 500, 500), np.float32, span=8 * np.pi, field_id=3), szref.ABS, 1e-2, 1e-3),
+    ("cfg4_cesm_1800x3600_rel", lambda: szref.smooth_field((1800, 3600), np.float32, span=8 * np.pi, field_id=5), szref.REL, 1e-4, 1e-4),
+    ("cfg5_s3d_4d_f64_absrel", lambda: szref.smooth_field((11, 40, 50, 60), np.float64, span=2 * np.pi), szref.ABS_AND_REL, 1e-3, 1e-3),
+    ("plane_120c_regression_heavy", lambda: szref.plane_field((120, 120, 120), np.float32), szref.ABS, 1e-1, 1e-3),
+    ("background_150c_use_mean", lambda: szref.background_field((150, 150, 150), np.float32), szref.REL, 1e-4, 1e-3),
+]
+
+
+@pytest.mark.parametrize("case", BIG, ids=[c[0] for c in BIG])
+def test_baseline_shapes_bit_exact_vs_oracle(sz, orc, case):
+    name, g, mode, ab, rl = case
+    a = g()
+    cfg = cases.make_cfg(mode, ab, rl, {})
+    sz.init(cfg)
+    orc.init(cfg)
+    s_gpu = sz.compress(a, mode, ab, rl)
+    s_orc = orc.compress(a, mode, ab, rl)
+    assert len(s_gpu) == len(s_orc)
+    assert s_gpu == s_orc
+    d_gpu = sz.decompress(s_gpu, a.dtype, a.shape)
+    d_orc = orc.decompress(s_orc, a.dtype, a.shape)
+    assert d_gpu.tobytes() == d_orc.tobytes()
+    sz.finalize()
+
+
+def test_device_pointer_api_roundtrip_and_determinism(sz):
+    import torch
+    a = szref.smooth_field((200, 210, 220), np.float32, span=6 * np.pi)
+    sz.init(dict(errorBoundMode="REL", relBoundRatio=1e-3))
+    s_host = sz.compress(a, sz.REL, 1e-4, 1e-3)
+    x = torch.from_numpy(a).cuda()
+    buf = torch.empty(sz.compress_bound(np.float32, a.shape), dtype=torch.uint8, device="cuda")
+    n1 = sz.compress_device(x, buf, sz.REL, 1e-4, 1e-3)
+    s_dev = bytes(buf[:n1].cpu().numpy().tobytes())
+    assert s_dev == s_host, "device-pointer and host-pointer entry points must produce the same stream"
+    n2 = sz.compress_device(x, buf, sz.REL, 1e-4, 1e-3)
+    assert n2 == n1 and bytes(buf[:n2].cpu().numpy().tobytes()) == s_host, "compression must be deterministic"
+    out = torch.empty_like(x)
+    sz.decompress_device(buf, n1, out)
+    rec = sz.decompress(s_host, np.float32, a.shape)
+    assert out.cpu().numpy().tobytes() == rec.tobytes()
+    eb = np.float32(1e-3 * float(np.float32(a.max()) - np.float32(a.min())))
+    assert float(np.max(np.abs(rec.astype(np.float64) - a.astype(np.float64)))) <= float(eb)
+    sz.finalize()
+
+
+def test_full_size_nyx_512_properties(sz):
+    """BASELINE.json configs[1] at full size: size-independent properties (the byte-for-byte check against the reference at
+    this size is part of bench.py's cpu_baseline leg, which runs the reference on the same field)."""
+    import torch
+    import bench
+    a = bench.make_field((512, 512, 512))
+    sz.init(dict(errorBoundMode="REL", relBoundRatio=1e-3))
+    x = torch.from_numpy(a).cuda()
+    buf = torch.empty(sz.compress_bound(np.float32, a.shape), dtype=torch.uint8, device="cuda")
+    n = sz.compress_device(x, buf, sz.REL, 1e-4, 1e-3)
+    st = sz.last_stats()
+    assert st.num_blocks == 85 ** 3 and st.intervals >= 32
+    h1 = hashlib.md5(buf[:n].cpu().numpy().tobytes()).hexdigest()
+    out = torch.empty_like(x)
+    sz.decompress_device(buf, n, out)
+    rng = float((x.max() - x.min()).item())
+    eb = float(np.float32(1e-3 * np.float64(np.float32(rng))))
+    assert float((out.double() - x.double()).abs().max().item()) <= eb
+    # idempotence of the round trip at the stream level: recompressing gives the same bytes
+    n2 = sz.compress_device(x, buf, sz.REL, 1e-4, 1e-3)
+    assert n2 == n and hashlib.md5(buf[:n2].cpu().numpy().tobytes()).hexdigest() == h1
+    assert 8 < a.nbytes / n < 30
+    sz.finalize()
+
+
+def test_unsupported_requests_fail_loudly(sz):
+    a = szref.smooth_field((32, 32, 32), np.float32)
+    sz.init(dict(szMode="SZ_BEST_COMPRESSION"))
+    with pytest.raises(sz.SZError):
+        sz.compress(a, sz.ABS, 1e-3, 0)
+    sz.init(dict())
+    with pytest.raises(sz.SZError):
+        sz.compress(a, 10, 1e-3, 0)             # PW_REL is outside this path
+    with pytest.raises(sz.SZError):
+        sz.compress(a.reshape(-1), sz.ABS, 1e-3, 0)   # 1D = SZ 1.4 path, not built
+    with pytest.raises(sz.SZError):
+        sz.decompress(b"\x02\x01\x0c" + b"\0" * 60, np.float32, (32, 32, 32))
+    sz.finalize()
