@@ -70,6 +70,22 @@ void *szb200_output_buffer(size_t bytes);
  * d_data is a DEVICE pointer.  vmin / vmax are the first-occurrence minimum and maximum (bit pattern preserved). */
 int szb200_range(int dtype, const void *d_data, size_t n, double *vmin, double *vmax);
 
+/* No counterpart in the reference.  Same reduction as szb200_range(), for callers that must not allocate device memory
+ * (codes that gave all of HBM to their own arena at start-up; threads that must not cause the device-wide synchronisation of
+ * cudaMalloc / cudaFree while other kernels run).  Calls no cudaMalloc, cudaFree or other allocating routine: the per-CTA
+ * partials and the completion counter live in a fixed 64 KiB + 256 B device array inside the library (held by every GPU that
+ * loads the library, until the process exits).
+ *   d_data        DEVICE pointer to n elements of dtype (SZ_FLOAT 0 / SZ_DOUBLE 1)
+ *   d_minmax_out  DEVICE pointer to two elements of the same type: [0] = minimum, [1] = maximum (value-exact; for an extreme
+ *                 that is a zero the sign is unspecified, unlike szb200_range())
+ *   stream        cudaStream_t as an opaque handle, NULL for the default stream; the call is asynchronous on it
+ * Limit: at most 512 MiB of input per call (2^27 floats or 2^26 doubles); more is refused with -4 and a message on stderr.
+ * Returns 0, -1 (CUDA error or bad argument), -3 (bad dtype) or -4 (input larger than the limit).
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that first call before
+ * starting any stream capture on that device.  All calls on a device share the array: it keeps the last call's contents, the
+ * counter is cleared at the start of every call, and calls whose kernels overlap on the GPU race -- serialise them. */
+int szb200_range_noalloc(int dtype, const void *d_data, size_t n, void *d_minmax_out, void *stream);
+
 /* replaces the body of SZ_compress_*_MDQ_nonblocked_with_blocked_regression (see szb200_job) from the element-count
  * field onwards (offset 4+MD): writes [N:8][block_size:4][eb:T][intervals:4]...[type bits].
  * d_data: DEVICE pointer to the original array.  dst: destination of the body (device pointer if dst_on_device). */
