@@ -101,65 +101,91 @@ struct HuffTreeDesc {           // per-tree I/O, all pointers to global memory
     uint32_t capacity;          // node capacity
 };
 
-struct HeapView { uint32_t *f, *n, *s; };
+// heap entry = (freq << 32) | node : one 64-bit shared-memory word, children (2i, 2i+1) fetched with one 128-bit load
+__device__ __forceinline__ uint32_t hf(unsigned long long e) { return (uint32_t)(e >> 32); }
 
-__device__ __forceinline__ void heap_insert(HeapView h, int &qend, uint32_t freq, uint32_t node, uint32_t size) {
-    int j, i = qend++;
-    while ((j = i >> 1)) {                                     // ref: Huffman.c:76-85
-        uint32_t fj = h.f[j];
-        if (fj <= freq) break;
-        h.f[i] = fj; h.n[i] = h.n[j]; h.s[i] = h.s[j]; i = j;
+__device__ __forceinline__ void heap_insert(unsigned long long *h, int &qend, uint32_t freq, uint32_t node) {
+    // ref: Huffman.c:76-85 (bottom-up sift).  All ancestors' slots are known up front, so their loads are issued together.
+    const int i0 = qend++;
+    unsigned long long anc[18];
+#pragma unroll
+    for (int d = 0; d < 18; d++) { int j = i0 >> (d + 1); anc[d] = j ? h[j] : 0ULL; }
+    int i = i0;
+#pragma unroll
+    for (int d = 0; d < 18; d++) {
+        int j = i0 >> (d + 1);
+        if (j == 0 || hf(anc[d]) <= freq) break;
+        h[i] = anc[d]; i = j;
     }
-    h.f[i] = freq; h.n[i] = node; h.s[i] = size;
+    h[i] = ((unsigned long long)freq << 32) | node;
 }
-__device__ __forceinline__ void heap_remove(HeapView h, int &qend, uint32_t &freq, uint32_t &node, uint32_t &size) {
-    freq = h.f[1]; node = h.n[1]; size = h.s[1];               // ref: Huffman.c:87-114
+__device__ __forceinline__ unsigned long long heap_remove(unsigned long long *h, int &qend) {
+    const unsigned long long top = h[1];                       // ref: Huffman.c:87-114
     qend--;
-    uint32_t mf = h.f[qend], mn = h.n[qend], ms = h.s[qend];   // element moved to the root, kept in registers ("hole" form of the swaps)
+    const unsigned long long m = h[qend];                      // element moved to the root, kept in a register ("hole" form of the swaps)
+    const uint32_t mf = hf(m);
     int i = 1, l;
     while ((l = i << 1) < qend) {
-        uint32_t fl = h.f[l];
-        if (l + 1 < qend) { uint32_t fr = h.f[l + 1]; if (fr < fl) { l++; fl = fr; } }
-        if (mf > fl) { h.f[i] = fl; h.n[i] = h.n[l]; h.s[i] = h.s[l]; i = l; }
+        const ulonglong2 ch = *reinterpret_cast<const ulonglong2 *>(h + l);    // h[l], h[l+1]: l is even -> 16-byte aligned
+        unsigned long long c = ch.x;
+        if (l + 1 < qend && hf(ch.y) < hf(ch.x)) { l++; c = ch.y; }
+        if (mf > hf(c)) { h[i] = c; i = l; }
         else break;
     }
-    h.f[i] = mf; h.n[i] = mn; h.s[i] = ms;
+    h[i] = m;
+    return top;
 }
 
-__global__ void __launch_bounds__(1024) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
-    extern __shared__ uint32_t s_heap[];
+constexpr int HUFF_TB = 256;
+__global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
+    extern __shared__ __align__(16) unsigned long long s_heap[];
     const HuffTreeDesc D = descs[blockIdx.x];
-    __shared__ uint32_t s_root, s_leaves, s_cnt[2], s_err;
+    __shared__ uint32_t s_scan[HUFF_TB];
+    __shared__ uint32_t s_root, s_leaves, s_cnt, s_err, s_lvl[72];
     const int t = threadIdx.x;
-    // ---- leaves in increasing symbol order: parallel count, serial insert ----
-    if (t == 0) {
-        uint32_t leaves = 0;
-        for (uint32_t i = 0; i < D.nbins; i++) if (D.hist[i]) leaves++;
-        s_leaves = leaves; s_err = 0;
-        HeapView h;
-        if (leaves + 2 <= smem_heap_capacity) { h.f = s_heap; h.n = s_heap + smem_heap_capacity; h.s = s_heap + 2 * smem_heap_capacity; }
-        else { h.f = D.heap_g; h.n = D.heap_g + D.capacity; h.s = D.heap_g + 2 * D.capacity; }
-        int qend = 1;
-        uint32_t nn = 0;
-        for (uint32_t i = 0; i < D.nbins; i++) {
+    // ---- phase A (parallel): ordered compaction of the non-empty bins -> leaf nodes 0..leaves-1 in increasing symbol order ----
+    uint32_t *lfreq = D.n_pre;                                  // scratch until phase E
+    {
+        const uint32_t per = (D.nbins + blockDim.x - 1) / blockDim.x;
+        const uint32_t lo = min(D.nbins, t * per), hi = min(D.nbins, lo + per);
+        uint32_t cnt = 0;
+        for (uint32_t i = lo; i < hi; i++) cnt += (D.hist[i] != 0);
+        s_scan[t] = cnt;
+        __syncthreads();
+        for (int o = 1; o < HUFF_TB; o <<= 1) { uint32_t v = (t >= o) ? s_scan[t - o] : 0; __syncthreads(); s_scan[t] += v; __syncthreads(); }
+        uint32_t k = s_scan[t] - cnt;
+        for (uint32_t i = lo; i < hi; i++) {
             uint32_t f = D.hist[i];
-            if (f) { D.n_left[nn] = 0xffffffffu; D.n_right[nn] = 0xffffffffu; D.n_sizeL[nn] = 0; D.n_sym[nn] = i; heap_insert(h, qend, f, nn, 1u); nn++; }
+            if (f) { D.n_sym[k] = i; lfreq[k] = f; D.n_left[k] = 0xffffffffu; D.n_right[k] = 0xffffffffu; k++; }
         }
-        while (qend > 2) {
-            uint32_t fb, nb_, sb, fa, na, sa;
-            heap_remove(h, qend, fb, nb_, sb);     // first removed -> right
-            heap_remove(h, qend, fa, na, sa);      // second removed -> left
-            D.n_left[nn] = na; D.n_right[nn] = nb_; D.n_sizeL[nn] = sa; D.n_sym[nn] = 0;
-            heap_insert(h, qend, fa + fb, nn, sa + sb + 1u);
-            nn++;
-        }
-        s_root = (leaves > 0) ? h.n[1] : 0;
+        if (t == HUFF_TB - 1) { s_leaves = s_scan[HUFF_TB - 1]; s_err = 0; }
+        for (uint32_t i = t; i < D.nbins; i += blockDim.x) { D.code[i] = 0; D.clen[i] = 0; }
+        __syncthreads();
     }
-    __syncthreads();
     const uint32_t leaves = s_leaves;
     const uint32_t nodeCount = leaves ? 2 * leaves - 1 : 0;
-    for (uint32_t i = t; i < D.nbins; i += blockDim.x) { D.code[i] = 0; D.clen[i] = 0; }
     if (leaves == 0) { if (t == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = 0; D.out[3] = 0; } return; }
+    // ---- phase B (serial): exact emulation of the reference's heap ----
+    if (t == 0) {
+        unsigned long long *h = (leaves + 4 <= smem_heap_capacity) ? s_heap : reinterpret_cast<unsigned long long *>(D.heap_g);
+        int qend = 1;
+        uint32_t k = 0;
+        for (; k + 4 <= leaves; k += 4) {                       // leaf frequencies are fetched four at a time, off the sift chain
+            uint32_t f0 = lfreq[k], f1 = lfreq[k + 1], f2 = lfreq[k + 2], f3 = lfreq[k + 3];
+            heap_insert(h, qend, f0, k); heap_insert(h, qend, f1, k + 1); heap_insert(h, qend, f2, k + 2); heap_insert(h, qend, f3, k + 3);
+        }
+        for (; k < leaves; k++) heap_insert(h, qend, lfreq[k], k);
+        uint32_t nn = leaves;
+        while (qend > 2) {
+            const unsigned long long b = heap_remove(h, qend);  // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+            const unsigned long long a = heap_remove(h, qend);  // second removed -> left
+            D.n_left[nn] = (uint32_t)a; D.n_right[nn] = (uint32_t)b;
+            heap_insert(h, qend, hf(a) + hf(b), nn);
+            nn++;
+        }
+        s_root = (uint32_t)h[1];
+    }
+    __syncthreads();
     // ---- serialised layout (ref: Huffman.c:503-585): [endian:1][L: w*n][R: w*n][C: 4*n][t: n], native endian ----
     const uint32_t w = nodeCount <= 256 ? 1u : (nodeCount <= 65536 ? 2u : 4u);
     unsigned char *tb = D.tree_bytes;
@@ -169,44 +195,67 @@ __global__ void __launch_bounds__(1024) huff_build_kernel(const HuffTreeDesc *de
         else if (w == 2) { base[2 * idx] = (unsigned char)v; base[2 * idx + 1] = (unsigned char)(v >> 8); }
         else { base[4 * idx] = (unsigned char)v; base[4 * idx + 1] = (unsigned char)(v >> 8); base[4 * idx + 2] = (unsigned char)(v >> 16); base[4 * idx + 3] = (unsigned char)(v >> 24); }
     };
-    // ---- breadth-first: pre-order index + code per node ----
-    uint32_t *fr0 = D.frontier, *fr1 = D.frontier + D.capacity;
-    if (t == 0) { tb[0] = 0; fr0[0] = s_root; D.n_pre[s_root] = 0; D.n_code[s_root] = 0; D.n_len[s_root] = 0; s_cnt[0] = 1; s_cnt[1] = 0; }
+    // ---- phase C (parallel): breadth-first order of the finished tree: order[] = nodes level by level, s_lvl[] = level starts ----
+    uint32_t *order = D.frontier;                               // [capacity]
+    uint32_t *nsize = D.frontier + D.capacity;                  // [capacity] subtree sizes (in nodes)
+    if (t == 0) { order[0] = s_root; s_lvl[0] = 0; s_lvl[1] = 1; s_cnt = 1; }
     __syncthreads();
-    int cur = 0;
-    for (int depth = 0; depth < 70; depth++) {
-        uint32_t cnt = s_cnt[cur];
-        if (cnt == 0) break;
-        uint32_t *fin = cur ? fr1 : fr0, *fout = cur ? fr0 : fr1;
-        for (uint32_t q = t; q < cnt; q += blockDim.x) {
-            uint32_t n = fin[q];
-            uint32_t pre = D.n_pre[n]; uint64_t code = D.n_code[n]; uint32_t len = D.n_len[n];
-            uint32_t l = D.n_left[n], r = D.n_right[n];
+    int nlev = 1;
+    for (; nlev < 70; nlev++) {
+        const uint32_t lo = s_lvl[nlev - 1], hi = s_lvl[nlev];
+        if (lo == hi) break;
+        for (uint32_t q = lo + t; q < hi; q += blockDim.x) {
+            const uint32_t n = order[q];
+            const uint32_t l = D.n_left[n];
+            if (l != 0xffffffffu) { uint32_t o = atomicAdd(&s_cnt, 2u); order[o] = l; order[o + 1] = D.n_right[n]; }
+        }
+        __syncthreads();
+        if (t == 0) s_lvl[nlev + 1] = s_cnt;
+        __syncthreads();
+    }
+    // s_lvl[nlev-1] == s_lvl[nlev]: levels 0 .. nlev-2 are non-empty
+    const int last_level = nlev - 2;
+    if (t == 0 && s_lvl[nlev - 1] != s_lvl[nlev]) s_err = 1;    // deeper than 68 levels: codes would not fit 64 bits anyway
+    // ---- phase D (parallel, bottom-up): subtree sizes ----
+    for (int lv = last_level; lv >= 0; lv--) {
+        const uint32_t lo = s_lvl[lv], hi = s_lvl[lv + 1];
+        for (uint32_t q = lo + t; q < hi; q += blockDim.x) {
+            const uint32_t n = order[q];
+            const uint32_t l = D.n_left[n];
+            nsize[n] = (l == 0xffffffffu) ? 1u : 1u + nsize[l] + nsize[D.n_right[n]];
+        }
+        __syncthreads();
+    }
+    // ---- phase E (parallel, top-down): pre-order index (pad_tree_*, Huffman.c:443-501), codes (build_code, :122-157), serialised arrays ----
+    if (t == 0) { tb[0] = 0; D.n_pre[s_root] = 0; D.n_code[s_root] = 0; D.n_len[s_root] = 0; }
+    __syncthreads();
+    for (int lv = 0; lv <= last_level; lv++) {
+        const uint32_t lo = s_lvl[lv], hi = s_lvl[lv + 1];
+        for (uint32_t q = lo + t; q < hi; q += blockDim.x) {
+            const uint32_t n = order[q];
+            const uint32_t pre = D.n_pre[n]; const uint64_t code = D.n_code[n]; const uint32_t len = D.n_len[n];
+            const uint32_t l = D.n_left[n];
             if (l == 0xffffffffu) {            // leaf
-                uint32_t sym = D.n_sym[n];
+                const uint32_t sym = D.n_sym[n];
                 put_w(pl, pre, 0); put_w(pr, pre, 0);
                 pc[4 * pre] = (unsigned char)sym; pc[4 * pre + 1] = (unsigned char)(sym >> 8); pc[4 * pre + 2] = (unsigned char)(sym >> 16); pc[4 * pre + 3] = (unsigned char)(sym >> 24);
                 pt[pre] = 1;
                 if (len > 64) s_err = 1;
                 D.code[sym] = code; D.clen[sym] = (uint8_t)len;
             } else {
-                uint32_t pre_l = pre + 1, pre_r = pre + 1 + D.n_sizeL[n];
+                const uint32_t r = D.n_right[n];
+                const uint32_t pre_l = pre + 1, pre_r = pre + 1 + nsize[l];
                 put_w(pl, pre, pre_l); put_w(pr, pre, pre_r);
                 pc[4 * pre] = 0; pc[4 * pre + 1] = 0; pc[4 * pre + 2] = 0; pc[4 * pre + 3] = 0;
                 pt[pre] = 0;
                 D.n_pre[l] = pre_l; D.n_pre[r] = pre_r;
                 D.n_code[l] = code << 1; D.n_code[r] = (code << 1) | 1ULL;
                 D.n_len[l] = (uint8_t)(len + 1); D.n_len[r] = (uint8_t)(len + 1);
-                uint32_t o = atomicAdd(&s_cnt[cur ^ 1], 2u);
-                fout[o] = l; fout[o + 1] = r;
             }
         }
         __syncthreads();
-        if (t == 0) s_cnt[cur] = 0;
-        cur ^= 1;
-        __syncthreads();
     }
-    if (t == 0) { D.out[0] = 1 + 2 * w * nodeCount + 4 * nodeCount + nodeCount; D.out[1] = nodeCount; D.out[2] = leaves; D.out[3] = s_err | (s_cnt[cur] ? 1u : 0u); }
+    if (t == 0) { D.out[0] = 1 + 2 * w * nodeCount + 4 * nodeCount + nodeCount; D.out[1] = nodeCount; D.out[2] = leaves; D.out[3] = s_err; }
 }
 
 // =====================================================================================================================

@@ -293,7 +293,7 @@ static int tree_ws(Ctx &c, int idx, uint32_t nbins, TreeWs &w) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     size_t o_hist = take(4ull * nbins), o_left = take(4ull * cap), o_right = take(4ull * cap), o_sizeL = take(4ull * cap), o_sym = take(4ull * cap),
-           o_pre = take(4ull * cap), o_code_n = take(8ull * cap), o_len_n = take(cap), o_front = take(8ull * cap), o_heap = take(12ull * cap),
+           o_pre = take(4ull * cap), o_code_n = take(8ull * cap), o_len_n = take(cap), o_front = take(8ull * cap), o_heap = take(8ull * cap + 64),
            o_code = take(8ull * nbins), o_clen = take(nbins), o_tree = take(16 + 13ull * cap), o_out = take(64);
     unsigned char *base = (unsigned char *)c.get(name, off); if (!base) return SZ_NSCS;
     w.hist = (uint32_t *)(base + o_hist);
@@ -511,10 +511,10 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         HuffTreeDesc hd[8];
         for (int i = 0; i < ntrees; i++) hd[i] = tw[i].d;
         CU(cudaMemcpyAsync(d_desc, hd, sizeof(HuffTreeDesc) * ntrees, cudaMemcpyHostToDevice, c.stream));   // pageable: staged before return
-        uint32_t heap_cap = (uint32_t)((c.smem_optin - 1024) / 12);
-        size_t sm = 12ull * heap_cap;
+        uint32_t heap_cap = (uint32_t)((c.smem_optin - 8192) / 8);
+        size_t sm = 8ull * heap_cap;
         CU(cudaFuncSetAttribute(huff_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        huff_build_kernel<<<ntrees, 1024, sm, c.stream>>>(d_desc, heap_cap); KCHECK();
+        huff_build_kernel<<<ntrees, HUFF_TB, sm, c.stream>>>(d_desc, heap_cap); KCHECK();
     }
     if (mark(ST_TREE)) return SZ_NSCS;
 

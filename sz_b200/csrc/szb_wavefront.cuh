@@ -19,6 +19,8 @@ namespace szb {
 constexpr int WF_CH = 32;            // chunk length along the fast axis
 constexpr int WF_W = 2 * WF_CH;      // ring length
 constexpr int WF_S = WF_W + 1;       // padded ring stride (elements)
+constexpr int WF_IW = 4 * WF_CH;     // input ring length: chunks c-1 .. c+2 (prefetch runs two chunks ahead)
+constexpr int WF_IS = WF_IW + 1;     // padded input ring stride
 
 template <int DIM> struct Pencil;
 template <> struct Pencil<3> { static constexpr int PI = 8, PJ = 4; };
@@ -41,8 +43,19 @@ struct WfParams {
 template <typename T>
 __host__ __device__ constexpr size_t wf_smem_per_warp(int dim) {
     return (size_t)(dim == 3 ? (9 * 5) : (2 * 33)) * WF_S * sizeof(T)   // reconstruction ring incl. halo rows
-           + (size_t)32 * WF_S * sizeof(T);                               // input ring (x, or codes widened to T-sized slots)
+           + (size_t)32 * WF_IS * sizeof(T);                              // input ring (x, or codes widened to T-sized slots)
 }
+
+// asynchronous global -> shared copy of one element (LDGSTS): the data never passes through registers, so the warp does not
+// stall on the load; completion is observed with cp.async.wait_group
+template <typename T>
+__device__ __forceinline__ void cp_async_elem(T *smem_dst, const T *gmem_src) {
+    const unsigned int d = (unsigned int)__cvta_generic_to_shared(smem_dst);
+    if (sizeof(T) == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem_src) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // wait until flags[p] >= need; returns false on timeout / error
 __device__ __forceinline__ bool wf_wait(const int *flag, int need, int *err) {
@@ -77,7 +90,7 @@ __global__ void __launch_bounds__(256) wavefront_kernel(WfParams P, const T *__r
     const T *row_b = ring + ((size_t)(li + 1) * RJ + lj) * WF_S;        // (li, lj-1)
     const T *row_c = ring + ((size_t)li * RJ + (lj + 1)) * WF_S;        // (li-1, lj)
     const T *row_f = ring + ((size_t)li * RJ + lj) * WF_S;              // (li-1, lj-1)
-    const T *my_in = inr + (size_t)lane * WF_S;
+    const T *my_in = inr + (size_t)lane * WF_IS;
     const uint32_t nchunks = (n2 + WF_CH - 1) / WF_CH;
 
     for (;;) {
@@ -108,67 +121,98 @@ __global__ void __launch_bounds__(256) wavefront_kernel(WfParams P, const T *__r
         bool ok = true;
         __syncwarp();
 
-        // cooperative staging of the input rows of chunk c into the input ring (row r of the pencil <-> lane r)
-        auto stage_input = [&](uint32_t c) {
+        // cooperative staging of the input rows of chunk c into the input ring (row r of the pencil <-> lane r).
+        // compress: LDGSTS (asynchronous); decompress: the u16 codes are loaded in one batch and widened to T.
+        // decompress: the u16 codes of a chunk are loaded into registers one chunk before they are needed and widened into
+        // the input ring at the next chunk boundary, so the load latency is hidden behind a whole chunk of work
+        uint16_t cv[32];
+        auto load_codes = [&](uint32_t c) {
             const uint32_t k0 = c * WF_CH;
-            if (k0 >= n2) return;
-            const uint32_t kcnt = min((uint32_t)WF_CH, n2 - k0);
-            const uint32_t slot0 = (c & 1) * WF_CH;
-#pragma unroll 4
+            const uint32_t kcnt = k0 < n2 ? min((uint32_t)WF_CH, n2 - k0) : 0u;
+#pragma unroll
             for (int r = 0; r < 32; r++) {
                 const uint32_t ri = i0 + ((DIM == 3) ? r / PJ : 0), rj = j0 + ((DIM == 3) ? r % PJ : r);
-                if (ri >= n0 || rj >= n1) continue;
-                const uint64_t rb = ((uint64_t)ri * n1 + rj) * n2 + k0;
-                if ((uint32_t)lane < kcnt) {
-                    if (DECOMP) inr[(size_t)r * WF_S + slot0 + lane] = (T)codes[rb + lane];     // codes < 65536: exact in T
-                    else inr[(size_t)r * WF_S + slot0 + lane] = __ldg(x + rb + lane);
-                }
+                cv[r] = ((uint32_t)lane < kcnt && ri < n0 && rj < n1) ? __ldg(codes + ((uint64_t)ri * n1 + rj) * n2 + k0 + lane) : (uint16_t)0;
             }
         };
-        // halo rows of chunk c from the neighbouring pencils' published reconstruction (L2 loads, never L1)
+        auto store_codes = [&](uint32_t c) {
+            const uint32_t slot0 = (c & 3) * WF_CH;
+#pragma unroll
+            for (int r = 0; r < 32; r++) inr[(size_t)r * WF_IS + slot0 + lane] = (T)cv[r];      // codes < 65536: exact in T
+        };
+        auto stage_input = [&](uint32_t c) {
+            const uint32_t k0 = c * WF_CH;
+            if (!DECOMP && k0 < n2) {
+                const uint32_t kcnt = min((uint32_t)WF_CH, n2 - k0);
+                const uint32_t slot0 = (c & 3) * WF_CH;
+                if (!DECOMP) {
+                    if ((uint32_t)lane < kcnt) {
+#pragma unroll 8
+                        for (int r = 0; r < 32; r++) {
+                            const uint32_t ri = i0 + ((DIM == 3) ? r / PJ : 0), rj = j0 + ((DIM == 3) ? r % PJ : r);
+                            if (ri < n0 && rj < n1) cp_async_elem<T>(inr + (size_t)r * WF_IS + slot0 + lane, x + ((uint64_t)ri * n1 + rj) * n2 + k0 + lane);
+                        }
+                    }
+                }
+            }
+            if (!DECOMP) cp_async_commit();          // one group per chunk, even when empty, keeps the wait count uniform
+        };
+        // halo rows of chunk c from the neighbouring pencils' published reconstruction (L2 loads, never L1): all loads are
+        // issued before the first shared-memory store so that they overlap
         auto stage_halo = [&](uint32_t c) {
             const uint32_t k0 = c * WF_CH;
             const uint32_t kcnt = min((uint32_t)WF_CH, n2 - k0);
             const uint32_t slot0 = (c & 1) * WF_CH;
             if ((uint32_t)lane >= kcnt) return;
+            T hu[PJ + 1], hl[PI];
             if (DIM == 3 && pa > 0) {
 #pragma unroll
                 for (int q = -1; q < PJ; q++) {               // rows (i0-1, j0+q)
                     const int64_t rj = (int64_t)j0 + q;
-                    if (rj < 0 || rj >= (int64_t)n1) continue;
-                    const uint64_t rb = ((uint64_t)(i0 - 1) * n1 + (uint64_t)rj) * n2 + k0;
-                    ring[((size_t)0 * RJ + (q + 1)) * WF_S + slot0 + lane] = __ldcg(recon + rb + lane);
+                    hu[q + 1] = (rj >= 0 && rj < (int64_t)n1) ? __ldcg(recon + ((uint64_t)(i0 - 1) * n1 + (uint64_t)rj) * n2 + k0 + lane) : (T)0;
                 }
             }
             if (pb > 0) {
 #pragma unroll
                 for (int q = 0; q < PI; q++) {                // rows (i0+q, j0-1)
                     const uint32_t ri = i0 + q;
-                    if (ri >= n0) continue;
-                    const uint64_t rb = ((uint64_t)ri * n1 + (j0 - 1)) * n2 + k0;
-                    ring[((size_t)(q + 1) * RJ + 0) * WF_S + slot0 + lane] = __ldcg(recon + rb + lane);
+                    hl[q] = (ri < n0) ? __ldcg(recon + ((uint64_t)ri * n1 + (j0 - 1)) * n2 + k0 + lane) : (T)0;
                 }
+            }
+            if (DIM == 3 && pa > 0) {
+#pragma unroll
+                for (int q = -1; q < PJ; q++) ring[((size_t)0 * RJ + (q + 1)) * WF_S + slot0 + lane] = hu[q + 1];
+            }
+            if (pb > 0) {
+#pragma unroll
+                for (int q = 0; q < PI; q++) ring[((size_t)(q + 1) * RJ + 0) * WF_S + slot0 + lane] = hl[q];
             }
         };
 
         const int *flag_up = (DIM == 3 && pa > 0) ? P.flags + (pid - P.pencils_b) : nullptr;
         const int *flag_left = (pb > 0) ? P.flags + (pid - 1) : nullptr;
         const uint32_t tsteps = n2 + DMAX;
+        // input prefetch runs two chunks ahead of the chunk lane 0 is in
+        if (!DECOMP) { stage_input(0); stage_input(1); }
+        else { load_codes(0); store_codes(0); load_codes(1); }
         for (uint32_t t = 0; t < tsteps; t++) {
             if ((t % WF_CH) == 0 && t < n2) {
                 const uint32_t c = t / WF_CH;
-                if (flag_up) ok = ok && wf_wait(flag_up, (int)c + 1, P.err);
-                if (flag_left) ok = ok && wf_wait(flag_left, (int)c + 1, P.err);
-                ok = __all_sync(0xffffffffu, ok);
+                if (lane == 0) {
+                    if (flag_up) ok = ok && wf_wait(flag_up, (int)c + 1, P.err);
+                    if (flag_left) ok = ok && wf_wait(flag_left, (int)c + 1, P.err);
+                }
+                ok = __shfl_sync(0xffffffffu, (int)ok, 0) != 0;
                 if (!ok) break;
                 stage_halo(c);
-                stage_input(c);
+                if (!DECOMP) { stage_input(c + 2); cp_async_wait<2>(); }   // chunk c has landed (groups c+1, c+2 may still be in flight)
+                else { if (c > 0) store_codes(c); load_codes(c + 1); }
                 __syncwarp();
             }
             const int64_t ks = (int64_t)t - delay;
             if (active && ks >= 0 && ks < (int64_t)n2) {
                 const uint32_t k = (uint32_t)ks;
-                const uint32_t slot = k % WF_W;
+                const uint32_t slot = k % WF_W, islot = k % WF_IW;
                 if (kk == sz) { bk++; kk = 0; sz = g.ax[2].edge(bk); }
                 if (kk == 0) {
                     const uint32_t bid = g.block_id(b0, b1, bk);
@@ -186,7 +230,7 @@ __global__ void __launch_bounds__(256) wavefront_kernel(WfParams P, const T *__r
                     }
                 }
                 const T rb = row_b[slot], rc = (DIM == 3) ? row_c[slot] : (T)0, rf = (DIM == 3) ? row_f[slot] : (T)0;
-                const T in = my_in[slot];
+                const T in = my_in[islot];
                 T rec;
                 if (!DECOMP) {
                     const T cur = in;
@@ -254,6 +298,7 @@ __global__ void __launch_bounds__(256) wavefront_kernel(WfParams P, const T *__r
                 if (lane == 0) st_release(P.flags + pid, (int)((t - DMAX) / WF_CH) + 1);
             }
         }
+        if (!DECOMP) cp_async_wait<0>();
         if (!ok) return;
         __threadfence();
         __syncwarp();
