@@ -11,7 +11,7 @@ SZ_FLOAT, SZ_DOUBLE = 0, 1
 ABS, REL, ABS_AND_REL, ABS_OR_REL = 0, 1, 2, 3
 _MODE_NAMES = {ABS: "ABS", REL: "REL", ABS_AND_REL: "ABS_AND_REL", ABS_OR_REL: "ABS_OR_REL"}
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libSZ_b200.so")
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", os.environ.get("SZB200_LIB", "libSZ_b200.so"))
 
 
 class SZError(RuntimeError):

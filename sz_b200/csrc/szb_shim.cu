@@ -331,6 +331,10 @@ static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, in
     CU(cudaMemcpyAsync(d_order, order.data(), 4ull * P.num_pencils, cudaMemcpyHostToDevice, c.stream));
     CU(cudaMemsetAsync(d_flags, 0, 4ull * P.num_pencils, c.stream));
     CU(cudaMemsetAsync(d_misc, 0, 64, c.stream));
+    P.prof = nullptr;
+#ifdef SZB_WF_PROFILE
+    { unsigned long long *pr = (unsigned long long *)c.get("wf_prof", 64); if (!pr) return SZ_NSCS; CU(cudaMemsetAsync(pr, 0, 64, c.stream)); P.prof = pr; }
+#endif
     P.order = d_order; P.flags = d_flags; P.ticket = d_misc; P.err = (int *)(d_misc + 4); P.indicator = indicator; P.write_all_recon = write_all;
     const size_t per_warp = wf_smem_per_warp<T>(DIM);
     int warps = sizeof(T) == 4 ? 4 : 2;
@@ -348,6 +352,12 @@ static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, in
     if (decomp) rc = use_mean ? run(wavefront_kernel<T, DIM, true, true>) : run(wavefront_kernel<T, DIM, false, true>);
     else rc = use_mean ? run(wavefront_kernel<T, DIM, true, false>) : run(wavefront_kernel<T, DIM, false, false>);
     if (rc) return rc;
+#ifdef SZB_WF_PROFILE
+    { unsigned long long h[8]; CU(cudaMemcpyAsync(h, P.prof, 64, cudaMemcpyDeviceToHost, c.stream)); CU(cudaStreamSynchronize(c.stream));
+      fprintf(stderr, "[wf-prof] pencils=%u warps/cta=%d grid=%d | per pencil: total=%.0f cyc, wait=%.0f, halo=%.0f, boundary-other=%.0f, publish=%.0f | steps/pencil=%.0f -> %.0f cyc/step excl. wait\n",
+              P.num_pencils, warps, grid, (double)h[3] / P.num_pencils, (double)h[0] / P.num_pencils, (double)h[1] / P.num_pencils, (double)h[5] / P.num_pencils, (double)h[2] / P.num_pencils,
+              (double)h[4] / P.num_pencils, ((double)h[3] - (double)h[0]) / (double)h[4]); }
+#endif
     return 0;
 }
 
