@@ -105,17 +105,12 @@ struct HuffTreeDesc {           // per-tree I/O, all pointers to global memory
 __device__ __forceinline__ uint32_t hf(unsigned long long e) { return (uint32_t)(e >> 32); }
 
 __device__ __forceinline__ void heap_insert(unsigned long long *h, int &qend, uint32_t freq, uint32_t node) {
-    // ref: Huffman.c:76-85 (bottom-up sift).  All ancestors' slots are known up front, so their loads are issued together.
-    const int i0 = qend++;
-    unsigned long long anc[18];
-#pragma unroll
-    for (int d = 0; d < 18; d++) { int j = i0 >> (d + 1); anc[d] = j ? h[j] : 0ULL; }
-    int i = i0;
-#pragma unroll
-    for (int d = 0; d < 18; d++) {
-        int j = i0 >> (d + 1);
-        if (j == 0 || hf(anc[d]) <= freq) break;
-        h[i] = anc[d]; i = j;
+    // ref: Huffman.c:76-85 (bottom-up sift: parents with a STRICTLY larger frequency move down; usually 0-2 levels)
+    int i = qend++, j;
+    while ((j = i >> 1)) {
+        const unsigned long long pj = h[j];
+        if (hf(pj) <= freq) break;
+        h[i] = pj; i = j;
     }
     h[i] = ((unsigned long long)freq << 32) | node;
 }
@@ -143,6 +138,7 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     __shared__ uint32_t s_scan[HUFF_TB];
     __shared__ uint32_t s_root, s_leaves, s_cnt, s_err, s_lvl[72];
     const int t = threadIdx.x;
+    const long long tk0 = clock64();
     // ---- phase A (parallel): ordered compaction of the non-empty bins -> leaf nodes 0..leaves-1 in increasing symbol order ----
     uint32_t *lfreq = D.n_pre;                                  // scratch until phase E
     {
@@ -166,6 +162,7 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     const uint32_t nodeCount = leaves ? 2 * leaves - 1 : 0;
     if (leaves == 0) { if (t == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = 0; D.out[3] = 0; } return; }
     // ---- phase B (serial): exact emulation of the reference's heap ----
+    const long long tk1 = clock64();
     if (t == 0) {
         unsigned long long *h = (leaves + 4 <= smem_heap_capacity) ? s_heap : reinterpret_cast<unsigned long long *>(D.heap_g);
         int qend = 1;
@@ -175,6 +172,7 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
             heap_insert(h, qend, f0, k); heap_insert(h, qend, f1, k + 1); heap_insert(h, qend, f2, k + 2); heap_insert(h, qend, f3, k + 3);
         }
         for (; k < leaves; k++) heap_insert(h, qend, lfreq[k], k);
+        D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
         uint32_t nn = leaves;
         while (qend > 2) {
             const unsigned long long b = heap_remove(h, qend);  // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
@@ -184,8 +182,10 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
             nn++;
         }
         s_root = (uint32_t)h[1];
+        D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
     }
     __syncthreads();
+    const long long tk2 = clock64();
     // ---- serialised layout (ref: Huffman.c:503-585): [endian:1][L: w*n][R: w*n][C: 4*n][t: n], native endian ----
     const uint32_t w = nodeCount <= 256 ? 1u : (nodeCount <= 65536 ? 2u : 4u);
     unsigned char *tb = D.tree_bytes;
@@ -255,7 +255,8 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         }
         __syncthreads();
     }
-    if (t == 0) { D.out[0] = 1 + 2 * w * nodeCount + 4 * nodeCount + nodeCount; D.out[1] = nodeCount; D.out[2] = leaves; D.out[3] = s_err; }
+    if (t == 0) { D.out[0] = 1 + 2 * w * nodeCount + 4 * nodeCount + nodeCount; D.out[1] = nodeCount; D.out[2] = leaves; D.out[3] = s_err;
+                  D.out[4] = (uint32_t)((tk1 - tk0) >> 10); D.out[7] = (uint32_t)((clock64() - tk2) >> 10); }   // phase cycles / 1024 (profiling aid)
 }
 
 // =====================================================================================================================

@@ -49,7 +49,8 @@ struct Buf { void *p = nullptr; size_t cap = 0; };
 
 struct Ctx {
     int dev = -1;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: side branch (coefficient histograms / trees / bit lengths)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::map<std::string, Buf> bufs;
     void *pinned = nullptr; size_t pinned_cap = 0;
     cudaEvent_t ev[ST_COUNT + 2];
@@ -67,6 +68,8 @@ struct Ctx {
         dev = d;
         CU(cudaSetDevice(d));
         CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
         for (auto &e : ev) CU(cudaEventCreate(&e));
         ev_ok = true;
         cudaDeviceProp pr; CU(cudaGetDeviceProperties(&pr, d));
@@ -305,14 +308,14 @@ static int tree_ws(Ctx &c, int idx, uint32_t nbins, TreeWs &w) {
     return 0;
 }
 
-static int launch_hist(Ctx &c, const uint16_t *s, uint64_t n, uint32_t nbins, uint32_t *hist) {
-    CU(cudaMemsetAsync(hist, 0, 4ull * nbins, c.stream));
+static int launch_hist(Ctx &c, cudaStream_t st, const uint16_t *s, uint64_t n, uint32_t nbins, uint32_t *hist) {
+    CU(cudaMemsetAsync(hist, 0, 4ull * nbins, st));
     if (n == 0) return 0;
     int use_smem = nbins <= 16384;
     size_t sm = use_smem ? 4ull * nbins : 0;
     if (sm > 48 * 1024) CU(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     uint64_t want = (n / 8 + 511) / 512; int grid = (int)std::min<uint64_t>(std::max<uint64_t>(want, 1), (uint64_t)c.sm_count * 4);
-    hist_kernel<<<grid, 512, sm, c.stream>>>(s, n, nbins, hist, use_smem); KCHECK();
+    hist_kernel<<<grid, 512, sm, st>>>(s, n, nbins, hist, use_smem); KCHECK();
     return 0;
 }
 
@@ -488,14 +491,49 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     if (reg_count > 0) {
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, ncoef, d_reg, d_regc, d_list); KCHECK();
         const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
-        coeff_chain_kernel<T><<<1, 32, 0, c.stream>>>(d_regc, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
+        ChainStep<T> *d_steps = (ChainStep<T> *)c.get("chain_steps", sizeof(ChainStep<T>) * (size_t)ncoef * reg_count + 256); if (!d_steps) return SZ_NSCS;
+        chain_prep_kernel<T><<<dim3((reg_count + 255) / 256, ncoef), 256, 0, c.stream>>>(d_regc, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_steps); KCHECK();
+        coeff_chain_kernel<T><<<1, 128, 0, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
     }
     if (mark(ST_CHAIN)) return SZ_NSCS;
 
-    // ---- wavefront predict + quantise ----
+    // ---- side branch on stream2 (needs only the chain's output): coefficient histograms, their Huffman trees (exact heap
+    //      emulation, the longest serial stage) and bit lengths run concurrently with the wavefront / main-tree / main-length work ----
+    TreeWs tw[5];
+    const int ntrees = 1 + (reg_count > 0 ? ncoef : 0);
+    if (tree_ws(c, 0, intervals, tw[0])) return SZ_NSCS;
+    for (int e = 0; e < ntrees - 1; e++) if (tree_ws(c, 1 + e, 65536, tw[1 + e])) return SZ_NSCS;
+    HuffTreeDesc *d_desc = (HuffTreeDesc *)c.get("tree_desc", sizeof(HuffTreeDesc) * 8); if (!d_desc) return SZ_NSCS;
+    const uint32_t heap_cap = (uint32_t)((c.smem_optin - 8192) / 8);
+    const size_t heap_sm = 8ull * heap_cap;
+    CU(cudaFuncSetAttribute(huff_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heap_sm));
+    const uint64_t nchunk_main = (N + ENC_CHUNK - 1) / ENC_CHUNK, nchunk_c = reg_count ? ((uint64_t)reg_count + ENC_CHUNK - 1) / ENC_CHUNK : 0;
+    const uint64_t nch_all = nchunk_main + 4 * nchunk_c + 8;
+    uint32_t *d_cb = (uint32_t *)c.get("enc_cb", 4 * nch_all), *d_cz = (uint32_t *)c.get("enc_cz", 4 * nch_all);
+    unsigned long long *d_cbo = (unsigned long long *)c.get("enc_cbo", 8 * nch_all), *d_czo = (unsigned long long *)c.get("enc_czo", 8 * nch_all);
     uint16_t *d_codes = (uint16_t *)c.get("codes", 2ull * N + 64);
     T *d_recon = (T *)c.get("recon", sizeof(T) * N + 64);
-    if (!d_codes || !d_recon) return SZ_NSCS;
+    if (!d_cb || !d_cz || !d_cbo || !d_czo || !d_codes || !d_recon) return SZ_NSCS;
+    {
+        HuffTreeDesc hd[8];
+        for (int i = 0; i < ntrees; i++) hd[i] = tw[i].d;
+        CU(cudaMemcpyAsync(d_desc, hd, sizeof(HuffTreeDesc) * ntrees, cudaMemcpyHostToDevice, c.stream));   // pageable: staged before return
+    }
+    if (ntrees > 1) {
+        CU(cudaEventRecord(c.ev_fork, c.stream));
+        CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+        for (int e = 0; e < ntrees - 1; e++)
+            if (launch_hist(c, c.stream2, d_ctype + (size_t)e * nb, reg_count, 65536, tw[1 + e].hist)) return SZ_NSCS;
+        huff_build_kernel<<<ntrees - 1, HUFF_TB, heap_sm, c.stream2>>>(d_desc + 1, heap_cap); KCHECK();
+        for (int e = 0; e < ntrees - 1; e++) {
+            const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
+            enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream2>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
+            scan_kernel<uint32_t><<<1, 1024, 0, c.stream2>>>(d_cb + o, nchunk_c, d_cbo + o, d_tot + 3 + e); KCHECK();
+        }
+        CU(cudaEventRecord(c.ev_join, c.stream2));
+    }
+
+    // ---- wavefront predict + quantise ----
     const int write_all = getenv("SZB200_DEBUG_RECON") ? 1 : 0;
     {
         int rc = (job.dim == 3) ? launch_wavefront<T, 3>(c, g, false, use_mean, (int)intervals, d_ind, d_x, d_codes, d_recon, d_clast, eb, recip_eb, mean, write_all)
@@ -504,51 +542,24 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     }
     if (mark(ST_WAVE)) return SZ_NSCS;
 
-    // ---- histograms ----
-    TreeWs tw[5];
-    if (tree_ws(c, 0, intervals, tw[0])) return SZ_NSCS;
-    if (launch_hist(c, d_codes, N, intervals, tw[0].hist)) return SZ_NSCS;
-    const int ntrees = 1 + (reg_count > 0 ? ncoef : 0);
-    for (int e = 0; e < ntrees - 1; e++) {
-        if (tree_ws(c, 1 + e, 65536, tw[1 + e])) return SZ_NSCS;
-        if (launch_hist(c, d_ctype + (size_t)e * nb, reg_count, 65536, tw[1 + e].hist)) return SZ_NSCS;
-    }
+    // ---- main histogram, main tree, main bit lengths ----
+    if (launch_hist(c, c.stream, d_codes, N, intervals, tw[0].hist)) return SZ_NSCS;
     if (mark(ST_HIST)) return SZ_NSCS;
-
-    // ---- Huffman trees (one CTA each) ----
-    HuffTreeDesc *d_desc = (HuffTreeDesc *)c.get("tree_desc", sizeof(HuffTreeDesc) * 8); if (!d_desc) return SZ_NSCS;
-    {
-        HuffTreeDesc hd[8];
-        for (int i = 0; i < ntrees; i++) hd[i] = tw[i].d;
-        CU(cudaMemcpyAsync(d_desc, hd, sizeof(HuffTreeDesc) * ntrees, cudaMemcpyHostToDevice, c.stream));   // pageable: staged before return
-        uint32_t heap_cap = (uint32_t)((c.smem_optin - 8192) / 8);
-        size_t sm = 8ull * heap_cap;
-        CU(cudaFuncSetAttribute(huff_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        huff_build_kernel<<<ntrees, HUFF_TB, sm, c.stream>>>(d_desc, heap_cap); KCHECK();
-    }
+    huff_build_kernel<<<1, HUFF_TB, heap_sm, c.stream>>>(d_desc, heap_cap); KCHECK();
     if (mark(ST_TREE)) return SZ_NSCS;
-
-    // ---- encode pass 1: chunk bit lengths (+ zero counts for the main array), prefix sums ----
-    const uint64_t nchunk_main = (N + ENC_CHUNK - 1) / ENC_CHUNK, nchunk_c = reg_count ? ((uint64_t)reg_count + ENC_CHUNK - 1) / ENC_CHUNK : 0;
-    const uint64_t nch_all = nchunk_main + 4 * nchunk_c + 8;
-    uint32_t *d_cb = (uint32_t *)c.get("enc_cb", 4 * nch_all), *d_cz = (uint32_t *)c.get("enc_cz", 4 * nch_all);
-    unsigned long long *d_cbo = (unsigned long long *)c.get("enc_cbo", 8 * nch_all), *d_czo = (unsigned long long *)c.get("enc_czo", 8 * nch_all);
-    if (!d_cb || !d_cz || !d_cbo || !d_czo) return SZ_NSCS;
     enc_len_kernel<true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.clen, d_cb, d_cz); KCHECK();
     scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cb, nchunk_main, d_cbo, d_tot + 1); KCHECK();
     scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cz, nchunk_main, d_czo, d_tot + 2); KCHECK();
-    for (int e = 0; e < ntrees - 1; e++) {
-        const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
-        enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
-        scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cb + o, nchunk_c, d_cbo + o, d_tot + 3 + e); KCHECK();
-    }
+    if (ntrees > 1) CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0));      // join the side branch
     // read back sizes
-    unsigned long long h_tot[8]; uint32_t h_tree[5][4]; ChainOut h_chain;
+    unsigned long long h_tot[8]; uint32_t h_tree[5][8]; ChainOut h_chain;
     CU(cudaMemcpyAsync(h_tot, d_tot, sizeof(h_tot), cudaMemcpyDeviceToHost, c.stream));
-    for (int i = 0; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 16, cudaMemcpyDeviceToHost, c.stream));
+    for (int i = 0; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
     if (check_wf_err(c)) return SZ_NSCS;
+    if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
+        fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
     for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err("Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
     const uint64_t main_bits = h_tot[1], total_unpred = h_tot[2];
     const uint64_t main_bytes = (main_bits + 7) / 8;
@@ -685,55 +696,60 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     // ---- device copy of the body (aligned), host copy of its parseable head ----
     unsigned char *d_body = (unsigned char *)c.get("dec_body", body_len + 256); if (!d_body) return SZ_NSCS;
     CU(cudaMemcpyAsync(d_body, body, body_len, body_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c.stream));
-    std::vector<unsigned char> hostcopy;
-    const unsigned char *hb;
-    if (body_on_device) {
-        // everything except the two big tails (unpredictable data, type bits) is parsed on the host: fetch lazily grown prefix
-        size_t want = std::min<size_t>(body_len, (size_t)(64 + 5 * (16 + 13ull * 2 * 65536) + (nb + 7) / 8 + 4ull * 4 * nb * 2 + 4096));
-        hostcopy.resize(want);
-        CU(cudaMemcpyAsync(hostcopy.data(), d_body, want, cudaMemcpyDeviceToHost, c.stream));
-        CU(cudaStreamSynchronize(c.stream));
-        hb = hostcopy.data();
-    } else hb = (const unsigned char *)body;
-    const size_t hlen = body_on_device ? hostcopy.size() : body_len;
+    // the small header fields are parsed on the host; for a device-resident stream only those few bytes are fetched
+    // (a handful of short D2H reads), never the big sections
+    std::vector<unsigned char> scratch;
+    bool fetch_failed = false;
+    auto fetch = [&](size_t off, size_t len) -> const unsigned char * {
+        if (off + len > body_len) { fetch_failed = true; static const unsigned char zeros[64] = {0}; scratch.assign(len + 64, 0); (void)zeros; return scratch.data(); }
+        if (!body_on_device) return (const unsigned char *)body + off;
+        scratch.resize(len + 16);
+        if (cudaMemcpyAsync(scratch.data(), d_body + off, len, cudaMemcpyDeviceToHost, c.stream) != cudaSuccess || cudaStreamSynchronize(c.stream) != cudaSuccess) fetch_failed = true;
+        return scratch.data();
+    };
     size_t o = 0;
-    auto need = [&](size_t n) -> bool { return o + n <= hlen; };
-    if (!need(4 + sizeof(T) + 12)) { set_err("truncated stream"); return SZ_NSCS; }
-    const uint32_t B = get_be32(hb + o); o += 4;
+    const unsigned char *hp = fetch(o, 4 + sizeof(T) + 12);
+    if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
+    const uint32_t B = get_be32(hp);
     if (B != (uint32_t)(job.dim == 3 ? 6 : 16)) { set_err("unexpected block size %u in stream", B); return SZ_NSCS; }
-    const T eb = get_beT<T>(hb + o); o += sizeof(T);
-    const uint32_t intervals = get_be32(hb + o); o += 4;
-    const uint32_t tree_size = get_be32(hb + o); o += 4;
-    const uint32_t nodeCount = get_be32(hb + o); o += 4;
+    const T eb = get_beT<T>(hp + 4);
+    const uint32_t intervals = get_be32(hp + 4 + sizeof(T));
+    const uint32_t tree_size = get_be32(hp + 8 + sizeof(T));
+    const uint32_t nodeCount = get_be32(hp + 12 + sizeof(T));
+    o += 4 + sizeof(T) + 12;
     if (intervals > 65536 || nodeCount == 0 || nodeCount > 2 * 65536) { set_err("unsupported stream: intervals=%u nodeCount=%u", intervals, nodeCount); return SZ_NSCS; }
     const size_t o_tree = o; o += tree_size;
-    if (!need(1 + sizeof(T))) { set_err("truncated stream"); return SZ_NSCS; }
-    const int use_mean = hb[o]; o += 1;
-    T mean; memcpy(&mean, hb + o, sizeof(T)); o += sizeof(T);
-    const size_t o_ind = o; const size_t ind_bytes = (nb - 1) / 8 + 1; o += ind_bytes;
-    if (!need(0)) { set_err("truncated stream"); return SZ_NSCS; }
+    const size_t ind_bytes = (nb - 1) / 8 + 1;
+    hp = fetch(o, 1 + sizeof(T) + ind_bytes);
+    if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
+    const int use_mean = hp[0];
+    T mean; memcpy(&mean, hp + 1, sizeof(T));
+    const size_t o_ind = o + 1 + sizeof(T);
     uint32_t reg_count = 0;
-    for (uint32_t b = 0; b < nb; b++) if (!((hb[o_ind + (b >> 3)] >> (7 - (b & 7))) & 1)) reg_count++;
+    { const unsigned char *ib = hp + 1 + sizeof(T); for (uint32_t b = 0; b < nb; b++) if (!((ib[b >> 3] >> (7 - (b & 7))) & 1)) reg_count++; }
+    o = o_ind + ind_bytes;
     T prec[4] = {0, 0, 0, 0}; int crad[4] = {0, 0, 0, 0}; size_t o_ctree[4], o_cbits[4], o_cunp[4]; uint32_t cnode[4], ctree_size[4], cunp_cnt[4]; uint64_t cbits_bytes[4];
     if (reg_count > 0) {
         for (int e = 0; e < ncoef; e++) {
-            if (!need(sizeof(T) + 12)) { set_err("truncated stream"); return SZ_NSCS; }
-            prec[e] = get_beT<T>(hb + o); o += sizeof(T);
-            crad[e] = (int)get_be32(hb + o); o += 4;
-            ctree_size[e] = get_be32(hb + o); o += 4;
-            cnode[e] = get_be32(hb + o); o += 4;
+            hp = fetch(o, sizeof(T) + 12);
+            if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
+            prec[e] = get_beT<T>(hp); crad[e] = (int)get_be32(hp + sizeof(T)); ctree_size[e] = get_be32(hp + sizeof(T) + 4); cnode[e] = get_be32(hp + sizeof(T) + 8);
+            o += sizeof(T) + 12;
             o_ctree[e] = o; o += ctree_size[e];
-            if (!need(8)) { set_err("truncated stream"); return SZ_NSCS; }
-            cbits_bytes[e] = get_be64(hb + o); o += 8;
+            hp = fetch(o, 8);
+            if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
+            cbits_bytes[e] = get_be64(hp); o += 8;
             o_cbits[e] = o; o += cbits_bytes[e];
-            if (!need(4)) { set_err("truncated stream"); return SZ_NSCS; }
-            cunp_cnt[e] = get_be32(hb + o); o += 4;
+            hp = fetch(o, 4);
+            if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
+            cunp_cnt[e] = get_be32(hp); o += 4;
             o_cunp[e] = o; o += (size_t)cunp_cnt[e] * sizeof(T);
             if (crad[e] != 32768 || cnode[e] == 0 || cnode[e] > 2 * 65536) { set_err("unsupported coefficient section"); return SZ_NSCS; }
         }
     }
-    if (!need(8)) { set_err("truncated stream"); return SZ_NSCS; }
-    uint64_t total_unpred; memcpy(&total_unpred, hb + o, 8); o += 8;
+    hp = fetch(o, 8);
+    if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
+    uint64_t total_unpred; memcpy(&total_unpred, hp, 8); o += 8;
     const size_t o_unp = o; o += total_unpred * sizeof(T);
     if (o > body_len) { set_err("truncated stream"); return SZ_NSCS; }
     const size_t o_bits = o; const uint64_t main_bytes = body_len - o;

@@ -462,59 +462,225 @@ __global__ void reg_gather_kernel(const unsigned char *__restrict__ indicator, c
 // =====================================================================================================================
 struct ChainOut { unsigned int unpred_count[4]; };
 
+// one step of the reference's coefficient quantiser as a function of `last` (exact formula, ref: sz_float.c:7130-7150)
 template <typename T>
-__global__ void __launch_bounds__(32) coeff_chain_kernel(const T *__restrict__ reg_c, const uint32_t *__restrict__ reg_list, uint32_t nb,
-                                                         uint32_t reg_count, int ncoef, T p0, T p1, T p2, T p3, int use_div,
-                                                         uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/,
-                                                         T *__restrict__ coeff_unpred /*[ncoef][nb]*/, ChainOut *out) {
-    constexpr int CH = 256;
-    __shared__ T s_in[4][CH];
-    __shared__ T s_last[4][CH];
-    __shared__ uint16_t s_type[4][CH];
-    __shared__ uint32_t s_blk[CH];
-    const int lane = threadIdx.x;
-    T prec = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : p3;
-    T rprec = (T)1 / prec;
-    T last = (T)0;
-    unsigned int ucnt = 0;
-    for (uint32_t r0 = 0; r0 < reg_count; r0 += CH) {
-        int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        for (int e = 0; e < ncoef; e++)
-            for (int i = lane; i < cnt; i += 32) s_in[e][i] = reg_c[(size_t)e * nb + r0 + i];
-        for (int i = lane; i < cnt; i += 32) s_blk[i] = reg_list[r0 + i];
-        __syncwarp();
-        if (lane < ncoef) {
+__device__ __forceinline__ int chain_step_exact(T cur, T last, T prec, T rprec, int use_div, T &nl) {
+    T diff = cur - last;
+    T itv = use_div ? TT<T>::abs(diff) / prec : TT<T>::abs(diff) * rprec;
+    itv = itv + (T)1;
+    if (itv < (T)65536) {
+        if (diff < (T)0) itv = -itv;
+        int ct = (int)(itv / (T)2) + 32768;
+        T dq = (T)(2 * (ct - 32768));
+        T v = dq * prec;
+        v = last + v;
+        T chk = cur - v;
+        if (TT<T>::abs(chk) > prec) { nl = cur; return 0; }
+        nl = v;
+        return ct;
+    }
+    nl = cur;
+    return 0;
+}
+
+// The chain is serial in `last`, but `last` entering step r is confined to a tiny interval around the previous
+// coefficient (the previous step verified |c[r-1] - last| <= prec, or reset last = c[r-1]).  Over that interval the
+// quantisation index is a monotone step function of `last` with at most a few pieces.  chain_prep_kernel finds, in
+// parallel and with the EXACT float formula, the interval, the (<= 3) pieces, their breakpoints and their increments;
+// the serial kernel then only compares, selects and adds.  Anything outside the prepared interval / piece budget takes
+// the exact formula in the serial kernel, so the result is bit-identical by construction.
+template <typename T> struct ChainStep {
+    T lo, hi;            // interval of `last` covered by the table
+    T thr1, thr2;        // piece 0: last <= thr1; piece 1: thr1 < last <= thr2; piece 2: last > thr2
+    T d0, d1, d2;        // increment fl(fl(2k) * prec) of each piece
+    T cur;               // the coefficient being quantised
+    uint16_t c0, c1, c2; // code (k + 32768) of each piece; 0 = beyond the 65536-interval capacity (unpredictable)
+    uint16_t np;         // number of pieces (0 = not tabulated: use the exact formula)
+};
+
+template <typename T> struct Ord;
+template <> struct Ord<float> {
+    typedef uint32_t U;
+    static __device__ __forceinline__ U to(float x) { uint32_t b = __float_as_uint(x); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+    static __device__ __forceinline__ float from(U o) { uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o; return __uint_as_float(b); }
+};
+template <> struct Ord<double> {
+    typedef unsigned long long U;
+    static __device__ __forceinline__ U to(double x) { unsigned long long b = (unsigned long long)__double_as_longlong(x); return (b >> 63) ? ~b : (b | 0x8000000000000000ULL); }
+    static __device__ __forceinline__ double from(U o) { unsigned long long b = (o >> 63) ? (o & 0x7fffffffffffffffULL) : ~o; return __longlong_as_double((long long)b); }
+};
+
+// piece id at `last` = x: the quantisation index k, or +-(1<<20) beyond the capacity (keeps the function monotone)
+template <typename T>
+__device__ __forceinline__ int chain_piece(T cur, T x, T prec, T rprec, int use_div) {
+    T diff = cur - x;
+    T itv = use_div ? TT<T>::abs(diff) / prec : TT<T>::abs(diff) * rprec;
+    itv = itv + (T)1;
+    if (!(itv < (T)65536)) return diff < (T)0 ? -(1 << 20) : (1 << 20);
+    if (diff < (T)0) itv = -itv;
+    return (int)(itv / (T)2);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ reg_c, uint32_t nb, uint32_t reg_count, int ncoef,
+                                                         T p0, T p1, T p2, T p3, int use_div, ChainStep<T> *__restrict__ steps /*[ncoef][reg_count]*/) {
+    typedef typename Ord<T>::U U;
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    const int e = blockIdx.y;
+    if (r >= reg_count || e >= ncoef) return;
+    const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
+    const T rprec = (T)1 / prec;
+    const T cur = reg_c[(size_t)e * nb + r];
+    ChainStep<T> st;
+    st.cur = cur; st.np = 0; st.c0 = st.c1 = st.c2 = 0; st.d0 = st.d1 = st.d2 = (T)0; st.thr1 = st.thr2 = (T)0;
+    T lo, hi;
+    if (r == 0) { lo = (T)0; hi = (T)0; }
+    else {
+        const T prev = reg_c[(size_t)e * nb + r - 1];
+        const T w = prec + prec * (T)0.015625;           // |prev - last| <= prec (1 + 2^-23): 1/64 of slack is plenty
+        lo = prev - w; hi = prev + w;
+        lo = Ord<T>::from(Ord<T>::to(lo) - 2); hi = Ord<T>::from(Ord<T>::to(hi) + 2);
+    }
+    st.lo = lo; st.hi = hi;
+    const U olo = Ord<T>::to(lo), ohi = Ord<T>::to(hi);
+    bool finite = (lo == lo) && (hi == hi) && TT<T>::abs(lo) < (T)1e30 && TT<T>::abs(hi) < (T)1e30 && TT<T>::abs(cur) < (T)1e30 && prec > (T)0;
+    if (finite) {
+        int pk[3]; U pend[3];
+        U a = olo;
+        int np = 0;
+        bool okp = true;
+        for (;;) {
+            const int k = chain_piece<T>(cur, Ord<T>::from(a), prec, rprec, use_div);
+            // largest ordinal b in [a, ohi] with piece(b) == k  (piece is monotone non-increasing in x)
+            U l = a, h = ohi;
+            while (l < h) {
+                const U m = l + (h - l + 1) / 2;
+                if (chain_piece<T>(cur, Ord<T>::from(m), prec, rprec, use_div) == k) l = m; else h = m - 1;
+            }
+            if (np == 3) { okp = false; break; }
+            pk[np] = k; pend[np] = l; np++;
+            if (l == ohi) break;
+            a = l + 1;
+        }
+        if (okp) {
+            auto code_of = [](int k) -> uint16_t { return (k == (1 << 20) || k == -(1 << 20)) ? (uint16_t)0 : (uint16_t)(k + 32768); };
+            auto delta_of = [&](int k) -> T { if (k == (1 << 20) || k == -(1 << 20)) return (T)0; T dq = (T)(2 * k); return dq * prec; };
+            st.np = (uint16_t)np;
+            st.c0 = code_of(pk[0]); st.d0 = delta_of(pk[0]);
+            const T big = hi;                               // thresholds beyond hi are never exceeded inside the interval
+            st.thr1 = np > 1 ? Ord<T>::from(pend[0]) : big;
+            st.thr2 = np > 2 ? Ord<T>::from(pend[1]) : big;
+            if (np > 1) { st.c1 = code_of(pk[1]); st.d1 = delta_of(pk[1]); }
+            if (np > 2) { st.c2 = code_of(pk[2]); st.d2 = delta_of(pk[2]); }
+        }
+    }
+    steps[(size_t)e * reg_count + r] = st;
+}
+
+// =====================================================================================================================
+// K5: coefficient DPCM chain (S1; ref: sz_float.c:7126-7152 no-mean "/precision", :6792-6812 mean "*recip", 2D :6035-6055;
+// double always "*recip").  last[e] threads through every regression block in raster order: one serial lane per
+// coefficient, the ncoef lanes side by side in one warp.  Per step: two compares select the prepared piece, one add
+// applies it, one subtract + compare verifies it (the reference's "machine-epsilon" guard).  128 steps at a time are
+// staged through shared memory by the whole warp so that global traffic is coalesced and off the chain.
+// =====================================================================================================================
+template <typename T>
+__global__ void __launch_bounds__(128) coeff_chain_kernel(const ChainStep<T> *__restrict__ steps, const uint32_t *__restrict__ reg_list, uint32_t nb,
+                                                          uint32_t reg_count, int ncoef, T p0, T p1, T p2, T p3, int use_div,
+                                                          uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/,
+                                                          T *__restrict__ coeff_unpred /*[ncoef][nb]*/, ChainOut *out) {
+    // Per chunk of CH steps:
+    //   (A) warp 0, lanes 0..ncoef-1: the serial part proper -- only the sequence of `last` values (compare, select, add,
+    //       verify); warps 1..3 meanwhile prefetch the next chunk of step tables into the other buffer;
+    //   (B) all four warps (warp e <-> coefficient e): codes and the ordered unpredictable list are recomputed from the
+    //       stored `last` sequence in parallel, and everything is written back coalesced.
+    constexpr int CH = sizeof(T) == 4 ? 128 : 64;
+    constexpr int WORDS = sizeof(ChainStep<T>) / 4;
+    __shared__ __align__(16) ChainStep<T> s_step[2][4][CH + 1];
+    __shared__ T s_last[4][CH + 1];                        // s_last[e][i] = value of last ENTERING step i (slot CH: leaving the chunk)
+    __shared__ uint32_t s_blk[2][CH];
+    __shared__ unsigned int s_ucnt[4];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid < 4) s_ucnt[tid] = 0;
+    auto load_chunk = [&](uint32_t r0, int buf, int t0, int nt) {
+        if (r0 >= reg_count) return;
+        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
+        for (int e = 0; e < ncoef; e++) {
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(steps + (size_t)e * reg_count + r0);
+            uint32_t *dst = reinterpret_cast<uint32_t *>(&s_step[buf][e][0]);
+#pragma unroll 8
+            for (int i = t0; i < cnt * WORDS; i += nt) dst[i] = __ldg(src + i);
+        }
+        for (int i = t0; i < cnt; i += nt) s_blk[buf][i] = reg_list[r0 + i];
+    };
+    load_chunk(0, 0, tid, 128);
+    T last = (T)0;                                          // carried by warp 0, lane e
+    const T precA = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : p3;
+    const T rprecA = (T)1 / precA;
+    const T precB = warp == 0 ? p0 : warp == 1 ? p1 : warp == 2 ? p2 : p3;
+    const T rprecB = (T)1 / precB;
+    __syncthreads();
+    int buf = 0;
+    for (uint32_t r0 = 0; r0 < reg_count; r0 += CH, buf ^= 1) {
+        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
+        // ---- (A) ----
+        if (warp > 0) load_chunk(r0 + CH, buf ^ 1, tid - 32, 96);
+        else if (lane < ncoef) {
             const int e = lane;
+            ChainStep<T> nxt = s_step[buf][e][0];
             for (int i = 0; i < cnt; i++) {
-                T cur = s_in[e][i];
-                T diff = cur - last;
-                T itv = use_div ? TT<T>::abs(diff) / prec : TT<T>::abs(diff) * rprec;
-                itv = itv + (T)1;
-                int ct = 0;
+                const ChainStep<T> st = nxt;
+                nxt = s_step[buf][e][i + 1];               // fetched while this step computes (slot CH is padding)
+                s_last[e][i] = last;
                 T nl;
-                if (itv < (T)65536) {
-                    if (diff < (T)0) itv = -itv;
-                    ct = (int)(itv / (T)2) + 32768;
-                    T dq = (T)(2 * (ct - 32768));
-                    nl = dq * prec;
-                    nl = last + nl;
-                    T chk = cur - nl;
-                    if (TT<T>::abs(chk) > prec) { ct = 0; nl = cur; coeff_unpred[(size_t)e * nb + ucnt++] = cur; }
-                } else { ct = 0; nl = cur; coeff_unpred[(size_t)e * nb + ucnt++] = cur; }
+                if (st.np != 0 && last >= st.lo && last <= st.hi) {
+                    const bool g1 = last > st.thr1, g2 = last > st.thr2;
+                    const T d = g2 ? st.d2 : (g1 ? st.d1 : st.d0);
+                    const bool cap = (g2 ? st.c2 : (g1 ? st.c1 : st.c0)) == 0;
+                    const T v = last + d;
+                    const T chk = st.cur - v;
+                    nl = (cap || TT<T>::abs(chk) > precA) ? st.cur : v;
+                } else {
+                    (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
+                }
                 last = nl;
-                s_type[e][i] = (uint16_t)ct;
-                s_last[e][i] = nl;
+            }
+            s_last[e][cnt] = last;
+        }
+        __syncthreads();
+        // ---- (B) ----
+        if (warp < ncoef) {
+            const int e = warp;
+            for (int i0 = 0; i0 < cnt; i0 += 32) {
+                const int i = i0 + lane;
+                int ct = 1; T cur = (T)0;
+                if (i < cnt) {
+                    const ChainStep<T> st = s_step[buf][e][i];
+                    const T lin = s_last[e][i];
+                    cur = st.cur;
+                    T nl;
+                    if (st.np != 0 && lin >= st.lo && lin <= st.hi) {
+                        const bool g1 = lin > st.thr1, g2 = lin > st.thr2;
+                        const T d = g2 ? st.d2 : (g1 ? st.d1 : st.d0);
+                        const int c = g2 ? st.c2 : (g1 ? st.c1 : st.c0);
+                        const T v = lin + d;
+                        const T chk = st.cur - v;
+                        ct = ((c == 0) || (TT<T>::abs(chk) > precB)) ? 0 : c;
+                    } else ct = chain_step_exact<T>(st.cur, lin, precB, rprecB, use_div, nl);
+                    coeff_type[(size_t)e * nb + r0 + i] = (uint16_t)ct;
+                    coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_last[e][i + 1];
+                }
+                const unsigned int zmask = __ballot_sync(0xffffffffu, i < cnt && ct == 0);
+                const unsigned int base = s_ucnt[e];
+                if (i < cnt && ct == 0) coeff_unpred[(size_t)e * nb + base + __popc(zmask & ((1u << lane) - 1u))] = cur;
+                __syncwarp();
+                if (lane == 0) s_ucnt[e] = base + __popc(zmask);
+                __syncwarp();
             }
         }
-        __syncwarp();
-        for (int e = 0; e < ncoef; e++)
-            for (int i = lane; i < cnt; i += 32) {
-                coeff_type[(size_t)e * nb + r0 + i] = s_type[e][i];
-                coeff_last[(size_t)e * nb + s_blk[i]] = s_last[e][i];
-            }
-        __syncwarp();
+        __syncthreads();
     }
-    if (lane < 4) out->unpred_count[lane] = (lane < ncoef) ? ucnt : 0u;
+    if (tid < 4) out->unpred_count[tid] = (tid < ncoef) ? s_ucnt[tid] : 0u;
 }
 
 }  // namespace szb
