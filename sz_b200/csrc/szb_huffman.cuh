@@ -101,11 +101,15 @@ struct HuffTreeDesc {           // per-tree I/O, all pointers to global memory
     uint32_t capacity;          // node capacity
 };
 
-// heap entry = (freq << 32) | node : one 64-bit shared-memory word, children (2i, 2i+1) fetched with one 128-bit load
+// heap entry = (freq << 32) | node : one 64-bit shared-memory word, children (2i, 2i+1) fetched with one 128-bit load.
+// Slots at or beyond qend always hold HEAP_INF, so "child does not exist" falls out of the ordinary comparisons and the
+// sift loops need no bound checks.  (A warp-cooperative variant -- speculative 5-level descent, ballot-based insert -- was
+// measured slower: every operation is a short dependent chain and the extra instructions cost more than the saved round trips.)
 __device__ __forceinline__ uint32_t hf(unsigned long long e) { return (uint32_t)(e >> 32); }
+constexpr unsigned long long HEAP_INF = ~0ULL;
 
 __device__ __forceinline__ void heap_insert(unsigned long long *h, int &qend, uint32_t freq, uint32_t node) {
-    // ref: Huffman.c:76-85 (bottom-up sift: parents with a STRICTLY larger frequency move down; usually 0-2 levels)
+    // ref: Huffman.c:76-85 (bottom-up sift: parents with a STRICTLY larger frequency move down)
     int i = qend++, j;
     while ((j = i >> 1)) {
         const unsigned long long pj = h[j];
@@ -114,18 +118,25 @@ __device__ __forceinline__ void heap_insert(unsigned long long *h, int &qend, ui
     }
     h[i] = ((unsigned long long)freq << 32) | node;
 }
-__device__ __forceinline__ unsigned long long heap_remove(unsigned long long *h, int &qend) {
-    const unsigned long long top = h[1];                       // ref: Huffman.c:87-114
+
+__device__ __forceinline__ unsigned long long heap_remove(unsigned long long *h, int &qend, int cap) {
+    // ref: Huffman.c:87-114.  The moved element m is kept in a register ("hole" form of the reference's swaps: identical
+    // final layout).  Right child only if STRICTLY smaller; descend only while m is STRICTLY larger than that child.
+    const unsigned long long top = h[1];
     qend--;
-    const unsigned long long m = h[qend];                      // element moved to the root, kept in a register ("hole" form of the swaps)
+    const unsigned long long m = h[qend];
+    h[qend] = HEAP_INF;
+    if (qend == 1) return top;
     const uint32_t mf = hf(m);
-    int i = 1, l;
-    while ((l = i << 1) < qend) {
-        const ulonglong2 ch = *reinterpret_cast<const ulonglong2 *>(h + l);    // h[l], h[l+1]: l is even -> 16-byte aligned
-        unsigned long long c = ch.x;
-        if (l + 1 < qend && hf(ch.y) < hf(ch.x)) { l++; c = ch.y; }
-        if (mf > hf(c)) { h[i] = c; i = l; }
-        else break;
+    int i = 1;
+    const int lim = cap >> 1;                                   // positions >= lim have no slots for children
+    while (i < lim) {
+        const ulonglong2 ch = *reinterpret_cast<const ulonglong2 *>(h + 2 * i);    // h[2i], h[2i+1]: 16-byte aligned
+        const bool r = hf(ch.y) < hf(ch.x);
+        const unsigned long long c = r ? ch.y : ch.x;
+        if (!(mf > hf(c))) break;
+        h[i] = c;
+        i = 2 * i + (r ? 1 : 0);
     }
     h[i] = m;
     return top;
@@ -163,26 +174,32 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     if (leaves == 0) { if (t == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = 0; D.out[3] = 0; } return; }
     // ---- phase B (serial): exact emulation of the reference's heap ----
     const long long tk1 = clock64();
-    if (t == 0) {
-        unsigned long long *h = (leaves + 4 <= smem_heap_capacity) ? s_heap : reinterpret_cast<unsigned long long *>(D.heap_g);
-        int qend = 1;
-        uint32_t k = 0;
-        for (; k + 4 <= leaves; k += 4) {                       // leaf frequencies are fetched four at a time, off the sift chain
-            uint32_t f0 = lfreq[k], f1 = lfreq[k + 1], f2 = lfreq[k + 2], f3 = lfreq[k + 3];
-            heap_insert(h, qend, f0, k); heap_insert(h, qend, f1, k + 1); heap_insert(h, qend, f2, k + 2); heap_insert(h, qend, f3, k + 3);
+    {
+        const bool in_smem = leaves + 8 <= smem_heap_capacity;
+        unsigned long long *h = in_smem ? s_heap : reinterpret_cast<unsigned long long *>(D.heap_g);
+        const int hcap = in_smem ? (int)smem_heap_capacity : (int)D.capacity;
+        for (int q = t; q < hcap; q += blockDim.x) h[q] = HEAP_INF;
+        __syncthreads();
+        if (t == 0) {                                            // one thread runs the heap (see the note at heap_insert)
+            int qend = 1;
+            uint32_t k = 0;
+            for (; k + 4 <= leaves; k += 4) {                    // leaf frequencies are fetched four at a time, off the sift chain
+                uint32_t f0 = lfreq[k], f1 = lfreq[k + 1], f2 = lfreq[k + 2], f3 = lfreq[k + 3];
+                heap_insert(h, qend, f0, k); heap_insert(h, qend, f1, k + 1); heap_insert(h, qend, f2, k + 2); heap_insert(h, qend, f3, k + 3);
+            }
+            for (; k < leaves; k++) heap_insert(h, qend, lfreq[k], k);
+            D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
+            uint32_t nn = leaves;
+            while (qend > 2) {
+                const unsigned long long b = heap_remove(h, qend, hcap);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+                const unsigned long long a = heap_remove(h, qend, hcap);    // second removed -> left
+                D.n_left[nn] = (uint32_t)a; D.n_right[nn] = (uint32_t)b;
+                heap_insert(h, qend, hf(a) + hf(b), nn);
+                nn++;
+            }
+            s_root = (uint32_t)h[1];
+            D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
         }
-        for (; k < leaves; k++) heap_insert(h, qend, lfreq[k], k);
-        D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
-        uint32_t nn = leaves;
-        while (qend > 2) {
-            const unsigned long long b = heap_remove(h, qend);  // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
-            const unsigned long long a = heap_remove(h, qend);  // second removed -> left
-            D.n_left[nn] = (uint32_t)a; D.n_right[nn] = (uint32_t)b;
-            heap_insert(h, qend, hf(a) + hf(b), nn);
-            nn++;
-        }
-        s_root = (uint32_t)h[1];
-        D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
     }
     __syncthreads();
     const long long tk2 = clock64();
