@@ -399,11 +399,57 @@ __global__ void dec_tree_unpack_kernel(const unsigned char *__restrict__ tb, uin
     L[i] = l < nodeCount ? l : 0; R[i] = r < nodeCount ? r : 0; C[i] = c; leaf[i] = pt[i] ? 1 : 0;
 }
 
-struct DecTree { const uint32_t *L, *R, *C; const uint8_t *leaf; uint32_t nodeCount; };
+constexpr int DEC_K = 11;                                   // first-level lookup width (2^11 x 4 B = 8 KB of shared memory per CTA)
+constexpr uint32_t DEC_LEAF = 0x80000000u;
 
-__device__ __forceinline__ uint32_t dec_bit(const uint32_t *__restrict__ words, uint64_t pos) {
-    uint32_t wv = bswap32(__ldg(words + (pos >> 5)));
-    return (wv >> (31 - (uint32_t)(pos & 31))) & 1u;
+struct DecTree { const uint32_t *L, *R, *C; const uint8_t *leaf; uint32_t nodeCount; const uint32_t *lut; };
+
+// lut[v], v = the next DEC_K stream bits (MSB first): a codeword of length <= DEC_K that prefixes v -> LEAF | len << 16 | symbol;
+// otherwise the index of the internal node reached after DEC_K bits (the walk continues from there bit by bit).
+__global__ void dec_lut_kernel(const uint32_t *__restrict__ L, const uint32_t *__restrict__ R, const uint32_t *__restrict__ C,
+                               const uint8_t *__restrict__ leaf, uint32_t *__restrict__ lut) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= (1u << DEC_K)) return;
+    uint32_t node = 0, e = 0;
+    bool done = false;
+    for (int d = 0; d < DEC_K; d++) {
+        const uint32_t bit = (v >> (DEC_K - 1 - d)) & 1u;
+        node = bit ? R[node] : L[node];
+        if (leaf[node] || node == 0) { e = DEC_LEAF | ((uint32_t)(d + 1) << 16) | (C[node] & 0xffffu); done = true; break; }
+    }
+    lut[v] = done ? e : node;
+}
+
+// MSB-first bit reader over the 4-byte aligned, zero-padded copy of the payload (big-endian words)
+struct BitReader {
+    const uint32_t *words; uint64_t wi; uint64_t buf; int nbits; uint64_t pos;
+    __device__ __forceinline__ void init(const uint32_t *w, uint64_t p) {
+        words = w; pos = p; wi = p >> 5;
+        const int off = (int)(p & 31);
+        buf = (((uint64_t)bswap32(__ldg(words + wi)) << 32) | (uint64_t)bswap32(__ldg(words + wi + 1))) << off;
+        nbits = 64 - off; wi += 2;
+    }
+    __device__ __forceinline__ void refill() {               // keeps at least 32 valid bits in buf
+        if (nbits < 32) { buf |= (uint64_t)bswap32(__ldg(words + wi)) << (32 - nbits); wi++; nbits += 32; }
+    }
+    __device__ __forceinline__ void consume(int n) { buf <<= n; nbits -= n; pos += (uint64_t)n; }
+};
+
+// decode ONE symbol at the reader's position (exactly the reference's bit-serial walk, ref: Huffman.c:310-343)
+__device__ __forceinline__ uint32_t dec_symbol(BitReader &br, const uint32_t *s_lut, const DecTree &tr) {
+    br.refill();
+    const uint32_t e = s_lut[(uint32_t)(br.buf >> (64 - DEC_K))];
+    if (e & DEC_LEAF) { br.consume((int)((e >> 16) & 63u)); return e & 0xffffu; }
+    uint32_t node = e;
+    br.consume(DEC_K);
+    for (int guard = 0; guard < 64; guard++) {
+        br.refill();
+        const uint32_t bit = (uint32_t)(br.buf >> 63);
+        br.consume(1);
+        node = bit ? tr.R[node] : tr.L[node];
+        if (tr.leaf[node] || node == 0) break;
+    }
+    return tr.C[node];
 }
 
 // one Jacobi round.  start_used[s] = start position used by the most recent decode of sub-sequence s (init ~0).
@@ -411,23 +457,23 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const uint32_t *__restric
                                                        const unsigned long long *__restrict__ end_prev, unsigned long long *end_cur,
                                                        unsigned long long *start_used, uint32_t *count, uint32_t *zcount,
                                                        int first_round, unsigned int *changed) {
+    __shared__ uint32_t s_lut[1 << DEC_K];
+    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
+    __syncthreads();
     uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (sidx >= nsub) return;
     uint64_t lo = sidx * DEC_SUB_BITS, hi = lo + DEC_SUB_BITS;
     uint64_t start = (sidx == 0) ? 0 : (first_round ? lo : end_prev[sidx - 1]);
     if (!first_round && start == start_used[sidx]) { end_cur[sidx] = end_prev[sidx]; return; }
-    uint64_t pos = start;
     uint32_t cnt = 0, zc = 0;
     const uint64_t limit = total_bits + 64;
-    while (pos < hi && pos < limit) {
-        uint32_t node = 0;
-        do {
-            uint32_t bit = dec_bit(words, pos); pos++;
-            node = bit ? tr.R[node] : tr.L[node];
-        } while (!tr.leaf[node] && node != 0 && pos < limit + 128);
-        cnt++; zc += (tr.C[node] == 0);
+    if (hi > limit) hi = limit;
+    BitReader br; br.init(words, start);
+    while (br.pos < hi) {
+        const uint32_t sym = dec_symbol(br, s_lut, tr);
+        cnt++; zc += (sym == 0);
     }
-    start_used[sidx] = start; end_cur[sidx] = pos; count[sidx] = cnt; zcount[sidx] = zc;
+    start_used[sidx] = start; end_cur[sidx] = br.pos; count[sidx] = cnt; zcount[sidx] = zc;
     *changed = 1u;
 }
 
@@ -438,22 +484,22 @@ __global__ void __launch_bounds__(256) dec_write_kernel(const uint32_t *__restri
                                                         const unsigned long long *__restrict__ start_used,
                                                         const unsigned long long *__restrict__ sym_off, const unsigned long long *__restrict__ zero_off,
                                                         uint64_t n, Geom g, uint16_t *codes_out, const T *__restrict__ unpred, uint64_t unpred_count, T *field_out) {
+    __shared__ uint32_t s_lut[1 << DEC_K];
+    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
+    __syncthreads();
     uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (sidx >= nsub) return;
     uint64_t p = sym_off[sidx];
     if (p >= n) return;
     uint64_t zr = zero_off ? zero_off[sidx] : 0;
-    uint64_t hi = (sidx + 1) * DEC_SUB_BITS, pos = start_used[sidx];
+    uint64_t hi = (sidx + 1) * DEC_SUB_BITS;
     const uint64_t limit = total_bits + 64;
+    if (hi > limit) hi = limit;
+    BitReader br; br.init(words, start_used[sidx]);
     BMIter it;
     if (BLOCKMAJOR) it.init(g, p);
-    while (pos < hi && pos < limit && p < n) {
-        uint32_t node = 0;
-        do {
-            uint32_t bit = dec_bit(words, pos); pos++;
-            node = bit ? tr.R[node] : tr.L[node];
-        } while (!tr.leaf[node] && node != 0 && pos < limit + 128);
-        uint32_t sym = tr.C[node];
+    while (br.pos < hi && p < n) {
+        const uint32_t sym = dec_symbol(br, s_lut, tr);
         if (BLOCKMAJOR) {
             codes_out[it.raster] = (uint16_t)sym;
             if (sym == 0 && field_out) { if (zr < unpred_count) field_out[it.raster] = unpred[zr]; zr++; }
@@ -468,24 +514,74 @@ __global__ void fill_u16_kernel(uint16_t *out, uint64_t n, uint16_t v) {
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) out[i] = v;
 }
 
-// coefficient chain decode (S1, decoder side; ref: szd_float.c:5809-5819): pure add chain per coefficient lane
+// coefficient chain decode (S1, decoder side; ref: szd_float.c:5809-5819): last = last + 2(t-R)*prec, or the next stored raw
+// value when t == 0.  Only the running float addition is serial.  Per chunk: warps 1..3 prepare the NEXT chunk (increments
+// fl(fl(2(t-R)) * prec), reset flags, the raw values picked by a ballot-ranked cursor) while lanes 0..ncoef-1 of warp 0
+// run the add chain of the CURRENT chunk out of shared memory; then everybody scatters the results to the block ids.
 template <typename T>
-__global__ void __launch_bounds__(32) coeff_chain_decode_kernel(const uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, uint32_t nb, uint32_t reg_count, int ncoef,
-                                                                const uint32_t *__restrict__ reg_list, T p0, T p1, T p2, T p3, int r0_, int r1_, int r2_, int r3_,
-                                                                const T *__restrict__ cu0, const T *__restrict__ cu1, const T *__restrict__ cu2, const T *__restrict__ cu3,
-                                                                T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
-    const int e = threadIdx.x;
-    if (e >= ncoef) return;
-    const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
-    const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
-    const T *cu = e == 0 ? cu0 : e == 1 ? cu1 : e == 2 ? cu2 : cu3;
+__global__ void __launch_bounds__(128) coeff_chain_decode_kernel(const uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, uint32_t nb, uint32_t reg_count, int ncoef,
+                                                                 const uint32_t *__restrict__ reg_list, T p0, T p1, T p2, T p3, int r0_, int r1_, int r2_, int r3_,
+                                                                 const T *__restrict__ cu0, const T *__restrict__ cu1, const T *__restrict__ cu2, const T *__restrict__ cu3,
+                                                                 T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
+    constexpr int CH = 96;                                   // one element per preparing thread (warps 1..3)
+    __shared__ T s_val[2][4][CH];                            // increment, or the raw value when s_rst is set
+    __shared__ unsigned char s_rst[2][4][CH];
+    __shared__ T s_out[4][CH];
+    __shared__ uint32_t s_blk[2][CH];
+    __shared__ unsigned int s_cur[4];                        // cursor into each coefficient's raw-value list
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid < 4) s_cur[tid] = 0;
+    __syncthreads();
+    auto prepare = [&](uint32_t r0, int buf) {               // executed by warps 1..3 (96 threads, whole warps)
+        if (r0 >= reg_count) return;
+        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
+        const int i = tid - 32;                              // 0..95
+        if (i < cnt) s_blk[buf][i] = reg_list[r0 + i];
+        for (int e = 0; e < ncoef; e++) {
+            const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
+            const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
+            const T *cu = e == 0 ? cu0 : e == 1 ? cu1 : e == 2 ? cu2 : cu3;
+            const int tcode = (i < cnt) ? (int)coeff_type[(size_t)e * nb + r0 + i] : 1;
+            const bool z = (i < cnt) && tcode == 0;
+            // ordered rank of this zero among the chunk's zeros: three warps, in warp order
+            const unsigned int zm = __ballot_sync(0xffffffffu, z);
+            __shared__ unsigned int s_wz[3];
+            if (lane == 0) s_wz[warp - 1] = __popc(zm);
+            asm volatile("bar.sync 1, 96;" ::: "memory");    // named barrier: only the three preparing warps
+            unsigned int before = 0;
+            for (int w2 = 0; w2 < warp - 1; w2++) before += s_wz[w2];
+            const unsigned int tot = s_wz[0] + s_wz[1] + s_wz[2];
+            const unsigned int base = s_cur[e];
+            if (i < cnt) {
+                if (z) { s_val[buf][e][i] = cu[base + before + __popc(zm & ((1u << lane) - 1u))]; s_rst[buf][e][i] = 1; }
+                else { T dq = (T)(2 * (tcode - rad)); s_val[buf][e][i] = dq * prec; s_rst[buf][e][i] = 0; }
+            }
+            asm volatile("bar.sync 1, 96;" ::: "memory");
+            if (tid == 32) s_cur[e] = base + tot;
+            asm volatile("bar.sync 1, 96;" ::: "memory");
+        }
+    };
+    if (warp > 0) prepare(0, 0);
+    __syncthreads();
     T last = (T)0;
-    uint32_t ui = 0;
-    for (uint32_t r = 0; r < reg_count; r++) {
-        int tcode = coeff_type[(size_t)e * nb + r];
-        if (tcode != 0) { T dq = (T)(2 * (tcode - rad)); T v = dq * prec; last = last + v; }
-        else last = cu[ui++];
-        coeff_last[(size_t)e * nb + reg_list[r]] = last;
+    int buf = 0;
+    for (uint32_t r0 = 0; r0 < reg_count; r0 += CH, buf ^= 1) {
+        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
+        if (warp > 0) prepare(r0 + CH, buf ^ 1);
+        else if (lane < ncoef) {
+            const int e = lane;
+#pragma unroll 4
+            for (int i = 0; i < cnt; i++) {
+                const T v = s_val[buf][e][i];
+                const T sum = last + v;
+                last = s_rst[buf][e][i] ? v : sum;
+                s_out[e][i] = last;
+            }
+        }
+        __syncthreads();
+        for (int e = 0; e < ncoef; e++)
+            for (int i = tid; i < cnt; i += 128) coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_out[e][i];
+        __syncthreads();
     }
 }
 

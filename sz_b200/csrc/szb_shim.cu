@@ -636,8 +636,9 @@ static int huff_decode(Ctx &c, int slot, const unsigned char *d_tree, uint32_t n
                        uint64_t nsym, const Geom &g, uint16_t *d_out, const T *d_unpred, uint64_t unpred_count, T *d_field) {
     char nm[48];
     snprintf(nm, sizeof(nm), "dec_tree%d", slot);
-    unsigned char *tb = (unsigned char *)c.get(nm, 16ull * nodeCount + 1024); if (!tb) return SZ_NSCS;
-    uint32_t *L = (uint32_t *)tb, *R = L + nodeCount, *C = R + nodeCount; uint8_t *leaf = (uint8_t *)(C + nodeCount);
+    unsigned char *tb = (unsigned char *)c.get(nm, 16ull * nodeCount + 1024 + 4ull * (1u << DEC_K)); if (!tb) return SZ_NSCS;
+    uint32_t *lut = (uint32_t *)tb;
+    uint32_t *L = lut + (1u << DEC_K), *R = L + nodeCount, *C = R + nodeCount; uint8_t *leaf = (uint8_t *)(C + nodeCount);
     dec_tree_unpack_kernel<<<(nodeCount + 255) / 256, 256, 0, c.stream>>>(d_tree, nodeCount, L, R, C, leaf); KCHECK();
     // single-leaf tree: constant symbol array, empty payload
     uint8_t root_leaf = 0; uint32_t root_sym = 0;
@@ -664,7 +665,8 @@ static int huff_decode(Ctx &c, int slot, const unsigned char *d_tree, uint32_t n
     unsigned long long *endA = (unsigned long long *)sb, *endB = endA + nsub + 1, *start_used = endB + nsub + 1, *sym_off = start_used + nsub + 1, *zero_off = sym_off + nsub + 1;
     uint32_t *count = (uint32_t *)(zero_off + nsub + 1), *zcount = count + nsub + 1;
     unsigned int *d_changed = (unsigned int *)c.get("dec_changed", 64); if (!d_changed) return SZ_NSCS;
-    DecTree tr{L, R, C, leaf, nodeCount};
+    dec_lut_kernel<<<((1u << DEC_K) + 255) / 256, 256, 0, c.stream>>>(L, R, C, leaf, lut); KCHECK();
+    DecTree tr{L, R, C, leaf, nodeCount, lut};
     const unsigned grid = (unsigned)((nsub + 255) / 256);
     unsigned long long *ep = endA, *ec = endB;
     for (int round = 0;; round++) {
@@ -783,7 +785,7 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
         scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_flags, nb, d_rank, nullptr); KCHECK();
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, 0, d_dummy, d_dummy2, d_list); KCHECK();
         for (int e = 0; e < ncoef; e++) if (cunp_cnt[e]) CU(cudaMemcpyAsync(d_cu + (size_t)e * nb, d_body + o_cunp[e], sizeof(T) * cunp_cnt[e], cudaMemcpyDeviceToDevice, c.stream));
-        coeff_chain_decode_kernel<T><<<1, 32, 0, c.stream>>>(d_ctype, nb, reg_count, ncoef, d_list, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3],
+        coeff_chain_decode_kernel<T><<<1, 128, 0, c.stream>>>(d_ctype, nb, reg_count, ncoef, d_list, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3],
                                                              d_cu, d_cu + nb, d_cu + 2ull * nb, d_cu + 3ull * nb, d_clast); KCHECK();
     }
     if (mark(ST_DCHAIN)) return SZ_NSCS;
