@@ -308,6 +308,19 @@ static int tree_ws(Ctx &c, int idx, uint32_t nbins, TreeWs &w) {
     return 0;
 }
 
+// exclusive scan helper (tile sums -> offsets -> apply); `slot` selects a private tile-sum buffer so that scans on different
+// streams never share scratch
+static int launch_scan(Ctx &c, cudaStream_t st, int slot, const uint32_t *in, uint64_t n, unsigned long long *out, unsigned long long *total) {
+    if (n == 0) { if (total) CU(cudaMemsetAsync(total, 0, 8, st)); return 0; }
+    const uint32_t ntiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
+    char nm[32]; snprintf(nm, sizeof(nm), "scan_tiles%d", slot);
+    unsigned long long *tiles = (unsigned long long *)c.get(nm, 8ull * ntiles + 64); if (!tiles) return SZ_NSCS;
+    scan_tile_sum_kernel<uint32_t><<<ntiles, SCAN_TB, 0, st>>>(in, n, tiles); KCHECK();
+    scan_tile_offsets_kernel<<<1, SCAN_TB, 0, st>>>(tiles, ntiles, total); KCHECK();
+    scan_apply_kernel<uint32_t><<<ntiles, SCAN_TB, 0, st>>>(in, n, tiles, out); KCHECK();
+    return 0;
+}
+
 static int launch_hist(Ctx &c, cudaStream_t st, const uint16_t *s, uint64_t n, uint32_t nbins, uint32_t *hist) {
     CU(cudaMemsetAsync(hist, 0, 4ull * nbins, st));
     if (n == 0) return 0;
@@ -477,7 +490,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         else fit_select_kernel<T, 2><<<grid, 128, 0, c.stream>>>(d_x, g, noise, use_mean, mean, d_reg, d_ind);
         KCHECK();
         reg_flag_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_flags); KCHECK();
-        scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_flags, nb, d_rank, d_tot); KCHECK();
+        if (launch_scan(c, c.stream, 0, d_flags, nb, d_rank, d_tot)) return SZ_NSCS;
     }
     unsigned long long reg_count_ll = 0;
     CU(cudaMemcpyAsync(&reg_count_ll, d_tot, 8, cudaMemcpyDeviceToHost, c.stream));
@@ -528,7 +541,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         for (int e = 0; e < ntrees - 1; e++) {
             const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
             enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream2>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
-            scan_kernel<uint32_t><<<1, 1024, 0, c.stream2>>>(d_cb + o, nchunk_c, d_cbo + o, d_tot + 3 + e); KCHECK();
+            if (launch_scan(c, c.stream2, 1, d_cb + o, nchunk_c, d_cbo + o, d_tot + 3 + e)) return SZ_NSCS;
         }
         CU(cudaEventRecord(c.ev_join, c.stream2));
     }
@@ -548,8 +561,8 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     huff_build_kernel<<<1, HUFF_TB, heap_sm, c.stream>>>(d_desc, heap_cap); KCHECK();
     if (mark(ST_TREE)) return SZ_NSCS;
     enc_len_kernel<true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.clen, d_cb, d_cz); KCHECK();
-    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cb, nchunk_main, d_cbo, d_tot + 1); KCHECK();
-    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_cz, nchunk_main, d_czo, d_tot + 2); KCHECK();
+    if (launch_scan(c, c.stream, 0, d_cb, nchunk_main, d_cbo, d_tot + 1)) return SZ_NSCS;
+    if (launch_scan(c, c.stream, 0, d_cz, nchunk_main, d_czo, d_tot + 2)) return SZ_NSCS;
     if (ntrees > 1) CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0));      // join the side branch
     // read back sizes
     unsigned long long h_tot[8]; uint32_t h_tree[5][8]; ChainOut h_chain;
@@ -630,59 +643,87 @@ extern "C" int szb200_compress_blocked(const szb200_job *job, const void *d_data
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// decode one Huffman-coded symbol array.  tree bytes + payload are device pointers into the (aligned copy of the) stream.
-template <typename T, bool BLOCKMAJOR>
-static int huff_decode(Ctx &c, int slot, const unsigned char *d_tree, uint32_t nodeCount, const unsigned char *d_payload, uint64_t payload_bytes,
-                       uint64_t nsym, const Geom &g, uint16_t *d_out, const T *d_unpred, uint64_t unpred_count, T *d_field) {
+// Huffman decode of several symbol arrays driven together (main type array + the coefficient arrays): the Jacobi
+// synchronisation rounds of all of them are launched back to back and their "changed" flags are read with ONE host sync per
+// pair of rounds.  tree bytes + payloads are device pointers into the (aligned copy of the) stream.
+struct DecJob {
+    int slot; const unsigned char *d_tree; uint32_t nodeCount; const unsigned char *d_payload; uint64_t payload_bytes, nsym;
+    bool blockmajor; uint16_t *d_out;
+    // internal
+    uint32_t *lut, *L, *R, *C; uint8_t *leaf; uint32_t *words; uint64_t total_bits, nsub;
+    unsigned long long *ep, *ec, *start_used, *sym_off, *zero_off; uint32_t *count, *zcount;
+    bool single_leaf, converged; uint32_t root_sym;
+};
+
+template <typename T>
+static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const T *d_unpred, uint64_t unpred_count, T *d_field) {
     char nm[48];
-    snprintf(nm, sizeof(nm), "dec_tree%d", slot);
-    unsigned char *tb = (unsigned char *)c.get(nm, 16ull * nodeCount + 1024 + 4ull * (1u << DEC_K)); if (!tb) return SZ_NSCS;
-    uint32_t *lut = (uint32_t *)tb;
-    uint32_t *L = lut + (1u << DEC_K), *R = L + nodeCount, *C = R + nodeCount; uint8_t *leaf = (uint8_t *)(C + nodeCount);
-    dec_tree_unpack_kernel<<<(nodeCount + 255) / 256, 256, 0, c.stream>>>(d_tree, nodeCount, L, R, C, leaf); KCHECK();
-    // single-leaf tree: constant symbol array, empty payload
-    uint8_t root_leaf = 0; uint32_t root_sym = 0;
-    CU(cudaMemcpyAsync(&root_leaf, leaf, 1, cudaMemcpyDeviceToHost, c.stream));
-    CU(cudaMemcpyAsync(&root_sym, C, 4, cudaMemcpyDeviceToHost, c.stream));
+    struct RootInfo { uint8_t leaf; uint32_t sym; } roots[8];
+    for (int j = 0; j < njobs; j++) {
+        DecJob &J = jobs[j];
+        snprintf(nm, sizeof(nm), "dec_tree%d", J.slot);
+        unsigned char *tb = (unsigned char *)c.get(nm, 16ull * J.nodeCount + 1024 + 4ull * (1u << DEC_K)); if (!tb) return SZ_NSCS;
+        J.lut = (uint32_t *)tb; J.L = J.lut + (1u << DEC_K); J.R = J.L + J.nodeCount; J.C = J.R + J.nodeCount; J.leaf = (uint8_t *)(J.C + J.nodeCount);
+        dec_tree_unpack_kernel<<<(J.nodeCount + 255) / 256, 256, 0, c.stream>>>(J.d_tree, J.nodeCount, J.L, J.R, J.C, J.leaf); KCHECK();
+        CU(cudaMemcpyAsync(&roots[j].leaf, J.leaf, 1, cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaMemcpyAsync(&roots[j].sym, J.C, 4, cudaMemcpyDeviceToHost, c.stream));
+    }
     CU(cudaStreamSynchronize(c.stream));
-    if (root_leaf) {
-        if (BLOCKMAJOR && root_sym == 0) { set_err("all-unpredictable stream with a single-leaf tree is not supported"); return SZ_NSCS; }
-        fill_u16_kernel<<<c.sm_count * 4, 256, 0, c.stream>>>(d_out, nsym, (uint16_t)root_sym); KCHECK();
-        return 0;
+    unsigned int *d_changed = (unsigned int *)c.get("dec_changed", 256); if (!d_changed) return SZ_NSCS;
+    for (int j = 0; j < njobs; j++) {
+        DecJob &J = jobs[j];
+        J.single_leaf = roots[j].leaf != 0; J.root_sym = roots[j].sym; J.converged = false;
+        if (J.single_leaf) {            // constant symbol array, empty payload (ref: Huffman.c:316-321)
+            if (J.blockmajor && J.root_sym == 0) { set_err("all-unpredictable stream with a single-leaf tree is not supported"); return SZ_NSCS; }
+            fill_u16_kernel<<<c.sm_count * 4, 256, 0, c.stream>>>(J.d_out, J.nsym, (uint16_t)J.root_sym); KCHECK();
+            J.converged = true;
+            continue;
+        }
+        dec_lut_kernel<<<((1u << DEC_K) + 255) / 256, 256, 0, c.stream>>>(J.L, J.R, J.C, J.leaf, J.lut); KCHECK();
+        snprintf(nm, sizeof(nm), "dec_words%d", J.slot);
+        J.total_bits = J.payload_bytes * 8;
+        const size_t wbytes = ((J.payload_bytes + 3) & ~(size_t)3) + 256;
+        J.words = (uint32_t *)c.get(nm, wbytes); if (!J.words) return SZ_NSCS;
+        CU(cudaMemsetAsync((unsigned char *)J.words + (J.payload_bytes & ~(size_t)3), 0, wbytes - (J.payload_bytes & ~(size_t)3), c.stream));
+        CU(cudaMemcpyAsync(J.words, J.d_payload, J.payload_bytes, cudaMemcpyDeviceToDevice, c.stream));
+        J.nsub = (J.total_bits + DEC_SUB_BITS - 1) / DEC_SUB_BITS;
+        if (J.nsub == 0) { set_err("empty Huffman payload for %llu symbols", (unsigned long long)J.nsym); return SZ_NSCS; }
+        snprintf(nm, sizeof(nm), "dec_sub%d", J.slot);
+        unsigned char *sb = (unsigned char *)c.get(nm, (8 * 5 + 4 * 2) * (J.nsub + 8) + 256); if (!sb) return SZ_NSCS;
+        J.ep = (unsigned long long *)sb; J.ec = J.ep + J.nsub + 1; J.start_used = J.ec + J.nsub + 1; J.sym_off = J.start_used + J.nsub + 1; J.zero_off = J.sym_off + J.nsub + 1;
+        J.count = (uint32_t *)(J.zero_off + J.nsub + 1); J.zcount = J.count + J.nsub + 1;
     }
-    // aligned, zero-padded copy of the payload
-    snprintf(nm, sizeof(nm), "dec_words%d", slot);
-    const uint64_t total_bits = payload_bytes * 8;
-    const size_t wbytes = ((payload_bytes + 3) & ~(size_t)3) + 256;
-    uint32_t *words = (uint32_t *)c.get(nm, wbytes); if (!words) return SZ_NSCS;
-    CU(cudaMemsetAsync((unsigned char *)words + (payload_bytes & ~(size_t)3), 0, wbytes - (payload_bytes & ~(size_t)3), c.stream));
-    CU(cudaMemcpyAsync(words, d_payload, payload_bytes, cudaMemcpyDeviceToDevice, c.stream));
-    const uint64_t nsub = (total_bits + DEC_SUB_BITS - 1) / DEC_SUB_BITS;
-    if (nsub == 0) { set_err("empty Huffman payload for %llu symbols", (unsigned long long)nsym); return SZ_NSCS; }
-    snprintf(nm, sizeof(nm), "dec_sub%d", slot);
-    const size_t per = 8 * 5 + 4 * 2;
-    unsigned char *sb = (unsigned char *)c.get(nm, per * (nsub + 8) + 256); if (!sb) return SZ_NSCS;
-    unsigned long long *endA = (unsigned long long *)sb, *endB = endA + nsub + 1, *start_used = endB + nsub + 1, *sym_off = start_used + nsub + 1, *zero_off = sym_off + nsub + 1;
-    uint32_t *count = (uint32_t *)(zero_off + nsub + 1), *zcount = count + nsub + 1;
-    unsigned int *d_changed = (unsigned int *)c.get("dec_changed", 64); if (!d_changed) return SZ_NSCS;
-    dec_lut_kernel<<<((1u << DEC_K) + 255) / 256, 256, 0, c.stream>>>(L, R, C, leaf, lut); KCHECK();
-    DecTree tr{L, R, C, leaf, nodeCount, lut};
-    const unsigned grid = (unsigned)((nsub + 255) / 256);
-    unsigned long long *ep = endA, *ec = endB;
+    // Jacobi rounds: round 0 is the speculative decode; a job has converged when a whole round moved no start position
     for (int round = 0;; round++) {
-        CU(cudaMemsetAsync(d_changed, 0, 4, c.stream));
-        dec_sync_kernel<<<grid, 256, 0, c.stream>>>(words, total_bits, nsub, tr, ep, ec, start_used, count, zcount, round == 0 ? 1 : 0, d_changed); KCHECK();
-        std::swap(ep, ec);
-        if (round == 0) continue;
-        unsigned int ch = 0;
-        CU(cudaMemcpyAsync(&ch, d_changed, 4, cudaMemcpyDeviceToHost, c.stream));
+        bool any = false;
+        for (int j = 0; j < njobs; j++) {
+            DecJob &J = jobs[j];
+            if (J.converged) continue;
+            any = true;
+            DecTree tr{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
+            CU(cudaMemsetAsync(d_changed + j, 0, 4, c.stream));
+            dec_sync_kernel<<<(unsigned)((J.nsub + 255) / 256), 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.ep, J.ec, J.start_used, J.count, J.zcount, round == 0 ? 1 : 0, d_changed + j); KCHECK();
+            std::swap(J.ep, J.ec);
+        }
+        if (!any) break;
+        if (round == 0 || (round & 1)) continue;                 // read the flags every second round only
+        unsigned int ch[8];
+        CU(cudaMemcpyAsync(ch, d_changed, 4 * njobs, cudaMemcpyDeviceToHost, c.stream));
         CU(cudaStreamSynchronize(c.stream));
-        if (!ch) break;
-        if (round > (int)nsub + 2) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
+        for (int j = 0; j < njobs; j++) if (!jobs[j].converged && !ch[j]) jobs[j].converged = true;
+        if (round > 100000) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
     }
-    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(count, nsub, sym_off, nullptr); KCHECK();
-    scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(zcount, nsub, zero_off, nullptr); KCHECK();
-    dec_write_kernel<T, BLOCKMAJOR><<<grid, 256, 0, c.stream>>>(words, total_bits, nsub, tr, start_used, sym_off, zero_off, nsym, g, d_out, d_unpred, unpred_count, d_field); KCHECK();
+    for (int j = 0; j < njobs; j++) {
+        DecJob &J = jobs[j];
+        if (J.single_leaf) continue;
+        DecTree tr{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
+        if (launch_scan(c, c.stream, 0, J.count, J.nsub, J.sym_off, nullptr)) return SZ_NSCS;
+        if (launch_scan(c, c.stream, 0, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS;
+        const unsigned grid = (unsigned)((J.nsub + 255) / 256);
+        if (J.blockmajor) dec_write_kernel<T, true><<<grid, 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
+        else dec_write_kernel<T, false><<<grid, 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, (const T *)nullptr, 0, (T *)nullptr);
+        KCHECK();
+    }
     return 0;
 }
 
@@ -765,12 +806,18 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
 
     // ---- Huffman decode: main codes -> raster code array (+ unpredictable values pre-placed in the output) ----
     uint16_t *d_codes = (uint16_t *)c.get("codes", 2ull * N + 64); if (!d_codes) return SZ_NSCS;
-    if (huff_decode<T, true>(c, 0, d_body + o_tree, nodeCount, d_body + o_bits, main_bytes, N, g, d_codes, d_unp, total_unpred, d_out)) return SZ_NSCS;
     T *d_clast = (T *)c.get("coeff_last", sizeof(T) * 4ull * nb); if (!d_clast) return SZ_NSCS;
     uint16_t *d_ctype = (uint16_t *)c.get("coeff_type", 2ull * 4 * nb + 64); if (!d_ctype) return SZ_NSCS;
-    if (reg_count > 0) {
-        for (int e = 0; e < ncoef; e++)
-            if (huff_decode<T, false>(c, 1 + e, d_body + o_ctree[e], cnode[e], d_body + o_cbits[e], cbits_bytes[e], reg_count, g, d_ctype + (size_t)e * nb, (const T *)nullptr, 0, (T *)nullptr)) return SZ_NSCS;
+    {
+        DecJob jobs[5]; memset(jobs, 0, sizeof(jobs));
+        int nj = 0;
+        jobs[nj].slot = 0; jobs[nj].d_tree = d_body + o_tree; jobs[nj].nodeCount = nodeCount; jobs[nj].d_payload = d_body + o_bits; jobs[nj].payload_bytes = main_bytes;
+        jobs[nj].nsym = N; jobs[nj].blockmajor = true; jobs[nj].d_out = d_codes; nj++;
+        if (reg_count > 0) for (int e = 0; e < ncoef; e++) {
+            jobs[nj].slot = 1 + e; jobs[nj].d_tree = d_body + o_ctree[e]; jobs[nj].nodeCount = cnode[e]; jobs[nj].d_payload = d_body + o_cbits[e]; jobs[nj].payload_bytes = cbits_bytes[e];
+            jobs[nj].nsym = reg_count; jobs[nj].blockmajor = false; jobs[nj].d_out = d_ctype + (size_t)e * nb; nj++;
+        }
+        if (huff_decode_all<T>(c, jobs, nj, g, d_unp, total_unpred, d_out)) return SZ_NSCS;
     }
     if (mark(ST_DECODE)) return SZ_NSCS;
 
@@ -782,7 +829,7 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
         T *d_dummy = (T *)c.get("reg", sizeof(T) * 4ull * nb), *d_dummy2 = (T *)c.get("reg_c", sizeof(T) * 4ull * nb);
         if (!d_flags || !d_list || !d_rank || !d_cu || !d_dummy || !d_dummy2) return SZ_NSCS;
         reg_flag_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_flags); KCHECK();
-        scan_kernel<uint32_t><<<1, 1024, 0, c.stream>>>(d_flags, nb, d_rank, nullptr); KCHECK();
+        if (launch_scan(c, c.stream, 0, d_flags, nb, d_rank, nullptr)) return SZ_NSCS;
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, 0, d_dummy, d_dummy2, d_list); KCHECK();
         for (int e = 0; e < ncoef; e++) if (cunp_cnt[e]) CU(cudaMemcpyAsync(d_cu + (size_t)e * nb, d_body + o_cunp[e], sizeof(T) * cunp_cnt[e], cudaMemcpyDeviceToDevice, c.stream));
         coeff_chain_decode_kernel<T><<<1, 128, 0, c.stream>>>(d_ctype, nb, reg_count, ncoef, d_list, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3],

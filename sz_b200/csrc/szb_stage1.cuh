@@ -414,29 +414,67 @@ __global__ void __launch_bounds__(128) fit_select_kernel(const T *__restrict__ x
 }
 
 // =====================================================================================================================
-// single-CTA exclusive scan (u32 in -> u64 out); used for block compaction, unpredictable ranks and bit offsets.
+// exclusive scan (u32 in -> u64 out) over tiles of 8192 elements: tile sums, scan of the tile sums, per-tile scan.
+// Used for block compaction, unpredictable ranks and bit offsets.
 // =====================================================================================================================
-template <typename InT>
-__global__ void __launch_bounds__(1024) scan_kernel(const InT *__restrict__ in, uint64_t n, unsigned long long *__restrict__ out,
-                                                    unsigned long long *total) {
-    __shared__ unsigned long long s_part[1024];
-    int t = threadIdx.x;
-    uint64_t per = (n + 1023) / 1024;
-    uint64_t lo = (uint64_t)t * per, hi = lo + per; if (hi > n) hi = n; if (lo > n) lo = n;
-    unsigned long long local = 0;
-    for (uint64_t i = lo; i < hi; i++) local += in[i];
-    s_part[t] = local;
+constexpr int SCAN_TB = 1024, SCAN_PER = 8, SCAN_TILE = SCAN_TB * SCAN_PER;
+
+__device__ __forceinline__ unsigned long long block_exclusive_scan_1024(unsigned long long v, unsigned long long *s_warp /*[32]*/, unsigned long long &block_total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned long long inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+    if (lane == 31) s_warp[wid] = inc;
     __syncthreads();
-    // Hillis-Steele inclusive scan over 1024 partials
-    for (int o = 1; o < 1024; o <<= 1) {
-        unsigned long long v = (t >= o) ? s_part[t - o] : 0;
-        __syncthreads();
-        s_part[t] += v;
-        __syncthreads();
+    if (wid == 0) {
+        unsigned long long w = s_warp[lane], winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += u; }
+        s_warp[lane] = winc - w;                    // exclusive prefix of the warp totals
+        if (lane == 31) s_warp[32] = winc;          // block total
     }
-    unsigned long long run = s_part[t] - local;
-    for (uint64_t i = lo; i < hi; i++) { unsigned long long v = in[i]; out[i] = run; run += v; }
-    if (t == 1023 && total) *total = s_part[1023];
+    __syncthreads();
+    block_total = s_warp[32];
+    return s_warp[wid] + inc - v;
+}
+
+template <typename InT>
+__global__ void __launch_bounds__(SCAN_TB) scan_tile_sum_kernel(const InT *__restrict__ in, uint64_t n, unsigned long long *__restrict__ tile_sums) {
+    __shared__ unsigned long long s_warp[33];
+    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_PER;
+    unsigned long long v = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_PER; k++) if (base + k < n) v += in[base + k];
+    unsigned long long tot;
+    (void)block_exclusive_scan_1024(v, s_warp, tot);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(SCAN_TB) scan_tile_offsets_kernel(unsigned long long *tile_sums, uint32_t ntiles, unsigned long long *total) {
+    __shared__ unsigned long long s_warp[33];
+    const uint32_t per = (ntiles + SCAN_TB - 1) / SCAN_TB;
+    const uint32_t lo = min(ntiles, threadIdx.x * per), hi = min(ntiles, lo + per);
+    unsigned long long v = 0;
+    for (uint32_t i = lo; i < hi; i++) v += tile_sums[i];
+    unsigned long long tot;
+    unsigned long long run = block_exclusive_scan_1024(v, s_warp, tot);
+    for (uint32_t i = lo; i < hi; i++) { unsigned long long t = tile_sums[i]; tile_sums[i] = run; run += t; }
+    if (threadIdx.x == 0 && total) *total = tot;
+}
+
+template <typename InT>
+__global__ void __launch_bounds__(SCAN_TB) scan_apply_kernel(const InT *__restrict__ in, uint64_t n, const unsigned long long *__restrict__ tile_offsets,
+                                                              unsigned long long *__restrict__ out) {
+    __shared__ unsigned long long s_warp[33];
+    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_PER;
+    InT e[SCAN_PER];
+    unsigned long long v = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_PER; k++) { e[k] = (base + k < n) ? in[base + k] : (InT)0; v += e[k]; }
+    unsigned long long tot;
+    unsigned long long run = block_exclusive_scan_1024(v, s_warp, tot) + tile_offsets[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < SCAN_PER; k++) if (base + k < n) { out[base + k] = run; run += e[k]; }
 }
 
 // indicator -> (is regression) flags, and scatter of the compacted regression-block list + coefficients
