@@ -130,6 +130,8 @@ __device__ __forceinline__ unsigned long long heap_remove(unsigned long long *h,
     const uint32_t mf = hf(m);
     int i = 1;
     const int lim = cap >> 1;                                   // positions >= lim have no slots for children
+    // (fetching the grandchildren one level ahead was measured SLOWER: the loop is bound by instruction issue, not by the
+    //  shared-memory round trip)
     while (i < lim) {
         const ulonglong2 ch = *reinterpret_cast<const ulonglong2 *>(h + 2 * i);    // h[2i], h[2i+1]: 16-byte aligned
         const bool r = hf(ch.y) < hf(ch.x);
@@ -140,6 +142,28 @@ __device__ __forceinline__ unsigned long long heap_remove(unsigned long long *h,
     }
     h[i] = m;
     return top;
+}
+
+// leaf inserts + merge loop of one tree (one thread); returns the root node
+__device__ __forceinline__ uint32_t heap_build_tree(unsigned long long *h, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
+    int qend = 1;
+    uint32_t k = 0;
+    for (; k + 4 <= leaves; k += 4) {                    // leaf frequencies are fetched four at a time, off the sift chain
+        uint32_t f0 = lfreq[k], f1 = lfreq[k + 1], f2 = lfreq[k + 2], f3 = lfreq[k + 3];
+        heap_insert(h, qend, f0, k); heap_insert(h, qend, f1, k + 1); heap_insert(h, qend, f2, k + 2); heap_insert(h, qend, f3, k + 3);
+    }
+    for (; k < leaves; k++) heap_insert(h, qend, lfreq[k], k);
+    D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
+    uint32_t nn = leaves;
+    while (qend > 2) {
+        const unsigned long long b = heap_remove(h, qend, hcap);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+        const unsigned long long a = heap_remove(h, qend, hcap);    // second removed -> left
+        D.n_left[nn] = (uint32_t)a; D.n_right[nn] = (uint32_t)b;
+        heap_insert(h, qend, hf(a) + hf(b), nn);
+        nn++;
+    }
+    D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
+    return (uint32_t)h[1];
 }
 
 constexpr int HUFF_TB = 256;
@@ -175,30 +199,18 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     // ---- phase B (serial): exact emulation of the reference's heap ----
     const long long tk1 = clock64();
     {
+        // two inlined copies of the heap loop, so that the shared-memory one compiles to LDS/STS with 32-bit addresses instead
+        // of generic loads (a pointer that may be shared OR global forces the slower generic path)
         const bool in_smem = leaves + 8 <= smem_heap_capacity;
-        unsigned long long *h = in_smem ? s_heap : reinterpret_cast<unsigned long long *>(D.heap_g);
-        const int hcap = in_smem ? (int)smem_heap_capacity : (int)D.capacity;
-        for (int q = t; q < hcap; q += blockDim.x) h[q] = HEAP_INF;
-        __syncthreads();
-        if (t == 0) {                                            // one thread runs the heap (see the note at heap_insert)
-            int qend = 1;
-            uint32_t k = 0;
-            for (; k + 4 <= leaves; k += 4) {                    // leaf frequencies are fetched four at a time, off the sift chain
-                uint32_t f0 = lfreq[k], f1 = lfreq[k + 1], f2 = lfreq[k + 2], f3 = lfreq[k + 3];
-                heap_insert(h, qend, f0, k); heap_insert(h, qend, f1, k + 1); heap_insert(h, qend, f2, k + 2); heap_insert(h, qend, f3, k + 3);
-            }
-            for (; k < leaves; k++) heap_insert(h, qend, lfreq[k], k);
-            D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
-            uint32_t nn = leaves;
-            while (qend > 2) {
-                const unsigned long long b = heap_remove(h, qend, hcap);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
-                const unsigned long long a = heap_remove(h, qend, hcap);    // second removed -> left
-                D.n_left[nn] = (uint32_t)a; D.n_right[nn] = (uint32_t)b;
-                heap_insert(h, qend, hf(a) + hf(b), nn);
-                nn++;
-            }
-            s_root = (uint32_t)h[1];
-            D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
+        if (in_smem) {
+            for (int q = t; q < (int)smem_heap_capacity; q += blockDim.x) s_heap[q] = HEAP_INF;
+            __syncthreads();
+            if (t == 0) s_root = heap_build_tree(s_heap, (int)smem_heap_capacity, leaves, lfreq, D, tk1);
+        } else {
+            unsigned long long *hg = reinterpret_cast<unsigned long long *>(D.heap_g);
+            for (int q = t; q < (int)D.capacity; q += blockDim.x) hg[q] = HEAP_INF;
+            __syncthreads();
+            if (t == 0) s_root = heap_build_tree(hg, (int)D.capacity, leaves, lfreq, D, tk1);
         }
     }
     __syncthreads();
