@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
     const int radius = P.radius, cap = P.cap;
     const T caplf = (T)P.cap_l;
     const uint32_t nb2 = g.ax[2].nb, nblk = g.num_blocks;
+    const uint32_t ax2_split = g.ax[2].split, ax2_early = g.ax[2].early, ax2_late = g.ax[2].late;
     const unsigned char *__restrict__ indicator = P.indicator;
     const bool boundary_lane = (li == PI - 1) || (lj == PJ - 1) || P.write_all_recon;
 
@@ -138,8 +139,14 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
         const uint32_t bid0 = g.block_id(b0, b1, 0);     // block ids along axis 2 are consecutive
         const T iif = (T)ii, jjf = (T)jj;
         uint32_t bk = 0, kk = 0, rem = 0;               // rem = points left in the current block
-        bool lorenzo = true, next_lor = true;
-        if (active) next_lor = indicator[bid0] != 0;
+        bool lorenzo = true;
+        unsigned char next_ind = 1;                     // raw indicator byte of the next block (compared only when consumed, so the load is not waited for early)
+        T nc0 = (T)0, nc1 = (T)0, nc2 = (T)0, nc3 = (T)0;    // quantised coefficients of the next block (prefetched)
+        if (active) {
+            next_ind = indicator[bid0];
+            nc0 = coeff_last[bid0]; nc1 = coeff_last[nblk + bid0]; nc2 = coeff_last[2 * nblk + bid0];
+            if (DIM == 3) nc3 = coeff_last[3 * nblk + bid0];
+        }
         T c_base = (T)0, c_k = (T)0, c_d = (T)0;        // regression: pred = (c_base + c_k*kk) + c_d
         T ra = (T)0, rd = (T)0, re = (T)0, rg = (T)0;    // carried neighbours: a=(.,.,k-1) own, d=(li,lj-1,k-1), e=(li-1,lj,k-1), g=(li-1,lj-1,k-1)
         bool ok = true;
@@ -230,7 +237,9 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
                 if (lane == 0) {
                     if (flag_up) ok = ok && wf_wait(flag_up, (int)c + 1, P.err);
                     if (flag_left) ok = ok && wf_wait(flag_left, (int)c + 1, P.err);
-                    __threadfence();                          // acquire side of the flag hand-off
+                    // acquire side of the hand-off: ONE acquire load per flag after the relaxed polling (no full fence)
+                    if (flag_up) (void)ld_acquire(flag_up);
+                    if (flag_left) (void)ld_acquire(flag_left);
                 }
                 ok = __shfl_sync(0xffffffffu, (int)ok, 0) != 0;
                 if (!ok) break;
@@ -254,21 +263,21 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
             if (active && k < n2) {
                 const uint32_t slot = k & (W - 1), islot = k & (IW - 1);
                 if (rem == 0) {                               // enter the next block along the fast axis
-                    lorenzo = next_lor;
-                    const uint32_t bid = bid0 + bk;
-                    rem = g.ax[2].edge(bk);
+                    // mode and quantised coefficients of THIS block were requested one block ago (no stall on the loads here);
+                    // request the next block's now
+                    lorenzo = next_ind != 0;
+                    if (!lorenzo) {
+                        if (DIM == 3) { T m0 = nc0 * iif, m1 = nc1 * jjf; c_base = m0 + m1; c_k = nc2; c_d = nc3; }
+                        else { c_base = nc0 * jjf; c_k = nc1; c_d = nc2; }
+                    }
+                    rem = (bk < ax2_split) ? ax2_early : ax2_late;
                     kk = 0;
                     bk++;
-                    if (bk < nb2) next_lor = indicator[bid + 1] != 0;     // consumed one block later
-                    if (!lorenzo) {
-                        if (DIM == 3) {
-                            T l0 = coeff_last[bid], l1 = coeff_last[nblk + bid];
-                            T m0 = l0 * iif, m1 = l1 * jjf;
-                            c_base = m0 + m1; c_k = coeff_last[2 * nblk + bid]; c_d = coeff_last[3 * nblk + bid];
-                        } else {
-                            T l0 = coeff_last[bid];
-                            c_base = l0 * jjf; c_k = coeff_last[nblk + bid]; c_d = coeff_last[2 * nblk + bid];
-                        }
+                    if (bk < nb2) {
+                        const uint32_t bid = bid0 + bk;
+                        next_ind = indicator[bid];
+                        nc0 = coeff_last[bid]; nc1 = coeff_last[nblk + bid]; nc2 = coeff_last[2 * nblk + bid];
+                        if (DIM == 3) nc3 = coeff_last[3 * nblk + bid];
                     }
                 }
                 const T rb = row_b[slot], rc = (DIM == 3) ? row_c[slot] : (T)0, rf = (DIM == 3) ? row_f[slot] : (T)0;
@@ -334,7 +343,8 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
 #ifdef SZB_WF_PROFILE
                 long long q0 = clock64();
 #endif
-                __threadfence();
+                // release side: the warp barrier orders every lane's stores before lane 0's release store (cumulativity), so one
+                // release by one lane publishes the whole chunk -- no per-lane full fence
                 __syncwarp();
                 if (lane == 0) st_release(P.flags + pid, (int)((t - DMAX) / CH) + 1);
                 next_publish += CH;
@@ -348,7 +358,6 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
         if (lane == 0) { atomicAdd(P.prof + 3, (unsigned long long)(clock64() - pen0)); atomicAdd(P.prof + 4, (unsigned long long)tsteps); }
 #endif
         if (!ok) return;
-        __threadfence();
         __syncwarp();
         if (lane == 0) st_release(P.flags + pid, (int)nchunks);
         __syncwarp();
