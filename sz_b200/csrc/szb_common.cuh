@@ -2,6 +2,7 @@
 // Compiled with --fmad=false: every T operation below is a single IEEE-754 op, written one per statement in the
 // order of the reference, so results match the x86 (SSE2, no FMA) reference bit for bit.
 #pragma once
+#include <type_traits>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -73,10 +74,12 @@ template <typename T> struct TT;
 template <> struct TT<float> {
     typedef uint32_t bits_t;
     static __device__ __forceinline__ float abs(float v) { return fabsf(v); }
+    static __device__ __forceinline__ float trunc(float v) { return truncf(v); }
 };
 template <> struct TT<double> {
     typedef uint64_t bits_t;
     static __device__ __forceinline__ double abs(double v) { return fabs(v); }
+    static __device__ __forceinline__ double trunc(double v) { return ::trunc(v); }
 };
 
 // ---- linear-scaling quantiser (ref: sz_float.c:7160-7180, :7272-7290) ---------------------------------

@@ -52,6 +52,7 @@ struct Ctx {
     cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: side branch (coefficient histograms / trees / bit lengths)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::map<std::string, Buf> bufs;
+    uint32_t wf_epoch = 0;                               // tag of the most recent wavefront launch (see szb_wavefront.cuh)
     void *pinned = nullptr; size_t pinned_cap = 0;
     cudaEvent_t ev[ST_COUNT + 2];
     bool ev_ok = false;
@@ -341,17 +342,47 @@ static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, in
     P.pencils_a = (g.ax[0].n + PI - 1) / PI; P.pencils_b = (g.ax[1].n + PJ - 1) / PJ; P.num_pencils = P.pencils_a * P.pencils_b;
     std::vector<uint32_t> order; pencil_order(P.pencils_a, P.pencils_b, order);
     uint32_t *d_order = (uint32_t *)c.get("wf_order", 4ull * P.num_pencils); if (!d_order) return SZ_NSCS;
-    int *d_flags = (int *)c.get("wf_flags", 4ull * P.num_pencils + 64); if (!d_flags) return SZ_NSCS;
+    // tagged boundary words: zeroed when (re)allocated, afterwards every launch uses a fresh epoch as its tag
+    const size_t bnd_bytes = wf_bnd_bytes<T, DIM>(P.num_pencils, g.ax[2].n);
+    unsigned long long *d_bnd;
+    {
+        Buf &bb = c.bufs["wf_bnd"];
+        void *before = bb.p; const size_t cap_before = bb.cap;
+        d_bnd = (unsigned long long *)c.get("wf_bnd", bnd_bytes); if (!d_bnd) return SZ_NSCS;
+        bool fresh = (bb.p != before) || (bb.cap != cap_before);
+        if (++c.wf_epoch == 0) { c.wf_epoch = 1; fresh = true; }
+        if (fresh) CU(cudaMemsetAsync(d_bnd, 0, bb.cap, c.stream));
+    }
     unsigned int *d_misc = (unsigned int *)c.get("wf_misc", 64); if (!d_misc) return SZ_NSCS;
     // pageable source: the runtime stages it before returning, so `order` may die at scope exit
     CU(cudaMemcpyAsync(d_order, order.data(), 4ull * P.num_pencils, cudaMemcpyHostToDevice, c.stream));
-    CU(cudaMemsetAsync(d_flags, 0, 4ull * P.num_pencils, c.stream));
     CU(cudaMemsetAsync(d_misc, 0, 64, c.stream));
     P.prof = nullptr;
 #ifdef SZB_WF_PROFILE
-    { unsigned long long *pr = (unsigned long long *)c.get("wf_prof", 64); if (!pr) return SZ_NSCS; CU(cudaMemsetAsync(pr, 0, 64, c.stream)); P.prof = pr; }
+    { unsigned long long *pr = (unsigned long long *)c.get("wf_prof", 64 + 32ull * P.num_pencils + 2048); if (!pr) return SZ_NSCS; CU(cudaMemsetAsync(pr, 0, 64 + 32ull * P.num_pencils + 2048, c.stream)); P.prof = pr; }
 #endif
-    P.order = d_order; P.flags = d_flags; P.ticket = d_misc; P.err = (int *)(d_misc + 4); P.indicator = indicator; P.write_all_recon = write_all;
+    P.order = d_order; P.bnd = d_bnd; P.epoch = c.wf_epoch; P.ticket = d_misc; P.err = (int *)(d_misc + 4); P.write_all_recon = write_all;
+    // ---- pre-pass: neighbour-independent points -> merged input `xin` + one "given" bit per point ----
+    const uint32_t n2 = g.ax[2].n, rows = g.ax[0].n * g.ax[1].n, wpr = (n2 + 31) / 32;
+    std::vector<uint32_t> ktab(n2);
+    for (uint32_t k = 0; k < n2; k++) { uint32_t kk; const uint32_t bk = g.ax[2].block_of(k, kk); ktab[k] = (bk << 8) | kk; }
+    uint32_t *d_ktab = (uint32_t *)c.get("wf_ktab", 4ull * n2);
+    T *d_xin = (T *)c.get("wf_xin", sizeof(T) * g.N);
+    uint32_t *d_given = (uint32_t *)c.get("wf_given", 4ull * rows * wpr);
+    if (!d_ktab || !d_xin || !d_given) return SZ_NSCS;
+    CU(cudaMemcpyAsync(d_ktab, ktab.data(), 4ull * n2, cudaMemcpyHostToDevice, c.stream));
+    {
+        const int pgrid = (int)std::min<uint32_t>((rows + 7) / 8, (uint32_t)c.sm_count * 16u);
+        if (!decomp) {
+            if (use_mean) prepass_compress_kernel<T, DIM, true><<<pgrid, 256, 0, c.stream>>>(g, x, indicator, coeff_last, d_ktab, codes, d_xin, d_given, wpr, eb, recip, mean, cap, cap / 2);
+            else prepass_compress_kernel<T, DIM, false><<<pgrid, 256, 0, c.stream>>>(g, x, indicator, coeff_last, d_ktab, codes, d_xin, d_given, wpr, eb, recip, mean, cap, cap / 2);
+        } else {
+            if (use_mean) prepass_decompress_kernel<T, DIM, true><<<pgrid, 256, 0, c.stream>>>(g, codes, recon, indicator, coeff_last, d_ktab, d_xin, d_given, wpr, eb, mean, cap / 2);
+            else prepass_decompress_kernel<T, DIM, false><<<pgrid, 256, 0, c.stream>>>(g, codes, recon, indicator, coeff_last, d_ktab, d_xin, d_given, wpr, eb, mean, cap / 2);
+        }
+        KCHECK();
+    }
+    P.given = d_given; P.given_wpr = wpr;
     const size_t per_warp = wf_smem_per_warp<T>(DIM);
     int warps = sizeof(T) == 4 ? 4 : 2;
     while (warps > 1 && per_warp * warps > c.smem_optin) warps--;
@@ -361,18 +392,25 @@ static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, in
     int grid = (int)std::min<uint32_t>(need_ctas, (uint32_t)(c.sm_count * ctas_per_sm));
     auto run = [&](auto kern) -> int {
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<grid, warps * 32, smem, c.stream>>>(P, x, codes, recon, coeff_last, eb, recip, mean); KCHECK();
+        kern<<<grid, warps * 32, smem, c.stream>>>(P, (const T *)d_xin, codes, recon, eb, recip); KCHECK();
         return 0;
     };
     int rc;
-    if (decomp) rc = use_mean ? run(wavefront_kernel<T, DIM, true, true>) : run(wavefront_kernel<T, DIM, false, true>);
+    if (decomp) rc = run(wavefront_kernel<T, DIM, false, true>);
     else rc = use_mean ? run(wavefront_kernel<T, DIM, true, false>) : run(wavefront_kernel<T, DIM, false, false>);
     if (rc) return rc;
 #ifdef SZB_WF_PROFILE
     { unsigned long long h[8]; CU(cudaMemcpyAsync(h, P.prof, 64, cudaMemcpyDeviceToHost, c.stream)); CU(cudaStreamSynchronize(c.stream));
-      fprintf(stderr, "[wf-prof] pencils=%u warps/cta=%d grid=%d | per pencil: total=%.0f cyc, wait=%.0f, halo=%.0f, boundary-other=%.0f, publish=%.0f | steps/pencil=%.0f -> %.0f cyc/step excl. wait\n",
-              P.num_pencils, warps, grid, (double)h[3] / P.num_pencils, (double)h[0] / P.num_pencils, (double)h[1] / P.num_pencils, (double)h[5] / P.num_pencils, (double)h[2] / P.num_pencils,
-              (double)h[4] / P.num_pencils, ((double)h[3] - (double)h[0]) / (double)h[4]); }
+      fprintf(stderr, "[wf-prof] pencils=%u warps/cta=%d grid=%d | per pencil: total=%.0f cyc, neighbour wait + halo fetch=%.0f | steps/pencil=%.0f -> %.0f cyc/step outside the fetch\n",
+              P.num_pencils, warps, grid, (double)h[3] / P.num_pencils, (double)h[0] / P.num_pencils,
+              (double)h[4] / P.num_pencils, ((double)h[3] - (double)h[0]) / (double)h[4]);
+      if (const char *tl = getenv("SZB200_WF_TIMELINE")) {       // per-pencil timeline: ticket time, first-chunk start, end (ns), SM id
+          std::vector<unsigned long long> t(4ull * P.num_pencils);
+          CU(cudaMemcpy(t.data(), P.prof + 8, 32ull * P.num_pencils, cudaMemcpyDeviceToHost));
+          { unsigned long long tr[256]; CU(cudaMemcpy(tr, P.prof + 8 + 4ull * P.num_pencils, 2048, cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[wf-trace] chunk: enter(+cycles since previous exit) fetch-cycles spins stage-cycles\n");
+            for (int q = 0; q < 40 && tr[4*q+1]; q++) fprintf(stderr, "  c=%d +%lld fetch=%lld spins=%llu stage=%lld\n", q, q ? (long long)(tr[4*q] - tr[4*q-1]) : 0LL, (long long)(tr[4*q+1] - tr[4*q]), tr[4*q+2], (long long)(tr[4*q+3] - tr[4*q+1])); }
+          if (FILE *f = fopen(tl, "w")) { fprintf(f, "%u %u\n", P.pencils_a, P.pencils_b); for (uint32_t q = 0; q < P.num_pencils; q++) fprintf(f, "%llu %llu %llu %llu\n", t[4ull*q], t[4ull*q+1], t[4ull*q+2], t[4ull*q+3]); fclose(f); } } }
 #endif
     return 0;
 }
@@ -525,8 +563,9 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     uint32_t *d_cb = (uint32_t *)c.get("enc_cb", 4 * nch_all), *d_cz = (uint32_t *)c.get("enc_cz", 4 * nch_all);
     unsigned long long *d_cbo = (unsigned long long *)c.get("enc_cbo", 8 * nch_all), *d_czo = (unsigned long long *)c.get("enc_czo", 8 * nch_all);
     uint16_t *d_codes = (uint16_t *)c.get("codes", 2ull * N + 64);
-    T *d_recon = (T *)c.get("recon", sizeof(T) * N + 64);
-    if (!d_cb || !d_cz || !d_cbo || !d_czo || !d_codes || !d_recon) return SZ_NSCS;
+    const int write_all = getenv("SZB200_DEBUG_RECON") ? 1 : 0;      // debug: keep the full reconstructed field (szb200_debug_fetch(4))
+    T *d_recon = write_all ? (T *)c.get("recon", sizeof(T) * N + 64) : nullptr;
+    if (!d_cb || !d_cz || !d_cbo || !d_czo || !d_codes || (write_all && !d_recon)) return SZ_NSCS;
     {
         HuffTreeDesc hd[8];
         for (int i = 0; i < ntrees; i++) hd[i] = tw[i].d;
@@ -547,7 +586,6 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     }
 
     // ---- wavefront predict + quantise ----
-    const int write_all = getenv("SZB200_DEBUG_RECON") ? 1 : 0;
     {
         int rc = (job.dim == 3) ? launch_wavefront<T, 3>(c, g, false, use_mean, (int)intervals, d_ind, d_x, d_codes, d_recon, d_clast, eb, recip_eb, mean, write_all)
                                 : launch_wavefront<T, 2>(c, g, false, use_mean, (int)intervals, d_ind, d_x, d_codes, d_recon, d_clast, eb, recip_eb, mean, write_all);

@@ -6,15 +6,25 @@
 // Mapping (DESIGN.md "wavefront"): one warp owns a PENCIL of PI x PJ rows (3D: 8 x 4 rows of axis-2 lines; 2D: 1 x 32)
 // and sweeps it along the fast axis.  Lane (li,lj) handles point k = t - li - lj at step t, so every lane's seven
 // Lorenzo neighbours were produced at steps <= t-1 and are exchanged through a small shared-memory ring (plus four
-// carried registers).  Neighbouring pencils exchange their boundary rows through the global reconstruction array,
-// CH points at a time, guarded by per-pencil progress flags (release/acquire at gpu scope).  Pencils are handed out
-// by a global ticket counter in anti-diagonal order, so a waiting warp only ever waits for a ticket that has already
-// been taken: no deadlock regardless of how many CTAs are resident.  Every spin is bounded and raises an error flag
-// instead of hanging the GPU.
+// carried registers).
 //
-// The run time of this kernel is its dependency chain, (hops x (CH + DMAX + flag latency) + n2) steps, times the latency
-// of one step -- not bandwidth.  Hence: input rows arrive by LDGSTS two chunks ahead, block modes are fetched one block
-// ahead, everything loop-invariant lives in registers and the Lorenzo quantiser is branch-free.
+// Neighbouring pencils exchange their boundary rows (li = PI-1 or lj = PJ-1) through a global scratch of TAGGED 64-bit
+// words: {tag = launch epoch, 32 payload bits}, one word per fp32 value, two per fp64 value.  A 64-bit relaxed store / load
+// at gpu scope is single-copy atomic, so a consumer that sees the current epoch in a word also sees its payload: the data
+// carries its own "ready" bit.  There are no flags, no fences and no separate publish step -- the producer just stores, the
+// consumer loads the CH points of the next chunk from its up / left / up-left neighbours (one L2 round trip) and retries
+// until every tag matches.  Stale words of earlier launches carry older epochs and never match; the scratch is zeroed
+// when it is (re)allocated and epochs start at 1.
+// Pencils are handed out by a global ticket counter in anti-diagonal order, so a waiting warp only ever waits for a
+// ticket that has already been taken: no deadlock regardless of how many CTAs are resident.  Every spin is bounded
+// and raises an error flag instead of hanging the GPU.
+//
+// The run time of this kernel is its dependency chain, (hops x (CH + DMAX + hand-off latency) + n2) steps, times the
+// latency of one step -- not bandwidth.  Hence everything that does NOT depend on reconstructed neighbours is taken out
+// of the step: a fully parallel pre-pass (prepass_*_kernel below) resolves regression blocks, mean hits and (decompress)
+// unpredictable values and code de-quantisation into a merged input array `xin` plus one "given" bit per point.  The
+// wavefront step is then: one input (LDGSTS-staged two chunks ahead), three ring loads, the Lorenzo sum, the
+// branch-free quantiser (compress) or one add (decompress), one select on the given bit.
 #pragma once
 #include "szb_common.cuh"
 
@@ -40,13 +50,20 @@ struct WfParams {
     uint32_t pencils_a, pencils_b;   // pencil grid
     uint32_t num_pencils;
     const uint32_t *order;           // ticket -> pencil id (anti-diagonal order)
-    int *flags;                      // [num_pencils] chunks completed
+    unsigned long long *bnd;         // tagged boundary words [num_pencils][NR][n2][sizeof(T)/4]
+    uint32_t epoch;                  // tag of this launch (> 0)
     unsigned int *ticket;            // global ticket counter
     int *err;                        // error flag (1 = spin timeout)
-    const unsigned char *indicator;  // [num_blocks], 1 = Lorenzo
-    int write_all_recon;             // debug: store every reconstructed point (compress)
-    unsigned long long *prof;        // optional cycle counters (only with -DSZB_WF_PROFILE): [0] wait [1] halo [2] publish [3] pencil total [4] steps [5] boundary other
+    const uint32_t *given;           // [rows][given_wpr] bit k&31 of word k>>5: point resolved by the pre-pass
+    uint32_t given_wpr;              // words per row
+    int write_all_recon;             // debug: store every reconstructed point in the raster array (compress)
+    unsigned long long *prof;        // optional (only with -DSZB_WF_PROFILE): [0] wait+halo cycles [3] pencil total [4] steps; [8+4*pid..] timeline
 };
+
+// boundary rows a pencil exports: 3D bottom rows (li = PI-1; slot lj) + right rows (lj = PJ-1, li < PI-1; slot PJ+li); 2D the last row
+template <int DIM> struct WfBnd { static constexpr int NR = (DIM == 3) ? Pencil<DIM>::PI + Pencil<DIM>::PJ - 1 : 1; };
+template <typename T, int DIM>
+inline size_t wf_bnd_bytes(uint32_t num_pencils, uint32_t n2) { return (size_t)num_pencils * WfBnd<DIM>::NR * n2 * (sizeof(T) / 4) * 8; }
 
 template <typename T>
 __host__ __device__ constexpr size_t wf_smem_per_warp(int dim) {
@@ -71,52 +88,195 @@ __device__ __forceinline__ int ld_relaxed(const int *p) {
     asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+// 64-bit relaxed accesses at gpu scope (single-copy atomic; served by L2)
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// tagged boundary words of one value
+template <typename T> struct Tagged;
+template <> struct Tagged<float> {
+    static constexpr int WPE = 1;
+    static __device__ __forceinline__ void store(unsigned long long *p, float v, unsigned long long tag_hi) { st_relaxed_u64(p, tag_hi | (unsigned long long)__float_as_uint(v)); }
+    // words already loaded -> value; true when the tag matches
+    static __device__ __forceinline__ bool decode(const unsigned long long *w, uint32_t epoch, float &v) {
+        v = __uint_as_float((uint32_t)w[0]);
+        return (uint32_t)(w[0] >> 32) == epoch;
+    }
+};
+template <> struct Tagged<double> {
+    static constexpr int WPE = 2;
+    static __device__ __forceinline__ void store(unsigned long long *p, double v, unsigned long long tag_hi) {
+        const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+        st_relaxed_u64(p, tag_hi | (b & 0xffffffffull));
+        st_relaxed_u64(p + 1, tag_hi | (b >> 32));
+    }
+    static __device__ __forceinline__ bool decode(const unsigned long long *w, uint32_t epoch, double &v) {
+        v = __longlong_as_double((long long)((w[0] & 0xffffffffull) | (w[1] << 32)));
+        return (uint32_t)(w[0] >> 32) == epoch && (uint32_t)(w[1] >> 32) == epoch;
+    }
+};
 
-// wait until *flag >= need: polled by one lane with RELAXED loads (an acquire load would invalidate the SM's L1 on every
-// poll); the caller issues the acquire fence once after the wait.  false on timeout / error.
-__device__ __forceinline__ bool wf_wait(const int *flag, int need, int *err) {
-    unsigned int spins = 0;
-    while (ld_relaxed(flag) < need) {
-        __nanosleep(100);
-        if ((++spins & 0xff) == 0) {
-            if (ld_relaxed(err) != 0) return false;
-            if (spins > (1u << 23)) { atomicExch(err, 1); return false; }
+// ---- pre-pass: everything that is independent of reconstructed neighbours ------------------------------------------
+// One warp per row of the fast axis, 32 consecutive points per iteration (coalesced), one ballot per 32 points builds the
+// "given" word.  ktab[k] = (block index along axis 2) << 8 | (offset inside that block), built on the host.
+//
+// compress (ref: regression blocks sz_float.c:7098-7152 / 2D :6036-6078; mean hit :6929-6933):
+//   regression block : code = quantize(x, a*ii + b*jj + c*kk + d) -> codes[], xin = reconstructed value, given
+//   Lorenzo block    : mean hit (use_mean) -> code = radius, xin = mean, given;  else xin = x, not given
+template <typename T, int DIM, bool MEAN>
+__global__ void __launch_bounds__(256) prepass_compress_kernel(Geom g, const T *__restrict__ x, const unsigned char *__restrict__ indicator,
+                                                               const T *__restrict__ coeff_last, const uint32_t *__restrict__ ktab,
+                                                               uint16_t *__restrict__ codes, T *__restrict__ xin, uint32_t *__restrict__ given,
+                                                               uint32_t wpr, T eb, T recip_eb, T mean, int cap, int radius) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t n1 = g.ax[1].n, n2 = g.ax[2].n, nblk = g.num_blocks;
+    const uint32_t rows = g.ax[0].n * n1;
+    for (uint32_t row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += gridDim.x * (blockDim.x >> 5)) {
+        const uint32_t i = row / n1, j = row - i * n1;
+        uint32_t ii, jj;
+        const uint32_t b0 = g.ax[0].block_of(i, ii), b1 = g.ax[1].block_of(j, jj);
+        const uint32_t bid0 = g.block_id(b0, b1, 0);
+        const T iif = (T)ii, jjf = (T)jj;
+        const uint64_t base = (uint64_t)row * n2;
+        for (uint32_t k0 = 0; k0 < n2; k0 += 32) {
+            const uint32_t k = k0 + lane;
+            bool giv = false;
+            if (k < n2) {
+                const uint32_t kt = ktab[k];
+                const uint32_t bid = bid0 + (kt >> 8);
+                const T cur = x[base + k];
+                T v = cur;
+                if (indicator[bid] == 0) {
+                    T pred;
+                    if (DIM == 3) {
+                        T m0 = coeff_last[bid] * iif, m1 = coeff_last[nblk + bid] * jjf, m2 = coeff_last[2 * nblk + bid] * (T)(kt & 255u);
+                        pred = m0 + m1; pred = pred + m2; pred = pred + coeff_last[3 * nblk + bid];
+                    } else {
+                        T m1 = coeff_last[bid] * jjf, m2 = coeff_last[nblk + bid] * (T)(kt & 255u);
+                        pred = m1 + m2; pred = pred + coeff_last[2 * nblk + bid];
+                    }
+                    const int q = quantize<T>(cur, pred, recip_eb, eb, cap, radius, v);
+                    codes[base + k] = (uint16_t)q;
+                    giv = true;
+                } else if (MEAN) {
+                    const T dm = cur - mean;
+                    if (TT<T>::abs(dm) <= eb) { codes[base + k] = (uint16_t)radius; v = mean; giv = true; }
+                }
+                xin[base + k] = v;
+            }
+            const uint32_t w = __ballot_sync(0xffffffffu, giv);
+            if (lane == 0) given[(uint64_t)row * wpr + (k0 >> 5)] = w;
         }
     }
-    return true;
+}
+
+// decompress (ref: szd_float.c:3597-3748): out[] holds the unpredictable values at code-0 points (prefilled)
+//   regression block : code != 0 -> xin = pred + 2*(code-radius)*eb, given;  code == 0 -> xin = out (prefilled), given
+//   Lorenzo block    : code == 0 -> xin = out, given;  mean code -> xin = mean, given;
+//                      else xin = 2*(code'-radius)*eb (the term the wavefront adds to its prediction), not given
+template <typename T, int DIM, bool MEAN>
+__global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const uint16_t *__restrict__ codes, const T *__restrict__ out,
+                                                                 const unsigned char *__restrict__ indicator, const T *__restrict__ coeff_last,
+                                                                 const uint32_t *__restrict__ ktab, T *__restrict__ xin, uint32_t *__restrict__ given,
+                                                                 uint32_t wpr, T eb, T mean, int radius) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t n1 = g.ax[1].n, n2 = g.ax[2].n, nblk = g.num_blocks;
+    const uint32_t rows = g.ax[0].n * n1;
+    for (uint32_t row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += gridDim.x * (blockDim.x >> 5)) {
+        const uint32_t i = row / n1, j = row - i * n1;
+        uint32_t ii, jj;
+        const uint32_t b0 = g.ax[0].block_of(i, ii), b1 = g.ax[1].block_of(j, jj);
+        const uint32_t bid0 = g.block_id(b0, b1, 0);
+        const T iif = (T)ii, jjf = (T)jj;
+        const uint64_t base = (uint64_t)row * n2;
+        for (uint32_t k0 = 0; k0 < n2; k0 += 32) {
+            const uint32_t k = k0 + lane;
+            bool giv = false;
+            if (k < n2) {
+                const uint32_t kt = ktab[k];
+                const uint32_t bid = bid0 + (kt >> 8);
+                int tcode = (int)codes[base + k];
+                T v;
+                if (tcode == 0) { v = out[base + k]; giv = true; }
+                else if (indicator[bid] == 0) {
+                    T pred;
+                    if (DIM == 3) {
+                        T m0 = coeff_last[bid] * iif, m1 = coeff_last[nblk + bid] * jjf, m2 = coeff_last[2 * nblk + bid] * (T)(kt & 255u);
+                        pred = m0 + m1; pred = pred + m2; pred = pred + coeff_last[3 * nblk + bid];
+                    } else {
+                        T m1 = coeff_last[bid] * jjf, m2 = coeff_last[nblk + bid] * (T)(kt & 255u);
+                        pred = m1 + m2; pred = pred + coeff_last[2 * nblk + bid];
+                    }
+                    T dq = (T)(2 * (tcode - radius)); T w = dq * eb; v = pred + w;
+                    giv = true;
+                } else if (MEAN && tcode == radius) { v = mean; giv = true; }
+                else {
+                    if (MEAN && tcode < radius) tcode += 1;
+                    T dq = (T)(2 * (tcode - radius)); v = dq * eb;
+                }
+                xin[base + k] = v;
+            }
+            const uint32_t w = __ballot_sync(0xffffffffu, giv);
+            if (lane == 0) given[(uint64_t)row * wpr + (k0 >> 5)] = w;
+        }
+    }
+}
+
+// ---- the wavefront ----------------------------------------------------------------------------------------------
+// Both rings are indexed by TIME, not by position: element k of a row whose lane runs `d` steps behind lane 0 lives in slot
+// (k + d) mod ring length, i.e. in the slot of the step at which it is produced / consumed.  At step t every lane therefore
+// writes slot t, reads its neighbours at slots t-1 / t-2 and its input at slot t: all warp-uniform.  With the step loop unrolled
+// over one ring period (U = 2 chunks) every shared-memory offset and the chunk boundaries are compile-time constants and the
+// step body is straight-line code: 4 LDS, the 6-add Lorenzo chain, the quantiser, 1 STS, 1 warp barrier.
+template <typename T>
+__device__ __forceinline__ void cp_async_s32(unsigned int smem_dst, const T *gmem_src) {
+    if (sizeof(T) == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gmem_src) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_dst), "l"(gmem_src) : "memory");
 }
 
 template <typename T, int DIM, bool MEAN, bool DECOMP>
-__global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__restrict__ x /*compress: original field*/,
-                                                        uint16_t *codes /*raster; compress: out, decompress: in*/,
-                                                        T *recon /*raster; compress: boundary-row scratch, decompress: output (unpredictables prefilled)*/,
-                                                        const T *__restrict__ coeff_last /*[ncoef][num_blocks]*/, T eb, T recip_eb, T mean) {
+__global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__restrict__ xin /*merged input of the pre-pass*/,
+                                                        uint16_t *codes /*raster; compress: codes of the not-given points are written here*/,
+                                                        T *recon /*raster; decompress: output; compress: only with write_all_recon*/,
+                                                        T eb, T recip_eb) {
     constexpr int PI = Pencil<DIM>::PI, PJ = Pencil<DIM>::PJ;
     constexpr int CH = WfCfg<DIM>::CH, W = WfCfg<DIM>::W, S = WfCfg<DIM>::S, IW = WfCfg<DIM>::IW, IS = WfCfg<DIM>::IS;
+    constexpr int U = W;                               // steps per unrolled period (two chunks)
     constexpr int RJ = PJ + 1;                         // ring rows per li (incl. halo lj = -1)
     constexpr int DMAX = PI - 1 + PJ - 1;
-    static_assert(CH >= DMAX, "a chunk must cover the lane skew");
+    constexpr int NR = WfBnd<DIM>::NR, WPE = Tagged<T>::WPE;
+    static_assert(CH >= DMAX && DMAX >= 1 && DMAX < 32, "a chunk must cover the lane skew");
+    static_assert(U % 32 == 0, "given-bit windows are whole words");
+    constexpr int NW = U / 32;                         // given-bit words per period
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     T *ring = reinterpret_cast<T *>(smem_raw + (size_t)warp * wf_smem_per_warp<T>(DIM));
     T *inr = ring + (size_t)WfCfg<DIM>::ROWS * S;       // input ring [32][IS]
+    const unsigned int inr_s32 = (unsigned int)__cvta_generic_to_shared(inr);
     const Geom &g = P.g;
     const uint32_t n0 = g.ax[0].n, n1 = g.ax[1].n, n2 = g.ax[2].n;
+    const uint64_t SJ = n2, SI = (uint64_t)n1 * n2;    // element strides between rows
     const int li = (DIM == 3) ? lane / PJ : 0, lj = (DIM == 3) ? lane % PJ : lane;
     const int delay = li + lj;
+    // boundary slot this lane exports (-1: none)
+    const int bslot = (DIM == 3) ? (li == PI - 1 ? lj : (lj == PJ - 1 ? PJ + li : -1)) : (lj == PJ - 1 ? 0 : -1);
     T *my_row = ring + ((size_t)(li + 1) * RJ + (lj + 1)) * S;
     const T *row_b = ring + ((size_t)(li + 1) * RJ + lj) * S;        // (li, lj-1)
     const T *row_c = ring + ((size_t)li * RJ + (lj + 1)) * S;        // (li-1, lj)
     const T *row_f = ring + ((size_t)li * RJ + lj) * S;              // (li-1, lj-1)
     const T *my_in = inr + (size_t)lane * IS;
-    const uint32_t nchunks = (n2 + CH - 1) / CH;
-    // loop-invariant scalars in registers
-    const int radius = P.radius, cap = P.cap;
+    const int radius = P.radius;
     const T caplf = (T)P.cap_l;
-    const uint32_t nb2 = g.ax[2].nb, nblk = g.num_blocks;
-    const uint32_t ax2_split = g.ax[2].split, ax2_early = g.ax[2].early, ax2_late = g.ax[2].late;
-    const unsigned char *__restrict__ indicator = P.indicator;
-    const bool boundary_lane = (li == PI - 1) || (lj == PJ - 1) || P.write_all_recon;
+    const uint32_t wpr = P.given_wpr;
+    const uint32_t epoch = P.epoch;
+    const unsigned long long tag_hi = (unsigned long long)epoch << 32;
+    unsigned long long *const bnd = P.bnd;
+    const uint64_t prow = (uint64_t)n2 * WPE;          // words per boundary row
 
     for (;;) {
         unsigned int tk = 0;
@@ -126,240 +286,274 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
         const uint32_t pid = P.order[tk];
         const uint32_t pa = pid / P.pencils_b, pb = pid % P.pencils_b;
         const uint32_t i0 = pa * PI, j0 = pb * PJ;
-        const uint32_t i = i0 + li, j = j0 + lj;
-        const bool active = (i < n0) && (j < n1);
-        const uint64_t rowbase = ((uint64_t)i * n1 + j) * n2;
-        uint16_t *crow = codes + rowbase;
-        T *rrow = recon + rowbase;
+        const uint32_t vi = min((uint32_t)PI, n0 - i0), vj = min((uint32_t)PJ, n1 - j0);     // rows of the pencil inside the domain
+        const bool active = ((uint32_t)li < vi) && ((uint32_t)lj < vj);
+        const bool store_rec = active && (DECOMP || P.write_all_recon);
+        const bool exports = active && bslot >= 0;
+        const uint64_t pbase = ((uint64_t)i0 * n1 + j0) * n2;
+        const uint64_t rowid = (uint64_t)(i0 + li) * n1 + (j0 + lj);
+        const int64_t rowbase = (int64_t)(rowid * n2) - delay;      // + t = index of this lane's point at step t
+        const int64_t bbase = (int64_t)(((uint64_t)pid * NR + (uint32_t)max(bslot, 0)) * n2) - delay;
+        const uint32_t *grow = P.given + rowid * wpr;
         // zero the whole reconstruction ring (halo rows of domain-boundary pencils must read as +0.0)
         for (int q = lane; q < WfCfg<DIM>::ROWS * S; q += 32) ring[q] = (T)0;
-        // per-lane block bookkeeping along axes 0 and 1 (fixed for the whole pencil)
-        uint32_t ii = 0, jj = 0, b0 = 0, b1 = 0;
-        if (active) { b0 = g.ax[0].block_of(i, ii); b1 = g.ax[1].block_of(j, jj); }
-        const uint32_t bid0 = g.block_id(b0, b1, 0);     // block ids along axis 2 are consecutive
-        const T iif = (T)ii, jjf = (T)jj;
-        uint32_t bk = 0, kk = 0, rem = 0;               // rem = points left in the current block
-        bool lorenzo = true;
-        unsigned char next_ind = 1;                     // raw indicator byte of the next block (compared only when consumed, so the load is not waited for early)
-        T nc0 = (T)0, nc1 = (T)0, nc2 = (T)0, nc3 = (T)0;    // quantised coefficients of the next block (prefetched)
-        if (active) {
-            next_ind = indicator[bid0];
-            nc0 = coeff_last[bid0]; nc1 = coeff_last[nblk + bid0]; nc2 = coeff_last[2 * nblk + bid0];
-            if (DIM == 3) nc3 = coeff_last[3 * nblk + bid0];
-        }
-        T c_base = (T)0, c_k = (T)0, c_d = (T)0;        // regression: pred = (c_base + c_k*kk) + c_d
+        // "given" bits: gprev = word before the current period, gnext[] = words of the next period (requested one period ahead).
+        // Inactive lanes see all-ones, so that they never store a code.
+        uint32_t gprev = 0, gnext[NW];
+#pragma unroll
+        for (int h = 0; h < NW; h++) gnext[h] = active ? ((uint32_t)h < wpr ? grow[h] : 0u) : 0xffffffffu;
         T ra = (T)0, rd = (T)0, re = (T)0, rg = (T)0;    // carried neighbours: a=(.,.,k-1) own, d=(li,lj-1,k-1), e=(li-1,lj,k-1), g=(li-1,lj-1,k-1)
         bool ok = true;
         __syncwarp();
 
-        // decompress: the u16 codes of a chunk are loaded into registers one chunk before they are needed and widened into
-        // the input ring at the next chunk boundary, so the load latency is hidden behind a whole chunk of work
-        uint16_t cv[32];
-        auto load_codes = [&](uint32_t c) {
-            const uint32_t k0 = c * CH;
-            const uint32_t kcnt = k0 < n2 ? min((uint32_t)CH, n2 - k0) : 0u;
-#pragma unroll
-            for (int r = 0; r < 32; r++) {
-                const uint32_t ri = i0 + ((DIM == 3) ? r / PJ : 0), rj = j0 + ((DIM == 3) ? r % PJ : r);
-                cv[r] = ((uint32_t)lane < kcnt && ri < n0 && rj < n1) ? __ldg(codes + ((uint64_t)ri * n1 + rj) * n2 + k0 + lane) : (uint16_t)0;
-            }
-        };
-        auto store_codes = [&](uint32_t c) {
-            const uint32_t slot0 = (c & 3) * CH;
-            if (lane < CH) {
-#pragma unroll
-                for (int r = 0; r < 32; r++) inr[(size_t)r * IS + slot0 + lane] = (T)cv[r];      // codes < 65536: exact in T
-            }
-        };
-        // compress: cooperative LDGSTS staging of the input rows of chunk c (row r of the pencil <-> row r of the ring)
+        // cooperative LDGSTS staging of the input rows of chunk c: element k of pencil row r -> slot (k + delay_r) mod IW.
+        // Lane q copies point k0+q of every row (64 contiguous bytes per row and instruction).
         auto stage_input = [&](uint32_t c) {
             const uint32_t k0 = c * CH;
             if (k0 < n2) {
                 const uint32_t kcnt = min((uint32_t)CH, n2 - k0);
-                const uint32_t slot0 = (c & 3) * CH;
                 if ((uint32_t)lane < kcnt) {
-#pragma unroll 8
-                    for (int r = 0; r < 32; r++) {
-                        const uint32_t ri = i0 + ((DIM == 3) ? r / PJ : 0), rj = j0 + ((DIM == 3) ? r % PJ : r);
-                        if (ri < n0 && rj < n1) cp_async_elem<T>(inr + (size_t)r * IS + slot0 + lane, x + ((uint64_t)ri * n1 + rj) * n2 + k0 + lane);
+                    const uint32_t kk = k0 + lane;
+                    unsigned int so[DMAX + 1];
+#pragma unroll
+                    for (int dv = 0; dv <= DMAX; dv++) so[dv] = inr_s32 + (unsigned int)sizeof(T) * ((kk + dv) & (IW - 1));
+                    const T *gi = xin + pbase + kk;
+#pragma unroll
+                    for (int rli = 0; rli < PI; rli++) {
+                        const T *gj = gi;
+#pragma unroll
+                        for (int rlj = 0; rlj < PJ; rlj++) {
+                            if ((uint32_t)rli < vi && (uint32_t)rlj < vj)
+                                cp_async_s32<T>(so[rli + rlj] + (unsigned int)((rli * PJ + rlj) * IS * sizeof(T)), gj);
+                            gj += SJ;
+                        }
+                        gi += SI;
                     }
                 }
             }
             cp_async_commit();                      // one group per chunk, even when empty, keeps the wait count uniform
         };
-        // halo rows of chunk c from the neighbouring pencils' published reconstruction (L2 loads, never L1): all loads are
-        // issued before the first shared-memory store so that they overlap
-        auto stage_halo = [&](uint32_t c) {
+
+        // chunk boundary: fetch the CH boundary values of chunk c from the up / up-left / left pencils (tagged words, L2) and
+        // retry until every tag carries this launch's epoch; then put them into the halo rows of the ring and stage input
+        // chunk c+2.  Halo row (li,lj) with li = -1 or lj = -1 has the virtual delay li + lj: element k -> slot (k + li + lj) mod W.
+        const bool has_up = (DIM == 3) && pa > 0, has_left = pb > 0;
+        const unsigned long long *b_up = bnd + (uint64_t)(pid - (has_up ? P.pencils_b : 0u)) * NR * prow;
+        const unsigned long long *b_ul = bnd + ((uint64_t)(pid - (has_up && has_left ? P.pencils_b + 1u : 0u)) * NR + (PJ - 1)) * prow;
+        const unsigned long long *b_left = bnd + (uint64_t)(pid - (has_left ? 1u : 0u)) * NR * prow;
+        // tagged words of the halo of one chunk.  Every load is issued before any result is looked at: one L2 round trip for
+        // the whole halo.  Rows outside the domain read as {tag ok, +0.0}.
+        unsigned long long wu[(PJ + 1) * WPE], wl[PI * WPE];
+        bool pre_valid = false;                              // wu / wl hold a speculative fetch of the next chunk
+        auto load_halo = [&](uint32_t c) {
             const uint32_t k0 = c * CH;
-            const uint32_t kcnt = min((uint32_t)CH, n2 - k0);
-            const uint32_t slot0 = (c & 1) * CH;
-            if ((uint32_t)lane >= kcnt) return;
-            T hu[PJ + 1], hl[PI];
-            if (DIM == 3 && pa > 0) {
+            if (k0 + lane >= n2 || lane >= CH) return;
+            const uint64_t koff = (uint64_t)(k0 + lane) * WPE;
+            const unsigned long long fill = tag_hi;
+            if (has_up) {
 #pragma unroll
-                for (int q = -1; q < PJ; q++) {               // rows (i0-1, j0+q)
-                    const int64_t rj = (int64_t)j0 + q;
-                    hu[q + 1] = (rj >= 0 && rj < (int64_t)n1) ? __ldcg(recon + ((uint64_t)(i0 - 1) * n1 + (uint64_t)rj) * n2 + k0 + lane) : (T)0;
+                for (int w = 0; w < WPE; w++) wu[w] = has_left ? ld_relaxed_u64(b_ul + koff + w) : fill;                        // row (i0-1, j0-1)
+#pragma unroll
+                for (int q = 0; q < PJ; q++) {                                                                                    // rows (i0-1, j0+q)
+#pragma unroll
+                    for (int w = 0; w < WPE; w++) wu[(q + 1) * WPE + w] = ((uint32_t)q < vj) ? ld_relaxed_u64(b_up + (uint64_t)q * prow + koff + w) : fill;
                 }
             }
-            if (pb > 0) {
+            if (has_left) {
 #pragma unroll
-                for (int q = 0; q < PI; q++) {                // rows (i0+q, j0-1)
-                    const uint32_t ri = i0 + q;
-                    hl[q] = (ri < n0) ? __ldcg(recon + ((uint64_t)ri * n1 + (j0 - 1)) * n2 + k0 + lane) : (T)0;
+                for (int q = 0; q < PI; q++) {                                                                                    // rows (i0+q, j0-1)
+                    const int slot = (DIM == 3) ? (q == PI - 1 ? PJ - 1 : PJ + q) : 0;
+#pragma unroll
+                    for (int w = 0; w < WPE; w++) wl[q * WPE + w] = ((uint32_t)q < vi) ? ld_relaxed_u64(b_left + (uint64_t)slot * prow + koff + w) : fill;
                 }
-            }
-            if (DIM == 3 && pa > 0) {
-#pragma unroll
-                for (int q = -1; q < PJ; q++) ring[((size_t)0 * RJ + (q + 1)) * S + slot0 + lane] = hu[q + 1];
-            }
-            if (pb > 0) {
-#pragma unroll
-                for (int q = 0; q < PI; q++) ring[((size_t)(q + 1) * RJ + 0) * S + slot0 + lane] = hl[q];
             }
         };
-
-        const int *flag_up = (DIM == 3 && pa > 0) ? P.flags + (pid - P.pencils_b) : nullptr;
-        const int *flag_left = (pb > 0) ? P.flags + (pid - 1) : nullptr;
-        const uint32_t tsteps = n2 + DMAX;
+        // speculative fetch half a chunk ahead.  MEASURED SLOWER at 512^3 (the steps after the loads stretch from ~250 to ~800
+        // cycles; wavefront 3.2 -> 4.0 ms), so it is compiled out; kept because the trade-off may differ for other pencil shapes.
+        constexpr bool PREFETCH = false;
+        auto prefetch_halo = [&](uint32_t c) {
+            if (PREFETCH && (has_up || has_left) && c * CH < n2) { load_halo(c); pre_valid = true; }
+        };
+        auto boundary = [&](uint32_t c) {
 #ifdef SZB_WF_PROFILE
-        const long long pen0 = clock64();
+            long long p0 = clock64();
 #endif
-        if (!DECOMP) { stage_input(0); stage_input(1); }
-        else { load_codes(0); store_codes(0); load_codes(1); }
-        uint32_t next_boundary = 0, next_publish = CH - 1 + DMAX, cidx = 0;
-        for (uint32_t t = 0; t < tsteps; t++) {
-            if (t == next_boundary && t < n2) {
-                const uint32_t c = cidx;
-#ifdef SZB_WF_PROFILE
-                long long p0 = clock64();
-#endif
+            const uint32_t k0 = c * CH;
+            const uint32_t kcnt = min((uint32_t)CH, n2 - k0);
+            const bool mine = (uint32_t)lane < kcnt;
+            if (c == 0 && (has_up || has_left)) {
+                // a pencil may wait a long time for its first chunk: one lane polls one word per neighbour (the last point of the
+                // chunk in the neighbour's slowest exporting row) before the whole warp starts loading
                 if (lane == 0) {
-                    if (flag_up) ok = ok && wf_wait(flag_up, (int)c + 1, P.err);
-                    if (flag_left) ok = ok && wf_wait(flag_left, (int)c + 1, P.err);
-                    // acquire side of the hand-off: ONE acquire load per flag after the relaxed polling (no full fence)
-                    if (flag_up) (void)ld_acquire(flag_up);
-                    if (flag_left) (void)ld_acquire(flag_left);
+                    const uint64_t klast = (uint64_t)(kcnt - 1) * WPE;
+                    const unsigned long long *cu = has_up ? b_up + (uint64_t)(vj - 1) * prow + klast : nullptr;
+                    const unsigned long long *cl = nullptr;
+                    if (has_left) cl = b_left + (uint64_t)((DIM == 3) ? (vi == (uint32_t)PI ? PJ - 1 : PJ + vi - 1) : 0) * prow + klast;
+                    unsigned int spins = 0;
+                    for (;;) {
+                        const bool gu = !cu || (uint32_t)(ld_relaxed_u64(cu) >> 32) == epoch;
+                        const bool gl = !cl || (uint32_t)(ld_relaxed_u64(cl) >> 32) == epoch;
+                        if (gu && gl) break;
+                        __nanosleep(64);
+                        if ((++spins & 0xff) == 0) {
+                            if (ld_relaxed(P.err) != 0) { ok = false; break; }
+                            if (spins > (1u << 22)) { atomicExch(P.err, 1); ok = false; break; }
+                        }
+                    }
                 }
                 ok = __shfl_sync(0xffffffffu, (int)ok, 0) != 0;
-                if (!ok) break;
-#ifdef SZB_WF_PROFILE
-                long long p1 = clock64();
-#endif
-                stage_halo(c);
-#ifdef SZB_WF_PROFILE
-                __syncwarp();
-                long long p2 = clock64();
-#endif
-                if (!DECOMP) { stage_input(c + 2); cp_async_wait<2>(); }   // chunk c has landed (groups c+1, c+2 may still be in flight)
-                else { if (c > 0) store_codes(c); load_codes(c + 1); }
-                __syncwarp();
-#ifdef SZB_WF_PROFILE
-                if (lane == 0) { long long p3 = clock64(); atomicAdd(P.prof + 0, (unsigned long long)(p1 - p0)); atomicAdd(P.prof + 1, (unsigned long long)(p2 - p1)); atomicAdd(P.prof + 5, (unsigned long long)(p3 - p2)); }
-#endif
-                next_boundary += CH; cidx++;
             }
-            const uint32_t k = t - (uint32_t)delay;           // wraps to a huge value while t < delay
-            if (active && k < n2) {
-                const uint32_t slot = k & (W - 1), islot = k & (IW - 1);
-                if (rem == 0) {                               // enter the next block along the fast axis
-                    // mode and quantised coefficients of THIS block were requested one block ago (no stall on the loads here);
-                    // request the next block's now
-                    lorenzo = next_ind != 0;
-                    if (!lorenzo) {
-                        if (DIM == 3) { T m0 = nc0 * iif, m1 = nc1 * jjf; c_base = m0 + m1; c_k = nc2; c_d = nc3; }
-                        else { c_base = nc0 * jjf; c_k = nc1; c_d = nc2; }
+            T hu[PJ + 1], hl[PI];
+            unsigned int spins = 0;
+            bool use_pre = pre_valid;
+            pre_valid = false;
+            while (ok) {
+                bool good = true;
+                if (!use_pre) load_halo(c);
+                use_pre = false;
+                if (mine) {
+                    if (has_up) {
+#pragma unroll
+                        for (int q = 0; q <= PJ; q++) good &= Tagged<T>::decode(wu + q * WPE, epoch, hu[q]);
                     }
-                    rem = (bk < ax2_split) ? ax2_early : ax2_late;
-                    kk = 0;
-                    bk++;
-                    if (bk < nb2) {
-                        const uint32_t bid = bid0 + bk;
-                        next_ind = indicator[bid];
-                        nc0 = coeff_last[bid]; nc1 = coeff_last[nblk + bid]; nc2 = coeff_last[2 * nblk + bid];
-                        if (DIM == 3) nc3 = coeff_last[3 * nblk + bid];
+                    if (has_left) {
+#pragma unroll
+                        for (int q = 0; q < PI; q++) good &= Tagged<T>::decode(wl + q * WPE, epoch, hl[q]);
                     }
                 }
-                const T rb = row_b[slot], rc = (DIM == 3) ? row_c[slot] : (T)0, rf = (DIM == 3) ? row_f[slot] : (T)0;
-                const T in = my_in[islot];
-                T rec;
-                if (!DECOMP) {
-                    const T cur = in;
-                    int q;
-                    if (!lorenzo) {
-                        T pred = c_k * (T)kk; pred = c_base + pred; pred = pred + c_d;
-                        q = quantize<T>(cur, pred, recip_eb, eb, cap, radius, rec);
-                    } else {
-                        T pred;
-                        if (DIM == 3) {   // main-loop term order (ref: sz_float.c:7268-7269)
-                            pred = ra + rb; pred = pred + rc; pred = pred - rd; pred = pred - re; pred = pred - rf; pred = pred + rg;
-                        } else {          // ref: sz_float.c:6204
-                            pred = ra + rb; pred = pred - rd;
-                        }
-                        // branch-free form of the quantiser; out-of-range lanes compute garbage that is discarded
-                        const T diff = cur - pred;
-                        T itv = TT<T>::abs(diff) * recip_eb; itv = itv + (T)1;
-                        const bool inrange = itv < caplf;
-                        const T sitv = diff < (T)0 ? -itv : itv;
-                        int q0 = (int)(sitv / (T)2) + radius;
-                        const T dq = (T)(2 * (q0 - radius));
-                        T r0 = dq * eb; r0 = pred + r0;
-                        if (MEAN) { if (q0 <= radius) q0 -= 1; }      // ref: sz_float.c:6944 (the shift precedes the verification)
-                        const T chk = cur - r0;
-                        const bool good = inrange && !(TT<T>::abs(chk) > eb);
-                        q = good ? q0 : 0;
-                        rec = good ? r0 : cur;
-                        if (MEAN) { const T dm = cur - mean; if (TT<T>::abs(dm) <= eb) { q = radius; rec = mean; } }   // ref: :6929-6933
-                    }
-                    crow[k] = (uint16_t)q;
-                    if (boundary_lane) rrow[k] = rec;
-                } else {
-                    int tcode = (int)in;
-                    if (!lorenzo) {
-                        if (tcode != 0) {
-                            T pred = c_k * (T)kk; pred = c_base + pred; pred = pred + c_d;
-                            T dq = (T)(2 * (tcode - radius)); T w = dq * eb; rec = pred + w;
-                        } else rec = rrow[k];                             // unpredictable value, prefilled
-                    } else {
-                        if (MEAN && tcode == radius) rec = mean;
-                        else if (tcode == 0) rec = rrow[k];
-                        else {
-                            if (MEAN && tcode < radius) tcode += 1;
-                            T pred;
-                            if (DIM == 3) { pred = ra + rb; pred = pred + rc; pred = pred - rd; pred = pred - re; pred = pred - rf; pred = pred + rg; }
-                            else { pred = ra + rb; pred = pred - rd; }
-                            T dq = (T)(2 * (tcode - radius)); T w = dq * eb; rec = pred + w;
-                        }
-                    }
-                    rrow[k] = rec;
+                if (__all_sync(0xffffffffu, good)) break;
+                __nanosleep(40);
+                if ((++spins & 0xff) == 0) {
+                    if (ld_relaxed(P.err) != 0) ok = false;
+                    else if (spins > (1u << 22)) { atomicExch(P.err, 1); ok = false; }
+                    ok = __shfl_sync(0xffffffffu, (int)ok, 0) != 0;
                 }
-                my_row[slot] = rec;
-                ra = rec; rd = rb; re = rc; rg = rf;
-                kk++; rem--;
+            }
+#ifdef SZB_WF_PROFILE
+            if (lane == 0 && pid == P.num_pencils / 2 + P.pencils_b / 2 && c < 64) {        // per-chunk trace of one mid-field pencil
+                unsigned long long *tr = P.prof + 8 + 4 * (size_t)P.num_pencils + 4 * (size_t)c;
+                tr[0] = (unsigned long long)p0; tr[1] = (unsigned long long)clock64(); tr[2] = spins;
+            }
+            if (lane == 0) { atomicAdd(P.prof + 0, (unsigned long long)(clock64() - p0));
+                             if (c == 0) { unsigned long long gt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt)); P.prof[8 + 4 * (size_t)pid + 1] = gt; } }
+#endif
+            if (ok) {
+                if (mine) {
+                    if (has_up) {
+#pragma unroll
+                        for (int q = -1; q < PJ; q++) ring[((size_t)0 * RJ + (q + 1)) * S + ((k0 + lane + (q - 1)) & (W - 1))] = hu[q + 1];
+                    }
+                    if (has_left) {
+#pragma unroll
+                        for (int q = 0; q < PI; q++) ring[((size_t)(q + 1) * RJ + 0) * S + ((k0 + lane + (q - 1)) & (W - 1))] = hl[q];
+                    }
+                }
+                if (c > 0) stage_input(c + 2);              // (chunk 2 was requested before the wait for chunk 0)
+                cp_async_wait<2>();                         // input chunk c has landed (groups c+1, c+2 may still be in flight)
             }
             __syncwarp();
-            // publish chunk c once the slowest lane has finished it
-            if (t == next_publish) {
 #ifdef SZB_WF_PROFILE
-                long long q0 = clock64();
+            if (lane == 0 && pid == P.num_pencils / 2 + P.pencils_b / 2 && c < 64) P.prof[8 + 4 * (size_t)P.num_pencils + 4 * (size_t)c + 3] = (unsigned long long)clock64();
 #endif
-                // release side: the warp barrier orders every lane's stores before lane 0's release store (cumulativity), so one
-                // release by one lane publishes the whole chunk -- no per-lane full fence
-                __syncwarp();
-                if (lane == 0) st_release(P.flags + pid, (int)((t - DMAX) / CH) + 1);
-                next_publish += CH;
+        };
+
 #ifdef SZB_WF_PROFILE
-                if (lane == 0) atomicAdd(P.prof + 2, (unsigned long long)(clock64() - q0));
+        const long long pen0 = clock64();
+        if (lane == 0) { unsigned long long gt0; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt0)); unsigned int smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+                         P.prof[8 + 4 * (size_t)pid + 0] = gt0; P.prof[8 + 4 * (size_t)pid + 3] = smid; }
 #endif
+        stage_input(0); stage_input(1); stage_input(2);
+        const uint32_t tsteps = n2 + DMAX;
+        const uint32_t nper = (tsteps + U - 1) / U;
+
+        // one period of U steps.  CHK = false: every lane's point exists (DMAX <= t, t < n2 for all steps of the period)
+        auto period = [&](uint32_t m, auto chk_tag) {
+            constexpr bool CHK = decltype(chk_tag)::value;
+            const uint32_t t0 = m * U;
+            // given-bit windows of this period: bit s%32 of win[s/32] <-> this lane's point at step t0 + s
+            uint32_t win[NW];
+#pragma unroll
+            for (int h = 0; h < NW; h++) {
+                const uint32_t cur = gnext[h];
+                win[h] = __funnelshift_rc(gprev, cur, 32 - delay);
+                gprev = cur;
             }
+#pragma unroll
+            for (int h = 0; h < NW; h++) {
+                const uint32_t wi = (m + 1) * NW + h;
+                gnext[h] = active ? (wi < wpr ? grow[wi] : 0u) : 0xffffffffu;
+            }
+            const T *inp = my_in + (m & 1) * U;
+            uint16_t *cp = codes + (rowbase + (int64_t)t0);
+            T *rp = recon + (rowbase + (int64_t)t0);
+            unsigned long long *bp = bnd + (bbase + (int64_t)t0) * WPE;
+#pragma unroll
+            for (int s = 0; s < U; s++) {
+                if (s == 0 || s == CH) {
+                    const uint32_t c = 2 * m + (s == CH ? 1u : 0u);
+                    if (c * CH < n2 && ok) {
+                        if (has_up || has_left) boundary(c);
+                        else { if (c > 0) stage_input(c + 2); cp_async_wait<2>(); __syncwarp(); }
+                    }
+                }
+                if (s == CH / 2) prefetch_halo(2 * m + 1);
+                if (s == CH + CH / 2) prefetch_halo(2 * m + 2);
+                const bool giv = (win[s >> 5] >> (s & 31)) & 1u;
+                bool valid = true;
+                if (CHK) valid = active && (uint32_t)(t0 + s - (uint32_t)delay) < n2;
+                const T rb = row_b[(s + W - 1) & (W - 1)];
+                const T rc = (DIM == 3) ? row_c[(s + W - 1) & (W - 1)] : (T)0;
+                const T rf = (DIM == 3) ? row_f[(s + W - 2) & (W - 1)] : (T)0;
+                const T in = inp[s];
+                T pred;
+                if (DIM == 3) {   // main-loop term order (ref: sz_float.c:7268-7269)
+                    pred = ra + rb; pred = pred + rc; pred = pred - rd; pred = pred - re; pred = pred - rf; pred = pred + rg;
+                } else {          // ref: sz_float.c:6204
+                    pred = ra + rb; pred = pred - rd;
+                }
+                T rec;
+                if (!DECOMP) {
+                    // branch-free form of the quantiser; given / out-of-range lanes compute garbage that is discarded.
+                    // 2*trunc(v/2) in floating point equals (T)(2*(int)(v/2)) for every in-range v (up to the sign of a zero, which
+                    // no comparison or code can see) and keeps the two conversions off the dependency chain
+                    const T cur = in;
+                    const T diff = cur - pred;
+                    T itv = TT<T>::abs(diff) * recip_eb; itv = itv + (T)1;
+                    const bool inrange = itv < caplf;
+                    const T sitv = diff < (T)0 ? -itv : itv;
+                    const T half = TT<T>::trunc(sitv / (T)2);
+                    const T dq = half + half;
+                    T r0 = dq * eb; r0 = pred + r0;
+                    const T chk = cur - r0;
+                    const bool good = inrange && !(TT<T>::abs(chk) > eb);
+                    rec = (good && !giv) ? r0 : cur;
+                    int q0 = (int)half + radius;
+                    if (MEAN) { if (q0 <= radius) q0 -= 1; }      // ref: sz_float.c:6944 (the shift precedes the verification)
+                    if (!giv && valid) cp[s] = (uint16_t)(good ? q0 : 0);
+                } else {
+                    const T r0 = pred + in;                       // in = 2*(code-radius)*eb for the not-given points
+                    rec = giv ? in : r0;
+                }
+                if (CHK) { if (!valid) rec = (T)0; }
+                if (exports && valid) Tagged<T>::store(bp + s * WPE, rec, tag_hi);
+                if (store_rec && valid) rp[s] = rec;
+                my_row[s] = rec;
+                ra = rec;
+                if (CHK) { rd = valid ? rb : (T)0; re = valid ? rc : (T)0; rg = valid ? rf : (T)0; }
+                else { rd = rb; re = rc; rg = rf; }
+                __syncwarp();
+            }
+        };
+        for (uint32_t m = 0; m < nper && ok; m++) {
+            const bool full = (m > 0) && ((m + 1) * U <= n2);      // t - delay >= 0 and t < n2 for every step and lane
+            if (full) period(m, std::false_type{}); else period(m, std::true_type{});
         }
-        if (!DECOMP) cp_async_wait<0>();
+        cp_async_wait<0>();
 #ifdef SZB_WF_PROFILE
-        if (lane == 0) { atomicAdd(P.prof + 3, (unsigned long long)(clock64() - pen0)); atomicAdd(P.prof + 4, (unsigned long long)tsteps); }
+        if (lane == 0) { atomicAdd(P.prof + 3, (unsigned long long)(clock64() - pen0)); atomicAdd(P.prof + 4, (unsigned long long)tsteps);
+                         unsigned long long gt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt)); P.prof[8 + 4 * (size_t)pid + 2] = gt; }
 #endif
         if (!ok) return;
-        __syncwarp();
-        if (lane == 0) st_release(P.flags + pid, (int)nchunks);
         __syncwarp();
     }
 }
