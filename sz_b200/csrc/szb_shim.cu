@@ -39,9 +39,9 @@ static void set_err(const char *fmt, ...) {
 #define KCHECK()                                                                                              \
     do { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_err("%s:%d kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return SZ_NSCS; } c.launches++; } while (0)
 
-enum Stage { ST_OPT = 0, ST_MEAN, ST_FIT, ST_CHAIN, ST_WAVE, ST_HIST, ST_TREE, ST_ENC, ST_EMIT, ST_PARSE, ST_DECODE, ST_DCHAIN, ST_RECON, ST_COUNT };
+enum Stage { ST_OPT = 0, ST_MEAN, ST_FIT, ST_CHAIN, ST_WAVE, ST_HIST, ST_TREE, ST_ENC, ST_EMIT, ST_PARSE, ST_DECODE, ST_DCHAIN, ST_RECON, ST_JOIN, ST_COUNT };
 static const char *k_stage_names[16] = {"opt_intervals", "use_mean_mean", "fit_select", "coeff_chain", "wavefront_quant", "histogram", "huffman_tree",
-                                        "encode", "emit", "d_parse", "d_huffman_decode", "d_coeff_chain", "d_wavefront_recon", "", "", ""};
+                                        "encode", "emit", "d_parse", "d_huffman_decode", "d_coeff_chain", "d_wavefront_recon", "wait_coeff_trees_side_stream", "", ""};
 extern "C" const char *szb200_stage_name(int i) { return (i >= 0 && i < 16) ? k_stage_names[i] : ""; }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -54,7 +54,7 @@ struct Ctx {
     std::map<std::string, Buf> bufs;
     uint32_t wf_epoch = 0;                               // tag of the most recent wavefront launch (see szb_wavefront.cuh)
     void *pinned = nullptr; size_t pinned_cap = 0;
-    cudaEvent_t ev[ST_COUNT + 2];
+    cudaEvent_t ev[24];
     bool ev_ok = false;
     unsigned int launches = 0;
     int sm_count = 148;
@@ -445,7 +445,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     int evi = 0;
     CU(cudaEventRecord(c.ev[evi++], c.stream));
     float ms_stage[16]; memset(ms_stage, 0, sizeof(ms_stage));
-    int stage_of_ev[ST_COUNT + 2];
+    int stage_of_ev[24];
     auto mark = [&](int st) -> int { stage_of_ev[evi] = st; CU(cudaEventRecord(c.ev[evi++], c.stream)); return 0; };
 
     const T eb = (T)job.eb;                      // float path: the kernels see the narrowed value (ref: sz_float.c:6527 signature)
@@ -601,7 +601,8 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     enc_len_kernel<true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.clen, d_cb, d_cz); KCHECK();
     if (launch_scan(c, c.stream, 0, d_cb, nchunk_main, d_cbo, d_tot + 1)) return SZ_NSCS;
     if (launch_scan(c, c.stream, 0, d_cz, nchunk_main, d_czo, d_tot + 2)) return SZ_NSCS;
-    if (ntrees > 1) CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0));      // join the side branch
+    if (mark(ST_ENC)) return SZ_NSCS;
+    if (ntrees > 1) { CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0)); if (mark(ST_JOIN)) return SZ_NSCS; }      // join the side branch (coefficient trees)
     // read back sizes
     unsigned long long h_tot[8]; uint32_t h_tree[5][8]; ChainOut h_chain;
     CU(cudaMemcpyAsync(h_tot, d_tot, sizeof(h_tot), cudaMemcpyDeviceToHost, c.stream));
@@ -771,7 +772,7 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     const int ncoef = g.ncoef; const uint32_t nb = g.num_blocks; const uint64_t N = g.N;
     if (N >= (1ull << 32)) { set_err("arrays of 2^32 or more elements must be cut into slabs"); return SZ_DERR; }
     c.launches = 0;
-    int evi = 0; int stage_of_ev[ST_COUNT + 2];
+    int evi = 0; int stage_of_ev[24];
     CU(cudaEventRecord(c.ev[evi++], c.stream));
     auto mark = [&](int st) -> int { stage_of_ev[evi] = st; CU(cudaEventRecord(c.ev[evi++], c.stream)); return 0; };
     // ---- device copy of the body (aligned), host copy of its parseable head ----
