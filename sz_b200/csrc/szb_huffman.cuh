@@ -101,51 +101,103 @@ struct HuffTreeDesc {           // per-tree I/O, all pointers to global memory
     uint32_t capacity;          // node capacity
 };
 
-// heap entry = (freq << 32) | node : one 64-bit shared-memory word, children (2i, 2i+1) fetched with one 128-bit load.
-// Slots at or beyond qend always hold HEAP_INF, so "child does not exist" falls out of the ordinary comparisons and the
-// sift loops need no bound checks.  (A warp-cooperative variant -- speculative 5-level descent, ballot-based insert -- was
-// measured slower: every operation is a short dependent chain and the extra instructions cost more than the saved round trips.)
-__device__ __forceinline__ uint32_t hf(unsigned long long e) { return (uint32_t)(e >> 32); }
-constexpr unsigned long long HEAP_INF = ~0ULL;
+// The heap is two parallel arrays, frequencies f[] and node ids n[] (1-based, children of i at 2i and 2i+1).  Only the
+// frequencies decide the path of a sift; the node ids just follow it.  Slots at or beyond qend always hold HEAP_FINF, so
+// "child does not exist" falls out of the ordinary comparisons.
+//
+// One thread runs the whole thing (the final array layout of every operation must equal the reference's, ties included), so
+// the cost is the length of the dependent chain per heap level.  The sift-down therefore
+//   * reads the four GRANDCHILDREN f[4i..4i+3] with one 128-bit load one level ahead: when the smaller child is known, its
+//     children are already in registers, and the shared-memory round trip is off the chain;
+//   * moves the node ids one level late (load at level L, store at level L+1), so that no store waits for its load.
+// What remains per level is compare -> select -> compare -> branch.
+// (Measured slower, and dropped: a warp-cooperative variant with a speculative 5-level descent; a multi-warp pipelined heap;
+//  fully unrolled predicated sifts; grandchild prefetch on packed 64-bit entries, where the extra 64-bit selects ate the gain.)
+constexpr uint32_t HEAP_FINF = 0xffffffffu;
+struct HeapTop { uint32_t f, n; };
 
-__device__ __forceinline__ void heap_insert(unsigned long long *h, int &qend, uint32_t freq, uint32_t node) {
+// Accessors of the two arrays.  The shared-memory flavour addresses them through 32-bit shared-window addresses kept in
+// registers and explicit ld.shared / st.shared: with ordinary pointers the compiler re-derives the window base inside the
+// sift loop (a dozen uniform-datapath instructions per level).
+struct HeapSmem {
+    unsigned int fa, na;                 // shared addresses of f[0] and n[0]
+    __device__ __forceinline__ uint32_t ldf(int i) const { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(fa + 4u * (unsigned)i)); return v; }
+    __device__ __forceinline__ uint32_t ldn(int i) const { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(na + 4u * (unsigned)i)); return v; }
+    __device__ __forceinline__ void stf(int i, uint32_t v) const { asm volatile("st.shared.u32 [%0], %1;" ::"r"(fa + 4u * (unsigned)i), "r"(v) : "memory"); }
+    __device__ __forceinline__ void stn(int i, uint32_t v) const { asm volatile("st.shared.u32 [%0], %1;" ::"r"(na + 4u * (unsigned)i), "r"(v) : "memory"); }
+    __device__ __forceinline__ uint2 ldf2(int i) const { uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(fa + 4u * (unsigned)i)); return v; }
+    __device__ __forceinline__ uint4 ldf4(int i) const { uint4 v; asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(fa + 4u * (unsigned)i)); return v; }
+};
+struct HeapGmem {
+    uint32_t *f, *n;
+    __device__ __forceinline__ uint32_t ldf(int i) const { return f[i]; }
+    __device__ __forceinline__ uint32_t ldn(int i) const { return n[i]; }
+    __device__ __forceinline__ void stf(int i, uint32_t v) const { f[i] = v; }
+    __device__ __forceinline__ void stn(int i, uint32_t v) const { n[i] = v; }
+    __device__ __forceinline__ uint2 ldf2(int i) const { return *reinterpret_cast<const uint2 *>(f + i); }
+    __device__ __forceinline__ uint4 ldf4(int i) const { return *reinterpret_cast<const uint4 *>(f + i); }
+};
+
+template <typename H>
+__device__ __forceinline__ void heap_insert(const H &h, int &qend, uint32_t freq, uint32_t node) {
     // ref: Huffman.c:76-85 (bottom-up sift: parents with a STRICTLY larger frequency move down)
     int i = qend++, j;
+    int pend_i = 0; uint32_t pend_v = 0;                        // node id whose store is one level late (no store waits for its load)
     while ((j = i >> 1)) {
-        const unsigned long long pj = h[j];
-        if (hf(pj) <= freq) break;
-        h[i] = pj; i = j;
+        const uint32_t fj = h.ldf(j);
+        if (fj <= freq) break;
+        if (pend_i) h.stn(pend_i, pend_v);
+        pend_v = h.ldn(j); pend_i = i;
+        h.stf(i, fj); i = j;
     }
-    h[i] = ((unsigned long long)freq << 32) | node;
+    if (pend_i) h.stn(pend_i, pend_v);
+    h.stf(i, freq); h.stn(i, node);
 }
 
-__device__ __forceinline__ unsigned long long heap_remove(unsigned long long *h, int &qend, int cap) {
-    // ref: Huffman.c:87-114.  The moved element m is kept in a register ("hole" form of the reference's swaps: identical
+template <typename H>
+__device__ __forceinline__ HeapTop heap_remove(const H &h, int &qend, int cap) {
+    // ref: Huffman.c:87-114.  The moved element m is kept in registers ("hole" form of the reference's swaps: identical
     // final layout).  Right child only if STRICTLY smaller; descend only while m is STRICTLY larger than that child.
-    const unsigned long long top = h[1];
+    HeapTop top; top.f = h.ldf(1); top.n = h.ldn(1);
     qend--;
-    const unsigned long long m = h[qend];
-    h[qend] = HEAP_INF;
+    const uint32_t mf = h.ldf(qend), mn = h.ldn(qend);
+    h.stf(qend, HEAP_FINF);
     if (qend == 1) return top;
-    const uint32_t mf = hf(m);
+    const int lim = cap >> 1;                                   // positions >= lim have no child slots
+    const int qmax = cap - 4;                                   // last aligned quad
     int i = 1;
-    const int lim = cap >> 1;                                   // positions >= lim have no slots for children
-    // (fetching the grandchildren one level ahead was measured SLOWER: the loop is bound by instruction issue, not by the
-    //  shared-memory round trip)
-    while (i < lim) {
-        const ulonglong2 ch = *reinterpret_cast<const ulonglong2 *>(h + 2 * i);    // h[2i], h[2i+1]: 16-byte aligned
-        const bool r = hf(ch.y) < hf(ch.x);
-        const unsigned long long c = r ? ch.y : ch.x;
-        if (!(mf > hf(c))) break;
-        h[i] = c;
-        i = 2 * i + (r ? 1 : 0);
+    uint2 pr = h.ldf2(2);                                       // (f[2i], f[2i+1])
+    uint4 qa = h.ldf4(4), qb;                                   // f[4i .. 4i+3]; beyond the array a clamped (unused) quad is read
+    int pend_i = 0; uint32_t pend_v = 0;                        // node id whose store is one level late
+    // two levels per trip, the prefetched quad alternating between qa and qb: a single quad variable makes the compiler
+    // copy the freshly loaded registers at the loop edge, which waits for the load and puts its latency back on the chain
+#define SZB_SIFT_LEVEL(QCUR, QNEXT)                                                        \
+    {                                                                                      \
+        const bool r = pr.y < pr.x;                                                        \
+        const uint32_t fc = min(pr.x, pr.y);                                               \
+        if (!(mf > fc)) break;                                                             \
+        const int c = 2 * i + (r ? 1 : 0);                                                 \
+        if (pend_i) h.stn(pend_i, pend_v);                                                 \
+        pend_v = h.ldn(c); pend_i = i;                                                     \
+        h.stf(i, fc);                                                                      \
+        i = c;                                                                             \
+        pr = r ? make_uint2(QCUR.z, QCUR.w) : make_uint2(QCUR.x, QCUR.y);                  \
+        if (i >= lim) pr = make_uint2(HEAP_FINF, HEAP_FINF); /* no child slots: stop at the next compare (select, not branch) */ \
+        QNEXT = h.ldf4(min(4 * i, qmax)); /* 4i > qmax only when the next level has no slots: never used then */ \
     }
-    h[i] = m;
+    for (;;) {
+        SZB_SIFT_LEVEL(qa, qb)
+        SZB_SIFT_LEVEL(qb, qa)
+    }
+#undef SZB_SIFT_LEVEL
+    if (pend_i) h.stn(pend_i, pend_v);
+    h.stf(i, mf); h.stn(i, mn);
     return top;
 }
 
 // leaf inserts + merge loop of one tree (one thread); returns the root node
-__device__ __forceinline__ uint32_t heap_build_tree(unsigned long long *h, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
+template <typename H>
+__device__ __forceinline__ uint32_t heap_build_tree(const H &h, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
     int qend = 1;
     uint32_t k = 0;
     for (; k + 4 <= leaves; k += 4) {                    // leaf frequencies are fetched four at a time, off the sift chain
@@ -156,19 +208,19 @@ __device__ __forceinline__ uint32_t heap_build_tree(unsigned long long *h, int h
     D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
     uint32_t nn = leaves;
     while (qend > 2) {
-        const unsigned long long b = heap_remove(h, qend, hcap);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
-        const unsigned long long a = heap_remove(h, qend, hcap);    // second removed -> left
-        D.n_left[nn] = (uint32_t)a; D.n_right[nn] = (uint32_t)b;
-        heap_insert(h, qend, hf(a) + hf(b), nn);
+        const HeapTop b = heap_remove(h, qend, hcap);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+        const HeapTop a = heap_remove(h, qend, hcap);    // second removed -> left
+        D.n_left[nn] = a.n; D.n_right[nn] = b.n;
+        heap_insert(h, qend, a.f + b.f, nn);
         nn++;
     }
     D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
-    return (uint32_t)h[1];
+    return h.ldn(1);
 }
 
 constexpr int HUFF_TB = 256;
 __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
-    extern __shared__ __align__(16) unsigned long long s_heap[];
+    extern __shared__ __align__(16) uint32_t s_heap[];          // f[cap] then n[cap]
     const HuffTreeDesc D = descs[blockIdx.x];
     __shared__ uint32_t s_scan[HUFF_TB];
     __shared__ uint32_t s_root, s_leaves, s_cnt, s_err, s_lvl[72];
@@ -201,16 +253,25 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     {
         // two inlined copies of the heap loop, so that the shared-memory one compiles to LDS/STS with 32-bit addresses instead
         // of generic loads (a pointer that may be shared OR global forces the slower generic path)
-        const bool in_smem = leaves + 8 <= smem_heap_capacity;
+        const int scap = (int)(smem_heap_capacity & ~3u);      // entries per array (multiple of 4: 128-bit loads stay aligned)
+        const bool in_smem = leaves + 8 <= (uint32_t)scap;
         if (in_smem) {
-            for (int q = t; q < (int)smem_heap_capacity; q += blockDim.x) s_heap[q] = HEAP_INF;
+            for (int q = t; q < scap; q += blockDim.x) s_heap[q] = HEAP_FINF;
             __syncthreads();
-            if (t == 0) s_root = heap_build_tree(s_heap, (int)smem_heap_capacity, leaves, lfreq, D, tk1);
+            if (t == 0) {
+                // the addresses pass through an opaque asm so that the compiler keeps them in registers instead of
+                // re-deriving the shared window base (S2R + LEA) at every use inside the sift loops
+                HeapSmem h;
+                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * (unsigned)scap;
+                asm volatile("mov.u32 %0, %2;\n\tmov.u32 %1, %3;" : "=r"(h.fa), "=r"(h.na) : "r"(fa0), "r"(na0));
+                s_root = heap_build_tree(h, scap, leaves, lfreq, D, tk1);
+            }
         } else {
-            unsigned long long *hg = reinterpret_cast<unsigned long long *>(D.heap_g);
-            for (int q = t; q < (int)D.capacity; q += blockDim.x) hg[q] = HEAP_INF;
+            uint32_t *hg = reinterpret_cast<uint32_t *>(D.heap_g);       // capacity 64-bit words = two 32-bit arrays of that length
+            const int gcap = (int)(D.capacity & ~3u);
+            for (int q = t; q < gcap; q += blockDim.x) hg[q] = HEAP_FINF;
             __syncthreads();
-            if (t == 0) s_root = heap_build_tree(hg, (int)D.capacity, leaves, lfreq, D, tk1);
+            if (t == 0) { HeapGmem h; h.f = hg; h.n = hg + gcap; s_root = heap_build_tree(h, gcap, leaves, lfreq, D, tk1); }
         }
     }
     __syncthreads();
