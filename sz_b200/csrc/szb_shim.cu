@@ -544,7 +544,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
         ChainStep<T> *d_steps = (ChainStep<T> *)c.get("chain_steps", sizeof(ChainStep<T>) * (size_t)ncoef * reg_count + 256); if (!d_steps) return SZ_NSCS;
         chain_prep_kernel<T><<<dim3((reg_count + 255) / 256, ncoef), 256, 0, c.stream>>>(d_regc, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_steps); KCHECK();
-        coeff_chain_kernel<T><<<1, 128, 0, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
+        coeff_chain_kernel<T><<<1, CHAIN_THREADS, 0, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
     }
     if (mark(ST_CHAIN)) return SZ_NSCS;
 

@@ -527,10 +527,11 @@ __device__ __forceinline__ int chain_step_exact(T cur, T last, T prec, T rprec, 
 // parallel and with the EXACT float formula, the interval, the (<= 3) pieces, their breakpoints and their increments;
 // the serial kernel then only compares, selects and adds.  Anything outside the prepared interval / piece budget takes
 // the exact formula in the serial kernel, so the result is bit-identical by construction.
-template <typename T> struct ChainStep {
-    T lo, hi;            // interval of `last` covered by the table
+template <typename T> struct __align__(16) ChainStep {
+    T lo, hi;            // interval of `last` covered by the table; not tabulated: lo = +inf, hi = -inf (no `last` is inside)
     T thr1, thr2;        // piece 0: last <= thr1; piece 1: thr1 < last <= thr2; piece 2: last > thr2
-    T d0, d1, d2;        // increment fl(fl(2k) * prec) of each piece
+    T d0, d1, d2;        // increment fl(fl(2k) * prec) of each piece; +inf for a piece beyond the code capacity, which makes
+                         // the serial kernel's verification fail and the coefficient itself the new `last`, as the reference does
     T cur;               // the coefficient being quantised
     uint16_t c0, c1, c2; // code (k + 32768) of each piece; 0 = beyond the 65536-interval capacity (unpredictable)
     uint16_t np;         // number of pieces (0 = not tabulated: use the exact formula)
@@ -602,7 +603,7 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
         }
         if (okp) {
             auto code_of = [](int k) -> uint16_t { return (k == (1 << 20) || k == -(1 << 20)) ? (uint16_t)0 : (uint16_t)(k + 32768); };
-            auto delta_of = [&](int k) -> T { if (k == (1 << 20) || k == -(1 << 20)) return (T)0; T dq = (T)(2 * k); return dq * prec; };
+            auto delta_of = [&](int k) -> T { if (k == (1 << 20) || k == -(1 << 20)) return (T)INFINITY; T dq = (T)(2 * k); return dq * prec; };
             st.np = (uint16_t)np;
             st.c0 = code_of(pk[0]); st.d0 = delta_of(pk[0]);
             const T big = hi;                               // thresholds beyond hi are never exceeded inside the interval
@@ -612,6 +613,7 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
             if (np > 2) { st.c2 = code_of(pk[2]); st.d2 = delta_of(pk[2]); }
         }
     }
+    if (st.np == 0) { st.lo = (T)INFINITY; st.hi = -(T)INFINITY; }
     steps[(size_t)e * reg_count + r] = st;
 }
 
@@ -622,98 +624,126 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
 // applies it, one subtract + compare verifies it (the reference's "machine-epsilon" guard).  128 steps at a time are
 // staged through shared memory by the whole warp so that global traffic is coalesced and off the chain.
 // =====================================================================================================================
+constexpr int CHAIN_THREADS = 192;
 template <typename T>
-__global__ void __launch_bounds__(128) coeff_chain_kernel(const ChainStep<T> *__restrict__ steps, const uint32_t *__restrict__ reg_list, uint32_t nb,
+__global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainStep<T> *__restrict__ steps, const uint32_t *__restrict__ reg_list, uint32_t nb,
                                                           uint32_t reg_count, int ncoef, T p0, T p1, T p2, T p3, int use_div,
                                                           uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/,
                                                           T *__restrict__ coeff_unpred /*[ncoef][nb]*/, ChainOut *out) {
-    // Per chunk of CH steps:
-    //   (A) warp 0, lanes 0..ncoef-1: the serial part proper -- only the sequence of `last` values (compare, select, add,
-    //       verify); warps 1..3 meanwhile prefetch the next chunk of step tables into the other buffer;
-    //   (B) all four warps (warp e <-> coefficient e): codes and the ordered unpredictable list are recomputed from the
-    //       stored `last` sequence in parallel, and everything is written back coalesced.
-    constexpr int CH = sizeof(T) == 4 ? 128 : 64;
+    // A three-stage software pipeline over chunks of CH steps, one __syncthreads per chunk:
+    //   warp 0, lanes 0..ncoef-1 : (A) the serial part proper of chunk c -- only the sequence of `last` values.  All three
+    //                              pieces of the step table are evaluated speculatively (three independent add / verify
+    //                              chains) and selected at the end, so the dependent chain is add -> subtract -> compare -> select;
+    //   warps 1, 2, 3, 5 (one per coefficient; warp 4 would share warp 0's scheduler and only idles) : (B) codes and the ordered unpredictable list of chunk c-1, recomputed from the
+    //                              stored `last` sequence in parallel and written back coalesced; and the prefetch of the step
+    //                              tables of chunk c+1.
+    // The serial warp therefore never waits for anything but its own arithmetic.
+    constexpr int CH = sizeof(T) == 4 ? 64 : 32;
     constexpr int WORDS = sizeof(ChainStep<T>) / 4;
-    __shared__ __align__(16) ChainStep<T> s_step[2][4][CH + 1];
-    __shared__ T s_last[4][CH + 1];                        // s_last[e][i] = value of last ENTERING step i (slot CH: leaving the chunk)
-    __shared__ uint32_t s_blk[2][CH];
+    __shared__ __align__(16) ChainStep<T> s_step[3][4][CH + 1];
+    __shared__ T s_last[2][4][CH + 1];                     // s_last[.][e][i] = value of last ENTERING step i (slot cnt: leaving the chunk)
+    __shared__ uint32_t s_blk[3][CH];
     __shared__ unsigned int s_ucnt[4];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid < 4) s_ucnt[tid] = 0;
-    auto load_chunk = [&](uint32_t r0, int buf, int t0, int nt) {
+    // all loads of a chunk are issued before the first store (one L2 round trip per chunk, not one per coefficient)
+    auto load_chunk = [&](uint32_t chunk, int t0, int nt) {
+        const uint32_t r0 = chunk * CH;
         if (r0 >= reg_count) return;
+        const int buf = (int)(chunk % 3u);
         const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        for (int e = 0; e < ncoef; e++) {
+        const int per = cnt * WORDS;
+        constexpr int MAXQ = (CH * WORDS + 127) / 128;
+        uint32_t v[4][MAXQ];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
             const uint32_t *src = reinterpret_cast<const uint32_t *>(steps + (size_t)e * reg_count + r0);
-            uint32_t *dst = reinterpret_cast<uint32_t *>(&s_step[buf][e][0]);
-#pragma unroll 8
-            for (int i = t0; i < cnt * WORDS; i += nt) dst[i] = __ldg(src + i);
+#pragma unroll
+            for (int q = 0; q < MAXQ; q++) {
+                const int w = t0 + q * nt;
+                if (e < ncoef && w < per) v[e][q] = __ldg(src + w);
+            }
         }
-        for (int i = t0; i < cnt; i += nt) s_blk[buf][i] = reg_list[r0 + i];
+        const uint32_t blk = (t0 < cnt) ? reg_list[r0 + t0] : 0u;
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            uint32_t *dst = reinterpret_cast<uint32_t *>(&s_step[buf][e][0]);
+#pragma unroll
+            for (int q = 0; q < MAXQ; q++) {
+                const int w = t0 + q * nt;
+                if (e < ncoef && w < per) dst[w] = v[e][q];
+            }
+        }
+        if (t0 < cnt) s_blk[buf][t0] = blk;
     };
-    load_chunk(0, 0, tid, 128);
     T last = (T)0;                                          // carried by warp 0, lane e
     const T precA = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : p3;
     const T rprecA = (T)1 / precA;
-    const T precB = warp == 0 ? p0 : warp == 1 ? p1 : warp == 2 ? p2 : p3;
+    const int eB = warp == 5 ? 3 : ((warp == 4 || warp == 0) ? 99 : warp - 1);     // helper warps 1,2,3,5 <-> coefficient 0..3; warps 0 and 4: none
+    const int tB = eB * 32 + lane;                                   // thread index among the 128 helper threads
+    if (eB < 4 && eB >= 0) load_chunk(0, tB, 128);
+    const T precB = eB == 0 ? p0 : eB == 1 ? p1 : eB == 2 ? p2 : p3;
     const T rprecB = (T)1 / precB;
+    const uint32_t nchunks = (reg_count + CH - 1) / CH;
     __syncthreads();
-    int buf = 0;
-    for (uint32_t r0 = 0; r0 < reg_count; r0 += CH, buf ^= 1) {
-        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        // ---- (A) ----
-        if (warp > 0) load_chunk(r0 + CH, buf ^ 1, tid - 32, 96);
-        else if (lane < ncoef) {
-            const int e = lane;
-            ChainStep<T> nxt = s_step[buf][e][0];
-            for (int i = 0; i < cnt; i++) {
-                const ChainStep<T> st = nxt;
-                nxt = s_step[buf][e][i + 1];               // fetched while this step computes (slot CH is padding)
-                s_last[e][i] = last;
-                T nl;
-                if (st.np != 0 && last >= st.lo && last <= st.hi) {
+    for (uint32_t it = 0; it <= nchunks; it++) {
+        if (warp == 0) {
+            // ---- (A) chunk `it` ----
+            if (it < nchunks && lane < ncoef) {
+                const int e = lane, buf = (int)(it % 3u), lb = (int)(it & 1u);
+                const int cnt = (int)min((uint32_t)CH, reg_count - it * CH);
+                ChainStep<T> nxt = s_step[buf][e][0];
+                for (int i = 0; i < cnt; i++) {
+                    const ChainStep<T> st = nxt;
+                    nxt = s_step[buf][e][i + 1];           // fetched while this step computes (slot CH is padding)
+                    s_last[lb][e][i] = last;
+                    const bool in = last >= st.lo && last <= st.hi;
                     const bool g1 = last > st.thr1, g2 = last > st.thr2;
-                    const T d = g2 ? st.d2 : (g1 ? st.d1 : st.d0);
-                    const bool cap = (g2 ? st.c2 : (g1 ? st.c1 : st.c0)) == 0;
-                    const T v = last + d;
-                    const T chk = st.cur - v;
-                    nl = (cap || TT<T>::abs(chk) > precA) ? st.cur : v;
-                } else {
-                    (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
+                    const T v0 = last + st.d0, v1 = last + st.d1, v2 = last + st.d2;
+                    const T k0 = st.cur - v0, k1 = st.cur - v1, k2 = st.cur - v2;
+                    const T n0 = TT<T>::abs(k0) > precA ? st.cur : v0;
+                    const T n1 = TT<T>::abs(k1) > precA ? st.cur : v1;
+                    const T n2 = TT<T>::abs(k2) > precA ? st.cur : v2;
+                    T nl = g1 ? n1 : n0;
+                    nl = g2 ? n2 : nl;
+                    if (!in) (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
+                    last = nl;
                 }
-                last = nl;
+                s_last[lb][e][cnt] = last;
             }
-            s_last[e][cnt] = last;
-        }
-        __syncthreads();
-        // ---- (B) ----
-        if (warp < ncoef) {
-            const int e = warp;
-            for (int i0 = 0; i0 < cnt; i0 += 32) {
-                const int i = i0 + lane;
-                int ct = 1; T cur = (T)0;
-                if (i < cnt) {
-                    const ChainStep<T> st = s_step[buf][e][i];
-                    const T lin = s_last[e][i];
-                    cur = st.cur;
-                    T nl;
-                    if (st.np != 0 && lin >= st.lo && lin <= st.hi) {
-                        const bool g1 = lin > st.thr1, g2 = lin > st.thr2;
-                        const T d = g2 ? st.d2 : (g1 ? st.d1 : st.d0);
-                        const int c = g2 ? st.c2 : (g1 ? st.c1 : st.c0);
-                        const T v = lin + d;
-                        const T chk = st.cur - v;
-                        ct = ((c == 0) || (TT<T>::abs(chk) > precB)) ? 0 : c;
-                    } else ct = chain_step_exact<T>(st.cur, lin, precB, rprecB, use_div, nl);
-                    coeff_type[(size_t)e * nb + r0 + i] = (uint16_t)ct;
-                    coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_last[e][i + 1];
+        } else {
+            // ---- prefetch chunk it+1, then (B) chunk it-1 ----
+            if (it + 1 < nchunks && eB < 4) load_chunk(it + 1, tB, 128);
+            if (it >= 1 && eB < ncoef) {
+                const uint32_t cb = it - 1, r0 = cb * CH;
+                const int e = eB, buf = (int)(cb % 3u), lb = (int)(cb & 1u);
+                const int cnt = (int)min((uint32_t)CH, reg_count - r0);
+                for (int i0 = 0; i0 < cnt; i0 += 32) {
+                    const int i = i0 + lane;
+                    int ct = 1; T cur = (T)0;
+                    if (i < cnt) {
+                        const ChainStep<T> st = s_step[buf][e][i];
+                        const T lin = s_last[lb][e][i];
+                        cur = st.cur;
+                        T nl;
+                        if (st.np != 0 && lin >= st.lo && lin <= st.hi) {
+                            const bool g1 = lin > st.thr1, g2 = lin > st.thr2;
+                            const T d = g2 ? st.d2 : (g1 ? st.d1 : st.d0);
+                            const int c = g2 ? st.c2 : (g1 ? st.c1 : st.c0);
+                            const T v = lin + d;
+                            const T chk = st.cur - v;
+                            ct = ((c == 0) || (TT<T>::abs(chk) > precB)) ? 0 : c;
+                        } else ct = chain_step_exact<T>(st.cur, lin, precB, rprecB, use_div, nl);
+                        coeff_type[(size_t)e * nb + r0 + i] = (uint16_t)ct;
+                        coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_last[lb][e][i + 1];
+                    }
+                    const unsigned int zmask = __ballot_sync(0xffffffffu, i < cnt && ct == 0);
+                    const unsigned int base = s_ucnt[e];
+                    if (i < cnt && ct == 0) coeff_unpred[(size_t)e * nb + base + __popc(zmask & ((1u << lane) - 1u))] = cur;
+                    __syncwarp();
+                    if (lane == 0) s_ucnt[e] = base + __popc(zmask);
+                    __syncwarp();
                 }
-                const unsigned int zmask = __ballot_sync(0xffffffffu, i < cnt && ct == 0);
-                const unsigned int base = s_ucnt[e];
-                if (i < cnt && ct == 0) coeff_unpred[(size_t)e * nb + base + __popc(zmask & ((1u << lane) - 1u))] = cur;
-                __syncwarp();
-                if (lane == 0) s_ucnt[e] = base + __popc(zmask);
-                __syncwarp();
             }
         }
         __syncthreads();
