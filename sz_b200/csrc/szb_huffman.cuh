@@ -588,72 +588,125 @@ __global__ void fill_u16_kernel(uint16_t *out, uint64_t n, uint16_t v) {
 }
 
 // coefficient chain decode (S1, decoder side; ref: szd_float.c:5809-5819): last = last + 2(t-R)*prec, or the next stored raw
-// value when t == 0.  Only the running float addition is serial.  Per chunk: warps 1..3 prepare the NEXT chunk (increments
-// fl(fl(2(t-R)) * prec), reset flags, the raw values picked by a ballot-ranked cursor) while lanes 0..ncoef-1 of warp 0
-// run the add chain of the CURRENT chunk out of shared memory; then everybody scatters the results to the block ids.
+// value when t == 0.  Only the running float addition is serial; everything else is prepared by a parallel kernel first.
+// step 1 (parallel, one CTA per coefficient): every regression block's increment 2*(code-radius)*precision, or -- for an
+// unpredictable coefficient (code 0) -- its raw value, found by the ordered rank of the zero among the zeros before it
 template <typename T>
-__global__ void __launch_bounds__(128) coeff_chain_decode_kernel(const uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, uint32_t nb, uint32_t reg_count, int ncoef,
-                                                                 const uint32_t *__restrict__ reg_list, T p0, T p1, T p2, T p3, int r0_, int r1_, int r2_, int r3_,
-                                                                 const T *__restrict__ cu0, const T *__restrict__ cu1, const T *__restrict__ cu2, const T *__restrict__ cu3,
-                                                                 T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
-    constexpr int CH = 96;                                   // one element per preparing thread (warps 1..3)
-    __shared__ T s_val[2][4][CH];                            // increment, or the raw value when s_rst is set
-    __shared__ unsigned char s_rst[2][4][CH];
-    __shared__ T s_out[4][CH];
-    __shared__ uint32_t s_blk[2][CH];
-    __shared__ unsigned int s_cur[4];                        // cursor into each coefficient's raw-value list
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (tid < 4) s_cur[tid] = 0;
+__global__ void __launch_bounds__(1024) coeff_dec_prep_kernel(const uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, uint32_t nb, uint32_t reg_count,
+                                                              T p0, T p1, T p2, T p3, int r0_, int r1_, int r2_, int r3_,
+                                                              const T *__restrict__ cu /*[ncoef][nb] raw values in order*/,
+                                                              T *__restrict__ val /*[ncoef][reg_count]*/, unsigned char *__restrict__ rst /*[ncoef][reg_count]*/) {
+    const int e = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
+    const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
+    const T *cue = cu + (size_t)e * nb;
+    __shared__ unsigned int s_w[32];
+    __shared__ unsigned int s_run;
+    if (tid == 0) s_run = 0;
     __syncthreads();
-    auto prepare = [&](uint32_t r0, int buf) {               // executed by warps 1..3 (96 threads, whole warps)
-        if (r0 >= reg_count) return;
-        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        const int i = tid - 32;                              // 0..95
-        if (i < cnt) s_blk[buf][i] = reg_list[r0 + i];
-        for (int e = 0; e < ncoef; e++) {
-            const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
-            const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
-            const T *cu = e == 0 ? cu0 : e == 1 ? cu1 : e == 2 ? cu2 : cu3;
-            const int tcode = (i < cnt) ? (int)coeff_type[(size_t)e * nb + r0 + i] : 1;
-            const bool z = (i < cnt) && tcode == 0;
-            // ordered rank of this zero among the chunk's zeros: three warps, in warp order
-            const unsigned int zm = __ballot_sync(0xffffffffu, z);
-            __shared__ unsigned int s_wz[3];
-            if (lane == 0) s_wz[warp - 1] = __popc(zm);
-            asm volatile("bar.sync 1, 96;" ::: "memory");    // named barrier: only the three preparing warps
-            unsigned int before = 0;
-            for (int w2 = 0; w2 < warp - 1; w2++) before += s_wz[w2];
-            const unsigned int tot = s_wz[0] + s_wz[1] + s_wz[2];
-            const unsigned int base = s_cur[e];
-            if (i < cnt) {
-                if (z) { s_val[buf][e][i] = cu[base + before + __popc(zm & ((1u << lane) - 1u))]; s_rst[buf][e][i] = 1; }
-                else { T dq = (T)(2 * (tcode - rad)); s_val[buf][e][i] = dq * prec; s_rst[buf][e][i] = 0; }
-            }
-            asm volatile("bar.sync 1, 96;" ::: "memory");
-            if (tid == 32) s_cur[e] = base + tot;
-            asm volatile("bar.sync 1, 96;" ::: "memory");
-        }
-    };
-    if (warp > 0) prepare(0, 0);
-    __syncthreads();
-    T last = (T)0;
-    int buf = 0;
-    for (uint32_t r0 = 0; r0 < reg_count; r0 += CH, buf ^= 1) {
-        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        if (warp > 0) prepare(r0 + CH, buf ^ 1);
-        else if (lane < ncoef) {
-            const int e = lane;
-#pragma unroll 4
-            for (int i = 0; i < cnt; i++) {
-                const T v = s_val[buf][e][i];
-                const T sum = last + v;
-                last = s_rst[buf][e][i] ? v : sum;
-                s_out[e][i] = last;
-            }
+    for (uint32_t base = 0; base < reg_count; base += 1024) {
+        const uint32_t i = base + tid;
+        const int tcode = (i < reg_count) ? (int)coeff_type[(size_t)e * nb + i] : 1;
+        const bool z = tcode == 0;
+        const unsigned int zm = __ballot_sync(0xffffffffu, z);
+        if (lane == 0) s_w[warp] = __popc(zm);
+        __syncthreads();
+        unsigned int before = 0, tot = 0;
+#pragma unroll
+        for (int w2 = 0; w2 < 32; w2++) { const unsigned int c = s_w[w2]; before += (w2 < warp) ? c : 0u; tot += c; }
+        const unsigned int run = s_run;
+        if (i < reg_count) {
+            T v;
+            if (z) v = cue[run + before + __popc(zm & ((1u << lane) - 1u))];
+            else { T dq = (T)(2 * (tcode - rad)); v = dq * prec; }
+            val[(size_t)e * reg_count + i] = v;
+            rst[(size_t)e * reg_count + i] = z ? 1 : 0;
         }
         __syncthreads();
-        for (int e = 0; e < ncoef; e++)
-            for (int i = tid; i < cnt; i += 128) coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_out[e][i];
+        if (tid == 0) s_run = run + tot;
+        __syncthreads();
+    }
+}
+
+// step 2 (serial): last = reset ? value : last + increment, one lane per coefficient.  Same three-stage pipeline as the
+// compression-side chain: warp 0 runs the adds of chunk c, helper warps 1,2,3,5 (warp 4 would share warp 0's scheduler)
+// prefetch chunk c+1 and scatter the results of chunk c-1 to their block ids.
+constexpr int DCHAIN_THREADS = 192;
+template <typename T>
+__global__ void __launch_bounds__(DCHAIN_THREADS) coeff_chain_decode_kernel(const T *__restrict__ val, const unsigned char *__restrict__ rst, uint32_t nb,
+                                                                            uint32_t reg_count, int ncoef, const uint32_t *__restrict__ reg_list,
+                                                                            T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
+    constexpr int CH = 256, PER = CH / 128;
+    __shared__ __align__(16) T s_val[3][4][CH];
+    __shared__ __align__(16) unsigned char s_rst[3][4][CH];
+    __shared__ __align__(16) T s_out[2][4][CH];
+    __shared__ uint32_t s_blk[3][CH];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int eB = warp == 5 ? 3 : ((warp == 4 || warp == 0) ? 99 : warp - 1);
+    const int tB = eB * 32 + lane;                           // index among the 128 helper threads
+    auto load_chunk = [&](uint32_t chunk) {
+        const uint32_t r0 = chunk * CH;
+        if (r0 >= reg_count) return;
+        const int buf = (int)(chunk % 3u);
+        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
+        T v[4][PER]; unsigned char f[4][PER]; uint32_t bl[PER];
+#pragma unroll
+        for (int e = 0; e < 4; e++)
+#pragma unroll
+            for (int q = 0; q < PER; q++) {
+                const int i = tB + q * 128;
+                if (e < ncoef && i < cnt) { v[e][q] = val[(size_t)e * reg_count + r0 + i]; f[e][q] = rst[(size_t)e * reg_count + r0 + i]; }
+            }
+#pragma unroll
+        for (int q = 0; q < PER; q++) { const int i = tB + q * 128; if (i < cnt) bl[q] = reg_list[r0 + i]; }
+#pragma unroll
+        for (int e = 0; e < 4; e++)
+#pragma unroll
+            for (int q = 0; q < PER; q++) {
+                const int i = tB + q * 128;
+                if (e < ncoef && i < cnt) { s_val[buf][e][i] = v[e][q]; s_rst[buf][e][i] = f[e][q]; }
+            }
+#pragma unroll
+        for (int q = 0; q < PER; q++) { const int i = tB + q * 128; if (i < cnt) s_blk[buf][i] = bl[q]; }
+    };
+    if (eB < 4) load_chunk(0);
+    T last = (T)0;
+    const uint32_t nchunks = (reg_count + CH - 1) / CH;
+    __syncthreads();
+    for (uint32_t it = 0; it <= nchunks; it++) {
+        if (warp == 0) {
+            if (it < nchunks && lane < ncoef) {
+                const int e = lane, buf = (int)(it % 3u), lb = (int)(it & 1u);
+                const int cnt = (int)min((uint32_t)CH, reg_count - it * CH);
+                // eight steps at a time: all loads first, then the add chain in registers, then the stores (left to itself the
+                // compiler keeps every step's load behind the previous step's store and the chain pays a shared-memory round trip per step)
+                int i = 0;
+                for (; i + 8 <= cnt; i += 8) {
+                    T v[8], o[8]; unsigned char f[8];
+#pragma unroll
+                    for (int q = 0; q < 8; q++) { v[q] = s_val[buf][e][i + q]; f[q] = s_rst[buf][e][i + q]; }
+#pragma unroll
+                    for (int q = 0; q < 8; q++) { const T sum = last + v[q]; last = f[q] ? v[q] : sum; o[q] = last; }
+#pragma unroll
+                    for (int q = 0; q < 8; q++) s_out[lb][e][i + q] = o[q];
+                }
+                for (; i < cnt; i++) {
+                    const T v = s_val[buf][e][i];
+                    const T sum = last + v;
+                    last = s_rst[buf][e][i] ? v : sum;
+                    s_out[lb][e][i] = last;
+                }
+            }
+        } else if (eB < 4) {
+            if (it + 1 < nchunks) load_chunk(it + 1);
+            if (it >= 1) {
+                const uint32_t cb = it - 1, r0 = cb * CH;
+                const int buf = (int)(cb % 3u), lb = (int)(cb & 1u);
+                const int cnt = (int)min((uint32_t)CH, reg_count - r0);
+                for (int e = 0; e < ncoef; e++)
+                    for (int i = tB; i < cnt; i += 128) coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_out[lb][e][i];
+            }
+        }
         __syncthreads();
     }
 }

@@ -871,8 +871,11 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
         if (launch_scan(c, c.stream, 0, d_flags, nb, d_rank, nullptr)) return SZ_NSCS;
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, 0, d_dummy, d_dummy2, d_list); KCHECK();
         for (int e = 0; e < ncoef; e++) if (cunp_cnt[e]) CU(cudaMemcpyAsync(d_cu + (size_t)e * nb, d_body + o_cunp[e], sizeof(T) * cunp_cnt[e], cudaMemcpyDeviceToDevice, c.stream));
-        coeff_chain_decode_kernel<T><<<1, 128, 0, c.stream>>>(d_ctype, nb, reg_count, ncoef, d_list, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3],
-                                                             d_cu, d_cu + nb, d_cu + 2ull * nb, d_cu + 3ull * nb, d_clast); KCHECK();
+        T *d_dval = (T *)c.get("dchain_val", sizeof(T) * 4ull * reg_count + 64);
+        unsigned char *d_drst = (unsigned char *)c.get("dchain_rst", 4ull * reg_count + 64);
+        if (!d_dval || !d_drst) return SZ_NSCS;
+        coeff_dec_prep_kernel<T><<<ncoef, 1024, 0, c.stream>>>(d_ctype, nb, reg_count, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3], d_cu, d_dval, d_drst); KCHECK();
+        coeff_chain_decode_kernel<T><<<1, DCHAIN_THREADS, 0, c.stream>>>(d_dval, d_drst, nb, reg_count, ncoef, d_list, d_clast); KCHECK();
     }
     if (mark(ST_DCHAIN)) return SZ_NSCS;
 
