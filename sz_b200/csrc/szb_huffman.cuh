@@ -525,29 +525,58 @@ __device__ __forceinline__ uint32_t dec_symbol(BitReader &br, const uint32_t *s_
     return tr.C[node];
 }
 
-// one Jacobi round.  start_used[s] = start position used by the most recent decode of sub-sequence s (init ~0).
+// one GLOBAL Jacobi round.  start_used[s] = start position used by the most recent decode of sub-sequence s.
+// Inside the round every CTA iterates over its own 256 consecutive sub-sequences until none of them moves any more (the end
+// positions travel through shared memory), so a correction entering a CTA is propagated as far as it goes within ONE launch;
+// global rounds are only needed to carry corrections across CTA boundaries -- a handful instead of dozens.
+// *changed is raised when the end of a CTA's last sub-sequence differs from what the next CTA saw in the previous round.
 __global__ void __launch_bounds__(256) dec_sync_kernel(const uint32_t *__restrict__ words, uint64_t total_bits, uint64_t nsub, DecTree tr,
                                                        const unsigned long long *__restrict__ end_prev, unsigned long long *end_cur,
                                                        unsigned long long *start_used, uint32_t *count, uint32_t *zcount,
                                                        int first_round, unsigned int *changed) {
     __shared__ uint32_t s_lut[1 << DEC_K];
+    __shared__ unsigned long long s_end[256];
     for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
-    __syncthreads();
-    uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (sidx >= nsub) return;
-    uint64_t lo = sidx * DEC_SUB_BITS, hi = lo + DEC_SUB_BITS;
-    uint64_t start = (sidx == 0) ? 0 : (first_round ? lo : end_prev[sidx - 1]);
-    if (!first_round && start == start_used[sidx]) { end_cur[sidx] = end_prev[sidx]; return; }
-    uint32_t cnt = 0, zc = 0;
+    const int tid = threadIdx.x;
+    const uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + tid;
+    const bool active = sidx < nsub;
+    const uint64_t lo = sidx * DEC_SUB_BITS;
+    uint64_t hi = lo + DEC_SUB_BITS;
     const uint64_t limit = total_bits + 64;
     if (hi > limit) hi = limit;
-    BitReader br; br.init(words, start);
-    while (br.pos < hi) {
-        const uint32_t sym = dec_symbol(br, s_lut, tr);
-        cnt++; zc += (sym == 0);
+    unsigned long long my_end = (active && !first_round) ? end_prev[sidx] : 0ull;
+    unsigned long long my_start = (active && !first_round) ? start_used[sidx] : ~0ull;
+    const unsigned long long old_end = my_end;
+    // start handed in from the previous CTA: its last end of the previous global round (nothing is known in the first round)
+    const unsigned long long ext_start = (sidx == 0) ? 0ull : ((first_round || !active) ? lo : end_prev[sidx - 1]);
+    uint32_t cnt = 0, zc = 0;
+    bool wrote = false;
+    s_end[tid] = my_end;
+    __syncthreads();
+    for (int iter = 0; iter <= 256; iter++) {
+        unsigned long long start;
+        if (tid == 0 || sidx == 0) start = ext_start;
+        else if (first_round && iter == 0) start = lo;
+        else start = s_end[tid - 1];
+        const bool did = active && start != my_start;
+        if (did) {
+            cnt = 0; zc = 0;
+            BitReader br; br.init(words, start);
+            while (br.pos < hi) {
+                const uint32_t sym = dec_symbol(br, s_lut, tr);
+                cnt++; zc += (sym == 0);
+            }
+            my_end = br.pos; my_start = start; wrote = true;
+        }
+        __syncthreads();                          // everybody has read its predecessor's end
+        s_end[tid] = my_end;
+        if (!__syncthreads_or(did ? 1 : 0)) break;
     }
-    start_used[sidx] = start; end_cur[sidx] = br.pos; count[sidx] = cnt; zcount[sidx] = zc;
-    *changed = 1u;
+    if (active) {
+        end_cur[sidx] = my_end;
+        if (wrote) { start_used[sidx] = my_start; count[sidx] = cnt; zcount[sidx] = zc; }
+        if ((tid == 255 || sidx == nsub - 1) && (first_round || my_end != old_end)) *changed = 1u;
+    }
 }
 
 // final pass: decode each sub-sequence again and write symbols (block-major index = sym_off[s] + m).

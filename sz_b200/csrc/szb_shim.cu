@@ -601,29 +601,36 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     enc_len_kernel<true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.clen, d_cb, d_cz); KCHECK();
     if (launch_scan(c, c.stream, 0, d_cb, nchunk_main, d_cbo, d_tot + 1)) return SZ_NSCS;
     if (launch_scan(c, c.stream, 0, d_cz, nchunk_main, d_czo, d_tot + 2)) return SZ_NSCS;
-    if (mark(ST_ENC)) return SZ_NSCS;
-    if (ntrees > 1) { CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0)); if (mark(ST_JOIN)) return SZ_NSCS; }      // join the side branch (coefficient trees)
-    // read back sizes
+    // ---- sizes of the main stream (the side branch with the coefficient trees is still running; nothing here waits for it) ----
     unsigned long long h_tot[8]; uint32_t h_tree[5][8]; ChainOut h_chain;
-    CU(cudaMemcpyAsync(h_tot, d_tot, sizeof(h_tot), cudaMemcpyDeviceToHost, c.stream));
-    for (int i = 0; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
-    CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaMemcpyAsync(h_tot, d_tot, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaMemcpyAsync(h_tree[0], tw[0].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
     if (check_wf_err(c)) return SZ_NSCS;
-    if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
-        fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
-    for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err("Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
     const uint64_t main_bits = h_tot[1], total_unpred = h_tot[2];
     const uint64_t main_bytes = (main_bits + 7) / 8;
-    uint64_t cbytes[4] = {0, 0, 0, 0};
-    for (int e = 0; e < ntrees - 1; e++) cbytes[e] = (h_tot[3 + e] + 7) / 8;
 
-    // ---- encode pass 2 ----
+    // ---- encode pass 2, main codes + ordered unpredictable values + mode bits ----
     uint32_t *d_bits = (uint32_t *)c.get("enc_bits", main_bytes + 64);
     T *d_unp = (T *)c.get("unpred", sizeof(T) * (total_unpred + 8));
     if (!d_bits || !d_unp) return SZ_NSCS;
     CU(cudaMemsetAsync(d_bits, 0, main_bytes + 64, c.stream));
     enc_write_kernel<T, true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.code, tw[0].d.clen, d_cbo, d_czo, d_bits, d_x, d_unp); KCHECK();
+    unsigned char *d_indbits = (unsigned char *)c.get("ind_bits", (nb + 7) / 8 + 64); if (!d_indbits) return SZ_NSCS;
+    indicator_pack_kernel<<<((nb + 7) / 8 + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_indbits); KCHECK();
+    if (mark(ST_ENC)) return SZ_NSCS;
+
+    // ---- join the side branch (coefficient trees), then the coefficient bit streams ----
+    if (ntrees > 1) { CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0)); if (mark(ST_JOIN)) return SZ_NSCS; }
+    CU(cudaMemcpyAsync(h_tot + 3, d_tot + 3, 5 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+    for (int i = 1; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
+        fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
+    for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err("Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
+    uint64_t cbytes[4] = {0, 0, 0, 0};
+    for (int e = 0; e < ntrees - 1; e++) cbytes[e] = (h_tot[3 + e] + 7) / 8;
     uint32_t *d_cbits[4] = {nullptr, nullptr, nullptr, nullptr};
     for (int e = 0; e < ntrees - 1; e++) {
         char name[32]; snprintf(name, sizeof(name), "enc_cbits%d", e);
@@ -633,8 +640,6 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         enc_write_kernel<T, false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.code, tw[1 + e].d.clen, d_cbo + o, d_czo + o,
                                                                                       d_cbits[e], (const T *)nullptr, (T *)nullptr); KCHECK();
     }
-    unsigned char *d_indbits = (unsigned char *)c.get("ind_bits", (nb + 7) / 8 + 64); if (!d_indbits) return SZ_NSCS;
-    indicator_pack_kernel<<<((nb + 7) / 8 + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_indbits); KCHECK();
     if (mark(ST_ENC)) return SZ_NSCS;
 
     // ---- stream body (SURVEY.md Appendix A from offset 4+MD; ref: sz_float.c:7392-7489) ----
@@ -745,7 +750,7 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
             std::swap(J.ep, J.ec);
         }
         if (!any) break;
-        if (round == 0 || (round & 1)) continue;                 // read the flags every second round only
+        if (round == 0) continue;                                // the first round always changes something
         unsigned int ch[8];
         CU(cudaMemcpyAsync(ch, d_changed, 4 * njobs, cudaMemcpyDeviceToHost, c.stream));
         CU(cudaStreamSynchronize(c.stream));
