@@ -137,17 +137,44 @@ def compress(a, mode, abs_eb=0.0, rel=0.0):
     return out
 
 
-def decompress(stream, dtype, shape):
-    """SZ_decompress of a HOST byte stream -> numpy array."""
+class _Malloced(object):
+    """owner of a malloc'ed block returned by the C API; frees it when the last numpy view dies"""
+
+    def __init__(self, ptr, nbytes):
+        self.ptr, self.nbytes = ptr, nbytes
+        self.__array_interface__ = {"data": (ptr, False), "shape": (nbytes,), "typestr": "|u1", "version": 3}
+
+    def __del__(self):
+        if self.ptr:
+            _libc.free(self.ptr)
+            self.ptr = 0
+
+
+def compress_view(a, mode, abs_eb=0.0, rel=0.0):
+    """SZ_compress_args on a HOST numpy array -> uint8 numpy array that WRAPS the buffer the C call returned (no second copy;
+    the buffer is freed with the array).  This is the call bench.py times as `e2e`."""
+    L = lib()
+    a = np.ascontiguousarray(a)
+    n = C.c_size_t(0)
+    p = L.SZ_compress_args(_code(a.dtype), a.ctypes.data, C.byref(n), int(mode), float(abs_eb), float(rel), 0.0, *_dims5(a.shape))
+    if not p:
+        raise SZError("SZ_compress_args failed: %s" % L.szb200_last_error().decode())
+    return np.asarray(_Malloced(p, n.value))
+
+
+def decompress(stream, dtype, shape, out=None):
+    """SZ_decompress_args of a HOST byte stream -> numpy array (written straight into `out` when given)."""
     L = lib()
     dt = np.dtype(dtype)
     buf = np.frombuffer(stream, dtype=np.uint8)
-    p = L.SZ_decompress(_code(dt), buf.ctypes.data, buf.size, *_dims5(shape))
-    if not p:
-        raise SZError("SZ_decompress failed: %s" % L.szb200_last_error().decode())
-    n = int(np.prod(shape))
-    out = np.frombuffer(C.string_at(p, n * dt.itemsize), dtype=dt).reshape(shape).copy()
-    _libc.free(p)
+    if out is None:
+        out = np.empty(shape, dtype=dt)
+    assert out.dtype == dt and out.flags.c_contiguous and out.size == int(np.prod(shape))
+    if out.size == 0:
+        return out
+    got = L.SZ_decompress_args(_code(dt), buf.ctypes.data, buf.size, out.ctypes.data, *_dims5(shape))
+    if got != out.size:
+        raise SZError("SZ_decompress_args failed: %s" % L.szb200_last_error().decode())
     return out
 
 

@@ -8,9 +8,32 @@
  * Everything data-parallel is delegated to kernels; nothing here touches the bulk data on the CPU and there is
  * no CPU fallback: if the shim reports an error the call fails (NULL / SZ_NSCS).
  */
+#define _GNU_SOURCE
 #include <ctype.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdio.h>
 #include <math.h>
 #include <pthread.h>
+#include <time.h>
+#include <sys/mman.h>
+/* Buffers handed back to the caller (free()-able).  Large ones are 2 MiB-aligned and marked for transparent huge pages: a
+ * device-to-host copy into FRESH 4 KiB pages is bound by page faults (measured 2 GB/s); with huge pages it is not. */
+static void *host_alloc_result(size_t n) {
+    const size_t HP = (size_t)2 << 20;
+    if (n >= 2 * HP) {
+        void *p = NULL;
+        const size_t len = (n + HP - 1) & ~(HP - 1);
+        if (posix_memalign(&p, HP, len) == 0 && p) {
+#ifdef MADV_HUGEPAGE
+            (void)madvise(p, len, MADV_HUGEPAGE);
+#endif
+            return p;
+        }
+    }
+    return malloc(n ? n : 1);
+}
+static double now_ms(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1e3 + t.tv_nsec * 1e-6; }
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -404,6 +427,8 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     if (r5 != 0) { printf("Error: doesn't support 5 dimensions for now.\n"); return SZ_DERR; }
     if (confparams_cpr->randomAccess) { printf("Error: randomAccess is not supported by libSZ_b200.\n"); return SZ_NSCS; }
 
+    const int hprof = getenv("SZB200_HOST_PROFILE") != NULL;
+    const double hp0 = hprof ? now_ms() : 0.0;
     const void *d_in = data;
     if (!data_on_device) { d_in = szb200_stage_input(data, N * ts); if (!d_in) { printf("Error: %s\n", szb200_last_error()); return SZ_NSCS; } }
     double vmin, vmax;
@@ -455,29 +480,43 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     const size_t lossless_total = 3 + md + 8 + 1 + ts * N;
     size_t cap = 4 + md + szb200_body_capacity(&job);
     if (cap < lossless_total + 16) cap = lossless_total + 16;
-    unsigned char *out = NULL;
+    unsigned char *out = NULL;       /* where the stream is assembled: the caller's device buffer, or the context's device staging buffer */
     if (to_dev) { if (dev_cap < lossless_total) { printf("Error: device stream buffer too small (need at least %zu bytes)\n", lossless_total); return SZ_NSCS; } cap = dev_cap; out = (unsigned char *)dev_out; }
-    else { out = (unsigned char *)malloc(cap); if (!out) return SZ_NSCS; }
+    else { out = (unsigned char *)szb200_output_buffer(cap); if (!out) { printf("Error: %s\n", szb200_last_error()); return SZ_NSCS; } }
     size_t body = 0;
     szb200_stats st;
-    int rc = szb200_compress_blocked(&job, d_in, out + 4 + md, to_dev, cap - 4 - md, &body, &st);
-    if (rc != SZ_SCES) { printf("Error: %s\n", szb200_last_error()); if (!to_dev) free(out); return rc; }
+    const double hp1 = hprof ? now_ms() : 0.0;
+    int rc = szb200_compress_blocked(&job, d_in, out + 4 + md, 1, cap - 4 - md, &body, &st);
+    const double hp2 = hprof ? now_ms() : 0.0;
+    if (rc != SZ_SCES) { printf("Error: %s\n", szb200_last_error()); return rc; }
     if (exe_params->optQuantMode == 1) updateQuantizationInfo((int)st.intervals);   /* side effect of the reference (sz_float.c:6651) */
     size_t total = 4 + md + body;
     unsigned char same = 0x80 | 0x40;                   /* initRandomAccessBytes, ref: dataCompression.c:686-709 */
     if (confparams_cpr->protectValueRange) same |= 0x04;
-    if (total >= N * ts + 3 + md + 8 + 1) {             /* SZ_compress_args_*_StoreOriData, ref: sz_float.c:526-559, trigger :2979 */
-        same = 80;
-        unsigned char nb8[8]; put_be64(nb8, (uint64_t)N);
-        if (to_dev) { if (szb200_copy(out + 4 + md, nb8, 8, 0)) return SZ_NSCS; } else memcpy(out + 4 + md, nb8, 8);
-        if (szb200_swap_copy(dataType, d_in, 1, out + 4 + md + 8, to_dev, N)) { printf("Error: %s\n", szb200_last_error()); if (!to_dev) free(out); return SZ_NSCS; }
-        total = lossless_total;
-    }
+    const int lossless = total >= N * ts + 3 + md + 8 + 1;   /* SZ_compress_args_*_StoreOriData, ref: sz_float.c:526-559, trigger :2979 */
+    if (lossless) { same = 80; total = lossless_total; }
     hdr[3] = same;
     convertSZParamsToBytes(confparams_cpr, hdr + 4);
-    if (to_dev) { if (szb200_copy(out, hdr, 4 + md, 0)) return SZ_NSCS; }
-    else { memcpy(out, hdr, 4 + md); unsigned char *sh = (unsigned char *)realloc(out, total ? total : 1); if (sh) out = sh; *host_out = out; }
+    unsigned char nb8[8]; put_be64(nb8, (uint64_t)N);
+    if (to_dev) {
+        if (lossless) {
+            if (szb200_copy(out + 4 + md, nb8, 8, 0)) return SZ_NSCS;
+            if (szb200_swap_copy(dataType, d_in, 1, out + 4 + md + 8, 1, N)) { printf("Error: %s\n", szb200_last_error()); return SZ_NSCS; }
+        }
+        if (szb200_copy(out, hdr, 4 + md, 0)) return SZ_NSCS;
+    } else {
+        /* the stream was assembled in device memory; the host result is allocated at its exact size and filled by ONE copy */
+        unsigned char *h = (unsigned char *)host_alloc_result(total);
+        if (!h) return SZ_NSCS;
+        memcpy(h, hdr, 4 + md);
+        if (lossless) {
+            memcpy(h + 4 + md, nb8, 8);
+            if (szb200_swap_copy(dataType, d_in, 1, h + 4 + md + 8, 0, N)) { printf("Error: %s\n", szb200_last_error()); free(h); return SZ_NSCS; }
+        } else if (body && szb200_copy(h + 4 + md, out + 4 + md, body, 1)) { printf("Error: %s\n", szb200_last_error()); free(h); return SZ_NSCS; }
+        *host_out = h;
+    }
     *outSize = total;
+    if (hprof) fprintf(stderr, "[host-prof] H2D + range %.2f ms | blocked compress call %.2f ms (device %.2f ms) | header + shrink %.2f ms\n", hp1 - hp0, hp2 - hp1, st.ms_total, now_ms() - hp2);
     return status;
 }
 
@@ -604,6 +643,17 @@ static void reset_dec_state(void) {                   /* ref: sz/src/sz.c:497-51
     detect_endianness();
 }
 
+/* decode on the device, then ONE device-to-host copy into `dst` (NULL: a fresh malloc, returned through *made) */
+static int decompress_to_host(int dataType, unsigned char *bytes, size_t byteLength, void *dst, void **made, const size_t r[5]) {
+    const size_t ts = dataType == SZ_FLOAT ? 4 : 8;
+    const size_t N = computeDataLength(r[4], r[3], r[2], r[1], r[0]);
+    void *dbuf = szb200_output_buffer(N * ts + 64);
+    if (!dbuf || decompress_core(dataType, bytes, byteLength, 0, dbuf, r) != SZ_SCES) return SZ_NSCS;
+    if (!dst) { dst = host_alloc_result(N * ts); if (!dst) return SZ_NSCS; *made = dst; }
+    if (N && szb200_copy(dst, dbuf, N * ts, 1) != SZ_SCES) { if (made && *made) { free(*made); *made = NULL; } return SZ_NSCS; }
+    return SZ_SCES;
+}
+
 /* ref: sz/src/sz.c:486-577 */
 void *SZ_decompress(int dataType, unsigned char *bytes, size_t byteLength, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
     if (dataType != SZ_FLOAT && dataType != SZ_DOUBLE) { printf("Error: data type cannot be the types other than SZ_FLOAT or SZ_DOUBLE\n"); return NULL; }
@@ -611,28 +661,25 @@ void *SZ_decompress(int dataType, unsigned char *bytes, size_t byteLength, size_
     size_t r[5];
     filterDimension(r5, r4, r3, r2, r1, r);
     reset_dec_state();
-    const size_t ts = dataType == SZ_FLOAT ? 4 : 8;
-    const size_t N = computeDataLength(r[4], r[3], r[2], r[1], r[0]);
     void *out = NULL;
-    void *dbuf = szb200_output_buffer(N * ts + 64);
-    if (dbuf && decompress_core(dataType, bytes, byteLength, 0, dbuf, r) == SZ_SCES) {
-        out = malloc(N * ts ? N * ts : 1);
-        if (out && N && szb200_copy(out, dbuf, N * ts, 1) != SZ_SCES) { free(out); out = NULL; }
-    }
+    if (decompress_to_host(dataType, bytes, byteLength, NULL, &out, r) != SZ_SCES) out = NULL;
     pthread_mutex_unlock(&g_api_mu);
     return out;
 }
 
-/* ref: sz/src/sz.c:584-680 */
+/* ref: sz/src/sz.c:584-680.  The reference decompresses into a fresh array and copies; here the device result goes straight
+ * into the caller's array (pinned memory makes this the fastest host-side call). */
 size_t SZ_decompress_args(int dataType, unsigned char *bytes, size_t byteLength, void *decompressed_array, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
+    if (dataType != SZ_FLOAT && dataType != SZ_DOUBLE) { printf("Error: data type cannot be the types other than SZ_FLOAT or SZ_DOUBLE\n"); return 0; }
+    if (!decompressed_array) return 0;
+    pthread_mutex_lock(&g_api_mu);
     size_t r[5];
     filterDimension(r5, r4, r3, r2, r1, r);
-    size_t nbEle = computeDataLength(r[4], r[3], r[2], r[1], r[0]);
-    void *data = SZ_decompress(dataType, bytes, byteLength, r5, r4, r3, r2, r1);
-    if (!data) return 0;
-    memcpy(decompressed_array, data, nbEle * (dataType == SZ_FLOAT ? 4 : 8));
-    free(data);
-    return nbEle;
+    reset_dec_state();
+    const size_t nbEle = computeDataLength(r[4], r[3], r[2], r[1], r[0]);
+    const int rc = decompress_to_host(dataType, bytes, byteLength, decompressed_array, NULL, r);
+    pthread_mutex_unlock(&g_api_mu);
+    return rc == SZ_SCES ? nbEle : 0;
 }
 
 int szb200_decompress_device(int dataType, const void *d_stream, size_t byteLength, void *d_out, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
