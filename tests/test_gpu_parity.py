@@ -99,6 +99,13 @@ BIG = [
     ("cfg5_s3d_4d_f64_absrel", lambda: szref.smooth_field((11, 40, 50, 60), np.float64, span=2 * np.pi), szref.ABS_AND_REL, 1e-3, 1e-3),
     ("plane_120c_regression_heavy", lambda: szref.plane_field((120, 120, 120), np.float32), szref.ABS, 1e-1, 1e-3),
     ("background_150c_use_mean", lambda: szref.background_field((150, 150, 150), np.float32), szref.REL, 1e-4, 1e-3),
+    # partial pencils / chunks in every direction, fp64 in 3D, fp32 in 4D, a long thin 2D field
+    ("odd_f64_131x77x203_rel", lambda: szref.smooth_field((131, 77, 203), np.float64, span=6 * np.pi), szref.REL, 1e-4, 1e-4),
+    ("odd_f32_4d_7x33x41x59_abs", lambda: szref.smooth_field((7, 33, 41, 59), np.float32, span=4 * np.pi), szref.ABS, 1e-3, 1e-3),
+    ("odd_f64_2d_611x1031_rel", lambda: szref.smooth_field((611, 1031), np.float64, span=10 * np.pi), szref.REL, 1e-4, 1e-5),
+    ("thin_f32_2d_5000x37_abs", lambda: szref.smooth_field((5000, 37), np.float32, span=40 * np.pi), szref.ABS, 1e-3, 1e-3),
+    ("noisy_f32_90x100x110_rel", lambda: (szref.smooth_field((90, 100, 110), np.float32, span=4 * np.pi)
+                                          + 0.02 * szref.random_field((90, 100, 110), np.float32)).astype(np.float32), szref.REL, 1e-4, 1e-3),
 ]
 
 
@@ -113,6 +120,46 @@ def test_baseline_shapes_bit_exact_vs_oracle(sz, orc, case):
     s_orc = orc.compress(a, mode, ab, rl)
     assert len(s_gpu) == len(s_orc)
     assert s_gpu == s_orc
+    d_gpu = sz.decompress(s_gpu, a.dtype, a.shape)
+    d_orc = orc.decompress(s_orc, a.dtype, a.shape)
+    assert d_gpu.tobytes() == d_orc.tobytes()
+    sz.finalize()
+
+
+def _fuzz_case(seed):
+    """seeded odd-shaped field: smooth + a noisy slab + a constant slab + a few spikes (regression, Lorenzo, mean-free and
+    unpredictable points all occur), random dtype / rank / mode / bound"""
+    rng = np.random.RandomState(1000 + seed)
+    rank = [2, 3, 3, 3, 4][seed % 5]
+    if rank == 2:
+        shape = (int(rng.randint(17, 300)), int(rng.randint(17, 300)))
+    elif rank == 3:
+        shape = tuple(int(v) for v in rng.randint(6, 70, size=3))
+    else:
+        shape = tuple(int(v) for v in rng.randint(3, 24, size=4))
+    dt = np.float32 if seed % 2 == 0 else np.float64
+    a = szref.smooth_field(shape, dt, span=float(rng.uniform(1.0, 12.0)), field_id=seed).astype(np.float64)
+    flat = a.reshape(shape[0], -1)
+    k = shape[0] // 3
+    flat[k:k + max(1, shape[0] // 5)] += 0.05 * rng.standard_normal(flat[k:k + max(1, shape[0] // 5)].shape)
+    flat[-max(1, shape[0] // 6):] = 0.75
+    idx = rng.randint(0, a.size, size=max(1, a.size // 500))
+    a.reshape(-1)[idx] += rng.uniform(-50, 50, size=idx.size)
+    mode = [szref.REL, szref.ABS, szref.ABS_AND_REL, szref.ABS_OR_REL][seed % 4]
+    rel = float(10.0 ** rng.uniform(-5, -2))
+    ab = float(10.0 ** rng.uniform(-4, -1))
+    return np.ascontiguousarray(a.astype(dt)), mode, ab, rel
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_fuzzed_shapes_bit_exact_vs_oracle(sz, orc, seed):
+    a, mode, ab, rl = _fuzz_case(seed)
+    cfg = cases.make_cfg(mode, ab, rl, {})
+    sz.init(cfg)
+    orc.init(cfg)
+    s_gpu = sz.compress(a, mode, ab, rl)
+    s_orc = orc.compress(a, mode, ab, rl)
+    assert s_gpu == s_orc, "stream differs for shape %s dtype %s mode %d" % (a.shape, a.dtype, mode)
     d_gpu = sz.decompress(s_gpu, a.dtype, a.shape)
     d_orc = orc.decompress(s_orc, a.dtype, a.shape)
     assert d_gpu.tobytes() == d_orc.tobytes()
