@@ -121,6 +121,28 @@ int szb200_compress_args_device(int dataType, const void *d_data, void *d_stream
                                 size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
 int szb200_decompress_device(int dataType, const void *d_stream, size_t byteLength, void *d_out,
                              size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+/* ---- batches of independent fields (BASELINE configs 3 and 4: 13 and 77 calls of the same shape) --------------------------
+ * No counterpart in the reference, whose callers loop over SZ_compress_args; the closest precedent is the one-thread-per-slab
+ * pattern of example/test_threadsafe.c:40-58.  Every item is compressed exactly as szb200_compress_args_device would compress it
+ * (same stream, byte for byte); `lanes` worker threads (1..16), each with its own streams and workspace, pull items from a
+ * queue, so the serial stages of one field (coefficient chain, Huffman trees) overlap the bandwidth stages of the others.
+ * The exported parameter globals are read once at entry and not modified. */
+typedef struct szb200_batch_item {
+    const void *d_data;        /* in : DEVICE pointer to the field */
+    void *d_stream;            /* in : DEVICE buffer for the stream (compress) / DEVICE pointer to the stream (decompress) */
+    size_t stream_capacity;    /* in : bytes available at d_stream (compress) / stream length in bytes (decompress) */
+    size_t out_size;           /* out: stream length (compress) */
+    void *d_out;               /* in : DEVICE pointer to the output field (decompress) */
+    int rc;                    /* out: SZ_SCES or a negative SZ_* code */
+} szb200_batch_item;
+int szb200_compress_batch_device(int dataType, szb200_batch_item *items, int n_items, int lanes, int errBoundMode, double absErrBound,
+                                 double relBoundRatio, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+int szb200_decompress_batch_device(int dataType, szb200_batch_item *items, int n_items, int lanes,
+                                   size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+/* worker-lane selection of the calling thread (0 = the default context); used by the batch entry points */
+int szb200_set_lane(int lane);
+int szb200_current_device(void);
+
 /* statistics of the most recent job on this context */
 int szb200_last_stats(szb200_stats *out);
 

@@ -208,6 +208,51 @@ def decompress_device(stream, nbytes, out):
     return out
 
 
+class BatchItem(C.Structure):
+    """szb200_batch_item (include/szb200.h)"""
+    _fields_ = [("d_data", C.c_void_p), ("d_stream", C.c_void_p), ("stream_capacity", C.c_size_t), ("out_size", C.c_size_t),
+                ("d_out", C.c_void_p), ("rc", C.c_int)]
+
+
+def compress_batch_device(xs, outs, mode, abs_eb=0.0, rel=0.0, lanes=4):
+    """Compress a batch of equally shaped CUDA tensors (BASELINE configs 3 / 4) on `lanes` concurrent worker lanes.
+    outs[i] is a uint8 CUDA tensor of at least compress_bound() bytes; returns the list of stream lengths."""
+    import torch
+    assert len(xs) == len(outs) and len(xs) > 0
+    shape, dt = tuple(xs[0].shape), xs[0].dtype
+    items = (BatchItem * len(xs))()
+    for i, (x, o) in enumerate(zip(xs, outs)):
+        assert x.is_cuda and o.is_cuda and x.is_contiguous() and tuple(x.shape) == shape and x.dtype == dt and o.dtype == torch.uint8
+        items[i].d_data, items[i].d_stream, items[i].stream_capacity = x.data_ptr(), o.data_ptr(), o.numel()
+    L = lib()
+    L.szb200_compress_batch_device.argtypes = [C.c_int, C.POINTER(BatchItem), C.c_int, C.c_int, C.c_int, C.c_double, C.c_double] + [C.c_size_t] * 5
+    L.szb200_compress_batch_device.restype = C.c_int
+    code = SZ_FLOAT if dt == torch.float32 else SZ_DOUBLE
+    rc = L.szb200_compress_batch_device(code, items, len(xs), int(lanes), int(mode), float(abs_eb), float(rel), *_dims5(shape))
+    if rc != 0:
+        raise SZError("szb200_compress_batch_device rc=%d (items: %s)" % (rc, [it.rc for it in items]))
+    return [int(it.out_size) for it in items]
+
+
+def decompress_batch_device(streams, sizes, outs, lanes=4):
+    """Decompress a batch of device-resident streams into equally shaped CUDA tensors."""
+    import torch
+    assert len(streams) == len(sizes) == len(outs) and len(outs) > 0
+    shape, dt = tuple(outs[0].shape), outs[0].dtype
+    items = (BatchItem * len(outs))()
+    for i, (st, n, o) in enumerate(zip(streams, sizes, outs)):
+        assert st.is_cuda and o.is_cuda and o.is_contiguous() and tuple(o.shape) == shape and o.dtype == dt
+        items[i].d_stream, items[i].stream_capacity, items[i].d_out = st.data_ptr(), int(n), o.data_ptr()
+    L = lib()
+    L.szb200_decompress_batch_device.argtypes = [C.c_int, C.POINTER(BatchItem), C.c_int, C.c_int] + [C.c_size_t] * 5
+    L.szb200_decompress_batch_device.restype = C.c_int
+    code = SZ_FLOAT if dt == torch.float32 else SZ_DOUBLE
+    rc = L.szb200_decompress_batch_device(code, items, len(outs), int(lanes), *_dims5(shape))
+    if rc != 0:
+        raise SZError("szb200_decompress_batch_device rc=%d (items: %s)" % (rc, [it.rc for it in items]))
+    return outs
+
+
 def last_stats():
     s = Stats()
     if lib().szb200_last_stats(C.byref(s)) != 0:

@@ -49,6 +49,15 @@ int sysEndianType = LITTLE_ENDIAN_SYSTEM;
 sz_params *confparams_cpr = NULL;
 sz_params *confparams_dec = NULL;
 sz_exedata *exe_params = NULL;
+/* The batch entry points run several jobs at once on worker threads.  Every worker owns private copies of the three parameter
+ * blocks and publishes them through these thread-local overrides; the single-call API leaves them NULL and works on the
+ * exported globals exactly like the reference. */
+static __thread sz_params *tl_cpr = NULL, *tl_dec = NULL;
+static __thread sz_exedata *tl_exe = NULL;
+static inline sz_params *CPR(void) { return tl_cpr ? tl_cpr : confparams_cpr; }
+static inline sz_params *DEC(void) { return tl_dec ? tl_dec : confparams_dec; }
+static inline sz_exedata *EXE(void) { return tl_exe ? tl_exe : exe_params; }
+
 
 static pthread_mutex_t g_api_mu = PTHREAD_MUTEX_INITIALIZER;   /* the globals above are shared state */
 
@@ -292,7 +301,7 @@ int filterDimension(size_t r5, size_t r4, size_t r3, size_t r2, size_t r1, size_
 
 /* ref: sz/src/ByteToolkit.c:874-972 */
 void convertSZParamsToBytes(sz_params *params, unsigned char *result) {
-    unsigned char buf = (unsigned char)exe_params->optQuantMode;
+    unsigned char buf = (unsigned char)EXE()->optQuantMode;
     buf = (unsigned char)((buf << 1) | dataEndianType);
     buf = (unsigned char)((buf << 1) | sysEndianType);
     buf = (unsigned char)((buf << 2) | params->szMode);
@@ -318,7 +327,7 @@ void convertSZParamsToBytes(sz_params *params, unsigned char *result) {
     case PW_REL: memset(&result[6], 0, 4); put_be_float(&result[10], (float)params->pw_relBoundRatio); break;
     }
     result[14] = (unsigned char)params->sol_ID;
-    put_be32(&result[16], exe_params->optQuantMode == 1 ? params->max_quant_intervals : params->quantization_intervals);
+    put_be32(&result[16], EXE()->optQuantMode == 1 ? params->max_quant_intervals : params->quantization_intervals);
     if (params->dataType == SZ_FLOAT) { put_be_float(&result[20], params->fmin); put_be_float(&result[24], params->fmax); }
     else { put_be_double(&result[20], params->dmin); put_be_double(&result[28], params->dmax); }
 }
@@ -326,7 +335,7 @@ void convertSZParamsToBytes(sz_params *params, unsigned char *result) {
 /* ref: sz/src/ByteToolkit.c:974-1063 */
 void convertBytesToSZParams(unsigned char *bytes, sz_params *params) {
     unsigned char flag1 = bytes[0];
-    exe_params->optQuantMode = (char)((flag1 & 0x40) >> 6);
+    EXE()->optQuantMode = (char)((flag1 & 0x40) >> 6);
     dataEndianType = (flag1 & 0x20) >> 5;
     params->szMode = (flag1 & 0x0c) >> 2;
     switch (flag1 & 0x03) { case 0: params->gzipMode = 1; break; case 1: params->gzipMode = 0; break; case 2: params->gzipMode = 9; break; }
@@ -347,7 +356,7 @@ void convertBytesToSZParams(unsigned char *bytes, sz_params *params) {
     case PW_REL: params->pw_relBoundRatio = get_be_float(&bytes[10]); break;
     }
     params->sol_ID = (int)bytes[14];
-    if (exe_params->optQuantMode == 1) { params->max_quant_intervals = get_be32(&bytes[16]); params->quantization_intervals = 0; }
+    if (EXE()->optQuantMode == 1) { params->max_quant_intervals = get_be32(&bytes[16]); params->quantization_intervals = 0; }
     else { params->max_quant_intervals = 0; params->quantization_intervals = get_be32(&bytes[16]); }
     if (params->dataType == SZ_FLOAT) { params->fmin = get_be_float(&bytes[20]); params->fmax = get_be_float(&bytes[24]); }
     else if (params->dataType == SZ_DOUBLE) { params->dmin = get_be_double(&bytes[20]); params->dmax = get_be_double(&bytes[28]); }
@@ -402,8 +411,8 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     const size_t r1 = r[0], r2 = r[1], r3 = r[2], r4 = r[3], r5 = r[4];
     const size_t ts = dataType == SZ_FLOAT ? 4 : 8;
     const size_t md = dataType == SZ_FLOAT ? MetaDataByteLength : MetaDataByteLength_double;
-    confparams_cpr->dataType = dataType;
-    confparams_cpr->errorBoundMode = mode;
+    CPR()->dataType = dataType;
+    CPR()->errorBoundMode = mode;
     const size_t N = computeDataLength(r5, r4, r3, r2, r1);
     const int to_dev = (host_out == NULL);
     if (N <= MIN_NUM_OF_ELEMENTS) {                   /* SZ_skip_compress_*, ref: sz_float.c:37-43: raw bytes, no header */
@@ -416,16 +425,16 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
         printf("Error: libSZ_b200 supports errorBoundMode ABS, REL, ABS_AND_REL and ABS_OR_REL only (got %d).\n", mode);
         return SZ_BERR;
     }
-    if (confparams_cpr->szMode != SZ_BEST_SPEED) {
+    if (CPR()->szMode != SZ_BEST_SPEED) {
         printf("Error: libSZ_b200 implements szMode = SZ_BEST_SPEED only (the lossless back-end is out of scope); set szMode = SZ_BEST_SPEED.\n");
         return SZ_MERR;
     }
-    if (r2 == 0 || confparams_cpr->withRegression == SZ_NO_REGRESSION) {
+    if (r2 == 0 || CPR()->withRegression == SZ_NO_REGRESSION) {
         printf("Error: libSZ_b200 implements the SZ 2.1 blocked-regression path (2D/3D/4D, withLinearRegression = YES) only.\n");
         return SZ_DERR;
     }
     if (r5 != 0) { printf("Error: doesn't support 5 dimensions for now.\n"); return SZ_DERR; }
-    if (confparams_cpr->randomAccess) { printf("Error: randomAccess is not supported by libSZ_b200.\n"); return SZ_NSCS; }
+    if (CPR()->randomAccess) { printf("Error: randomAccess is not supported by libSZ_b200.\n"); return SZ_NSCS; }
 
     const int hprof = getenv("SZB200_HOST_PROFILE") != NULL;
     const double hp0 = hprof ? now_ms() : 0.0;
@@ -436,14 +445,14 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     double range_d;
     if (dataType == SZ_FLOAT) {                        /* range and max are computed in T (ref: dataCompression.c:116, sz_float.c:2846) */
         float mn = (float)vmin, mx = (float)vmax, range = mx - mn, maxr = mn + range;
-        confparams_cpr->fmin = mn; confparams_cpr->fmax = maxr; range_d = (double)range;
+        CPR()->fmin = mn; CPR()->fmax = maxr; range_d = (double)range;
     } else {
         double range = vmax - vmin, maxr = vmin + range;
-        confparams_cpr->dmin = vmin; confparams_cpr->dmax = maxr; range_d = range;
+        CPR()->dmin = vmin; CPR()->dmax = maxr; range_d = range;
     }
     int status = SZ_SCES;
     double realPrecision = real_precision(dataType, range_d, mode, absb, relb, &status);
-    confparams_cpr->absErrBound = realPrecision;
+    CPR()->absErrBound = realPrecision;
 
     unsigned char hdr[4 + MetaDataByteLength_double + 8 + 8];
     memset(hdr, 0, sizeof(hdr));
@@ -451,9 +460,9 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
 
     if (range_d <= realPrecision) {                    /* constant container, ref: sz_float.c:2728-2753, TightDataPointStorageF.c:590-629 */
         unsigned char same = 0x01 | 0x40;
-        if (confparams_cpr->protectValueRange) same |= 0x04;
+        if (CPR()->protectValueRange) same |= 0x04;
         hdr[3] = same;
-        convertSZParamsToBytes(confparams_cpr, hdr + 4);
+        convertSZParamsToBytes(CPR(), hdr + 4);
         put_be64(hdr + 4 + md, (uint64_t)N);
         unsigned char first[8];
         if (data_on_device) { if (szb200_copy(first, data, ts, 1)) return SZ_NSCS; } else memcpy(first, data, ts);
@@ -472,10 +481,10 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     else if (r4 == 0) { job.dim = 3; job.n0 = r3; job.n1 = r2; job.n2 = r1; }
     else { job.dim = 3; job.n0 = r4 * r3; job.n1 = r2; job.n2 = r1; }          /* 4D flattened, ref: sz_float.c:3010 */
     job.eb = realPrecision;
-    job.max_quant_intervals = confparams_cpr->max_quant_intervals;
-    job.quantization_intervals = exe_params->optQuantMode == 1 ? 0 : (unsigned int)exe_params->intvCapacity;
-    job.sampleDistance = confparams_cpr->sampleDistance;
-    job.predThreshold = confparams_cpr->predThreshold;
+    job.max_quant_intervals = CPR()->max_quant_intervals;
+    job.quantization_intervals = EXE()->optQuantMode == 1 ? 0 : (unsigned int)EXE()->intvCapacity;
+    job.sampleDistance = CPR()->sampleDistance;
+    job.predThreshold = CPR()->predThreshold;
 
     const size_t lossless_total = 3 + md + 8 + 1 + ts * N;
     size_t cap = 4 + md + szb200_body_capacity(&job);
@@ -489,14 +498,14 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     int rc = szb200_compress_blocked(&job, d_in, out + 4 + md, 1, cap - 4 - md, &body, &st);
     const double hp2 = hprof ? now_ms() : 0.0;
     if (rc != SZ_SCES) { printf("Error: %s\n", szb200_last_error()); return rc; }
-    if (exe_params->optQuantMode == 1) updateQuantizationInfo((int)st.intervals);   /* side effect of the reference (sz_float.c:6651) */
+    if (EXE()->optQuantMode == 1) { EXE()->intvCapacity = (int)st.intervals; EXE()->intvRadius = (int)st.intervals / 2; }   /* side effect of the reference (sz_float.c:6651) */
     size_t total = 4 + md + body;
     unsigned char same = 0x80 | 0x40;                   /* initRandomAccessBytes, ref: dataCompression.c:686-709 */
-    if (confparams_cpr->protectValueRange) same |= 0x04;
+    if (CPR()->protectValueRange) same |= 0x04;
     const int lossless = total >= N * ts + 3 + md + 8 + 1;   /* SZ_compress_args_*_StoreOriData, ref: sz_float.c:526-559, trigger :2979 */
     if (lossless) { same = 80; total = lossless_total; }
     hdr[3] = same;
-    convertSZParamsToBytes(confparams_cpr, hdr + 4);
+    convertSZParamsToBytes(CPR(), hdr + 4);
     unsigned char nb8[8]; put_be64(nb8, (uint64_t)N);
     if (to_dev) {
         if (lossless) {
@@ -596,13 +605,13 @@ static int decompress_core(int dataType, const unsigned char *bytes, size_t len,
         return SZ_NSCS;
     }
     const unsigned char same = head[3];
-    exe_params->SZ_SIZE_TYPE = ((same & 0x40) >> 6) == 1 ? 8 : 4;
-    if (exe_params->SZ_SIZE_TYPE != 8) { printf("Error: streams with a 4-byte size type are not supported.\n"); return SZ_NSCS; }
-    confparams_dec->protectValueRange = (same & 0x04) >> 2;
-    convertBytesToSZParams(head + 4, confparams_dec);
-    confparams_dec->szMode = SZ_BEST_SPEED;
-    if (confparams_dec->dataType != dataType) { printf("Error: stream holds dataType %d, caller asked for %d.\n", confparams_dec->dataType, dataType); return SZ_NSCS; }
-    if (confparams_dec->sol_ID != SZ) { printf("Error: unsupported sol_ID %d in stream.\n", confparams_dec->sol_ID); return SZ_NSCS; }
+    EXE()->SZ_SIZE_TYPE = ((same & 0x40) >> 6) == 1 ? 8 : 4;
+    if (EXE()->SZ_SIZE_TYPE != 8) { printf("Error: streams with a 4-byte size type are not supported.\n"); return SZ_NSCS; }
+    DEC()->protectValueRange = (same & 0x04) >> 2;
+    convertBytesToSZParams(head + 4, DEC());
+    DEC()->szMode = SZ_BEST_SPEED;
+    if (DEC()->dataType != dataType) { printf("Error: stream holds dataType %d, caller asked for %d.\n", DEC()->dataType, dataType); return SZ_NSCS; }
+    if (DEC()->sol_ID != SZ) { printf("Error: unsupported sol_ID %d in stream.\n", DEC()->sol_ID); return SZ_NSCS; }
     const size_t Ns = (size_t)get_be64(head + 4 + md);
     if (Ns != N) { printf("Error: stream holds %zu elements, dimensions say %zu.\n", Ns, N); return SZ_DERR; }
     const unsigned char *body = bytes + 4 + md + 8;
@@ -626,9 +635,9 @@ static int decompress_core(int dataType, const unsigned char *bytes, size_t len,
         rc = szb200_decompress_blocked(&job, body, body_len, on_device, d_out, NULL);
     } else { printf("Error: SZ 1.4 (non-regression) streams are not supported by libSZ_b200.\n"); return SZ_NSCS; }
     if (rc != SZ_SCES) { printf("Error: %s\n", szb200_last_error()); return rc; }
-    if (confparams_dec->protectValueRange) {           /* ref: szd_float.c:161-176 */
-        double mn = dataType == SZ_FLOAT ? (double)confparams_dec->fmin : confparams_dec->dmin;
-        double mx = dataType == SZ_FLOAT ? (double)confparams_dec->fmax : confparams_dec->dmax;
+    if (DEC()->protectValueRange) {           /* ref: szd_float.c:161-176 */
+        double mn = dataType == SZ_FLOAT ? (double)DEC()->fmin : DEC()->dmin;
+        double mx = dataType == SZ_FLOAT ? (double)DEC()->fmax : DEC()->dmax;
         rc = szb200_clamp(dataType, d_out, N, mn, mx);
     }
     return rc;
@@ -689,6 +698,94 @@ int szb200_decompress_device(int dataType, const void *d_stream, size_t byteLeng
     filterDimension(r5, r4, r3, r2, r1, r);
     reset_dec_state();
     int rc = decompress_core(dataType, (const unsigned char *)d_stream, byteLength, 1, d_out, r);
+    pthread_mutex_unlock(&g_api_mu);
+    return rc;
+}
+
+/* ---- batches (include/szb200.h) ------------------------------------------------------------------------------------------- */
+typedef struct batch_shared {
+    int dataType, decompress, mode, device;
+    double absb, relb;
+    size_t r[5];
+    szb200_batch_item *items; int n_items;
+    int next;                                   /* guarded by mu */
+    pthread_mutex_t mu;
+    sz_params cpr0; sz_exedata exe0;            /* snapshot of the caller's configuration */
+} batch_shared;
+typedef struct batch_worker { batch_shared *sh; int lane; } batch_worker;
+
+static void *batch_thread(void *arg) {
+    batch_worker *w = (batch_worker *)arg;
+    batch_shared *sh = w->sh;
+    sz_params cpr, dec; sz_exedata exe;
+    if (szb200_set_device(sh->device) != 0 || szb200_set_lane(w->lane) != 0 || szb200_set_device(sh->device) != 0) return NULL;
+    tl_cpr = &cpr; tl_dec = &dec; tl_exe = &exe;
+    for (;;) {
+        pthread_mutex_lock(&sh->mu);
+        const int i = sh->next < sh->n_items ? sh->next++ : -1;
+        pthread_mutex_unlock(&sh->mu);
+        if (i < 0) break;
+        szb200_batch_item *it = &sh->items[i];
+        if (!sh->decompress) {
+            cpr = sh->cpr0; exe = sh->exe0;     /* every item starts from the caller's configuration, like a fresh call */
+            size_t n = 0;
+            it->rc = compress_core(sh->dataType, it->d_data, 1, NULL, it->d_stream, it->stream_capacity, &n, sh->mode, sh->absb, sh->relb, sh->r);
+            it->out_size = n;
+        } else {
+            memset(&dec, 0, sizeof(dec)); memset(&exe, 0, sizeof(exe)); exe.SZ_SIZE_TYPE = 8;      /* == reset_dec_state() */
+            it->rc = decompress_core(sh->dataType, (const unsigned char *)it->d_stream, it->stream_capacity, 1, it->d_out, sh->r);
+        }
+    }
+    tl_cpr = tl_dec = NULL; tl_exe = NULL;
+    szb200_set_lane(0);
+    return NULL;
+}
+
+static int run_batch(batch_shared *sh, int lanes) {
+    if (lanes < 1) lanes = 1;
+    if (lanes > 16) lanes = 16;
+    if (lanes > sh->n_items) lanes = sh->n_items;
+    pthread_t th[16]; batch_worker wk[16];
+    pthread_mutex_init(&sh->mu, NULL);
+    sh->next = 0;
+    int started = 0;
+    for (int k = 0; k < lanes; k++) { wk[k].sh = sh; wk[k].lane = k; if (pthread_create(&th[k], NULL, batch_thread, &wk[k]) != 0) break; started++; }
+    for (int k = 0; k < started; k++) pthread_join(th[k], NULL);
+    pthread_mutex_destroy(&sh->mu);
+    if (started == 0) return SZ_NSCS;
+    int rc = SZ_SCES;
+    for (int i = 0; i < sh->n_items; i++) if (sh->items[i].rc != SZ_SCES) rc = sh->items[i].rc;
+    return sh->next >= sh->n_items ? rc : SZ_NSCS;
+}
+
+int szb200_compress_batch_device(int dataType, szb200_batch_item *items, int n_items, int lanes, int errBoundMode, double absErrBound,
+                                 double relBoundRatio, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
+    if ((dataType != SZ_FLOAT && dataType != SZ_DOUBLE) || !items || n_items <= 0) return SZ_NSCS;
+    batch_shared sh; memset(&sh, 0, sizeof(sh));
+    pthread_mutex_lock(&g_api_mu);
+    lazy_init();
+    sh.cpr0 = *confparams_cpr; sh.exe0 = *exe_params;
+    sh.dataType = dataType; sh.decompress = 0; sh.mode = errBoundMode; sh.absb = absErrBound; sh.relb = relBoundRatio;
+    sh.device = szb200_current_device();
+    filterDimension(r5, r4, r3, r2, r1, sh.r);
+    sh.items = items; sh.n_items = n_items;
+    for (int i = 0; i < n_items; i++) { items[i].rc = SZ_NSCS; items[i].out_size = 0; }
+    const int rc = sh.device < 0 ? SZ_NSCS : run_batch(&sh, lanes);
+    pthread_mutex_unlock(&g_api_mu);
+    return rc;
+}
+
+int szb200_decompress_batch_device(int dataType, szb200_batch_item *items, int n_items, int lanes,
+                                   size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
+    if ((dataType != SZ_FLOAT && dataType != SZ_DOUBLE) || !items || n_items <= 0) return SZ_NSCS;
+    batch_shared sh; memset(&sh, 0, sizeof(sh));
+    pthread_mutex_lock(&g_api_mu);
+    sh.dataType = dataType; sh.decompress = 1;
+    sh.device = szb200_current_device();
+    filterDimension(r5, r4, r3, r2, r1, sh.r);
+    sh.items = items; sh.n_items = n_items;
+    for (int i = 0; i < n_items; i++) items[i].rc = SZ_NSCS;
+    const int rc = sh.device < 0 ? SZ_NSCS : run_batch(&sh, lanes);
     pthread_mutex_unlock(&g_api_mu);
     return rc;
 }

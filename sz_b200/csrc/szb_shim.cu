@@ -105,17 +105,24 @@ struct Ctx {
 static std::mutex g_mu;
 static std::map<int, Ctx *> g_ctx;
 
+// A context (streams + grow-only workspace) exists per (device, lane).  Lane 0 is what every single call uses; the batch entry
+// points give each of their worker threads its own lane, so that the jobs of a batch overlap on the GPU.
+static thread_local int g_lane = 0;
+constexpr int SZB_MAX_LANES = 16;
 static Ctx *ctx() {
     int d = 0;
     if (cudaGetDevice(&d) != cudaSuccess) { set_err("no CUDA device: %s", cudaGetErrorString(cudaGetLastError())); return nullptr; }
     std::lock_guard<std::mutex> lk(g_mu);
-    auto it = g_ctx.find(d);
+    const int key = d * SZB_MAX_LANES + g_lane;
+    auto it = g_ctx.find(key);
     if (it != g_ctx.end()) return it->second;
     Ctx *c = new Ctx();
     if (c->init(d) != 0) { delete c; return nullptr; }
-    g_ctx[d] = c;
+    g_ctx[key] = c;
     return c;
 }
+extern "C" int szb200_set_lane(int lane) { if (lane < 0 || lane >= SZB_MAX_LANES) return SZ_NSCS; g_lane = lane; return 0; }
+extern "C" int szb200_current_device(void) { int d = -1; if (cudaGetDevice(&d) != cudaSuccess) { cudaGetLastError(); return -1; } return d; }
 
 extern "C" int szb200_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
 extern "C" int szb200_set_device(int device) { CU(cudaSetDevice(device)); return ctx() ? 0 : SZ_NSCS; }

@@ -166,6 +166,30 @@ def test_fuzzed_shapes_bit_exact_vs_oracle(sz, orc, seed):
     sz.finalize()
 
 
+def test_batch_of_fields_equals_individual_calls(sz):
+    """BASELINE configs 3 / 4 in miniature: a batch of equally shaped fields on concurrent worker lanes gives, item by item,
+    the stream of the single call (which the other tests pin to the reference), and decodes back bit-exactly."""
+    import torch
+    for shape, dt, mode, ab, rl in (((40, 60, 50), np.float32, szref.ABS, 1e-2, 1e-3), ((200, 360), np.float32, szref.REL, 1e-4, 1e-4),
+                                    ((24, 30, 36), np.float64, szref.ABS_AND_REL, 1e-3, 1e-3)):
+        sz.init(cases.make_cfg(mode, ab, rl, {}))
+        fields = [szref.smooth_field(shape, dt, span=6 * np.pi, field_id=k) for k in range(7)]
+        fields[3] = szref.background_field(shape, dt) if len(shape) == 3 else fields[3]          # a use_mean field inside the batch
+        singles = [sz.compress(a, mode, ab, rl) for a in fields]
+        xs = [torch.from_numpy(a).cuda() for a in fields]
+        cap = sz.compress_bound(dt, shape)
+        outs = [torch.empty(cap, dtype=torch.uint8, device="cuda") for _ in fields]
+        for lanes in (1, 3):
+            sizes = sz.compress_batch_device(xs, outs, mode, ab, rl, lanes=lanes)
+            for k, (n, o) in enumerate(zip(sizes, outs)):
+                assert bytes(o[:n].cpu().numpy()) == singles[k], "batch item %d differs (lanes=%d)" % (k, lanes)
+            recs = [torch.empty_like(x) for x in xs]
+            sz.decompress_batch_device(outs, sizes, recs, lanes=lanes)
+            for k, r in enumerate(recs):
+                assert r.cpu().numpy().tobytes() == sz.decompress(singles[k], dt, shape).tobytes()
+        sz.finalize()
+
+
 def test_device_pointer_api_roundtrip_and_determinism(sz):
     import torch
     a = szref.smooth_field((200, 210, 220), np.float32, span=6 * np.pi)
