@@ -309,7 +309,7 @@ void szo_default_config(szo_config *c)
     memset(c, 0, sizeof(*c));
     c->max_quant_intervals = 65536; c->quantization_intervals = 0; c->sampleDistance = 100; c->predThreshold = 0.99f;
     c->szMode = 0; c->gzipMode = 3; c->protectValueRange = 0; c->sol_ID = 101; c->dataEndianType = 0;
-    c->conf_absErrBound = 1e-4; c->conf_relBoundRatio = 1e-4;
+    c->conf_absErrBound = 1e-4; c->conf_relBoundRatio = 1e-4; c->psnr = 80; c->normErr = 0.05;
 }
 
 int szo_compress(int dtype, const void *data, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1,

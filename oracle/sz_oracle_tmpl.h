@@ -539,6 +539,13 @@ static int FN(compress_args)(const T *x, const size_t *r /* r[0]=r1.. */, int mo
 #else
         double a = absb, b = relb * range; eb_d = (a > b ? a : b);
 #endif
+    } else if (mode == 4) {                        /* PSNR: sz_float.c:2852-2856 + conf.c:54-60; the stream is an ABS stream */
+        double v1 = cfg->psnr + 10 * log10(1 - 2.0 / 3.0 * (double)cfg->predThreshold);
+        double v2 = v1 / (-20);
+        double v3 = pow(10, v2);
+        eb_d = (double)range * v3; mode = SZO_ABS;
+    } else if (mode == 5) {                        /* NORM: sz_float.c:2858-2862 + conf.c:62-65 */
+        eb_d = sqrt(3.0 / N) * cfg->normErr; mode = SZO_ABS;
     } else { return -6; }
     szo_hdr hdr; memset(&hdr, 0, sizeof(hdr));
     hdr.cfg = cfg; hdr.mode = mode; hdr.dtype = IS_FLOAT ? SZO_FLOAT : SZO_DOUBLE;

@@ -108,6 +108,7 @@ def init(cfg=None, path=None):
                 for k in ("withLinearRegression", "protectValueRange", "sampleDistance", "quantization_intervals", "max_quant_intervals", "szMode", "errorBoundMode"):
                     f.write("%s = %s\n" % (k, c[k]))
                 f.write("predThreshold = %r\nabsErrBound = %r\nrelBoundRatio = %r\n" % (c["predThreshold"], float(c["absErrBound"]), float(c["relBoundRatio"])))
+                f.write("psnr = %r\nnormErr = %r\n" % (float(c.get("psnr", 80.0)), float(c.get("normErr", 0.05))))
             rc = L.SZ_Init(p.encode())
         finally:
             os.unlink(p)

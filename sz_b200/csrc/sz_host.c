@@ -421,8 +421,8 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
         *outSize = N * ts;
         return SZ_SCES;
     }
-    if (mode != ABS && mode != REL && mode != ABS_AND_REL && mode != ABS_OR_REL) {
-        printf("Error: libSZ_b200 supports errorBoundMode ABS, REL, ABS_AND_REL and ABS_OR_REL only (got %d).\n", mode);
+    if (mode != ABS && mode != REL && mode != ABS_AND_REL && mode != ABS_OR_REL && mode != PSNR && mode != NORM) {
+        printf("Error: libSZ_b200 supports errorBoundMode ABS, REL, ABS_AND_REL, ABS_OR_REL, PSNR and NORM only (got %d).\n", mode);
         return SZ_BERR;
     }
     if (CPR()->szMode != SZ_BEST_SPEED) {
@@ -451,7 +451,17 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
         CPR()->dmin = vmin; CPR()->dmax = maxr; range_d = range;
     }
     int status = SZ_SCES;
-    double realPrecision = real_precision(dataType, range_d, mode, absb, relb, &status);
+    double realPrecision;
+    if (mode == PSNR) {                                /* ref: sz_float.c:2852-2856, conf.c:54-60: the stream is an ordinary ABS stream */
+        CPR()->errorBoundMode = ABS;
+        const double v1 = CPR()->psnr + 10 * log10(1 - 2.0 / 3.0 * (double)CPR()->predThreshold);
+        const double v2 = v1 / (-20);
+        const double v3 = pow(10, v2);
+        realPrecision = range_d * v3;
+    } else if (mode == NORM) {                         /* ref: sz_float.c:2858-2862, conf.c:62-65 */
+        CPR()->errorBoundMode = ABS;
+        realPrecision = sqrt(3.0 / N) * CPR()->normErr;
+    } else realPrecision = real_precision(dataType, range_d, mode, absb, relb, &status);
     CPR()->absErrBound = realPrecision;
 
     unsigned char hdr[4 + MetaDataByteLength_double + 8 + 8];

@@ -5,7 +5,7 @@ import os
 import numpy as np
 
 import szref
-from szref import ABS, REL, ABS_AND_REL, ABS_OR_REL
+from szref import ABS, REL, ABS_AND_REL, ABS_OR_REL, PSNR, NORM
 
 _DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -69,6 +69,9 @@ for _dt, _tag in ((F32, "f32"), (F64, "f64")):
     add("fixed_itv256_40c_" + _tag, gen(szref.smooth_field, (40, 40, 40), _dt, span=TWO_PI), ABS, 1e-3, 1e-3, quantization_intervals=256)
     add("sd7_40c_" + _tag, gen(szref.smooth_field, (40, 40, 40), _dt, span=TWO_PI), ABS, 1e-3, 1e-3, sampleDistance=7)
     add("protect_40c_" + _tag, gen(szref.smooth_field, (40, 40, 40), _dt, span=TWO_PI), ABS, 1e-3, 1e-3, protectValueRange="YES")
+    add("psnr70_40c_" + _tag, gen(szref.smooth_field, (40, 40, 40), _dt, span=TWO_PI), PSNR, 1e-3, 1e-3, psnr=70.0)
+    add("psnr95_2d_90x120_" + _tag, gen(szref.smooth_field, (90, 120), _dt, span=TWO_PI), PSNR, 1e-3, 1e-3, psnr=95.0)
+    add("norm_40c_" + _tag, gen(szref.smooth_field, (40, 40, 40), _dt, span=TWO_PI), NORM, 1e-3, 1e-3, normErr=0.8)
     add("maxitv1024_40c_" + _tag, gen(szref.random_field, (40, 40, 40), _dt), ABS, 1e-4, 1e-3, max_quant_intervals=1024)
 
 CASE_IDS = [c[0] for c in CASES]

@@ -16,7 +16,8 @@ ORACLE_SO = os.path.join(ROOT, "oracle", "libszoracle.so")
 
 SZ_FLOAT, SZ_DOUBLE = 0, 1
 ABS, REL, ABS_AND_REL, ABS_OR_REL = 0, 1, 2, 3
-MODE_NAMES = {ABS: "ABS", REL: "REL", ABS_AND_REL: "ABS_AND_REL", ABS_OR_REL: "ABS_OR_REL"}
+PSNR, NORM = 4, 5
+MODE_NAMES = {ABS: "ABS", REL: "REL", ABS_AND_REL: "ABS_AND_REL", ABS_OR_REL: "ABS_OR_REL", PSNR: "PSNR", NORM: "NORM"}
 
 
 def have_ref():
@@ -44,7 +45,7 @@ def dims5(shape):
 DEFAULT_CFG = dict(
     max_quant_intervals=65536, quantization_intervals=0, sampleDistance=100, predThreshold=0.99,
     szMode="SZ_BEST_SPEED", protectValueRange="NO", withLinearRegression="YES",
-    errorBoundMode="ABS", absErrBound=1e-4, relBoundRatio=1e-4,
+    errorBoundMode="ABS", absErrBound=1e-4, relBoundRatio=1e-4, psnr=80.0, normErr=0.05,
 )
 
 
@@ -65,7 +66,7 @@ def write_config(path, cfg):
         f.write("errorBoundMode = %s\n" % c["errorBoundMode"])
         f.write("absErrBound = %s\n" % repr(float(c["absErrBound"])))
         f.write("relBoundRatio = %s\n" % repr(float(c["relBoundRatio"])))
-        f.write("psnr = 80\nnormErr = 0.05\npw_relBoundRatio = 1E-2\naccelerate_pw_rel_compression = 1\n")
+        f.write("psnr = %s\nnormErr = %s\npw_relBoundRatio = 1E-2\naccelerate_pw_rel_compression = 1\n" % (repr(float(c["psnr"])), repr(float(c["normErr"]))))
     return c
 
 
@@ -133,7 +134,8 @@ class SZLib:
 class szo_config(C.Structure):
     _fields_ = [("max_quant_intervals", C.c_uint), ("quantization_intervals", C.c_uint), ("sampleDistance", C.c_int),
                 ("predThreshold", C.c_float), ("szMode", C.c_int), ("gzipMode", C.c_int), ("protectValueRange", C.c_int),
-                ("sol_ID", C.c_int), ("dataEndianType", C.c_int), ("conf_absErrBound", C.c_double), ("conf_relBoundRatio", C.c_double)]
+                ("sol_ID", C.c_int), ("dataEndianType", C.c_int), ("conf_absErrBound", C.c_double), ("conf_relBoundRatio", C.c_double),
+                ("psnr", C.c_double), ("normErr", C.c_double)]
 
 
 class szo_trace(C.Structure):
@@ -187,6 +189,8 @@ class Oracle:
         self.cfg.protectValueRange = 1 if c["protectValueRange"] == "YES" else 0
         self.cfg.conf_absErrBound = c["absErrBound"]
         self.cfg.conf_relBoundRatio = c["relBoundRatio"]
+        self.cfg.psnr = c["psnr"]
+        self.cfg.normErr = c["normErr"]
 
     def compress(self, a, mode, abs_eb=0.0, rel=0.0, trace=False):
         a = np.ascontiguousarray(a)
