@@ -188,6 +188,14 @@ unsigned char* SZ_compress_customize_threadsafe(const char* cmprName, void* user
 void* SZ_decompress_customize(const char* appName, void* userPara, int dataType, unsigned char* bytes, size_t byteLength, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1, int* status);
 void* SZ_decompress_customize_threadsafe(const char* cmprName, void* userPara, int dataType, unsigned char* bytes, size_t byteLength, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1, int *status);
 
+/* ---- file helpers used by the reference's example programs (ref: sz/include/rw.h:43-70), implemented in sz_io.c ---- */
+unsigned char *readByteData(char *srcFilePath, size_t *byteLength, int *status);
+double *readDoubleData(char *srcFilePath, size_t *nbEle, int *status);
+float *readFloatData(char *srcFilePath, size_t *nbEle, int *status);
+void writeByteData(unsigned char *bytes, size_t byteLength, char *tgtFilePath, int *status);
+void writeFloatData_inBytes(float *data, size_t nbEle, char *tgtFilePath, int *status);
+void writeDoubleData_inBytes(double *data, size_t nbEle, char *tgtFilePath, int *status);
+
 #ifdef __cplusplus
 }
 #endif

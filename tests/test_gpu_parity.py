@@ -190,6 +190,31 @@ def test_batch_of_fields_equals_individual_calls(sz):
         sz.finalize()
 
 
+_DROPIN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "dropin")
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(_DROPIN, "testfloat_compress")), reason="relinked reference examples (make -C oracle dropin) not present")
+@pytest.mark.parametrize("kind", ["float", "double"])
+def test_reference_example_programs_run_unmodified_on_the_library(sz, tmp_path, kind):
+    """the reference's own example/test{float,double}_{compress,decompress}.c, compiled unmodified and linked
+    against libSZ_b200.so instead of libSZ, write the reference's .sz file and decode it back (digests of the reference)."""
+    import hashlib
+    import shutil
+    import subprocess
+    dat = "test%s_8_8_128.dat" % kind
+    shutil.copy(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", dat), tmp_path / dat)
+    szref.write_config(str(tmp_path / "sz.config"), cases.make_cfg(szref.ABS, 1e-4, 1e-3, {}))
+    gold = GOLD["test%s_8_8_128_abs" % kind] if kind == "float" else GOLD["cfg1_testdouble_8_8_128_abs"]
+    r = subprocess.run([os.path.join(_DROPIN, "test%s_compress" % kind), "sz.config", dat, "8", "8", "128"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "done" in r.stdout, r.stdout + r.stderr
+    stream = (tmp_path / (dat + ".sz")).read_bytes()
+    assert len(stream) == gold["size"] and hashlib.md5(stream).hexdigest() == gold["md5"]
+    r = subprocess.run([os.path.join(_DROPIN, "test%s_decompress" % kind), dat + ".sz", "8", "8", "128"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = (tmp_path / (dat + ".sz.out")).read_bytes()
+    assert hashlib.md5(out).hexdigest() == gold["dec_md5"], r.stdout
+
+
 def test_device_pointer_api_roundtrip_and_determinism(sz):
     import torch
     a = szref.smooth_field((200, 210, 220), np.float32, span=6 * np.pi)
