@@ -692,22 +692,43 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
             if (it < nchunks && lane < ncoef) {
                 const int e = lane, buf = (int)(it % 3u), lb = (int)(it & 1u);
                 const int cnt = (int)min((uint32_t)CH, reg_count - it * CH);
-                ChainStep<T> nxt = s_step[buf][e][0];
-                for (int i = 0; i < cnt; i++) {
-                    const ChainStep<T> st = nxt;
-                    nxt = s_step[buf][e][i + 1];           // fetched while this step computes (slot CH is padding)
-                    s_last[lb][e][i] = last;
-                    const bool in = last >= st.lo && last <= st.hi;
-                    const bool g1 = last > st.thr1, g2 = last > st.thr2;
-                    const T v0 = last + st.d0, v1 = last + st.d1, v2 = last + st.d2;
-                    const T k0 = st.cur - v0, k1 = st.cur - v1, k2 = st.cur - v2;
-                    const T n0 = TT<T>::abs(k0) > precA ? st.cur : v0;
-                    const T n1 = TT<T>::abs(k1) > precA ? st.cur : v1;
-                    const T n2 = TT<T>::abs(k2) > precA ? st.cur : v2;
-                    T nl = g1 ? n1 : n0;
-                    nl = g2 ? n2 : nl;
-                    if (!in) (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
-                    last = nl;
+                // The chunk is first run on the tables alone, without a branch in the step; `allin` records whether every `last`
+                // fell inside its tabulated interval.  If one did not (rare: a table is missing or the slack around the previous
+                // coefficient was not enough) the chunk is run again with the exact formula available at every step.
+                const T last0 = last;
+                bool allin = true;
+                {
+                    ChainStep<T> nxt = s_step[buf][e][0];
+                    for (int i = 0; i < cnt; i++) {
+                        const ChainStep<T> st = nxt;
+                        nxt = s_step[buf][e][i + 1];           // fetched while this step computes (slot CH is padding)
+                        s_last[lb][e][i] = last;
+                        allin = allin && (last >= st.lo) && (last <= st.hi);
+                        const bool g1 = last > st.thr1, g2 = last > st.thr2;
+                        T d = g1 ? st.d1 : st.d0;
+                        d = g2 ? st.d2 : d;
+                        const T v = last + d;
+                        const T k = st.cur - v;
+                        last = TT<T>::abs(k) > precA ? st.cur : v;
+                    }
+                }
+                if (!allin) {
+                    last = last0;
+                    ChainStep<T> nxt = s_step[buf][e][0];
+                    for (int i = 0; i < cnt; i++) {
+                        const ChainStep<T> st = nxt;
+                        nxt = s_step[buf][e][i + 1];
+                        s_last[lb][e][i] = last;
+                        const bool in = last >= st.lo && last <= st.hi;
+                        const bool g1 = last > st.thr1, g2 = last > st.thr2;
+                        T d = g1 ? st.d1 : st.d0;
+                        d = g2 ? st.d2 : d;
+                        const T v = last + d;
+                        const T k = st.cur - v;
+                        T nl = TT<T>::abs(k) > precA ? st.cur : v;
+                        if (!in) (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
+                        last = nl;
+                    }
                 }
                 s_last[lb][e][cnt] = last;
             }
