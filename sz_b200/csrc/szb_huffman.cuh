@@ -218,6 +218,132 @@ __device__ __forceinline__ uint32_t heap_build_tree(const H &h, int hcap, uint32
     return h.ldn(1);
 }
 
+// ---- two-thread form of the same heap (shared-memory case) -----------------------------------------------------------
+// Only the frequencies decide what a sift does; the node ids merely follow.  Thread A (warp 0) therefore runs the sifts on f[]
+// alone and describes each operation to thread B (warp 1, another scheduler) with one queue entry -- for a removal the final
+// position of the moved element (the path is its chain of ancestors), for an insertion the start and final positions -- and B
+// replays the node-id moves on n[] and writes the children of every merged node.  A never reads n[], so the queue is one-way:
+// single producer, single consumer, entries tagged with their sequence number.  This takes the node-id traffic (a quarter of
+// the instructions of a sift level) off the serial thread.
+constexpr int HQ_CAP = 512;                                   // queue entries (one 64-bit word each)
+enum { HQ_REMOVE = 0, HQ_INSERT = 1, HQ_FIN = 2 };
+// entry = [tag:10 | kind:2 | c:18 | b:17 | a:17], written and read with ONE 64-bit shared-memory access (single-copy atomic), so the
+// consumer sees either the old or the new entry, never a mixture, and no fence is needed: nothing else is shared between the
+// two threads.  tag = (sequence number + 1) mod 1024; the ring holds 512 entries, so the entry that occupied a slot one lap
+// earlier differs in the tag, and so does the all-zero initial state for the first lap.
+struct HeapQueue {
+    unsigned int qa;                                          // shared address of the ring
+    unsigned int *done;                                       // consumer progress (generic pointer into shared memory)
+    uint32_t t;                                               // producer: next sequence number
+    __device__ __forceinline__ void push(uint32_t kind, uint32_t a, uint32_t b, uint32_t c) {
+        if ((t & 127u) == 0 && t >= HQ_CAP - 128) {           // back-pressure, checked every 128 entries
+            while (t - *(volatile unsigned int *)done > HQ_CAP - 128) { }
+        }
+        const unsigned long long e = ((unsigned long long)(((t + 1) & 1023u) << 2 | kind) << 52) | ((unsigned long long)c << 34) | ((unsigned long long)b << 17) | a;
+        asm volatile("st.volatile.shared.u64 [%0], %1;" ::"r"(qa + 8u * (t & (HQ_CAP - 1))), "l"(e) : "memory");
+        t++;
+    }
+};
+
+// thread A: frequencies only
+__device__ __forceinline__ void heap2_insert(const HeapSmem &h, HeapQueue &Q, int &qend, uint32_t freq, uint32_t node) {
+    const int q0 = qend++;
+    int i = q0, j;
+    while ((j = i >> 1)) {
+        const uint32_t fj = h.ldf(j);
+        if (fj <= freq) break;
+        h.stf(i, fj); i = j;
+    }
+    h.stf(i, freq);
+    Q.push(HQ_INSERT, (uint32_t)q0, (uint32_t)i, node);
+}
+__device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, HeapQueue &Q, int &qend, int cap, uint32_t out_code) {
+    const uint32_t topf = h.ldf(1);
+    qend--;
+    const uint32_t mf = h.ldf(qend);
+    h.stf(qend, HEAP_FINF);
+    if (qend == 1) { Q.push(HQ_REMOVE, 0u, 1u, out_code); return topf; }
+    const int lim = cap >> 1;
+    const int qmax = cap - 4;
+    int i = 1;
+    uint2 pr = h.ldf2(2);
+    uint4 qa = h.ldf4(4), qb;
+#define SZB_SIFT2_LEVEL(QCUR, QNEXT)                                                       \
+    {                                                                                      \
+        const bool r = pr.y < pr.x;                                                        \
+        const uint32_t fc = min(pr.x, pr.y);                                               \
+        if (!(mf > fc)) break;                                                             \
+        h.stf(i, fc);                                                                      \
+        i = 2 * i + (r ? 1 : 0);                                                           \
+        pr = r ? make_uint2(QCUR.z, QCUR.w) : make_uint2(QCUR.x, QCUR.y);                  \
+        if (i >= lim) pr = make_uint2(HEAP_FINF, HEAP_FINF);                               \
+        QNEXT = h.ldf4(min(4 * i, qmax));                                                  \
+    }
+    for (;;) {
+        SZB_SIFT2_LEVEL(qa, qb)
+        SZB_SIFT2_LEVEL(qb, qa)
+    }
+#undef SZB_SIFT2_LEVEL
+    h.stf(i, mf);
+    Q.push(HQ_REMOVE, (uint32_t)i, (uint32_t)qend, out_code);
+    return topf;
+}
+__device__ __forceinline__ void heap2_thread_a(const HeapSmem &h, HeapQueue &Q, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
+    int qend = 1;
+    uint32_t k = 0;
+    for (; k + 4 <= leaves; k += 4) {
+        uint32_t f0 = lfreq[k], f1 = lfreq[k + 1], f2 = lfreq[k + 2], f3 = lfreq[k + 3];
+        heap2_insert(h, Q, qend, f0, k); heap2_insert(h, Q, qend, f1, k + 1); heap2_insert(h, Q, qend, f2, k + 2); heap2_insert(h, Q, qend, f3, k + 3);
+    }
+    for (; k < leaves; k++) heap2_insert(h, Q, qend, lfreq[k], k);
+    D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
+    uint32_t nn = leaves;
+    while (qend > 2) {
+        const uint32_t fb = heap2_remove(h, Q, qend, hcap, (nn << 1) | 1u);   // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+        const uint32_t fa = heap2_remove(h, Q, qend, hcap, (nn << 1) | 0u);   // second removed -> left
+        heap2_insert(h, Q, qend, fa + fb, nn);
+        nn++;
+    }
+    Q.push(HQ_FIN, 0u, 0u, 0u);
+    D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
+}
+// thread B: node ids.  Returns the root node.
+__device__ __forceinline__ uint32_t heap2_thread_b(const HeapSmem &h, unsigned int qaddr, unsigned int *done, const HuffTreeDesc &D) {
+    for (uint32_t t = 0;; t++) {
+        const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
+        unsigned long long e;
+        do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 54) != ((t + 1) & 1023u));
+        const uint32_t kind = (uint32_t)(e >> 52) & 3u;
+        const uint32_t a = (uint32_t)e & 0x1ffffu, b = (uint32_t)(e >> 17) & 0x1ffffu, c = (uint32_t)(e >> 34) & 0x3ffffu;
+        if (kind == HQ_FIN) break;
+        if (kind == HQ_REMOVE) {
+            // a = final position of the moved element (0: the heap became empty), b = position it was taken from
+            const uint32_t topn = h.ldn(1);
+            if (c & 1u) D.n_right[c >> 1] = topn; else D.n_left[c >> 1] = topn;
+            if (a != 0) {
+                const uint32_t mn = h.ldn((int)b);
+                const int depth = 31 - __clz(a);
+                // the path is the chain of ancestors of a; every node moves up one level, top-down (each source is still intact)
+                uint32_t v = depth > 0 ? h.ldn((int)(a >> (depth - 1))) : 0u;
+                for (int j = 1; j <= depth; j++) {
+                    const uint32_t src = a >> (depth - j);
+                    const uint32_t vn = (j < depth) ? h.ldn((int)(a >> (depth - j - 1))) : 0u;      // next source, fetched before the store
+                    h.stn((int)(src >> 1), v);
+                    v = vn;
+                }
+                h.stn((int)a, mn);
+            }
+        } else {
+            // insertion: a = position appended at, b = final position, c = node id; ancestors move down one level, bottom-up
+            uint32_t pos = a;
+            while (pos != b) { h.stn((int)pos, h.ldn((int)(pos >> 1))); pos >>= 1; }
+            h.stn((int)b, c);
+        }
+        if ((t & 63u) == 63u) *(volatile unsigned int *)done = t + 1;
+    }
+    return h.ldn(1);
+}
+
 constexpr int HUFF_TB = 256;
 __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
     extern __shared__ __align__(16) uint32_t s_heap[];          // f[cap] then n[cap]
@@ -253,18 +379,25 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     {
         // two inlined copies of the heap loop, so that the shared-memory one compiles to LDS/STS with 32-bit addresses instead
         // of generic loads (a pointer that may be shared OR global forces the slower generic path)
-        const int scap = (int)(smem_heap_capacity & ~3u);      // entries per array (multiple of 4: 128-bit loads stay aligned)
+        // shared memory: f[scap], n[scap], then the queue of the two-thread form
+        const int scap = (int)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 8u) & ~3u);      // entries per array (multiple of 4: 128-bit loads stay aligned)
         const bool in_smem = leaves + 8 <= (uint32_t)scap;
+        __shared__ unsigned int s_qdone;
         if (in_smem) {
+            uint32_t *s_queue = s_heap + 2 * scap;
             for (int q = t; q < scap; q += blockDim.x) s_heap[q] = HEAP_FINF;
+            for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
+            if (t == 0) s_qdone = 0u;
             __syncthreads();
-            if (t == 0) {
+            if (t == 0 || t == 32) {
                 // the addresses pass through an opaque asm so that the compiler keeps them in registers instead of
                 // re-deriving the shared window base (S2R + LEA) at every use inside the sift loops
                 HeapSmem h;
-                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * (unsigned)scap;
-                asm volatile("mov.u32 %0, %2;\n\tmov.u32 %1, %3;" : "=r"(h.fa), "=r"(h.na) : "r"(fa0), "r"(na0));
-                s_root = heap_build_tree(h, scap, leaves, lfreq, D, tk1);
+                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * (unsigned)scap, qa0 = na0 + 4u * (unsigned)scap;
+                unsigned int qaddr;
+                asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
+                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a(h, Q, scap, leaves, lfreq, D, tk1); }
+                else s_root = heap2_thread_b(h, qaddr, &s_qdone, D);
             }
         } else {
             uint32_t *hg = reinterpret_cast<uint32_t *>(D.heap_g);       // capacity 64-bit words = two 32-bit arrays of that length
