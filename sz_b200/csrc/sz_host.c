@@ -33,6 +33,19 @@ static void *host_alloc_result(size_t n) {
     }
     return malloc(n ? n : 1);
 }
+/* The result buffer of the host-pointer compress call is allocated BEFORE the GPU work, from the size of the previous stream,
+ * and a helper thread touches its pages while the GPU is busy; the final copy then lands on resident pages.  A wrong guess
+ * only costs a second allocation. */
+typedef struct prefault_job { unsigned char *p; size_t n; } prefault_job;
+static void *prefault_thread(void *arg) {
+    prefault_job *j = (prefault_job *)arg;
+#ifdef MADV_POPULATE_WRITE
+    if (madvise(j->p, j->n, MADV_POPULATE_WRITE) == 0) return NULL;
+#endif
+    for (size_t o = 0; o < j->n; o += 4096) ((volatile unsigned char *)j->p)[o] = 0;
+    return NULL;
+}
+static size_t g_last_stream_bytes = 0;                /* guarded by g_api_mu like the rest of the global state */
 static double now_ms(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1e3 + t.tv_nsec * 1e-6; }
 #include <stdio.h>
 #include <stdlib.h>
@@ -505,9 +518,20 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     size_t body = 0;
     szb200_stats st;
     const double hp1 = hprof ? now_ms() : 0.0;
+    /* host destination: guess the size, allocate and pre-fault while the GPU works */
+    unsigned char *early = NULL; size_t early_cap = 0; pthread_t pf_thread; int pf_started = 0; prefault_job pf;
+    if (!to_dev && tl_cpr == NULL) {
+        size_t guess = g_last_stream_bytes ? g_last_stream_bytes + g_last_stream_bytes / 4 : N * ts / 12;
+        if (guess > lossless_total) guess = lossless_total;
+        if (guess >= ((size_t)4 << 20)) {
+            early = (unsigned char *)host_alloc_result(guess);
+            if (early) { early_cap = guess; pf.p = early; pf.n = guess; pf_started = pthread_create(&pf_thread, NULL, prefault_thread, &pf) == 0; }
+        }
+    }
     int rc = szb200_compress_blocked(&job, d_in, out + 4 + md, 1, cap - 4 - md, &body, &st);
+    if (pf_started) pthread_join(pf_thread, NULL);
     const double hp2 = hprof ? now_ms() : 0.0;
-    if (rc != SZ_SCES) { printf("Error: %s\n", szb200_last_error()); return rc; }
+    if (rc != SZ_SCES) { printf("Error: %s\n", szb200_last_error()); free(early); return rc; }
     if (EXE()->optQuantMode == 1) { EXE()->intvCapacity = (int)st.intervals; EXE()->intvRadius = (int)st.intervals / 2; }   /* side effect of the reference (sz_float.c:6651) */
     size_t total = 4 + md + body;
     unsigned char same = 0x80 | 0x40;                   /* initRandomAccessBytes, ref: dataCompression.c:686-709 */
@@ -525,8 +549,10 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
         if (szb200_copy(out, hdr, 4 + md, 0)) return SZ_NSCS;
     } else {
         /* the stream was assembled in device memory; the host result is allocated at its exact size and filled by ONE copy */
-        unsigned char *h = (unsigned char *)host_alloc_result(total);
+        unsigned char *h = NULL;
+        if (early && total <= early_cap) { h = early; early = NULL; } else { free(early); early = NULL; h = (unsigned char *)host_alloc_result(total); }
         if (!h) return SZ_NSCS;
+        g_last_stream_bytes = total;
         memcpy(h, hdr, 4 + md);
         if (lossless) {
             memcpy(h + 4 + md, nb8, 8);
