@@ -315,3 +315,16 @@ def poly_field(shape, dtype=np.float32, order=2):
     i = np.arange(n, dtype=np.float64) / n
     f = sum(((-1) ** k) * (k + 1) * i ** k for k in range(order + 1))
     return np.ascontiguousarray(f.reshape(shape).astype(dtype))
+
+
+def blocky_field(n, dtype, seed=7):
+    """n^3 field (n a multiple of 6) that is an independent random plane inside every 6^3 block: every block is a regression
+    block and the quantised coefficients are spread over tens of thousands of distinct codes -- the case in which the four
+    coefficient Huffman trees are as large as they get."""
+    rng = np.random.RandomState(seed)
+    nb = n // 6
+    A, B, Cc, D = [rng.uniform(-1, 1, size=(nb, nb, nb)) for _ in range(4)]
+    ii = np.arange(n) % 6
+    up = lambda X: np.repeat(np.repeat(np.repeat(X, 6, 0), 6, 1), 6, 2)
+    f = up(A) * ii[:, None, None] + up(B) * ii[None, :, None] + up(Cc) * ii[None, None, :] + 10 * up(D)
+    return np.ascontiguousarray(f.astype(dtype))

@@ -104,6 +104,9 @@ BIG = [
     ("odd_f32_4d_7x33x41x59_abs", lambda: szref.smooth_field((7, 33, 41, 59), np.float32, span=4 * np.pi), szref.ABS, 1e-3, 1e-3),
     ("odd_f64_2d_611x1031_rel", lambda: szref.smooth_field((611, 1031), np.float64, span=10 * np.pi), szref.REL, 1e-4, 1e-5),
     ("thin_f32_2d_5000x37_abs", lambda: szref.smooth_field((5000, 37), np.float32, span=40 * np.pi), szref.ABS, 1e-3, 1e-3),
+    # coefficient Huffman trees with 30-40 thousand leaves each (beyond the shared-memory heap)
+    ("blocky_240c_f32_huge_coefficient_trees", lambda: szref.blocky_field(240, np.float32), szref.ABS, 1e-2, 1e-3),
+    ("blocky_210c_f64_large_coefficient_trees", lambda: szref.blocky_field(210, np.float64, seed=11), szref.ABS, 1e-2, 1e-3),
     ("noisy_f32_90x100x110_rel", lambda: (szref.smooth_field((90, 100, 110), np.float32, span=4 * np.pi)
                                           + 0.02 * szref.random_field((90, 100, 110), np.float32)).astype(np.float32), szref.REL, 1e-4, 1e-3),
 ]
