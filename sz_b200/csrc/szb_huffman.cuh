@@ -344,6 +344,48 @@ __device__ __forceinline__ uint32_t heap2_thread_b(const HeapSmem &h, unsigned i
     return h.ldn(1);
 }
 
+// the node-id side for trees whose two arrays do not both fit into shared memory: f[] keeps all of it (up to ~54 k entries)
+// and n[] lives in global memory.  One WARP replays each operation: every lane fetches one node of the ancestor chain (all the
+// loads of an operation are in flight together: one L2 round trip), the warp synchronises, every lane stores its value one
+// level up.  Returns the root node (lane 0).
+__device__ __forceinline__ uint32_t heap2_warp_b_global(uint32_t *ng, unsigned int qaddr, unsigned int *done, const HuffTreeDesc &D) {
+    const int lane = threadIdx.x & 31;
+    for (uint32_t t = 0;; t++) {
+        unsigned long long e = 0;
+        if (lane == 0) {
+            const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
+            do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 54) != ((t + 1) & 1023u));
+        }
+        e = __shfl_sync(0xffffffffu, e, 0);
+        const uint32_t kind = (uint32_t)(e >> 52) & 3u;
+        const uint32_t a = (uint32_t)e & 0x1ffffu, b = (uint32_t)(e >> 17) & 0x1ffffu, c = (uint32_t)(e >> 34) & 0x3ffffu;
+        if (kind == HQ_FIN) break;
+        if (kind == HQ_REMOVE) {
+            const int depth = a ? 31 - __clz(a) : 0;
+            uint32_t v = 0;
+            if (lane == 0) v = __ldcg(ng + 1);                                           // the removed root
+            else if (a != 0 && lane <= depth) v = __ldcg(ng + (a >> (depth - lane)));    // path node p_lane
+            else if (a != 0 && lane == 31) v = __ldcg(ng + b);                           // the element that was taken from the end
+            __syncwarp();
+            if (lane == 0) { if (c & 1u) D.n_right[c >> 1] = v; else D.n_left[c >> 1] = v; }
+            else if (a != 0 && lane <= depth) ng[(a >> (depth - lane)) >> 1] = v;        // p_lane moves up to p_(lane-1)
+            else if (a != 0 && lane == 31) ng[a] = v;
+            __syncwarp();
+        } else {
+            const int k = (31 - __clz(a)) - (31 - __clz(b));                             // ancestors that move down
+            uint32_t v = 0;
+            if (lane < k) v = __ldcg(ng + (a >> (lane + 1)));
+            __syncwarp();
+            if (lane < k) ng[a >> lane] = v;
+            else if (lane == 31) ng[b] = c;
+            __syncwarp();
+        }
+        if (lane == 0 && (t & 63u) == 63u) *(volatile unsigned int *)done = t + 1;
+    }
+    __syncwarp();
+    return __ldcg(ng + 1);
+}
+
 constexpr int HUFF_TB = 256;
 __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
     extern __shared__ __align__(16) uint32_t s_heap[];          // f[cap] then n[cap]
@@ -398,6 +440,23 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
                 asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
                 if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a(h, Q, scap, leaves, lfreq, D, tk1); }
                 else s_root = heap2_thread_b(h, qaddr, &s_qdone, D);
+            }
+        } else if (leaves + 8 <= (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u)) {
+            // f[] alone fills the shared memory, n[] lives in global memory and is maintained by warp 1
+            const int fcap = (int)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u);
+            uint32_t *s_queue = s_heap + fcap;
+            for (int q = t; q < fcap; q += blockDim.x) s_heap[q] = HEAP_FINF;
+            for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
+            if (t == 0) s_qdone = 0u;
+            __syncthreads();
+            if (t == 0 || (t >= 32 && t < 64)) {
+                HeapSmem h;
+                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), qa0 = fa0 + 4u * (unsigned)fcap;
+                unsigned int qaddr;
+                asm volatile("mov.u32 %0, %2;\n\tmov.u32 %1, %3;" : "=r"(h.fa), "=r"(qaddr) : "r"(fa0), "r"(qa0));
+                h.na = 0;
+                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a(h, Q, fcap, leaves, lfreq, D, tk1); }
+                else { const uint32_t root = heap2_warp_b_global(reinterpret_cast<uint32_t *>(D.heap_g), qaddr, &s_qdone, D); if (t == 32) s_root = root; }
             }
         } else {
             uint32_t *hg = reinterpret_cast<uint32_t *>(D.heap_g);       // capacity 64-bit words = two 32-bit arrays of that length
