@@ -717,6 +717,85 @@ __device__ __forceinline__ uint32_t dec_symbol(BitReader &br, const uint32_t *s_
     return tr.C[node];
 }
 
+// ---- D1: walk the section headers of a stream body on the device (SURVEY Appendix A from the block_size field on; ref:
+// TightDataPointStorageF.c:54-126, szd_float.c:5750-5800) so that the host needs ONE small read-back instead of a dozen
+// synchronous ones.  All multi-byte fields are read bytewise (the sections are not aligned).
+struct DecHead {
+    uint32_t err;                     // 0 ok, 1 truncated, 2 unsupported field
+    uint32_t block_size, intervals, tree_size, node_count, use_mean, reg_count;
+    unsigned long long eb_bits, mean_bits;                       // raw bits of the T-typed fields (big-endian decoded / native)
+    unsigned long long o_tree, o_ind, o_unp, o_bits, total_unpred;
+    unsigned long long prec_bits[4], o_ctree[4], o_cbits[4], o_cunp[4], cbits_bytes[4];
+    uint32_t crad[4], ctree_size[4], cnode[4], cunp_cnt[4];
+};
+__device__ __forceinline__ unsigned long long rd_be(const unsigned char *b, int n) { unsigned long long v = 0; for (int i = 0; i < n; i++) v = (v << 8) | b[i]; return v; }
+__device__ __forceinline__ unsigned long long rd_le(const unsigned char *b, int n) { unsigned long long v = 0; for (int i = n - 1; i >= 0; i--) v = (v << 8) | b[i]; return v; }
+__global__ void __launch_bounds__(256) dec_parse_kernel(const unsigned char *__restrict__ body, unsigned long long body_len, int tsize /*sizeof(T)*/,
+                                                        int ncoef, uint32_t nb, DecHead *out) {
+    __shared__ DecHead H;
+    __shared__ uint32_t s_cnt[8];
+    const int t = threadIdx.x;
+    unsigned long long o = 0;
+    if (t == 0) {
+        memset(&H, 0, sizeof(H));
+        if (o + 4 + tsize + 12 > body_len) H.err = 1;
+        else {
+            H.block_size = (uint32_t)rd_be(body, 4); H.eb_bits = rd_be(body + 4, tsize); H.intervals = (uint32_t)rd_be(body + 4 + tsize, 4);
+            H.tree_size = (uint32_t)rd_be(body + 8 + tsize, 4); H.node_count = (uint32_t)rd_be(body + 12 + tsize, 4);
+            o = 4 + tsize + 12;
+            H.o_tree = o; o += H.tree_size;
+            const unsigned long long ind_bytes = (nb - 1) / 8 + 1;
+            if (o + 1 + tsize + ind_bytes > body_len) H.err = 1;
+            else { H.use_mean = body[o]; H.mean_bits = rd_le(body + o + 1, tsize); H.o_ind = o + 1 + tsize; }
+        }
+    }
+    __syncthreads();
+    if (H.err) { if (t == 0) *out = H; return; }
+    // regression blocks = zero bits of the indicator (MSB-first; the pad bits of the last byte do not count)
+    uint32_t zeros = 0;
+    const unsigned char *ib = body + H.o_ind;
+    for (uint32_t byte = t; byte < (nb + 7) / 8; byte += blockDim.x) {
+        unsigned int v = ib[byte];
+        const uint32_t valid = min(8u, nb - byte * 8u);
+        v >>= (8 - valid);                                   // keep the `valid` leading bits
+        zeros += valid - __popc(v);
+    }
+    for (int d = 16; d > 0; d >>= 1) zeros += __shfl_down_sync(0xffffffffu, zeros, d);
+    if ((t & 31) == 0) s_cnt[t >> 5] = zeros;
+    __syncthreads();
+    if (t == 0) {
+        uint32_t rc = 0; for (int w = 0; w < 8; w++) rc += s_cnt[w];
+        H.reg_count = rc;
+        o = H.o_ind + ((nb - 1) / 8 + 1);
+        if (rc > 0) {
+            for (int e = 0; e < ncoef && !H.err; e++) {
+                if (o + tsize + 12 > body_len) { H.err = 1; break; }
+                H.prec_bits[e] = rd_be(body + o, tsize); H.crad[e] = (uint32_t)rd_be(body + o + tsize, 4);
+                H.ctree_size[e] = (uint32_t)rd_be(body + o + tsize + 4, 4); H.cnode[e] = (uint32_t)rd_be(body + o + tsize + 8, 4);
+                o += tsize + 12;
+                H.o_ctree[e] = o; o += H.ctree_size[e];
+                if (o + 8 > body_len) { H.err = 1; break; }
+                H.cbits_bytes[e] = rd_be(body + o, 8); o += 8;
+                H.o_cbits[e] = o; o += H.cbits_bytes[e];
+                if (o + 4 > body_len || o < H.o_cbits[e]) { H.err = 1; break; }
+                H.cunp_cnt[e] = (uint32_t)rd_be(body + o, 4); o += 4;
+                H.o_cunp[e] = o; o += (unsigned long long)H.cunp_cnt[e] * tsize;
+            }
+        }
+        if (!H.err) {
+            if (o + 8 > body_len) H.err = 1;
+            else {
+                H.total_unpred = rd_le(body + o, 8); o += 8;
+                H.o_unp = o;
+                if (H.total_unpred > body_len) H.err = 1; else o += H.total_unpred * tsize;
+                if (o > body_len) H.err = 1;
+                H.o_bits = o;
+            }
+        }
+        *out = H;
+    }
+}
+
 // one GLOBAL Jacobi round.  start_used[s] = start position used by the most recent decode of sub-sequence s.
 // Inside the round every CTA iterates over its own 256 consecutive sub-sequences until none of them moves any more (the end
 // positions travel through shared memory), so a correction entering a CTA is propagated as far as it goes within ONE launch;

@@ -828,63 +828,35 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     // ---- device copy of the body (aligned), host copy of its parseable head ----
     unsigned char *d_body = (unsigned char *)c.get("dec_body", body_len + 256); if (!d_body) return SZ_NSCS;
     CU(cudaMemcpyAsync(d_body, body, body_len, body_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c.stream));
-    // the small header fields are parsed on the host; for a device-resident stream only those few bytes are fetched
-    // (a handful of short D2H reads), never the big sections
-    std::vector<unsigned char> scratch;
-    bool fetch_failed = false;
-    auto fetch = [&](size_t off, size_t len) -> const unsigned char * {
-        if (off + len > body_len) { fetch_failed = true; static const unsigned char zeros[64] = {0}; scratch.assign(len + 64, 0); (void)zeros; return scratch.data(); }
-        if (!body_on_device) return (const unsigned char *)body + off;
-        scratch.resize(len + 16);
-        if (cudaMemcpyAsync(scratch.data(), d_body + off, len, cudaMemcpyDeviceToHost, c.stream) != cudaSuccess || cudaStreamSynchronize(c.stream) != cudaSuccess) fetch_failed = true;
-        return scratch.data();
-    };
-    size_t o = 0;
-    const unsigned char *hp = fetch(o, 4 + sizeof(T) + 12);
-    if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
-    const uint32_t B = get_be32(hp);
-    if (B != (uint32_t)(job.dim == 3 ? 6 : 16)) { set_err("unexpected block size %u in stream", B); return SZ_NSCS; }
-    const T eb = get_beT<T>(hp + 4);
-    const uint32_t intervals = get_be32(hp + 4 + sizeof(T));
-    const uint32_t tree_size = get_be32(hp + 8 + sizeof(T));
-    const uint32_t nodeCount = get_be32(hp + 12 + sizeof(T));
-    o += 4 + sizeof(T) + 12;
+    // the section headers are walked on the device (dec_parse_kernel); the host reads the result back once
+    DecHead *d_head = (DecHead *)c.get("dec_head", sizeof(DecHead) + 64); if (!d_head) return SZ_NSCS;
+    dec_parse_kernel<<<1, 256, 0, c.stream>>>(d_body, (unsigned long long)body_len, (int)sizeof(T), ncoef, nb, d_head); KCHECK();
+    DecHead H;
+    CU(cudaMemcpyAsync(&H, d_head, sizeof(H), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    if (H.err) { set_err(H.err == 1 ? "truncated stream" : "unsupported stream"); return SZ_NSCS; }
+    if (H.block_size != (uint32_t)(job.dim == 3 ? 6 : 16)) { set_err("unexpected block size %u in stream", H.block_size); return SZ_NSCS; }
+    auto bitsT = [](unsigned long long b) -> T { T v; if (sizeof(T) == 4) { uint32_t u = (uint32_t)b; memcpy(&v, &u, 4); } else memcpy(&v, &b, 8); return v; };
+    const T eb = bitsT(H.eb_bits);
+    const uint32_t intervals = H.intervals, tree_size = H.tree_size, nodeCount = H.node_count;
     if (intervals > 65536 || nodeCount == 0 || nodeCount > 2 * 65536) { set_err("unsupported stream: intervals=%u nodeCount=%u", intervals, nodeCount); return SZ_NSCS; }
-    const size_t o_tree = o; o += tree_size;
-    const size_t ind_bytes = (nb - 1) / 8 + 1;
-    hp = fetch(o, 1 + sizeof(T) + ind_bytes);
-    if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
-    const int use_mean = hp[0];
-    T mean; memcpy(&mean, hp + 1, sizeof(T));
-    const size_t o_ind = o + 1 + sizeof(T);
-    uint32_t reg_count = 0;
-    { const unsigned char *ib = hp + 1 + sizeof(T); for (uint32_t b = 0; b < nb; b++) if (!((ib[b >> 3] >> (7 - (b & 7))) & 1)) reg_count++; }
-    o = o_ind + ind_bytes;
-    T prec[4] = {0, 0, 0, 0}; int crad[4] = {0, 0, 0, 0}; size_t o_ctree[4], o_cbits[4], o_cunp[4]; uint32_t cnode[4], ctree_size[4], cunp_cnt[4]; uint64_t cbits_bytes[4];
+    const size_t o_tree = (size_t)H.o_tree, o_ind = (size_t)H.o_ind;
+    const int use_mean = (int)H.use_mean;
+    const T mean = bitsT(H.mean_bits);
+    const uint32_t reg_count = H.reg_count;
+    T prec[4] = {0, 0, 0, 0}; int crad[4] = {0, 0, 0, 0}; size_t o_ctree[4] = {0, 0, 0, 0}, o_cbits[4] = {0, 0, 0, 0}, o_cunp[4] = {0, 0, 0, 0};
+    uint32_t cnode[4] = {0, 0, 0, 0}, cunp_cnt[4] = {0, 0, 0, 0}; uint64_t cbits_bytes[4] = {0, 0, 0, 0};
     if (reg_count > 0) {
         for (int e = 0; e < ncoef; e++) {
-            hp = fetch(o, sizeof(T) + 12);
-            if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
-            prec[e] = get_beT<T>(hp); crad[e] = (int)get_be32(hp + sizeof(T)); ctree_size[e] = get_be32(hp + sizeof(T) + 4); cnode[e] = get_be32(hp + sizeof(T) + 8);
-            o += sizeof(T) + 12;
-            o_ctree[e] = o; o += ctree_size[e];
-            hp = fetch(o, 8);
-            if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
-            cbits_bytes[e] = get_be64(hp); o += 8;
-            o_cbits[e] = o; o += cbits_bytes[e];
-            hp = fetch(o, 4);
-            if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
-            cunp_cnt[e] = get_be32(hp); o += 4;
-            o_cunp[e] = o; o += (size_t)cunp_cnt[e] * sizeof(T);
+            prec[e] = bitsT(H.prec_bits[e]); crad[e] = (int)H.crad[e]; cnode[e] = H.cnode[e]; cunp_cnt[e] = H.cunp_cnt[e]; cbits_bytes[e] = H.cbits_bytes[e];
+            o_ctree[e] = (size_t)H.o_ctree[e]; o_cbits[e] = (size_t)H.o_cbits[e]; o_cunp[e] = (size_t)H.o_cunp[e];
             if (crad[e] != 32768 || cnode[e] == 0 || cnode[e] > 2 * 65536) { set_err("unsupported coefficient section"); return SZ_NSCS; }
         }
     }
-    hp = fetch(o, 8);
-    if (fetch_failed) { set_err("truncated stream"); return SZ_NSCS; }
-    uint64_t total_unpred; memcpy(&total_unpred, hp, 8); o += 8;
-    const size_t o_unp = o; o += total_unpred * sizeof(T);
-    if (o > body_len) { set_err("truncated stream"); return SZ_NSCS; }
-    const size_t o_bits = o; const uint64_t main_bytes = body_len - o;
+    const uint64_t total_unpred = H.total_unpred;
+    const size_t o_unp = (size_t)H.o_unp, o_bits = (size_t)H.o_bits;
+    const uint64_t main_bytes = body_len - o_bits;
+    (void)tree_size;
     if (mark(ST_PARSE)) return SZ_NSCS;
 
     // ---- aligned copies of the T-typed sections ----
