@@ -801,15 +801,36 @@ __global__ void __launch_bounds__(256) dec_parse_kernel(const unsigned char *__r
 // positions travel through shared memory), so a correction entering a CTA is propagated as far as it goes within ONE launch;
 // global rounds are only needed to carry corrections across CTA boundaries -- a handful instead of dozens.
 // *changed is raised when the end of a CTA's last sub-sequence differs from what the next CTA saw in the previous round.
-__global__ void __launch_bounds__(256) dec_sync_kernel(const uint32_t *__restrict__ words, uint64_t total_bits, uint64_t nsub, DecTree tr,
-                                                       const unsigned long long *__restrict__ end_prev, unsigned long long *end_cur,
-                                                       unsigned long long *start_used, uint32_t *count, uint32_t *zcount,
-                                                       int first_round, unsigned int *changed) {
+// All streams of one decompression (the main code stream and up to four coefficient streams) are synchronised by ONE launch
+// per global round: a CTA finds its job from its block index.  (The coefficient streams are a few CTAs each with deep trees;
+// launched one after the other they cost more than the main stream.)
+struct DecJobDev {
+    const uint32_t *words; uint64_t total_bits, nsub; DecTree tr;
+    const unsigned long long *end_prev; unsigned long long *end_cur, *start_used; uint32_t *count, *zcount;
+    unsigned int *changed; uint32_t cta_begin, active;
+};
+constexpr int DEC_MAX_JOBS = 5;
+struct DecJobList { DecJobDev j[DEC_MAX_JOBS]; int n; };
+__global__ void __launch_bounds__(256) dec_sync_kernel(const DecJobList *__restrict__ list, int first_round) {
+    int jid = 0;
+    for (int q = 1; q < list->n; q++) if (blockIdx.x >= list->j[q].cta_begin) jid = q;
+    const DecJobDev &J = list->j[jid];
+    if (!J.active) return;
+    const uint32_t *__restrict__ words = J.words; const uint64_t total_bits = J.total_bits, nsub = J.nsub; const DecTree tr = J.tr;
+    const unsigned long long *__restrict__ end_prev = J.end_prev; unsigned long long *end_cur = J.end_cur, *start_used = J.start_used;
+    uint32_t *count = J.count, *zcount = J.zcount; unsigned int *changed = J.changed;
+    const uint32_t block = blockIdx.x - J.cta_begin;
+    // A re-decode from a corrected start usually falls back onto the code-word boundaries of the previous decode after a few
+    // symbols (self-synchronisation).  Every thread therefore keeps, for the 256 bit positions of its sub-sequence, one mask
+    // of the symbol starts of its latest decode and one of the starts of zero symbols (shared memory).  A re-decode stops at the
+    // first position whose old bit is set: from there on everything is known, and the counts follow from the masks.  The masks
+    // only live inside one launch; a thread's first decode in a launch always runs to the end.
     __shared__ uint32_t s_lut[1 << DEC_K];
     __shared__ unsigned long long s_end[256];
+    __shared__ uint32_t s_bm[256][9], s_zm[256][9];            // 8 words + 1 of padding (bank spread)
     for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
     const int tid = threadIdx.x;
-    const uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + tid;
+    const uint64_t sidx = (uint64_t)block * blockDim.x + tid;
     const bool active = sidx < nsub;
     const uint64_t lo = sidx * DEC_SUB_BITS;
     uint64_t hi = lo + DEC_SUB_BITS;
@@ -821,7 +842,8 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const uint32_t *__restric
     // start handed in from the previous CTA: its last end of the previous global round (nothing is known in the first round)
     const unsigned long long ext_start = (sidx == 0) ? 0ull : ((first_round || !active) ? lo : end_prev[sidx - 1]);
     uint32_t cnt = 0, zc = 0;
-    bool wrote = false;
+    bool wrote = false, have_mask = false;
+    uint32_t *bm = s_bm[tid], *zm = s_zm[tid];
     s_end[tid] = my_end;
     __syncthreads();
     for (int iter = 0; iter <= 256; iter++) {
@@ -831,13 +853,64 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const uint32_t *__restric
         else start = s_end[tid - 1];
         const bool did = active && start != my_start;
         if (did) {
-            cnt = 0; zc = 0;
             BitReader br; br.init(words, start);
-            while (br.pos < hi) {
-                const uint32_t sym = dec_symbol(br, s_lut, tr);
-                cnt++; zc += (sym == 0);
+            if (!have_mask) {
+                // full decode; symbol starts are collected 32 positions at a time in registers
+                cnt = 0; zc = 0;
+#pragma unroll
+                for (int w = 0; w < 8; w++) { bm[w] = 0u; zm[w] = 0u; }
+                uint32_t accb = 0, accz = 0; int curw = 0;
+                while (br.pos < hi) {
+                    const uint32_t off = (uint32_t)(br.pos - lo);
+                    const int w = (int)(off >> 5);
+                    if (w != curw) { bm[curw] = accb; zm[curw] = accz; accb = 0; accz = 0; curw = w; }
+                    const uint32_t sym = dec_symbol(br, s_lut, tr);
+                    accb |= 1u << (off & 31u);
+                    if (sym == 0) { accz |= 1u << (off & 31u); zc++; }
+                    cnt++;
+                }
+                bm[curw] = accb; zm[curw] = accz;
+                my_end = br.pos;
+                have_mask = true;
+            } else {
+                // re-decode until the new walk meets the old one.  `rem` / `remz` count the old symbol starts that the new walk
+                // replaces: those before the new start, and those inside every newly decoded code word.
+                uint32_t ncnt = 0, nzc = 0, rem = 0, remz = 0;
+                {
+                    const uint32_t so = (uint32_t)min((unsigned long long)(start - lo), (unsigned long long)DEC_SUB_BITS);
+                    for (int q = 0; q < 8; q++) {
+                        const uint32_t lo_q = (uint32_t)q << 5;
+                        if (so <= lo_q) break;
+                        const uint32_t m = (so - lo_q >= 32u) ? 0xffffffffu : ((1u << (so - lo_q)) - 1u);
+                        rem += __popc(bm[q] & m); remz += __popc(zm[q] & m);
+                        bm[q] &= ~m; zm[q] &= ~m;
+                    }
+                }
+                bool synced = false;
+                while (br.pos < hi) {
+                    const uint32_t off = (uint32_t)(br.pos - lo);
+                    const int w = (int)(off >> 5);
+                    const uint32_t bit = 1u << (off & 31u);
+                    if (bm[w] & bit) { synced = true; break; }
+                    const uint32_t sym = dec_symbol(br, s_lut, tr);
+                    ncnt++; nzc += (sym == 0);
+                    // the new code word covers [off, off1): old starts inside it disappear, its own start is recorded
+                    const uint32_t off1 = (uint32_t)min((unsigned long long)(br.pos - lo), (unsigned long long)DEC_SUB_BITS);
+                    for (uint32_t o2 = off; o2 < off1;) {
+                        const int w2 = (int)(o2 >> 5);
+                        const uint32_t upto = min(off1, (uint32_t)(w2 + 1) << 5);
+                        const uint32_t span = upto - o2;
+                        const uint32_t m = (span == 32u ? 0xffffffffu : ((1u << span) - 1u)) << (o2 & 31u);
+                        rem += __popc(bm[w2] & m); remz += __popc(zm[w2] & m);
+                        bm[w2] &= ~m; zm[w2] &= ~m;
+                        o2 = upto;
+                    }
+                    bm[w] |= bit; if (sym == 0) zm[w] |= bit;
+                }
+                cnt = cnt - rem + ncnt; zc = zc - remz + nzc;
+                if (!synced) my_end = br.pos;         // walked to the end: every old start was replaced (rem == old cnt)
             }
-            my_end = br.pos; my_start = start; wrote = true;
+            my_start = start; wrote = true;
         }
         __syncthreads();                          // everybody has read its predecessor's end
         s_end[tid] = my_end;

@@ -782,19 +782,29 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         J.ep = (unsigned long long *)sb; J.ec = J.ep + J.nsub + 1; J.start_used = J.ec + J.nsub + 1; J.sym_off = J.start_used + J.nsub + 1; J.zero_off = J.sym_off + J.nsub + 1;
         J.count = (uint32_t *)(J.zero_off + J.nsub + 1); J.zcount = J.count + J.nsub + 1;
     }
-    // Jacobi rounds: round 0 is the speculative decode; a job has converged when a whole round moved no start position
+    // Jacobi rounds: round 0 is the speculative decode; a job has converged when a whole round moved no start position.
+    // One launch per round covers every job that has not converged yet.
+    DecJobList *d_list = (DecJobList *)c.get("dec_joblist", sizeof(DecJobList) + 64); if (!d_list) return SZ_NSCS;
     for (int round = 0;; round++) {
-        bool any = false;
+        DecJobList L; memset(&L, 0, sizeof(L));
+        uint32_t ctas = 0; bool any = false;
         for (int j = 0; j < njobs; j++) {
             DecJob &J = jobs[j];
+            DecJobDev &D = L.j[j];
+            D.cta_begin = ctas; D.active = 0;
+            if (J.single_leaf) continue;
+            D.words = J.words; D.total_bits = J.total_bits; D.nsub = J.nsub; D.tr = DecTree{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
+            D.end_prev = J.ep; D.end_cur = J.ec; D.start_used = J.start_used; D.count = J.count; D.zcount = J.zcount; D.changed = d_changed + j;
+            ctas += (uint32_t)((J.nsub + 255) / 256);
             if (J.converged) continue;
-            any = true;
-            DecTree tr{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
-            CU(cudaMemsetAsync(d_changed + j, 0, 4, c.stream));
-            dec_sync_kernel<<<(unsigned)((J.nsub + 255) / 256), 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.ep, J.ec, J.start_used, J.count, J.zcount, round == 0 ? 1 : 0, d_changed + j); KCHECK();
+            D.active = 1; any = true;
             std::swap(J.ep, J.ec);
         }
+        L.n = njobs;
         if (!any) break;
+        CU(cudaMemsetAsync(d_changed, 0, 4 * 8, c.stream));
+        CU(cudaMemcpyAsync(d_list, &L, sizeof(L), cudaMemcpyHostToDevice, c.stream));       // pageable source: staged before the call returns
+        dec_sync_kernel<<<ctas, 256, 0, c.stream>>>(d_list, round == 0 ? 1 : 0); KCHECK();
         if (round == 0) continue;                                // the first round always changes something
         unsigned int ch[8];
         CU(cudaMemcpyAsync(ch, d_changed, 4 * njobs, cudaMemcpyDeviceToHost, c.stream));
@@ -802,17 +812,25 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         for (int j = 0; j < njobs; j++) if (!jobs[j].converged && !ch[j]) jobs[j].converged = true;
         if (round > 100000) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
     }
+    // prefix sums and the write pass: the main stream on the context's stream, the coefficient streams beside it on the second one
+    CU(cudaEventRecord(c.ev_fork, c.stream));
+    CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+    bool side_used = false;
     for (int j = 0; j < njobs; j++) {
         DecJob &J = jobs[j];
         if (J.single_leaf) continue;
         DecTree tr{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
-        if (launch_scan(c, c.stream, 0, J.count, J.nsub, J.sym_off, nullptr)) return SZ_NSCS;
-        if (launch_scan(c, c.stream, 0, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS;
+        cudaStream_t st = J.blockmajor ? c.stream : c.stream2;
+        const int slot = J.blockmajor ? 0 : 1;
+        if (!J.blockmajor) side_used = true;
+        if (launch_scan(c, st, slot, J.count, J.nsub, J.sym_off, nullptr)) return SZ_NSCS;
+        if (J.blockmajor) { if (launch_scan(c, st, slot, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS; }
         const unsigned grid = (unsigned)((J.nsub + 255) / 256);
-        if (J.blockmajor) dec_write_kernel<T, true><<<grid, 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
-        else dec_write_kernel<T, false><<<grid, 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, (const T *)nullptr, 0, (T *)nullptr);
+        if (J.blockmajor) dec_write_kernel<T, true><<<grid, 256, 0, st>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
+        else dec_write_kernel<T, false><<<grid, 256, 0, st>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, (const unsigned long long *)nullptr, J.nsym, g, J.d_out, (const T *)nullptr, 0, (T *)nullptr);
         KCHECK();
     }
+    if (side_used) { CU(cudaEventRecord(c.ev_join, c.stream2)); CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0)); }
     return 0;
 }
 
