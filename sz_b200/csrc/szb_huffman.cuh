@@ -808,6 +808,7 @@ struct DecJobDev {
     const uint32_t *words; uint64_t total_bits, nsub; DecTree tr;
     const unsigned long long *end_prev; unsigned long long *end_cur, *start_used; uint32_t *count, *zcount;
     unsigned int *changed; uint32_t cta_begin, active;
+    unsigned long long *sym_off; uint64_t nsym; uint16_t *out;          // write pass of the coefficient streams
 };
 constexpr int DEC_MAX_JOBS = 5;
 struct DecJobList { DecJobDev j[DEC_MAX_JOBS]; int n; };
@@ -953,6 +954,52 @@ __global__ void __launch_bounds__(256) dec_write_kernel(const uint32_t *__restri
         } else codes_out[p] = (uint16_t)sym;
         p++;
     }
+}
+
+// prefix sums and write pass of ALL coefficient streams of a call in one launch each (they are a few CTAs apiece; launched
+// separately their launch latencies add up to more than the work)
+__global__ void __launch_bounds__(1024) dec_coef_scan_kernel(const DecJobList *__restrict__ list) {
+    const DecJobDev &J = list->j[blockIdx.x];
+    if (!J.active) return;
+    __shared__ unsigned long long s_w[32];
+    __shared__ unsigned long long s_carry;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t == 0) s_carry = 0;
+    __syncthreads();
+    for (uint64_t base = 0; base < J.nsub; base += 1024) {
+        const uint64_t i = base + t;
+        const unsigned long long v = i < J.nsub ? (unsigned long long)J.count[i] : 0ull;
+        unsigned long long x = v;
+        for (int d = 1; d < 32; d <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+        if (lane == 31) s_w[warp] = x;
+        __syncthreads();
+        unsigned long long before = 0, tot = 0;
+        for (int w = 0; w < 32; w++) { const unsigned long long c = s_w[w]; before += (w < warp) ? c : 0ull; tot += c; }
+        const unsigned long long carry = s_carry;
+        if (i < J.nsub) J.sym_off[i] = carry + before + x - v;
+        __syncthreads();
+        if (t == 0) s_carry = carry + tot;
+        __syncthreads();
+    }
+}
+__global__ void __launch_bounds__(256) dec_coef_write_kernel(const DecJobList *__restrict__ list) {
+    int jid = 0;
+    for (int q = 1; q < list->n; q++) if (blockIdx.x >= list->j[q].cta_begin) jid = q;
+    const DecJobDev &J = list->j[jid];
+    if (!J.active) return;
+    const DecTree tr = J.tr;
+    __shared__ uint32_t s_lut[1 << DEC_K];
+    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
+    __syncthreads();
+    const uint64_t sidx = (uint64_t)(blockIdx.x - J.cta_begin) * blockDim.x + threadIdx.x;
+    if (sidx >= J.nsub) return;
+    uint64_t p = J.sym_off[sidx];
+    if (p >= J.nsym) return;
+    uint64_t hi = (sidx + 1) * DEC_SUB_BITS;
+    const uint64_t limit = J.total_bits + 64;
+    if (hi > limit) hi = limit;
+    BitReader br; br.init(J.words, J.start_used[sidx]);
+    while (br.pos < hi && p < J.nsym) { J.out[p] = (uint16_t)dec_symbol(br, s_lut, tr); p++; }
 }
 
 // single-leaf tree: every symbol is the root's symbol and the payload is empty (ref: Huffman.c:316-321)

@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <string>
@@ -71,7 +72,9 @@ struct Ctx {
         dev = d;
         CU(cudaSetDevice(d));
         CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-        CU(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+        // the side stream carries the few-CTA serial kernels (coefficient trees and chains): highest priority, so that their CTAs are
+        // placed as soon as an SM has room instead of queueing behind the big grids of the main stream
+        { int lo_p = 0, hi_p = 0; CU(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p)); CU(cudaStreamCreateWithPriority(&stream2, cudaStreamNonBlocking, hi_p)); }
         CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
         for (auto &e : ev) CU(cudaEventCreate(&e));
         ev_ok = true;
@@ -745,9 +748,14 @@ struct DecJob {
 };
 
 template <typename T>
-static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const T *d_unpred, uint64_t unpred_count, T *d_field) {
+static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const T *d_unpred, uint64_t unpred_count, T *d_field,
+                           const std::function<int(cudaStream_t)> &side_tail) {
     char nm[48];
     struct RootInfo { uint8_t leaf; uint32_t sym; } roots[8];
+    const bool prof = getenv("SZB200_DEC_PROFILE") != nullptr;
+    cudaEvent_t pe[6]; int npe = 0;
+    auto pmark = [&]() { if (prof && npe < 6) { cudaEventCreate(&pe[npe]); cudaEventRecord(pe[npe], c.stream); npe++; } };
+    pmark();
     for (int j = 0; j < njobs; j++) {
         DecJob &J = jobs[j];
         snprintf(nm, sizeof(nm), "dec_tree%d", J.slot);
@@ -758,6 +766,7 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         CU(cudaMemcpyAsync(&roots[j].sym, J.C, 4, cudaMemcpyDeviceToHost, c.stream));
     }
     CU(cudaStreamSynchronize(c.stream));
+    pmark();
     unsigned int *d_changed = (unsigned int *)c.get("dec_changed", 256); if (!d_changed) return SZ_NSCS;
     for (int j = 0; j < njobs; j++) {
         DecJob &J = jobs[j];
@@ -782,6 +791,7 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         J.ep = (unsigned long long *)sb; J.ec = J.ep + J.nsub + 1; J.start_used = J.ec + J.nsub + 1; J.sym_off = J.start_used + J.nsub + 1; J.zero_off = J.sym_off + J.nsub + 1;
         J.count = (uint32_t *)(J.zero_off + J.nsub + 1); J.zcount = J.count + J.nsub + 1;
     }
+    pmark();
     // Jacobi rounds: round 0 is the speculative decode; a job has converged when a whole round moved no start position.
     // One launch per round covers every job that has not converged yet.
     DecJobList *d_list = (DecJobList *)c.get("dec_joblist", sizeof(DecJobList) + 64); if (!d_list) return SZ_NSCS;
@@ -812,25 +822,54 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         for (int j = 0; j < njobs; j++) if (!jobs[j].converged && !ch[j]) jobs[j].converged = true;
         if (round > 100000) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
     }
-    // prefix sums and the write pass: the main stream on the context's stream, the coefficient streams beside it on the second one
+    pmark();
+    // prefix sums and the write pass: the main stream on the context's stream; all coefficient streams beside it on the second
+    // one, with one launch for their prefix sums and one for their write passes
     CU(cudaEventRecord(c.ev_fork, c.stream));
     CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
     bool side_used = false;
+    {
+        DecJobList L; memset(&L, 0, sizeof(L));
+        uint32_t ctas = 0;
+        for (int j = 0; j < njobs; j++) {
+            DecJob &J = jobs[j];
+            if (J.single_leaf || J.blockmajor) continue;
+            DecJobDev &D = L.j[L.n++];
+            D.words = J.words; D.total_bits = J.total_bits; D.nsub = J.nsub; D.tr = DecTree{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
+            D.start_used = J.start_used; D.count = J.count; D.sym_off = J.sym_off; D.nsym = J.nsym; D.out = J.d_out;
+            D.cta_begin = ctas; D.active = 1;
+            ctas += (uint32_t)((J.nsub + 255) / 256);
+        }
+        if (L.n > 0) {
+            DecJobList *d_clist = (DecJobList *)c.get("dec_joblist_coef", sizeof(DecJobList) + 64); if (!d_clist) return SZ_NSCS;
+            CU(cudaMemcpyAsync(d_clist, &L, sizeof(L), cudaMemcpyHostToDevice, c.stream2));
+            dec_coef_scan_kernel<<<L.n, 1024, 0, c.stream2>>>(d_clist); KCHECK();
+            dec_coef_write_kernel<<<ctas, 256, 0, c.stream2>>>(d_clist); KCHECK();
+            side_used = true;
+        }
+    }
     for (int j = 0; j < njobs; j++) {
         DecJob &J = jobs[j];
-        if (J.single_leaf) continue;
+        if (J.single_leaf || !J.blockmajor) continue;
         DecTree tr{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
-        cudaStream_t st = J.blockmajor ? c.stream : c.stream2;
-        const int slot = J.blockmajor ? 0 : 1;
-        if (!J.blockmajor) side_used = true;
-        if (launch_scan(c, st, slot, J.count, J.nsub, J.sym_off, nullptr)) return SZ_NSCS;
-        if (J.blockmajor) { if (launch_scan(c, st, slot, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS; }
+        if (launch_scan(c, c.stream, 0, J.count, J.nsub, J.sym_off, nullptr)) return SZ_NSCS;
+        if (launch_scan(c, c.stream, 0, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS;
         const unsigned grid = (unsigned)((J.nsub + 255) / 256);
-        if (J.blockmajor) dec_write_kernel<T, true><<<grid, 256, 0, st>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
-        else dec_write_kernel<T, false><<<grid, 256, 0, st>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, (const unsigned long long *)nullptr, J.nsym, g, J.d_out, (const T *)nullptr, 0, (T *)nullptr);
+        dec_write_kernel<T, true><<<grid, 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
         KCHECK();
     }
+    // work that only needs the coefficient codes (the coefficient chain) continues on the second stream, beside the main write pass
+    if (side_tail) { if (side_tail(c.stream2)) return SZ_NSCS; side_used = true; }
+    pmark();
     if (side_used) { CU(cudaEventRecord(c.ev_join, c.stream2)); CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0)); }
+    pmark();
+    if (prof) {
+        cudaStreamSynchronize(c.stream);
+        float ms[6] = {0, 0, 0, 0, 0, 0};
+        for (int q = 1; q < npe; q++) cudaEventElapsedTime(&ms[q], pe[q - 1], pe[q]);
+        fprintf(stderr, "[dec-prof] tree unpack + root read-back %.3f | luts, payload copies %.3f | sync rounds %.3f | main prefix sums + write %.3f | wait for the side stream %.3f ms\n", ms[1], ms[2], ms[3], ms[4], ms[5]);
+        for (int q = 0; q < npe; q++) cudaEventDestroy(pe[q]);
+    }
     return 0;
 }
 
@@ -887,6 +926,30 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     uint16_t *d_codes = (uint16_t *)c.get("codes", 2ull * N + 64); if (!d_codes) return SZ_NSCS;
     T *d_clast = (T *)c.get("coeff_last", sizeof(T) * 4ull * nb); if (!d_clast) return SZ_NSCS;
     uint16_t *d_ctype = (uint16_t *)c.get("coeff_type", 2ull * 4 * nb + 64); if (!d_ctype) return SZ_NSCS;
+    // ---- coefficient chain: needs the coefficient codes only, so it runs on the second stream beside the main write pass ----
+    // the list of regression blocks and the raw coefficient values do not depend on any decoded code: prepared up front
+    uint32_t *d_list = nullptr; T *d_cu = nullptr;
+    if (reg_count > 0) {
+        uint32_t *d_flags = (uint32_t *)c.get("reg_flags", 4ull * nb + 64);
+        d_list = (uint32_t *)c.get("reg_list", 4ull * nb + 64);
+        unsigned long long *d_rank = (unsigned long long *)c.get("reg_rank", 8ull * nb + 64);
+        d_cu = (T *)c.get("coeff_unpred", sizeof(T) * 4ull * nb);
+        T *d_dummy = (T *)c.get("reg", sizeof(T) * 4ull * nb), *d_dummy2 = (T *)c.get("reg_c", sizeof(T) * 4ull * nb);
+        if (!d_flags || !d_list || !d_rank || !d_cu || !d_dummy || !d_dummy2) return SZ_NSCS;
+        reg_flag_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_flags); KCHECK();
+        if (launch_scan(c, c.stream, 0, d_flags, nb, d_rank, nullptr)) return SZ_NSCS;
+        reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, 0, d_dummy, d_dummy2, d_list); KCHECK();
+        for (int e = 0; e < ncoef; e++) if (cunp_cnt[e]) CU(cudaMemcpyAsync(d_cu + (size_t)e * nb, d_body + o_cunp[e], sizeof(T) * cunp_cnt[e], cudaMemcpyDeviceToDevice, c.stream));
+    }
+    auto chain_tail = [&](cudaStream_t st) -> int {
+        if (reg_count == 0) return 0;
+        T *d_dval = (T *)c.get("dchain_val", sizeof(T) * 4ull * reg_count + 64);
+        unsigned char *d_drst = (unsigned char *)c.get("dchain_rst", 4ull * reg_count + 64);
+        if (!d_dval || !d_drst) return SZ_NSCS;
+        coeff_dec_prep_kernel<T><<<ncoef, 1024, 0, st>>>(d_ctype, nb, reg_count, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3], d_cu, d_dval, d_drst); KCHECK();
+        coeff_chain_decode_kernel<T><<<1, DCHAIN_THREADS, 0, st>>>(d_dval, d_drst, nb, reg_count, ncoef, d_list, d_clast); KCHECK();
+        return 0;
+    };
     {
         DecJob jobs[5]; memset(jobs, 0, sizeof(jobs));
         int nj = 0;
@@ -896,27 +959,10 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
             jobs[nj].slot = 1 + e; jobs[nj].d_tree = d_body + o_ctree[e]; jobs[nj].nodeCount = cnode[e]; jobs[nj].d_payload = d_body + o_cbits[e]; jobs[nj].payload_bytes = cbits_bytes[e];
             jobs[nj].nsym = reg_count; jobs[nj].blockmajor = false; jobs[nj].d_out = d_ctype + (size_t)e * nb; nj++;
         }
-        if (huff_decode_all<T>(c, jobs, nj, g, d_unp, total_unpred, d_out)) return SZ_NSCS;
+        if (huff_decode_all<T>(c, jobs, nj, g, d_unp, total_unpred, d_out, chain_tail)) return SZ_NSCS;
     }
     if (mark(ST_DECODE)) return SZ_NSCS;
 
-    // ---- coefficient chain ----
-    if (reg_count > 0) {
-        uint32_t *d_flags = (uint32_t *)c.get("reg_flags", 4ull * nb + 64), *d_list = (uint32_t *)c.get("reg_list", 4ull * nb + 64);
-        unsigned long long *d_rank = (unsigned long long *)c.get("reg_rank", 8ull * nb + 64);
-        T *d_cu = (T *)c.get("coeff_unpred", sizeof(T) * 4ull * nb);
-        T *d_dummy = (T *)c.get("reg", sizeof(T) * 4ull * nb), *d_dummy2 = (T *)c.get("reg_c", sizeof(T) * 4ull * nb);
-        if (!d_flags || !d_list || !d_rank || !d_cu || !d_dummy || !d_dummy2) return SZ_NSCS;
-        reg_flag_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_flags); KCHECK();
-        if (launch_scan(c, c.stream, 0, d_flags, nb, d_rank, nullptr)) return SZ_NSCS;
-        reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, 0, d_dummy, d_dummy2, d_list); KCHECK();
-        for (int e = 0; e < ncoef; e++) if (cunp_cnt[e]) CU(cudaMemcpyAsync(d_cu + (size_t)e * nb, d_body + o_cunp[e], sizeof(T) * cunp_cnt[e], cudaMemcpyDeviceToDevice, c.stream));
-        T *d_dval = (T *)c.get("dchain_val", sizeof(T) * 4ull * reg_count + 64);
-        unsigned char *d_drst = (unsigned char *)c.get("dchain_rst", 4ull * reg_count + 64);
-        if (!d_dval || !d_drst) return SZ_NSCS;
-        coeff_dec_prep_kernel<T><<<ncoef, 1024, 0, c.stream>>>(d_ctype, nb, reg_count, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3], d_cu, d_dval, d_drst); KCHECK();
-        coeff_chain_decode_kernel<T><<<1, DCHAIN_THREADS, 0, c.stream>>>(d_dval, d_drst, nb, reg_count, ncoef, d_list, d_clast); KCHECK();
-    }
     if (mark(ST_DCHAIN)) return SZ_NSCS;
 
     // ---- wavefront reconstruction ----
