@@ -415,22 +415,23 @@ static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, in
     std::vector<uint32_t> ktab(n2);
     for (uint32_t k = 0; k < n2; k++) { uint32_t kk; const uint32_t bk = g.ax[2].block_of(k, kk); ktab[k] = (bk << 8) | kk; }
     uint32_t *d_ktab = (uint32_t *)c.get("wf_ktab", 4ull * n2);
-    T *d_xin = (T *)c.get("wf_xin", sizeof(T) * g.N);
+    const uint32_t pitch = (n2 + WfCfg<DIM>::CH - 1) / WfCfg<DIM>::CH * WfCfg<DIM>::CH;      // rows of xin are whole chunks: 16-byte aligned bulk copies
+    T *d_xin = (T *)c.get("wf_xin", sizeof(T) * (size_t)rows * pitch + 256);
     uint32_t *d_given = (uint32_t *)c.get("wf_given", 4ull * rows * wpr);
     if (!d_ktab || !d_xin || !d_given) return SZ_NSCS;
     CU(cudaMemcpyAsync(d_ktab, ktab.data(), 4ull * n2, cudaMemcpyHostToDevice, c.stream));
     {
         const int pgrid = (int)std::min<uint32_t>((rows + 7) / 8, (uint32_t)c.sm_count * 16u);
         if (!decomp) {
-            if (use_mean) prepass_compress_kernel<T, DIM, true><<<pgrid, 256, 0, c.stream>>>(g, x, indicator, coeff_last, d_ktab, codes, d_xin, d_given, wpr, eb, recip, mean, cap, cap / 2);
-            else prepass_compress_kernel<T, DIM, false><<<pgrid, 256, 0, c.stream>>>(g, x, indicator, coeff_last, d_ktab, codes, d_xin, d_given, wpr, eb, recip, mean, cap, cap / 2);
+            if (use_mean) prepass_compress_kernel<T, DIM, true><<<pgrid, 256, 0, c.stream>>>(g, x, indicator, coeff_last, d_ktab, codes, d_xin, pitch, d_given, wpr, eb, recip, mean, cap, cap / 2);
+            else prepass_compress_kernel<T, DIM, false><<<pgrid, 256, 0, c.stream>>>(g, x, indicator, coeff_last, d_ktab, codes, d_xin, pitch, d_given, wpr, eb, recip, mean, cap, cap / 2);
         } else {
-            if (use_mean) prepass_decompress_kernel<T, DIM, true><<<pgrid, 256, 0, c.stream>>>(g, codes, recon, indicator, coeff_last, d_ktab, d_xin, d_given, wpr, eb, mean, cap / 2);
-            else prepass_decompress_kernel<T, DIM, false><<<pgrid, 256, 0, c.stream>>>(g, codes, recon, indicator, coeff_last, d_ktab, d_xin, d_given, wpr, eb, mean, cap / 2);
+            if (use_mean) prepass_decompress_kernel<T, DIM, true><<<pgrid, 256, 0, c.stream>>>(g, codes, recon, indicator, coeff_last, d_ktab, d_xin, pitch, d_given, wpr, eb, mean, cap / 2);
+            else prepass_decompress_kernel<T, DIM, false><<<pgrid, 256, 0, c.stream>>>(g, codes, recon, indicator, coeff_last, d_ktab, d_xin, pitch, d_given, wpr, eb, mean, cap / 2);
         }
         KCHECK();
     }
-    P.given = d_given; P.given_wpr = wpr;
+    P.given = d_given; P.given_wpr = wpr; P.pitch = pitch;
     const size_t per_warp = wf_smem_per_warp<T>(DIM);
     int warps = sizeof(T) == 4 ? 4 : 2;
     while (warps > 1 && per_warp * warps > c.smem_optin) warps--;

@@ -23,7 +23,7 @@
 // latency of one step -- not bandwidth.  Hence everything that does NOT depend on reconstructed neighbours is taken out
 // of the step: a fully parallel pre-pass (prepass_*_kernel below) resolves regression blocks, mean hits and (decompress)
 // unpredictable values and code de-quantisation into a merged input array `xin` plus one "given" bit per point.  The
-// wavefront step is then: one input (LDGSTS-staged two chunks ahead), three ring loads, the Lorenzo sum, the
+// wavefront step is then: one input (staged by bulk-asynchronous copies half a ring ahead), three ring loads, the Lorenzo sum, the
 // branch-free quantiser (compress) or one add (decompress), one select on the given bit.
 #pragma once
 #include "szb_common.cuh"
@@ -39,7 +39,7 @@ template <int DIM> struct WfCfg {
     static constexpr int W = 2 * CH;               // reconstruction ring length (chunks c-1, c)
     static constexpr int S = W + 1;                // padded stride
     static constexpr int IW = 4 * CH;              // input ring length (chunks c-1 .. c+2: prefetch runs two chunks ahead)
-    static constexpr int IS = IW + 1;
+    static constexpr int NSLOT = 2;                // the input ring is filled half by half (two chunks per copy), one mbarrier per half
     static constexpr int ROWS = (Pencil<DIM>::PI + 1) * (Pencil<DIM>::PJ + 1);   // incl. halo rows li = -1 / lj = -1
 };
 
@@ -56,6 +56,7 @@ struct WfParams {
     int *err;                        // error flag (1 = spin timeout)
     const uint32_t *given;           // [rows][given_wpr] bit k&31 of word k>>5: point resolved by the pre-pass
     uint32_t given_wpr;              // words per row
+    uint32_t pitch;                  // elements per row of xin (n2 rounded up to a whole chunk: every chunk copy is in bounds and aligned)
     int write_all_recon;             // debug: store every reconstructed point in the raster array (compress)
     unsigned long long *prof;        // optional (only with -DSZB_WF_PROFILE): [0] wait+halo cycles [3] pencil total [4] steps; [8+4*pid..] timeline
 };
@@ -65,23 +66,37 @@ template <int DIM> struct WfBnd { static constexpr int NR = (DIM == 3) ? Pencil<
 template <typename T, int DIM>
 inline size_t wf_bnd_bytes(uint32_t num_pencils, uint32_t n2) { return (size_t)num_pencils * WfBnd<DIM>::NR * n2 * (sizeof(T) / 4) * 8; }
 
+// Per-warp shared memory: [reconstruction ring incl. halo rows | input ring, one row per lane | one mbarrier per chunk slot].
+// The input ring is indexed by POSITION (k mod IW) and its rows are 16-byte aligned with a 16-byte pad (bank spread): every
+// chunk of every row is the destination of one bulk-asynchronous copy.
+template <typename T, int DIM> struct WfSmem {
+    static constexpr int IS = WfCfg<DIM>::IW + 16 / (int)sizeof(T);                                   // input row stride (elements)
+    static constexpr size_t RING = (((size_t)WfCfg<DIM>::ROWS * WfCfg<DIM>::S * sizeof(T)) + 15) & ~(size_t)15;
+    static constexpr size_t INR = (size_t)32 * IS * sizeof(T);
+    static constexpr size_t BARS = 8 * WfCfg<DIM>::NSLOT;
+    static constexpr size_t TOTAL = RING + INR + BARS;
+};
 template <typename T>
-__host__ __device__ constexpr size_t wf_smem_per_warp(int dim) {
-    // reconstruction ring incl. halo rows + input ring (x, or codes widened to T-sized slots)
-    return dim == 3 ? ((size_t)WfCfg<3>::ROWS * WfCfg<3>::S + (size_t)32 * WfCfg<3>::IS) * sizeof(T)
-                    : ((size_t)WfCfg<2>::ROWS * WfCfg<2>::S + (size_t)32 * WfCfg<2>::IS) * sizeof(T);
-}
+__host__ __device__ constexpr size_t wf_smem_per_warp(int dim) { return dim == 3 ? WfSmem<T, 3>::TOTAL : WfSmem<T, 2>::TOTAL; }
 
-// asynchronous global -> shared copy of one element (LDGSTS): the data never passes through registers, so the warp does not
-// stall on the load; completion is observed with cp.async.wait_group
-template <typename T>
-__device__ __forceinline__ void cp_async_elem(T *smem_dst, const T *gmem_src) {
-    const unsigned int d = (unsigned int)__cvta_generic_to_shared(smem_dst);
-    if (sizeof(T) == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem_src) : "memory");
-    else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+// ---- bulk-asynchronous copies (TMA, 1D) and their transaction barriers --------------------------------------------------
+__device__ __forceinline__ void mbar_init(unsigned int bar, unsigned int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned int bar, unsigned int bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned int bar, unsigned int parity) {
+    unsigned int done;
+    asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    return done != 0;
+}
+// one contiguous run of `bytes` (multiple of 16, both addresses 16-byte aligned) global -> shared; completion is counted on `bar`
+__device__ __forceinline__ void bulk_g2s(unsigned int smem_dst, const void *gmem_src, unsigned int bytes, unsigned int bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst), "l"(gmem_src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
 __device__ __forceinline__ int ld_relaxed(const int *p) {
     int v;
@@ -131,7 +146,7 @@ template <> struct Tagged<double> {
 template <typename T, int DIM, bool MEAN>
 __global__ void __launch_bounds__(256) prepass_compress_kernel(Geom g, const T *__restrict__ x, const unsigned char *__restrict__ indicator,
                                                                const T *__restrict__ coeff_last, const uint32_t *__restrict__ ktab,
-                                                               uint16_t *__restrict__ codes, T *__restrict__ xin, uint32_t *__restrict__ given,
+                                                               uint16_t *__restrict__ codes, T *__restrict__ xin, uint32_t pitch, uint32_t *__restrict__ given,
                                                                uint32_t wpr, T eb, T recip_eb, T mean, int cap, int radius) {
     const int lane = threadIdx.x & 31;
     const uint32_t n1 = g.ax[1].n, n2 = g.ax[2].n, nblk = g.num_blocks;
@@ -167,7 +182,7 @@ __global__ void __launch_bounds__(256) prepass_compress_kernel(Geom g, const T *
                     const T dm = cur - mean;
                     if (TT<T>::abs(dm) <= eb) { codes[base + k] = (uint16_t)radius; v = mean; giv = true; }
                 }
-                xin[base + k] = v;
+                xin[(uint64_t)row * pitch + k] = v;
             }
             const uint32_t w = __ballot_sync(0xffffffffu, giv);
             if (lane == 0) given[(uint64_t)row * wpr + (k0 >> 5)] = w;
@@ -182,7 +197,7 @@ __global__ void __launch_bounds__(256) prepass_compress_kernel(Geom g, const T *
 template <typename T, int DIM, bool MEAN>
 __global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const uint16_t *__restrict__ codes, const T *__restrict__ out,
                                                                  const unsigned char *__restrict__ indicator, const T *__restrict__ coeff_last,
-                                                                 const uint32_t *__restrict__ ktab, T *__restrict__ xin, uint32_t *__restrict__ given,
+                                                                 const uint32_t *__restrict__ ktab, T *__restrict__ xin, uint32_t pitch, uint32_t *__restrict__ given,
                                                                  uint32_t wpr, T eb, T mean, int radius) {
     const int lane = threadIdx.x & 31;
     const uint32_t n1 = g.ax[1].n, n2 = g.ax[2].n, nblk = g.num_blocks;
@@ -219,7 +234,7 @@ __global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const u
                     if (MEAN && tcode < radius) tcode += 1;
                     T dq = (T)(2 * (tcode - radius)); v = dq * eb;
                 }
-                xin[base + k] = v;
+                xin[(uint64_t)row * pitch + k] = v;
             }
             const uint32_t w = __ballot_sync(0xffffffffu, giv);
             if (lane == 0) given[(uint64_t)row * wpr + (k0 >> 5)] = w;
@@ -233,34 +248,38 @@ __global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const u
 // writes slot t, reads its neighbours at slots t-1 / t-2 and its input at slot t: all warp-uniform.  With the step loop unrolled
 // over one ring period (U = 2 chunks) every shared-memory offset and the chunk boundaries are compile-time constants and the
 // step body is straight-line code: 4 LDS, the 6-add Lorenzo chain, the quantiser, 1 STS, 1 warp barrier.
-template <typename T>
-__device__ __forceinline__ void cp_async_s32(unsigned int smem_dst, const T *gmem_src) {
-    if (sizeof(T) == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gmem_src) : "memory");
-    else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_dst), "l"(gmem_src) : "memory");
-}
-
 template <typename T, int DIM, bool MEAN, bool DECOMP>
 __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__restrict__ xin /*merged input of the pre-pass*/,
                                                         uint16_t *codes /*raster; compress: codes of the not-given points are written here*/,
                                                         T *recon /*raster; decompress: output; compress: only with write_all_recon*/,
                                                         T eb, T recip_eb) {
     constexpr int PI = Pencil<DIM>::PI, PJ = Pencil<DIM>::PJ;
-    constexpr int CH = WfCfg<DIM>::CH, W = WfCfg<DIM>::W, S = WfCfg<DIM>::S, IW = WfCfg<DIM>::IW, IS = WfCfg<DIM>::IS;
+    constexpr int CH = WfCfg<DIM>::CH, W = WfCfg<DIM>::W, S = WfCfg<DIM>::S, IW = WfCfg<DIM>::IW, IS = WfSmem<T, DIM>::IS, NSLOT = WfCfg<DIM>::NSLOT;
+    constexpr unsigned int CHUNK_BYTES = CH * sizeof(T);
     constexpr int U = W;                               // steps per unrolled period (two chunks)
     constexpr int RJ = PJ + 1;                         // ring rows per li (incl. halo lj = -1)
     constexpr int DMAX = PI - 1 + PJ - 1;
     constexpr int NR = WfBnd<DIM>::NR, WPE = Tagged<T>::WPE;
     static_assert(CH >= DMAX && DMAX >= 1 && DMAX < 32, "a chunk must cover the lane skew");
     static_assert(U % 32 == 0, "given-bit windows are whole words");
+    static_assert(U - 6 >= DMAX, "the next half of the input ring is requested at step U-6, when every lane has left the previous one");
     constexpr int NW = U / 32;                         // given-bit words per period
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     T *ring = reinterpret_cast<T *>(smem_raw + (size_t)warp * wf_smem_per_warp<T>(DIM));
-    T *inr = ring + (size_t)WfCfg<DIM>::ROWS * S;       // input ring [32][IS]
+    T *inr = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(ring) + WfSmem<T, DIM>::RING);       // input ring [32][IS], position-indexed
     const unsigned int inr_s32 = (unsigned int)__cvta_generic_to_shared(inr);
+    const unsigned int bars_s32 = inr_s32 + (unsigned int)WfSmem<T, DIM>::INR;                          // NSLOT mbarriers
+    if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < NSLOT; q++) mbar_init(bars_s32 + 8u * q, 1u);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    unsigned int phases = 0;                           // bit q: parity the next wait on barrier q expects
     const Geom &g = P.g;
     const uint32_t n0 = g.ax[0].n, n1 = g.ax[1].n, n2 = g.ax[2].n;
-    const uint64_t SJ = n2, SI = (uint64_t)n1 * n2;    // element strides between rows
+    const uint32_t pitch = P.pitch;
     const int li = (DIM == 3) ? lane / PJ : 0, lj = (DIM == 3) ? lane % PJ : lane;
     const int delay = li + lj;
     // boundary slot this lane exports (-1: none)
@@ -290,7 +309,6 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
         const bool active = ((uint32_t)li < vi) && ((uint32_t)lj < vj);
         const bool store_rec = active && (DECOMP || P.write_all_recon);
         const bool exports = active && bslot >= 0;
-        const uint64_t pbase = ((uint64_t)i0 * n1 + j0) * n2;
         const uint64_t rowid = (uint64_t)(i0 + li) * n1 + (j0 + lj);
         const int64_t rowbase = (int64_t)(rowid * n2) - delay;      // + t = index of this lane's point at step t
         const int64_t bbase = (int64_t)(((uint64_t)pid * NR + (uint32_t)max(bslot, 0)) * n2) - delay;
@@ -306,32 +324,32 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
         bool ok = true;
         __syncwarp();
 
-        // cooperative LDGSTS staging of the input rows of chunk c: element k of pencil row r -> slot (k + delay_r) mod IW.
-        // Lane q copies point k0+q of every row (64 contiguous bytes per row and instruction).
-        auto stage_input = [&](uint32_t c) {
-            const uint32_t k0 = c * CH;
-            if (k0 < n2) {
-                const uint32_t kcnt = min((uint32_t)CH, n2 - k0);
-                if ((uint32_t)lane < kcnt) {
-                    const uint32_t kk = k0 + lane;
-                    unsigned int so[DMAX + 1];
-#pragma unroll
-                    for (int dv = 0; dv <= DMAX; dv++) so[dv] = inr_s32 + (unsigned int)sizeof(T) * ((kk + dv) & (IW - 1));
-                    const T *gi = xin + pbase + kk;
-#pragma unroll
-                    for (int rli = 0; rli < PI; rli++) {
-                        const T *gj = gi;
-#pragma unroll
-                        for (int rlj = 0; rlj < PJ; rlj++) {
-                            if ((uint32_t)rli < vi && (uint32_t)rlj < vj)
-                                cp_async_s32<T>(so[rli + rlj] + (unsigned int)((rli * PJ + rlj) * IS * sizeof(T)), gj);
-                            gj += SJ;
-                        }
-                        gi += SI;
-                    }
+        // staging of the input: every lane issues ONE bulk-asynchronous copy per PAIR of chunks (pair h = chunks 2h, 2h+1 = one half
+        // of its ring row); lane 0 first tells the half's barrier how many bytes to expect.  A warp-wide bulk-copy instruction is 32
+        // separate requests and costs ~2000 cycles of issue whatever their size, so they are made as large as the ring allows and
+        // issued late in a period (step U-6), when the slowest lane has left the half that is overwritten and the neighbour
+        // pencils have already been handed what they wait for.  Rows of xin are padded to whole chunks.
+        const unsigned int nrows = (unsigned int)__popc(__ballot_sync(0xffffffffu, active));
+        const T *xrow = xin + rowid * pitch;
+        const unsigned int my_in_s32 = inr_s32 + (unsigned int)(lane * IS * sizeof(T));
+        auto stage_pair = [&](uint32_t h) {
+            const uint32_t k0 = 2 * h * CH;
+            if (k0 >= n2) return;
+            const unsigned int bytes = (unsigned int)min((uint32_t)(2 * CH), pitch - k0) * (unsigned int)sizeof(T);
+            const unsigned int half = h & 1u, bar = bars_s32 + 8u * half;
+            if (lane == 0) mbar_expect_tx(bar, nrows * bytes);
+            __syncwarp();
+            if (active) bulk_g2s(my_in_s32 + half * 2u * CHUNK_BYTES, xrow + k0, bytes, bar);
+        };
+        auto wait_pair = [&](uint32_t h) {
+            const unsigned int half = h & 1u, bar = bars_s32 + 8u * half, parity = (phases >> half) & 1u;
+            if (!mbar_try_wait(bar, parity)) {
+                const long long deadline = clock64() + 2000000000LL;         // ~1 s: a copy that has not landed by then never will
+                while (!mbar_try_wait(bar, parity)) {
+                    if (clock64() > deadline) { if (lane == 0) atomicExch(P.err, 1); ok = false; break; }
                 }
             }
-            cp_async_commit();                      // one group per chunk, even when empty, keeps the wait count uniform
+            phases ^= 1u << half;
         };
 
         // chunk boundary: fetch the CH boundary values of chunk c from the up / up-left / left pencils (tagged words, L2) and
@@ -448,8 +466,7 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
                         for (int q = 0; q < PI; q++) ring[((size_t)(q + 1) * RJ + 0) * S + ((k0 + lane + (q - 1)) & (W - 1))] = hl[q];
                     }
                 }
-                if (c > 0) stage_input(c + 2);              // (chunk 2 was requested before the wait for chunk 0)
-                cp_async_wait<2>();                         // input chunk c has landed (groups c+1, c+2 may still be in flight)
+                if ((c & 1u) == 0) wait_pair(c >> 1);       // the half holding chunks c, c+1 has landed
             }
             __syncwarp();
 #ifdef SZB_WF_PROFILE
@@ -462,7 +479,7 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
         if (lane == 0) { unsigned long long gt0; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt0)); unsigned int smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
                          P.prof[8 + 4 * (size_t)pid + 0] = gt0; P.prof[8 + 4 * (size_t)pid + 3] = smid; }
 #endif
-        stage_input(0); stage_input(1); stage_input(2);
+        stage_pair(0);
         const uint32_t tsteps = n2 + DMAX;
         const uint32_t nper = (tsteps + U - 1) / U;
 
@@ -483,7 +500,7 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
                 const uint32_t wi = (m + 1) * NW + h;
                 gnext[h] = active ? (wi < wpr ? grow[wi] : 0u) : 0xffffffffu;
             }
-            const T *inp = my_in + (m & 1) * U;
+            const uint32_t kin = t0 - (uint32_t)delay;                     // this lane's position at step t0 (wraps while t0 < delay: masked below)
             uint16_t *cp = codes + (rowbase + (int64_t)t0);
             T *rp = recon + (rowbase + (int64_t)t0);
             unsigned long long *bp = bnd + (bbase + (int64_t)t0) * WPE;
@@ -493,9 +510,10 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
                     const uint32_t c = 2 * m + (s == CH ? 1u : 0u);
                     if (c * CH < n2 && ok) {
                         if (has_up || has_left) boundary(c);
-                        else { if (c > 0) stage_input(c + 2); cp_async_wait<2>(); __syncwarp(); }
+                        else { if ((c & 1u) == 0) wait_pair(c >> 1); __syncwarp(); }
                     }
                 }
+                if (s == U - 6) stage_pair(m + 1);
                 if (s == CH / 2) prefetch_halo(2 * m + 1);
                 if (s == CH + CH / 2) prefetch_halo(2 * m + 2);
                 const bool giv = (win[s >> 5] >> (s & 31)) & 1u;
@@ -504,7 +522,7 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
                 const T rb = row_b[(s + W - 1) & (W - 1)];
                 const T rc = (DIM == 3) ? row_c[(s + W - 1) & (W - 1)] : (T)0;
                 const T rf = (DIM == 3) ? row_f[(s + W - 2) & (W - 1)] : (T)0;
-                const T in = inp[s];
+                const T in = my_in[(kin + s) & (IW - 1)];
                 T pred;
                 if (DIM == 3) {   // main-loop term order (ref: sz_float.c:7268-7269)
                     pred = ra + rb; pred = pred + rc; pred = pred - rd; pred = pred - re; pred = pred - rf; pred = pred + rg;
@@ -548,7 +566,6 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
             const bool full = (m > 0) && ((m + 1) * U <= n2);      // t - delay >= 0 and t < n2 for every step and lane
             if (full) period(m, std::false_type{}); else period(m, std::true_type{});
         }
-        cp_async_wait<0>();
 #ifdef SZB_WF_PROFILE
         if (lane == 0) { atomicAdd(P.prof + 3, (unsigned long long)(clock64() - pen0)); atomicAdd(P.prof + 4, (unsigned long long)tsteps);
                          unsigned long long gt; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt)); P.prof[8 + 4 * (size_t)pid + 2] = gt; }
