@@ -22,6 +22,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+_JSON_OUT = None          # duplicate of the real stdout when file descriptor 1 had to be redirected (multi-rank runs)
 sys.path.insert(0, ROOT)
 
 SHAPE = (512, 512, 512)
@@ -166,9 +167,12 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
-        # NCCL prints its version banner on stdout at VERSION level; stdout must carry the one JSON line only
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL prints its version banner on the C stdout; stdout must carry the one JSON line only, so file descriptor 1 is
+        # pointed at stderr for the run and the JSON line goes to a duplicate of the real stdout
+        global _JSON_OUT
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sz_b200.set_device(local)
@@ -301,7 +305,7 @@ def run_ours(args):
             "gpu_launches": int(launches), "clocks": clocks}
     if world == 1:
         line["cpu_baseline"] = cpu_baseline(harr, s_host)
-    print(json.dumps(line))
+    print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
