@@ -121,10 +121,19 @@ struct HeapTop { uint32_t f, n; };
 // sift loop (a dozen uniform-datapath instructions per level).
 struct HeapSmem {
     unsigned int fa, na;                 // shared addresses of f[0] and n[0]
+    bool n16 = false;                    // node ids stored as 16-bit values (two-thread form, trees with fewer than 32768 leaves)
     __device__ __forceinline__ uint32_t ldf(int i) const { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(fa + 4u * (unsigned)i)); return v; }
-    __device__ __forceinline__ uint32_t ldn(int i) const { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(na + 4u * (unsigned)i)); return v; }
+    __device__ __forceinline__ uint32_t ldn(int i) const {
+        uint32_t v;
+        if (n16) { unsigned short h; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(h) : "r"(na + 2u * (unsigned)i)); v = h; }
+        else asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(na + 4u * (unsigned)i));
+        return v;
+    }
     __device__ __forceinline__ void stf(int i, uint32_t v) const { asm volatile("st.shared.u32 [%0], %1;" ::"r"(fa + 4u * (unsigned)i), "r"(v) : "memory"); }
-    __device__ __forceinline__ void stn(int i, uint32_t v) const { asm volatile("st.shared.u32 [%0], %1;" ::"r"(na + 4u * (unsigned)i), "r"(v) : "memory"); }
+    __device__ __forceinline__ void stn(int i, uint32_t v) const {
+        if (n16) asm volatile("st.shared.u16 [%0], %1;" ::"r"(na + 2u * (unsigned)i), "h"((unsigned short)v) : "memory");
+        else asm volatile("st.shared.u32 [%0], %1;" ::"r"(na + 4u * (unsigned)i), "r"(v) : "memory");
+    }
     __device__ __forceinline__ uint2 ldf2(int i) const { uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(fa + 4u * (unsigned)i)); return v; }
     __device__ __forceinline__ uint4 ldf4(int i) const { uint4 v; asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(fa + 4u * (unsigned)i)); return v; }
 };
@@ -257,6 +266,9 @@ __device__ __forceinline__ void heap2_insert(const HeapSmem &h, HeapQueue &Q, in
     h.stf(i, freq);
     Q.push(HQ_INSERT, (uint32_t)q0, (uint32_t)i, node);
 }
+// LIM = false: the frequency array has room for the children of every position a sift can reach (cap >= 2 * (leaves + 2)), so the
+// "no child slots" test drops out of the level loop
+template <bool LIM>
 __device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, HeapQueue &Q, int &qend, int cap, uint32_t out_code) {
     const uint32_t topf = h.ldf(1);
     qend--;
@@ -276,7 +288,7 @@ __device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, HeapQueue &Q
         h.stf(i, fc);                                                                      \
         i = 2 * i + (r ? 1 : 0);                                                           \
         pr = r ? make_uint2(QCUR.z, QCUR.w) : make_uint2(QCUR.x, QCUR.y);                  \
-        if (i >= lim) pr = make_uint2(HEAP_FINF, HEAP_FINF);                               \
+        if (LIM && i >= lim) pr = make_uint2(HEAP_FINF, HEAP_FINF);                        \
         QNEXT = h.ldf4(min(4 * i, qmax));                                                  \
     }
     for (;;) {
@@ -288,6 +300,7 @@ __device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, HeapQueue &Q
     Q.push(HQ_REMOVE, (uint32_t)i, (uint32_t)qend, out_code);
     return topf;
 }
+template <bool LIM>
 __device__ __forceinline__ void heap2_thread_a(const HeapSmem &h, HeapQueue &Q, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
     int qend = 1;
     uint32_t k = 0;
@@ -299,8 +312,8 @@ __device__ __forceinline__ void heap2_thread_a(const HeapSmem &h, HeapQueue &Q, 
     D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
     uint32_t nn = leaves;
     while (qend > 2) {
-        const uint32_t fb = heap2_remove(h, Q, qend, hcap, (nn << 1) | 1u);   // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
-        const uint32_t fa = heap2_remove(h, Q, qend, hcap, (nn << 1) | 0u);   // second removed -> left
+        const uint32_t fb = heap2_remove<LIM>(h, Q, qend, hcap, (nn << 1) | 1u);   // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+        const uint32_t fa = heap2_remove<LIM>(h, Q, qend, hcap, (nn << 1) | 0u);   // second removed -> left
         heap2_insert(h, Q, qend, fa + fb, nn);
         nn++;
     }
@@ -425,7 +438,28 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         const int scap = (int)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 8u) & ~3u);      // entries per array (multiple of 4: 128-bit loads stay aligned)
         const bool in_smem = leaves + 8 <= (uint32_t)scap;
         __shared__ unsigned int s_qdone;
-        if (in_smem) {
+        // compact layout for trees with fewer than 32768 leaves (node ids fit 16 bits): f gets 2*(leaves+2) entries -- child slots exist
+        // for every position a sift can reach, so the level loop needs no "no child slots" test -- and n is an array of 16-bit ids
+        const uint32_t fcap_c = (2u * (leaves + 2u) + 3u) & ~3u;
+        const uint32_t n16_bytes = ((leaves + 8u) * 2u + 7u) & ~7u;
+        const bool compact = 2u * leaves < 65536u && (unsigned long long)fcap_c * 4u + n16_bytes + 8u * HQ_CAP <= (unsigned long long)smem_heap_capacity * 8u;
+        if (compact) {
+            unsigned char *s_bytes = reinterpret_cast<unsigned char *>(s_heap);
+            uint32_t *s_queue = reinterpret_cast<uint32_t *>(s_bytes + (size_t)fcap_c * 4u + n16_bytes);
+            for (int q = t; q < (int)fcap_c; q += blockDim.x) s_heap[q] = HEAP_FINF;
+            for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
+            if (t == 0) s_qdone = 0u;
+            __syncthreads();
+            if (t == 0 || t == 32) {
+                HeapSmem h;
+                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * fcap_c, qa0 = na0 + n16_bytes;
+                unsigned int qaddr;
+                asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
+                h.n16 = true;
+                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a<false>(h, Q, (int)fcap_c, leaves, lfreq, D, tk1); }
+                else s_root = heap2_thread_b(h, qaddr, &s_qdone, D);
+            }
+        } else if (in_smem) {
             uint32_t *s_queue = s_heap + 2 * scap;
             for (int q = t; q < scap; q += blockDim.x) s_heap[q] = HEAP_FINF;
             for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
@@ -438,7 +472,7 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
                 const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * (unsigned)scap, qa0 = na0 + 4u * (unsigned)scap;
                 unsigned int qaddr;
                 asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
-                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a(h, Q, scap, leaves, lfreq, D, tk1); }
+                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a<true>(h, Q, scap, leaves, lfreq, D, tk1); }
                 else s_root = heap2_thread_b(h, qaddr, &s_qdone, D);
             }
         } else if (leaves + 8 <= (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u)) {
@@ -455,7 +489,7 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
                 unsigned int qaddr;
                 asm volatile("mov.u32 %0, %2;\n\tmov.u32 %1, %3;" : "=r"(h.fa), "=r"(qaddr) : "r"(fa0), "r"(qa0));
                 h.na = 0;
-                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a(h, Q, fcap, leaves, lfreq, D, tk1); }
+                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a<true>(h, Q, fcap, leaves, lfreq, D, tk1); }
                 else { const uint32_t root = heap2_warp_b_global(reinterpret_cast<uint32_t *>(D.heap_g), qaddr, &s_qdone, D); if (t == 32) s_root = root; }
             }
         } else {
