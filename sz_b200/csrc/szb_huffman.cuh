@@ -236,10 +236,11 @@ __device__ __forceinline__ uint32_t heap_build_tree(const H &h, int hcap, uint32
 // the instructions of a sift level) off the serial thread.
 constexpr int HQ_CAP = 512;                                   // queue entries (one 64-bit word each)
 enum { HQ_REMOVE = 0, HQ_INSERT = 1, HQ_FIN = 2 };
-// entry = [tag:10 | kind:2 | c:18 | b:17 | a:17], written and read with ONE 64-bit shared-memory access (single-copy atomic), so the
-// consumer sees either the old or the new entry, never a mixture, and no fence is needed: nothing else is shared between the
-// two threads.  tag = (sequence number + 1) mod 1024; the ring holds 512 entries, so the entry that occupied a slot one lap
-// earlier differs in the tag, and so does the all-zero initial state for the first lap.
+// entry = {low word: a:16 | b:16, high word: c:18 | kind:2 | tag:12}, written and read with ONE 64-bit shared-memory access
+// (single-copy atomic), so the consumer sees either the old or the new entry, never a mixture, and no fence is needed: nothing
+// else is shared between the two threads.  Positions a, b are below 65536 in every shared-memory layout.  tag = (sequence
+// number + 1) mod 4096; the ring holds 512 entries, so the entry that occupied a slot one lap earlier differs in the tag, and
+// so does the all-zero initial state for the first lap.
 struct HeapQueue {
     unsigned int qa;                                          // shared address of the ring
     unsigned int *done;                                       // consumer progress (generic pointer into shared memory)
@@ -248,7 +249,9 @@ struct HeapQueue {
         if ((t & 127u) == 0 && t >= HQ_CAP - 128) {           // back-pressure, checked every 128 entries
             while (t - *(volatile unsigned int *)done > HQ_CAP - 128) { }
         }
-        const unsigned long long e = ((unsigned long long)(((t + 1) & 1023u) << 2 | kind) << 52) | ((unsigned long long)c << 34) | ((unsigned long long)b << 17) | a;
+        const uint32_t lo = a | (b << 16), hi = c | (kind << 18) | (((t + 1) & 4095u) << 20);
+        unsigned long long e;
+        asm volatile("mov.b64 %0, {%1, %2};" : "=l"(e) : "r"(lo), "r"(hi));
         asm volatile("st.volatile.shared.u64 [%0], %1;" ::"r"(qa + 8u * (t & (HQ_CAP - 1))), "l"(e) : "memory");
         t++;
     }
@@ -325,9 +328,9 @@ __device__ __forceinline__ uint32_t heap2_thread_b(const HeapSmem &h, unsigned i
     for (uint32_t t = 0;; t++) {
         const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
         unsigned long long e;
-        do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 54) != ((t + 1) & 1023u));
-        const uint32_t kind = (uint32_t)(e >> 52) & 3u;
-        const uint32_t a = (uint32_t)e & 0x1ffffu, b = (uint32_t)(e >> 17) & 0x1ffffu, c = (uint32_t)(e >> 34) & 0x3ffffu;
+        do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 52) != ((t + 1) & 4095u));
+        const uint32_t kind = (uint32_t)(e >> 50) & 3u;
+        const uint32_t a = (uint32_t)e & 0xffffu, b = ((uint32_t)e >> 16) & 0xffffu, c = (uint32_t)(e >> 32) & 0x3ffffu;
         if (kind == HQ_FIN) break;
         if (kind == HQ_REMOVE) {
             // a = final position of the moved element (0: the heap became empty), b = position it was taken from
@@ -367,11 +370,11 @@ __device__ __forceinline__ uint32_t heap2_warp_b_global(uint32_t *ng, unsigned i
         unsigned long long e = 0;
         if (lane == 0) {
             const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
-            do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 54) != ((t + 1) & 1023u));
+            do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 52) != ((t + 1) & 4095u));
         }
         e = __shfl_sync(0xffffffffu, e, 0);
-        const uint32_t kind = (uint32_t)(e >> 52) & 3u;
-        const uint32_t a = (uint32_t)e & 0x1ffffu, b = (uint32_t)(e >> 17) & 0x1ffffu, c = (uint32_t)(e >> 34) & 0x3ffffu;
+        const uint32_t kind = (uint32_t)(e >> 50) & 3u;
+        const uint32_t a = (uint32_t)e & 0xffffu, b = ((uint32_t)e >> 16) & 0xffffu, c = (uint32_t)(e >> 32) & 0x3ffffu;
         if (kind == HQ_FIN) break;
         if (kind == HQ_REMOVE) {
             const int depth = a ? 31 - __clz(a) : 0;
