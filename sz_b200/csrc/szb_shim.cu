@@ -139,9 +139,21 @@ extern "C" void *szb200_stream(void) { Ctx *c = ctx(); return c ? (void *)c->str
 extern "C" int szb200_sync(void) { Ctx *c = ctx(); if (!c) return SZ_NSCS; CU(cudaStreamSynchronize(c->stream)); return 0; }
 extern "C" int szb200_last_stats(szb200_stats *out) { Ctx *c = ctx(); if (!c || !c->have_last) return SZ_NSCS; *out = c->last; return 0; }
 
+static bool is_pinned_host(const void *p) {
+    cudaPointerAttributes at;
+    const bool pinned = cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return pinned;
+}
+static int ensure_bounce(Ctx &c);
+// Host-to-device copy from PAGEABLE memory through the pinned bounce buffers: two host threads fill a chunk while the DMA of the
+// previous one runs (the driver's own staging of pageable memory is a single-threaded copy).
+static int h2d_bounced(Ctx &c, void *dst, const void *src, size_t bytes);
+
 extern "C" void *szb200_stage_input(const void *host_ptr, size_t bytes) {
     Ctx *c = ctx(); if (!c) return nullptr;
     void *d = c->get("in_stage", bytes); if (!d) return nullptr;
+    if (bytes >= ((size_t)4 << 20) && !is_pinned_host(host_ptr)) { if (h2d_bounced(*c, d, host_ptr, bytes)) return nullptr; return d; }
     if (cudaMemcpyAsync(d, host_ptr, bytes, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) { set_err("H2D failed"); return nullptr; }
     return d;
 }
@@ -152,11 +164,37 @@ extern "C" void *szb200_output_buffer(size_t bytes) { Ctx *c = ctx(); return c ?
 // chunk i to its destination.  (A direct cudaMemcpy into pageable memory reaches ~4.7 GB/s here; the DMA alone does > 50 GB/s,
 // so the copy becomes as fast as the host can write its own pages.)
 constexpr size_t BOUNCE_CHUNK = (size_t)8 << 20;
-static int d2h_bounced(Ctx &c, void *dst, const void *src, size_t bytes) {
+static int ensure_bounce(Ctx &c) {
     if (!c.bounce) {
         if (cudaMallocHost((void **)&c.bounce, 2 * BOUNCE_CHUNK) != cudaSuccess) { c.bounce = nullptr; cudaGetLastError(); }
         else { cudaEventCreateWithFlags(&c.ev_bounce[0], cudaEventDisableTiming); cudaEventCreateWithFlags(&c.ev_bounce[1], cudaEventDisableTiming); }
     }
+    return c.bounce ? 0 : SZ_NSCS;
+}
+static void memcpy2(void *d, const void *s, size_t n) {          // one chunk, shared by two host threads
+    if (n >= ((size_t)1 << 20)) {
+        const size_t h = (n / 2) & ~(size_t)4095;
+        std::thread helper([=] { memcpy(d, s, h); });
+        memcpy((unsigned char *)d + h, (const unsigned char *)s + h, n - h);
+        helper.join();
+    } else memcpy(d, s, n);
+}
+static int h2d_bounced(Ctx &c, void *dst, const void *src, size_t bytes) {
+    if (ensure_bounce(c)) { CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream)); return 0; }
+    const size_t nchunks = (bytes + BOUNCE_CHUNK - 1) / BOUNCE_CHUNK;
+    for (size_t i = 0; i < nchunks; i++) {
+        const size_t off = i * BOUNCE_CHUNK, n = std::min(BOUNCE_CHUNK, bytes - off);
+        if (i >= 2) CU(cudaEventSynchronize(c.ev_bounce[i & 1]));       // the DMA that last read this buffer has finished
+        memcpy2(c.bounce + (i & 1) * BOUNCE_CHUNK, (const unsigned char *)src + off, n);
+        CU(cudaMemcpyAsync((unsigned char *)dst + off, c.bounce + (i & 1) * BOUNCE_CHUNK, n, cudaMemcpyHostToDevice, c.stream));
+        CU(cudaEventRecord(c.ev_bounce[i & 1], c.stream));
+    }
+    // the bounce buffers are reused by the next copy: let the last two DMAs finish before returning
+    CU(cudaEventSynchronize(c.ev_bounce[0])); if (nchunks > 1) CU(cudaEventSynchronize(c.ev_bounce[1]));
+    return 0;
+}
+static int d2h_bounced(Ctx &c, void *dst, const void *src, size_t bytes) {
+    (void)ensure_bounce(c);
     if (!c.bounce) { CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.stream)); CU(cudaStreamSynchronize(c.stream)); return 0; }
     const size_t nchunks = (bytes + BOUNCE_CHUNK - 1) / BOUNCE_CHUNK;
     auto issue = [&](size_t i) -> int {
@@ -171,13 +209,7 @@ static int d2h_bounced(Ctx &c, void *dst, const void *src, size_t bytes) {
         CU(cudaEventSynchronize(c.ev_bounce[i & 1]));
         const size_t off = i * BOUNCE_CHUNK, n = std::min(BOUNCE_CHUNK, bytes - off);
         // the host side of the copy is what bounds it (one core writes ~10 GB/s): two threads share every chunk
-        unsigned char *d = (unsigned char *)dst + off; const unsigned char *b = c.bounce + (i & 1) * BOUNCE_CHUNK;
-        if (n >= ((size_t)1 << 20)) {
-            const size_t h = (n / 2) & ~(size_t)4095;
-            std::thread helper([=] { memcpy(d, b, h); });
-            memcpy(d + h, b + h, n - h);
-            helper.join();
-        } else memcpy(d, b, n);
+        memcpy2((unsigned char *)dst + off, c.bounce + (i & 1) * BOUNCE_CHUNK, n);
     }
     return 0;
 }

@@ -20,5 +20,8 @@ for _ in range(4):
     st = sz_b200.last_stats()
     print("compress() wall %.2f ms, %d bytes" % ((t1 - t0) * 1e3, len(s)), {k: round(v, 2) for k, v in st.as_dict()["ms_stage"].items() if v > 0})
 for _ in range(3):
+    t0 = time.perf_counter(); s2 = sz_b200.compress_view(a, sz_b200.REL, 1e-4, 1e-3); t1 = time.perf_counter()
+    print("compress_view() from PAGEABLE input: wall %.2f ms, equal=%s" % ((t1 - t0) * 1e3, bytes(s2) == bytes(s)))
+for _ in range(3):
     t0 = time.perf_counter(); b = sz_b200.decompress(s, np.float32, a.shape); t1 = time.perf_counter()
     print("decompress() wall %.2f ms" % ((t1 - t0) * 1e3))
