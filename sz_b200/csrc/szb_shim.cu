@@ -925,7 +925,8 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     auto mark = [&](int st) -> int { stage_of_ev[evi] = st; CU(cudaEventRecord(c.ev[evi++], c.stream)); return 0; };
     // ---- device copy of the body (aligned), host copy of its parseable head ----
     unsigned char *d_body = (unsigned char *)c.get("dec_body", body_len + 256); if (!d_body) return SZ_NSCS;
-    CU(cudaMemcpyAsync(d_body, body, body_len, body_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c.stream));
+    if (!body_on_device && body_len >= ((size_t)4 << 20) && !is_pinned_host(body)) { if (h2d_bounced(c, d_body, body, body_len)) return SZ_NSCS; }
+    else CU(cudaMemcpyAsync(d_body, body, body_len, body_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c.stream));
     // the section headers are walked on the device (dec_parse_kernel); the host reads the result back once
     DecHead *d_head = (DecHead *)c.get("dec_head", sizeof(DecHead) + 64); if (!d_head) return SZ_NSCS;
     dec_parse_kernel<<<1, 256, 0, c.stream>>>(d_body, (unsigned long long)body_len, (int)sizeof(T), ncoef, nb, d_head); KCHECK();
