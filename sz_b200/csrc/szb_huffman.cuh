@@ -993,6 +993,53 @@ __global__ void __launch_bounds__(256) dec_write_kernel(const uint32_t *__restri
     }
 }
 
+// Main-stream write pass, block-major output.  Every warp's 32 sub-sequences hold one contiguous run of symbols in the
+// block-major code array; the warp decodes into shared memory and then writes the run with coalesced stores (a thread storing
+// its own symbols one by one touches a different 32-byte sector per lane and per symbol: ~0.7 ms of sector traffic at 512^3).
+// Unpredictable values (code 0, rare) are pre-placed into the output field at their raster position.
+constexpr int DECW_TB = 128, DECW_CAP = 4096;               // symbols a warp can stage; a longer run (codes < 2 bits on average) is stored directly
+template <typename T>
+__global__ void __launch_bounds__(DECW_TB) dec_write_bm_kernel(const uint32_t *__restrict__ words, uint64_t total_bits, uint64_t nsub, DecTree tr,
+                                                              const unsigned long long *__restrict__ start_used,
+                                                              const unsigned long long *__restrict__ sym_off, const unsigned long long *__restrict__ zero_off,
+                                                              uint64_t n, Geom g, uint16_t *__restrict__ codes_bm, const T *__restrict__ unpred,
+                                                              uint64_t unpred_count, T *field_out) {
+    __shared__ uint32_t s_lut[1 << DEC_K];
+    __shared__ uint16_t s_sym[DECW_TB / 32][DECW_CAP];
+    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t sfirst = sidx - lane;
+    if (sfirst >= nsub) return;                               // whole warp beyond the stream
+    const bool have = sidx < nsub;
+    uint64_t p = have ? min((uint64_t)sym_off[sidx], n) : n;
+    const uint64_t wbase = __shfl_sync(0xffffffffu, p, 0);
+    const uint64_t wend = (sfirst + 32 < nsub) ? min((uint64_t)sym_off[sfirst + 32], n) : n;
+    const bool staged = (wend - wbase) <= (uint64_t)DECW_CAP;
+    uint16_t *ss = s_sym[warp];
+    if (have && p < n) {
+        uint64_t zr = zero_off[sidx];
+        uint64_t hi = (sidx + 1) * DEC_SUB_BITS;
+        const uint64_t limit = total_bits + 64;
+        if (hi > limit) hi = limit;
+        BitReader br; br.init(words, start_used[sidx]);
+        BMIter it; it.init(g, p);
+        while (br.pos < hi && p < n) {
+            const uint32_t sym = dec_symbol(br, s_lut, tr);
+            if (staged) ss[p - wbase] = (uint16_t)sym; else codes_bm[p] = (uint16_t)sym;
+            if (sym == 0 && field_out) { if (zr < unpred_count) field_out[it.raster] = unpred[zr]; zr++; }
+            it.next(g);
+            p++;
+        }
+    }
+    __syncwarp();
+    if (staged) {
+        const uint32_t cnt = (uint32_t)(wend - wbase);
+        for (uint32_t q = lane; q < cnt; q += 32) codes_bm[wbase + q] = ss[q];
+    }
+}
+
 // prefix sums and write pass of ALL coefficient streams of a call in one launch each (they are a few CTAs apiece; launched
 // separately their launch latencies add up to more than the work)
 __global__ void __launch_bounds__(1024) dec_coef_scan_kernel(const DecJobList *__restrict__ list) {

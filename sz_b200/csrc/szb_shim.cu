@@ -895,8 +895,8 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         DecTree tr{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
         if (launch_scan(c, c.stream, 0, J.count, J.nsub, J.sym_off, nullptr)) return SZ_NSCS;
         if (launch_scan(c, c.stream, 0, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS;
-        const unsigned grid = (unsigned)((J.nsub + 255) / 256);
-        dec_write_kernel<T, true><<<grid, 256, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
+        const unsigned grid = (unsigned)((J.nsub + DECW_TB - 1) / DECW_TB);
+        dec_write_bm_kernel<T><<<grid, DECW_TB, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
         KCHECK();
     }
     // work that only needs the coefficient codes (the coefficient chain) continues on the second stream, beside the main write pass

@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(256) prepass_compress_kernel(Geom g, const T *
 //   Lorenzo block    : code == 0 -> xin = out, given;  mean code -> xin = mean, given;
 //                      else xin = 2*(code'-radius)*eb (the term the wavefront adds to its prediction), not given
 template <typename T, int DIM, bool MEAN>
-__global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const uint16_t *__restrict__ codes, const T *__restrict__ out,
+__global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const uint16_t *__restrict__ codes_bm /*block-major, as decoded*/, const T *__restrict__ out,
                                                                  const unsigned char *__restrict__ indicator, const T *__restrict__ coeff_last,
                                                                  const uint32_t *__restrict__ ktab, T *__restrict__ xin, uint32_t pitch, uint32_t *__restrict__ given,
                                                                  uint32_t wpr, T eb, T mean, int radius) {
@@ -209,13 +209,19 @@ __global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const u
         const uint32_t bid0 = g.block_id(b0, b1, 0);
         const T iif = (T)ii, jjf = (T)jj;
         const uint64_t base = (uint64_t)row * n2;
+        // block-major position of point (row, k): offset of the block (ref: sz_float.c:7064 type_offset) + (ii*sy + jj)*sz + kk
+        const uint32_t sx = g.ax[0].edge(b0), sy = g.ax[1].edge(b1);
+        const uint64_t bm_row = (uint64_t)g.ax[0].off(b0) * g.s0 + (uint64_t)sx * g.ax[1].off(b1) * n2;
+        const uint32_t sxy = sx * sy, rin = ii * sy + jj;
         for (uint32_t k0 = 0; k0 < n2; k0 += 32) {
             const uint32_t k = k0 + lane;
             bool giv = false;
             if (k < n2) {
                 const uint32_t kt = ktab[k];
                 const uint32_t bid = bid0 + (kt >> 8);
-                int tcode = (int)codes[base + k];
+                const uint32_t bk = kt >> 8;
+                const uint32_t bm = sxy * g.ax[2].off(bk) + rin * g.ax[2].edge(bk) + (kt & 255u);
+                int tcode = (int)codes_bm[bm_row + bm];
                 T v;
                 if (tcode == 0) { v = out[base + k]; giv = true; }
                 else if (indicator[bid] == 0) {
