@@ -961,38 +961,7 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const DecJobList *__restr
     }
 }
 
-// final pass: decode each sub-sequence again and write symbols (block-major index = sym_off[s] + m).
-// BLOCKMAJOR: scatter into the raster code array and pre-place unpredictable values into the output field.
-template <typename T, bool BLOCKMAJOR>
-__global__ void __launch_bounds__(256) dec_write_kernel(const uint32_t *__restrict__ words, uint64_t total_bits, uint64_t nsub, DecTree tr,
-                                                        const unsigned long long *__restrict__ start_used,
-                                                        const unsigned long long *__restrict__ sym_off, const unsigned long long *__restrict__ zero_off,
-                                                        uint64_t n, Geom g, uint16_t *codes_out, const T *__restrict__ unpred, uint64_t unpred_count, T *field_out) {
-    __shared__ uint32_t s_lut[1 << DEC_K];
-    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
-    __syncthreads();
-    uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (sidx >= nsub) return;
-    uint64_t p = sym_off[sidx];
-    if (p >= n) return;
-    uint64_t zr = zero_off ? zero_off[sidx] : 0;
-    uint64_t hi = (sidx + 1) * DEC_SUB_BITS;
-    const uint64_t limit = total_bits + 64;
-    if (hi > limit) hi = limit;
-    BitReader br; br.init(words, start_used[sidx]);
-    BMIter it;
-    if (BLOCKMAJOR) it.init(g, p);
-    while (br.pos < hi && p < n) {
-        const uint32_t sym = dec_symbol(br, s_lut, tr);
-        if (BLOCKMAJOR) {
-            codes_out[it.raster] = (uint16_t)sym;
-            if (sym == 0 && field_out) { if (zr < unpred_count) field_out[it.raster] = unpred[zr]; zr++; }
-            it.next(g);
-        } else codes_out[p] = (uint16_t)sym;
-        p++;
-    }
-}
-
+// ---- final pass: decode each sub-sequence again and write its symbols (block-major index = sym_off[s] + m) ----
 // Main-stream write pass, block-major output.  Every warp's 32 sub-sequences hold one contiguous run of symbols in the
 // block-major code array; the warp decodes into shared memory and then writes the run with coalesced stores (a thread storing
 // its own symbols one by one touches a different 32-byte sector per lane and per symbol: ~0.7 ms of sector traffic at 512^3).
