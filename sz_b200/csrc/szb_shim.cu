@@ -559,7 +559,12 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         memcpy(pin, pos.data(), 8ull * cnt);
         CU(cudaMemcpyAsync(d_pos, pin, 8ull * cnt, cudaMemcpyHostToDevice, c.stream));
         CU(cudaMemsetAsync(ob, 0, 4ull * 32768 + 4ull * 8192 + 256, c.stream));
-        sample_mean_kernel<T><<<1, 1024, 0, c.stream>>>(d_x, d_pos, cnt, d_vals, d_mean); KCHECK();
+        {
+            const size_t sm = sizeof(T) * (size_t)cnt + 16;
+            const int in_smem = sm <= c.smem_optin - 1024 ? 1 : 0;
+            if (in_smem) CU(cudaFuncSetAttribute(sample_mean_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+            sample_mean_kernel<T><<<1, 1024, in_smem ? sm : 0, c.stream>>>(d_x, d_pos, cnt, d_vals, d_mean, in_smem); KCHECK();
+        }
         const uint64_t rows = opt_row_limit(g, (uint32_t)job.sampleDistance);
         if (rows > 0) {
             int grid = (int)std::min<uint64_t>((rows + 255) / 256, (uint64_t)c.sm_count * 8);

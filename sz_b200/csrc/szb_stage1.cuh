@@ -99,17 +99,21 @@ __global__ void first_equal_kernel(const T *__restrict__ x, uint64_t n, T v, uns
 // =====================================================================================================================
 template <typename T>
 __global__ void __launch_bounds__(1024) sample_mean_kernel(const T *__restrict__ x, const uint64_t *__restrict__ pos, uint32_t count,
-                                                           T *vals, T *mean_out) {
-    for (uint32_t i = threadIdx.x; i < count; i += blockDim.x) vals[i] = x[pos[i]];
+                                                           T *vals, T *mean_out, int in_smem) {
+    // the gathered samples are staged in shared memory when they fit (the serial adder then reads at shared-memory latency,
+    // eight values per batch), else in the global scratch array
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    T *buf = in_smem ? reinterpret_cast<T *>(s_raw) : vals;
+    for (uint32_t i = threadIdx.x; i < count; i += blockDim.x) buf[i] = x[pos[i]];
     __syncthreads();
     if (threadIdx.x == 0) {
         T mean = (T)0;
         uint32_t i = 0;
         for (; i + 8 <= count; i += 8) {
-            T v0 = vals[i], v1 = vals[i + 1], v2 = vals[i + 2], v3 = vals[i + 3], v4 = vals[i + 4], v5 = vals[i + 5], v6 = vals[i + 6], v7 = vals[i + 7];
+            T v0 = buf[i], v1 = buf[i + 1], v2 = buf[i + 2], v3 = buf[i + 3], v4 = buf[i + 4], v5 = buf[i + 5], v6 = buf[i + 6], v7 = buf[i + 7];
             mean += v0; mean += v1; mean += v2; mean += v3; mean += v4; mean += v5; mean += v6; mean += v7;
         }
-        for (; i < count; i++) mean += vals[i];
+        for (; i < count; i++) mean += buf[i];
         if (count > 0) mean = mean / (T)(unsigned long long)count;
         *mean_out = mean;
     }
