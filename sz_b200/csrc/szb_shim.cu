@@ -808,10 +808,10 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         unsigned char *tb = (unsigned char *)c.get(nm, 16ull * J.nodeCount + 1024 + 4ull * (1u << DEC_K)); if (!tb) return SZ_NSCS;
         J.lut = (uint32_t *)tb; J.L = J.lut + (1u << DEC_K); J.R = J.L + J.nodeCount; J.C = J.R + J.nodeCount; J.leaf = (uint8_t *)(J.C + J.nodeCount);
         dec_tree_unpack_kernel<<<(J.nodeCount + 255) / 256, 256, 0, c.stream>>>(J.d_tree, J.nodeCount, J.L, J.R, J.C, J.leaf); KCHECK();
-        CU(cudaMemcpyAsync(&roots[j].leaf, J.leaf, 1, cudaMemcpyDeviceToHost, c.stream));
-        CU(cudaMemcpyAsync(&roots[j].sym, J.C, 4, cudaMemcpyDeviceToHost, c.stream));
+        // a tree whose root is a leaf has exactly one node (ref: Huffman.c:316-321); only then is the root's symbol needed on the host
+        roots[j].leaf = J.nodeCount == 1 ? 1 : 0; roots[j].sym = 0;
+        if (roots[j].leaf) { CU(cudaMemcpyAsync(&roots[j].sym, J.C, 4, cudaMemcpyDeviceToHost, c.stream)); CU(cudaStreamSynchronize(c.stream)); }
     }
-    CU(cudaStreamSynchronize(c.stream));
     pmark();
     unsigned int *d_changed = (unsigned int *)c.get("dec_changed", 256); if (!d_changed) return SZ_NSCS;
     for (int j = 0; j < njobs; j++) {
