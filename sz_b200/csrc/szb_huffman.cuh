@@ -689,7 +689,9 @@ __global__ void __launch_bounds__(ENC_THREADS) enc_write_kernel(const uint16_t *
 // =====================================================================================================================
 constexpr int DEC_SUB_BITS = 256;
 
-// unpack the serialised tree (arbitrary byte alignment) into u32 child arrays; leaf <=> t != 0
+// unpack the serialised tree (arbitrary byte alignment) into u32 child arrays; leaf <=> t != 0.  A child index carries
+// DEC_CHILD_LEAF when the child is a leaf, so that the bit-serial walk needs one load per bit, not two.
+constexpr uint32_t DEC_CHILD_LEAF = 0x80000000u;
 __global__ void dec_tree_unpack_kernel(const unsigned char *__restrict__ tb, uint32_t nodeCount, uint32_t *L, uint32_t *R, uint32_t *C, uint8_t *leaf) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nodeCount) return;
@@ -698,7 +700,8 @@ __global__ void dec_tree_unpack_kernel(const unsigned char *__restrict__ tb, uin
     uint32_t l = 0, r = 0;
     for (uint32_t b = 0; b < w; b++) { l |= (uint32_t)pl[(size_t)w * i + b] << (8 * b); r |= (uint32_t)pr[(size_t)w * i + b] << (8 * b); }
     uint32_t c = (uint32_t)pc[4 * (size_t)i] | ((uint32_t)pc[4 * (size_t)i + 1] << 8) | ((uint32_t)pc[4 * (size_t)i + 2] << 16) | ((uint32_t)pc[4 * (size_t)i + 3] << 24);
-    L[i] = l < nodeCount ? l : 0; R[i] = r < nodeCount ? r : 0; C[i] = c; leaf[i] = pt[i] ? 1 : 0;
+    L[i] = l < nodeCount ? (l | (pt[l] ? DEC_CHILD_LEAF : 0u)) : 0; R[i] = r < nodeCount ? (r | (pt[r] ? DEC_CHILD_LEAF : 0u)) : 0;
+    C[i] = c; leaf[i] = pt[i] ? 1 : 0;
 }
 
 constexpr int DEC_K = 11;                                   // first-level lookup width (2^11 x 4 B = 8 KB of shared memory per CTA)
@@ -716,8 +719,9 @@ __global__ void dec_lut_kernel(const uint32_t *__restrict__ L, const uint32_t *_
     bool done = false;
     for (int d = 0; d < DEC_K; d++) {
         const uint32_t bit = (v >> (DEC_K - 1 - d)) & 1u;
-        node = bit ? R[node] : L[node];
-        if (leaf[node] || node == 0) { e = DEC_LEAF | ((uint32_t)(d + 1) << 16) | (C[node] & 0xffffu); done = true; break; }
+        const uint32_t nx = bit ? R[node] : L[node];
+        node = nx & ~DEC_CHILD_LEAF;
+        if ((nx & DEC_CHILD_LEAF) || node == 0) { e = DEC_LEAF | ((uint32_t)(d + 1) << 16) | (C[node] & 0xffffu); done = true; break; }
     }
     lut[v] = done ? e : node;
 }
@@ -748,8 +752,9 @@ __device__ __forceinline__ uint32_t dec_symbol(BitReader &br, const uint32_t *s_
         br.refill();
         const uint32_t bit = (uint32_t)(br.buf >> 63);
         br.consume(1);
-        node = bit ? tr.R[node] : tr.L[node];
-        if (tr.leaf[node] || node == 0) break;
+        const uint32_t nx = bit ? tr.R[node] : tr.L[node];
+        node = nx & ~DEC_CHILD_LEAF;
+        if ((nx & DEC_CHILD_LEAF) || node == 0) break;
     }
     return tr.C[node];
 }
