@@ -1160,11 +1160,17 @@ __global__ void __launch_bounds__(DCHAIN_THREADS) coeff_chain_decode_kernel(cons
                 // compiler keeps every step's load behind the previous step's store and the chain pays a shared-memory round trip per step)
                 int i = 0;
                 for (; i + 8 <= cnt; i += 8) {
-                    T v[8], o[8]; unsigned char f[8];
+                    T v[8], o[8];
+                    const unsigned long long fw = *reinterpret_cast<const unsigned long long *>(&s_rst[buf][e][i]);      // the eight reset flags
 #pragma unroll
-                    for (int q = 0; q < 8; q++) { v[q] = s_val[buf][e][i + q]; f[q] = s_rst[buf][e][i + q]; }
+                    for (int q = 0; q < 8; q++) v[q] = s_val[buf][e][i + q];
+                    if (fw == 0ull) {                         // no raw value among the eight (the usual case): a bare add chain
 #pragma unroll
-                    for (int q = 0; q < 8; q++) { const T sum = last + v[q]; last = f[q] ? v[q] : sum; o[q] = last; }
+                        for (int q = 0; q < 8; q++) { last = last + v[q]; o[q] = last; }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 8; q++) { const T sum = last + v[q]; last = ((fw >> (8 * q)) & 0xffull) ? v[q] : sum; o[q] = last; }
+                    }
 #pragma unroll
                     for (int q = 0; q < 8; q++) s_out[lb][e][i + q] = o[q];
                 }
