@@ -90,6 +90,49 @@ def ref_lib():
     return szref.SZLib(szref.REF_SO), szref
 
 
+def _omp_variant(a, ncores):
+    """the reference's OpenMP compressor (sz/src/sz_omp.c:63, float 3D, ABS only, its own stream format) on the same field, in a
+    child process; a reported baseline beside the slab-parallel one.  None when the library is absent."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import szref
+    if not os.path.exists(szref.REF_OMP_SO):
+        return None
+    threads = 1
+    while threads * 2 <= ncores:
+        threads *= 2
+    code = (
+        "import sys, os, time, ctypes as C, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "import szref\n"
+        "a = np.load(%r)\n"
+        "L = C.CDLL(szref.REF_OMP_SO)\n"
+        "cfg = os.path.join(os.path.dirname(%r), 'omp.config'); szref.write_config(cfg, dict(errorBoundMode='ABS', absErrBound=1e-3))\n"
+        "L.SZ_Init.argtypes = [C.c_char_p]; assert L.SZ_Init(cfg.encode()) == 0\n"
+        "f = L.SZ_compress_float_3D_MDQ_openmp; f.restype = C.c_void_p\n"
+        "f.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float, C.POINTER(C.c_size_t)]\n"
+        "eb = %r * float(a.max() - a.min()); n = C.c_size_t(0); best = 1e9\n"
+        "for _ in range(3):\n"
+        "    t0 = time.perf_counter(); p = f(a.ctypes.data, a.shape[0], a.shape[1], a.shape[2], eb, C.byref(n)); best = min(best, time.perf_counter() - t0)\n"
+        "print('OMP', best, n.value)\n"
+    )
+    import tempfile
+    tmp = tempfile.NamedTemporaryFile(suffix=".npy", delete=False)
+    np.save(tmp.name, a)
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads))
+    try:
+        out = subprocess.run([sys.executable, "-c", code % (os.path.join(ROOT, "tests"), tmp.name, tmp.name, REL_BOUND)], env=env, capture_output=True, text=True, timeout=300)
+        for ln in out.stdout.splitlines():
+            if ln.startswith("OMP "):
+                _, t, nbytes = ln.split()
+                return {"value": a.nbytes / float(t) / 1e9, "unit": UNIT, "threads": threads, "stream_bytes": int(nbytes),
+                        "note": "reference sz_omp.c float 3D, ABS bound = rel x range; a different stream format, timing baseline only"}
+    except Exception:
+        pass
+    finally:
+        os.unlink(tmp.name)
+    return None
+
+
 def _ref_worker(args):
     """one slab compressed by the UNMODIFIED reference in its own process (its global state is not thread-safe)."""
     path, lo, hi, shape, rel = args
@@ -143,6 +186,7 @@ def run_reference(args):
     os.unlink(tmp.name)
     ms = 1e3 * sum(times) / len(times)
     gbps = a.nbytes / (ms * 1e-3) / 1e9
+    omp = _omp_variant(a, ncores) if lib is not None else None
     line = {"impl": "reference", "metric": METRIC, "value": gbps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "NYX-shape 512x512x512 fp32 synthetic smooth field, REL 1e-3, SZ_BEST_SPEED (BASELINE.json configs[1])",
@@ -151,6 +195,8 @@ def run_reference(args):
                              "sample": "one 512^3 field per step, cut into %d independent slabs (reference's slab-parallel pattern)" % len(bounds)},
             "e2e": {"value": gbps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "compressed_bytes": int(sum(sizes)), "ratio": a.nbytes / float(sum(sizes))}
+    if omp is not None:
+        line["openmp_variant"] = omp
     print(json.dumps(line))
 
 
