@@ -531,6 +531,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     if (job.max_quant_intervals > 65536 || job.quantization_intervals > 65536) { set_err("more than 65536 quantization intervals is not supported"); return SZ_NSCS; }
     if (job.sampleDistance < 2) { set_err("sampleDistance must be >= 2"); return SZ_NSCS; }
     c.launches = 0;
+    CU(cudaStreamSynchronize(c.stream2));       // a call that failed half-way may have left work on the side stream
     int evi = 0;
     CU(cudaEventRecord(c.ev[evi++], c.stream));
     float ms_stage[16]; memset(ms_stage, 0, sizeof(ms_stage));
@@ -925,6 +926,7 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     const int ncoef = g.ncoef; const uint32_t nb = g.num_blocks; const uint64_t N = g.N;
     if (N >= (1ull << 32)) { set_err("arrays of 2^32 or more elements must be cut into slabs"); return SZ_DERR; }
     c.launches = 0;
+    CU(cudaStreamSynchronize(c.stream2));       // a call that failed half-way may have left work on the side stream
     int evi = 0; int stage_of_ev[24];
     CU(cudaEventRecord(c.ev[evi++], c.stream));
     auto mark = [&](int st) -> int { stage_of_ev[evi] = st; CU(cudaEventRecord(c.ev[evi++], c.stream)); return 0; };
