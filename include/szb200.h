@@ -52,7 +52,8 @@ typedef struct szb200_stats {
 
 const char *szb200_stage_name(int i);
 
-/* device management: one context (stream + grow-only workspace) per device and host thread */
+/* device management: one context (two streams + grow-only workspace) per device and worker lane; every single call uses lane 0 of the
+ * current device, the batch entry points give each of their worker threads a lane of its own (szb200_set_lane) */
 int szb200_device_count(void);
 int szb200_set_device(int device);
 const char *szb200_last_error(void);
