@@ -851,6 +851,7 @@ struct DecJobDev {
     const unsigned long long *end_prev; unsigned long long *end_cur, *start_used; uint32_t *count, *zcount;
     unsigned int *changed; uint32_t cta_begin, active;
     unsigned long long *sym_off; uint64_t nsym; uint16_t *out;          // write pass of the coefficient streams
+    unsigned long long *total;                                          // number of symbols the stream really holds (checked by the host)
 };
 constexpr int DEC_MAX_JOBS = 5;
 struct DecJobList { DecJobDev j[DEC_MAX_JOBS]; int n; };
@@ -1039,6 +1040,7 @@ __global__ void __launch_bounds__(1024) dec_coef_scan_kernel(const DecJobList *_
         if (t == 0) s_carry = carry + tot;
         __syncthreads();
     }
+    if (t == 0 && J.total) *J.total = s_carry;
 }
 __global__ void __launch_bounds__(256) dec_coef_write_kernel(const DecJobList *__restrict__ list) {
     int jid = 0;

@@ -796,7 +796,7 @@ struct DecJob {
 
 template <typename T>
 static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const T *d_unpred, uint64_t unpred_count, T *d_field,
-                           const std::function<int(cudaStream_t)> &side_tail) {
+                           const std::function<int(cudaStream_t)> &side_tail, unsigned long long **d_totals_out, uint64_t *expect /*[5], 0 = not checked*/) {
     char nm[48];
     struct RootInfo { uint8_t leaf; uint32_t sym; } roots[8];
     const bool prof = getenv("SZB200_DEC_PROFILE") != nullptr;
@@ -870,6 +870,12 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         if (round > 100000) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
     }
     pmark();
+    // the prefix sums also give the number of symbols every stream really holds; the caller compares them with the counts the
+    // header promises once the job is done (a truncated stream otherwise decodes "successfully" into too few symbols)
+    unsigned long long *d_dtot = (unsigned long long *)c.get("dec_totals", 64); if (!d_dtot) return SZ_NSCS;
+    CU(cudaMemsetAsync(d_dtot, 0, 64, c.stream));
+    *d_totals_out = d_dtot;
+    for (int j = 0; j < 5; j++) expect[j] = (j < njobs && !jobs[j].single_leaf) ? jobs[j].nsym : 0;
     // prefix sums and the write pass: the main stream on the context's stream; all coefficient streams beside it on the second
     // one, with one launch for their prefix sums and one for their write passes
     CU(cudaEventRecord(c.ev_fork, c.stream));
@@ -883,7 +889,7 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
             if (J.single_leaf || J.blockmajor) continue;
             DecJobDev &D = L.j[L.n++];
             D.words = J.words; D.total_bits = J.total_bits; D.nsub = J.nsub; D.tr = DecTree{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
-            D.start_used = J.start_used; D.count = J.count; D.sym_off = J.sym_off; D.nsym = J.nsym; D.out = J.d_out;
+            D.start_used = J.start_used; D.count = J.count; D.sym_off = J.sym_off; D.nsym = J.nsym; D.out = J.d_out; D.total = d_dtot + j;
             D.cta_begin = ctas; D.active = 1;
             ctas += (uint32_t)((J.nsub + 255) / 256);
         }
@@ -899,7 +905,7 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         DecJob &J = jobs[j];
         if (J.single_leaf || !J.blockmajor) continue;
         DecTree tr{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
-        if (launch_scan(c, c.stream, 0, J.count, J.nsub, J.sym_off, nullptr)) return SZ_NSCS;
+        if (launch_scan(c, c.stream, 0, J.count, J.nsub, J.sym_off, d_dtot + j)) return SZ_NSCS;
         if (launch_scan(c, c.stream, 0, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS;
         const unsigned grid = (unsigned)((J.nsub + DECW_TB - 1) / DECW_TB);
         dec_write_bm_kernel<T><<<grid, DECW_TB, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
@@ -990,6 +996,7 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, 0, d_dummy, d_dummy2, d_list); KCHECK();
         for (int e = 0; e < ncoef; e++) if (cunp_cnt[e]) CU(cudaMemcpyAsync(d_cu + (size_t)e * nb, d_body + o_cunp[e], sizeof(T) * cunp_cnt[e], cudaMemcpyDeviceToDevice, c.stream));
     }
+    unsigned long long *d_dec_totals = nullptr; uint64_t dec_expect[5] = {0, 0, 0, 0, 0};
     auto chain_tail = [&](cudaStream_t st) -> int {
         if (reg_count == 0) return 0;
         T *d_dval = (T *)c.get("dchain_val", sizeof(T) * 4ull * reg_count + 64);
@@ -1012,7 +1019,7 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
             jobs[nj].slot = 1 + e; jobs[nj].d_tree = d_body + o_ctree[e]; jobs[nj].nodeCount = cnode[e]; jobs[nj].d_payload = d_body + o_cbits[e]; jobs[nj].payload_bytes = cbits_bytes[e];
             jobs[nj].nsym = reg_count; jobs[nj].blockmajor = false; jobs[nj].d_out = d_ctype + (size_t)e * nb; nj++;
         }
-        if (huff_decode_all<T>(c, jobs, nj, g, d_unp, total_unpred, d_out, chain_tail)) return SZ_NSCS;
+        if (huff_decode_all<T>(c, jobs, nj, g, d_unp, total_unpred, d_out, chain_tail, &d_dec_totals, dec_expect)) return SZ_NSCS;
     }
     if (mark(ST_DECODE)) return SZ_NSCS;
 
@@ -1026,7 +1033,14 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
         if (rc) return rc;
     }
     if (mark(ST_RECON)) return SZ_NSCS;
-    if (check_wf_err(c)) return SZ_NSCS;
+    unsigned long long h_dec_totals[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (d_dec_totals) CU(cudaMemcpyAsync(h_dec_totals, d_dec_totals, sizeof(h_dec_totals), cudaMemcpyDeviceToHost, c.stream));
+    if (check_wf_err(c)) return SZ_NSCS;          // (synchronises the stream)
+    for (int j = 0; j < 5; j++)
+        if (dec_expect[j] && h_dec_totals[j] < dec_expect[j]) {
+            set_err("truncated stream: Huffman section %d holds %llu symbols, %llu expected", j, h_dec_totals[j], (unsigned long long)dec_expect[j]);
+            return SZ_NSCS;
+        }
     szb200_stats st; memset(&st, 0, sizeof(st));
     st.intervals = intervals; st.use_mean = use_mean; st.mean = (double)mean; st.num_blocks = nb; st.reg_count = reg_count; st.total_unpred = total_unpred;
     st.tree_bytes = tree_size; st.node_count = nodeCount; st.type_bits_bytes = main_bytes; st.body_bytes = body_len; st.launches = c.launches;

@@ -193,6 +193,32 @@ def test_batch_of_fields_equals_individual_calls(sz):
         sz.finalize()
 
 
+def test_batch_reports_a_bad_item_without_spoiling_the_others(sz):
+    """one truncated stream inside a batch: its item fails loudly (negative rc), the other items still decode bit-exactly"""
+    import ctypes as C
+    import torch
+    from sz_b200.api import BatchItem
+    shape, dt, mode, ab, rl = (40, 44, 48), np.float32, szref.ABS, 1e-3, 1e-3
+    sz.init(cases.make_cfg(mode, ab, rl, {}))
+    fields = [szref.smooth_field(shape, dt, span=5 * np.pi, field_id=k) for k in range(4)]
+    streams = [sz.compress(a, mode, ab, rl) for a in fields]
+    dev = [torch.from_numpy(np.frombuffer(s, dtype=np.uint8).copy()).cuda() for s in streams]
+    outs = [torch.empty(shape, dtype=torch.float32, device="cuda") for _ in fields]
+    items = (BatchItem * 4)()
+    for i in range(4):
+        items[i].d_stream, items[i].stream_capacity, items[i].d_out = dev[i].data_ptr(), len(streams[i]), outs[i].data_ptr()
+    items[2].stream_capacity = len(streams[2]) // 3            # truncated
+    L = sz.lib()
+    L.szb200_decompress_batch_device.argtypes = [C.c_int, C.POINTER(BatchItem), C.c_int, C.c_int] + [C.c_size_t] * 5
+    L.szb200_decompress_batch_device.restype = C.c_int
+    rc = L.szb200_decompress_batch_device(sz.SZ_FLOAT, items, 4, 2, 0, 0, *shape)
+    assert rc != 0 and items[2].rc != 0
+    for i in (0, 1, 3):
+        assert items[i].rc == 0
+        assert outs[i].cpu().numpy().tobytes() == sz.decompress(streams[i], dt, shape).tobytes()
+    sz.finalize()
+
+
 _DROPIN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "dropin")
 
 
