@@ -195,6 +195,16 @@ float *readFloatData(char *srcFilePath, size_t *nbEle, int *status);
 void writeByteData(unsigned char *bytes, size_t byteLength, char *tgtFilePath, int *status);
 void writeFloatData_inBytes(float *data, size_t nbEle, char *tgtFilePath, int *status);
 void writeDoubleData_inBytes(double *data, size_t nbEle, char *tgtFilePath, int *status);
+/* ---- what the reference's command-line tool (example/sz.c) needs beyond those (ref: sz/include/rw.h:31,66,67,78 and
+ *      sz/include/utility.h:34-38), also in sz_io.c.  A file that carries a zstd/gzip pass (szMode != SZ_BEST_SPEED) is recognised
+ *      and refused: that back-end is outside this library. ---- */
+int checkFileExistance(char *filePath);
+void writeStrings(int nbStr, char *str[], char *tgtFilePath, int *status);
+void writeFloatData(float *data, size_t nbEle, char *tgtFilePath, int *status);
+void writeDoubleData(double *data, size_t nbEle, char *tgtFilePath, int *status);
+void *detransposeData(void *data, int dataType, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+int is_lossless_compressed_data(unsigned char *compressedBytes, size_t cmpSize);
+unsigned long sz_lossless_decompress65536bytes(int losslessCompressor, unsigned char *compressBytes, unsigned long cmpSize, unsigned char **oriData);
 
 #ifdef __cplusplus
 }

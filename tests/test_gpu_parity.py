@@ -244,6 +244,43 @@ def test_reference_example_programs_run_unmodified_on_the_library(sz, tmp_path, 
     assert hashlib.md5(out).hexdigest() == gold["dec_md5"], r.stdout
 
 
+@pytest.mark.skipif(not os.path.exists(os.path.join(_DROPIN, "sz")), reason="relinked reference command-line tool (make -C oracle dropin) not present")
+@pytest.mark.parametrize("kind", ["float", "double"])
+def test_reference_command_line_tool_runs_unmodified_on_the_library(sz, tmp_path, kind):
+    """the reference's command-line tool (example/sz.c), compiled unmodified and linked against libSZ_b200.so:
+    `sz -z` writes the reference's stream, `sz -x` the reference's reconstruction, `-a` reports the bound as held, `-p` prints
+    the stream's metadata."""
+    import hashlib
+    import shutil
+    import subprocess
+    exe = os.path.join(_DROPIN, "sz")
+    flag = "-f" if kind == "float" else "-d"
+    dat = "test%s_8_8_128.dat" % kind
+    shutil.copy(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", dat), tmp_path / dat)
+    szref.write_config(str(tmp_path / "sz.config"), cases.make_cfg(szref.ABS, 1e-4, 1e-3, {}))
+    gold = GOLD["test%s_8_8_128_abs" % kind] if kind == "float" else GOLD["cfg1_testdouble_8_8_128_abs"]
+    r = subprocess.run([exe, "-z", flag, "-c", "sz.config", "-i", dat, "-3", "8", "8", "128"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "compressed data file" in r.stdout, r.stdout + r.stderr
+    stream = (tmp_path / (dat + ".sz")).read_bytes()
+    assert len(stream) == gold["size"] and hashlib.md5(stream).hexdigest() == gold["md5"]
+    r = subprocess.run([exe, "-x", flag, "-s", dat + ".sz", "-i", dat, "-3", "8", "8", "128", "-a"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "decompressed data file" in r.stdout, r.stdout + r.stderr
+    out = (tmp_path / (dat + ".sz.out")).read_bytes()
+    assert hashlib.md5(out).hexdigest() == gold["dec_md5"], r.stdout
+    line = [l for l in r.stdout.splitlines() if l.startswith("Max absolute error")]
+    assert line and float(line[0].split("=")[1]) <= 1e-4, r.stdout
+    r = subprocess.run([exe, "-p", "-s", dat + ".sz"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ABS" in r.stdout, r.stdout + r.stderr
+    # the -M / -A overrides of the tool write into confparams_cpr directly: the library must honour them
+    r = subprocess.run([exe, "-z", flag, "-c", "sz.config", "-i", dat, "-M", "REL", "-R", "1E-3", "-3", "8", "8", "128"], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    a = np.fromfile(tmp_path / dat, dtype=np.float32 if kind == "float" else np.float64).reshape(128, 8, 8)
+    sz.init(dict(errorBoundMode="REL", relBoundRatio=1e-3))
+    want = sz.compress(a, sz.REL, 1e-4, 1e-3)
+    sz.finalize()
+    assert (tmp_path / (dat + ".sz")).read_bytes() == bytes(want)
+
+
 def test_device_pointer_api_roundtrip_and_determinism(sz):
     import torch
     a = szref.smooth_field((200, 210, 220), np.float32, span=6 * np.pi)
