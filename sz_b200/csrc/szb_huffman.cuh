@@ -227,179 +227,205 @@ __device__ __forceinline__ uint32_t heap_build_tree(const H &h, int hcap, uint32
     return h.ldn(1);
 }
 
-// ---- two-thread form of the same heap (shared-memory case) -----------------------------------------------------------
-// Only the frequencies decide what a sift does; the node ids merely follow.  Thread A (warp 0) therefore runs the sifts on f[]
-// alone and describes each operation to thread B (warp 1, another scheduler) with one queue entry -- for a removal the final
-// position of the moved element (the path is its chain of ancestors), for an insertion the start and final positions -- and B
-// replays the node-id moves on n[] and writes the children of every merged node.  A never reads n[], so the queue is one-way:
-// single producer, single consumer, entries tagged with their sequence number.  This takes the node-id traffic (a quarter of
-// the instructions of a sift level) off the serial thread.
+// ---- two-warp form of the same heap (frequencies in shared memory) ------------------------------------------------------
+// Only the frequencies decide what a sift does; the node ids merely follow.  Warp 0 (the producer) therefore runs the sifts on
+// f[] alone and describes them to warp 1 (the consumer, another scheduler) with ONE queue entry per merge -- the final positions
+// of the two removals and of the insertion; everything else (where an element is taken from or appended, the node number) the
+// consumer counts along -- and the consumer replays the node-id moves on n[] and writes the children of every merged node.  The
+// producer never reads n[], so the queue is one-way: single producer, single consumer, entries tagged with their sequence number.
 constexpr int HQ_CAP = 512;                                   // queue entries (one 64-bit word each)
-enum { HQ_REMOVE = 0, HQ_INSERT = 1, HQ_FIN = 2 };
-// entry = {low word: a:16 | b:16, high word: c:18 | kind:2 | tag:12}, written and read with ONE 64-bit shared-memory access
-// (single-copy atomic), so the consumer sees either the old or the new entry, never a mixture, and no fence is needed: nothing
-// else is shared between the two threads.  Positions a, b are below 65536 in every shared-memory layout.  tag = (sequence
-// number + 1) mod 4096; the ring holds 512 entries, so the entry that occupied a slot one lap earlier differs in the tag, and
-// so does the all-zero initial state for the first lap.
+enum { HQ_MERGE = 0, HQ_LEAF = 1, HQ_FIN = 2 };
+// entry = {low word: p1:16 | p2:16, high word: p3:16 | kind:2 | -:2 | tag:12}, written and read with ONE 64-bit shared-memory
+// access (single-copy atomic), so the consumer sees either the old or the new entry, never a mixture, and no fence is needed:
+// nothing else is shared between the two warps.  Positions are below 65536 in every shared-memory layout.  tag = (sequence number
+// + 1) mod 4096; the ring holds 512 entries, so the entry that occupied a slot one lap earlier differs in the tag, and so does the
+// all-zero initial state for the first lap.
 struct HeapQueue {
     unsigned int qa;                                          // shared address of the ring
     unsigned int *done;                                       // consumer progress (generic pointer into shared memory)
     uint32_t t;                                               // producer: next sequence number
-    __device__ __forceinline__ void push(uint32_t kind, uint32_t a, uint32_t b, uint32_t c) {
+    bool lane0;                                               // every lane of the producer runs push(), lane 0 stores
+    __device__ __forceinline__ void push(uint32_t kind, uint32_t p1, uint32_t p2, uint32_t p3) {
         if ((t & 127u) == 0 && t >= HQ_CAP - 128) {           // back-pressure, checked every 128 entries
             while (t - *(volatile unsigned int *)done > HQ_CAP - 128) { }
         }
-        const uint32_t lo = a | (b << 16), hi = c | (kind << 18) | (((t + 1) & 4095u) << 20);
+        const uint32_t lo = p1 | (p2 << 16), hi = p3 | (kind << 16) | (((t + 1) & 4095u) << 20);
         unsigned long long e;
         asm volatile("mov.b64 %0, {%1, %2};" : "=l"(e) : "r"(lo), "r"(hi));
-        asm volatile("st.volatile.shared.u64 [%0], %1;" ::"r"(qa + 8u * (t & (HQ_CAP - 1))), "l"(e) : "memory");
+        if (lane0) asm volatile("st.volatile.shared.u64 [%0], %1;" ::"r"(qa + 8u * (t & (HQ_CAP - 1))), "l"(e) : "memory");
         t++;
     }
 };
 
-// thread A: frequencies only
-__device__ __forceinline__ void heap2_insert(const HeapSmem &h, HeapQueue &Q, int &qend, uint32_t freq, uint32_t node) {
+// The producer is a WARP whose 32 lanes run the same code on the same values (the removals are simply executed redundantly: same
+// addresses, same data).  The lanes serve the insertion: the positions an inserted element can pass are the ancestors of the slot
+// it is appended at, a chain known up front, so lane k fetches the ancestor k levels up, one vote finds the first ancestor that
+// stays (frequency <= the new one, Huffman.c:76-85), and the lanes below it store their value one level down.  Returns the final
+// position.
+// WITH_N: the node ids travel in the same pass (leaf phase, n[] in shared memory: the consumer then has nothing to do for it).
+// The heap is ordered, so up the chain the frequencies only fall: the ancestors that move are a prefix of the chain and their
+// number is a population count.  The removals before an insertion need no barrier (every lane ran all of their stores itself); the
+// insertion's stores come from different lanes, hence the barrier after it.
+template <bool WITH_N>
+__device__ __forceinline__ uint32_t heap2_insert_warp(const HeapSmem &h, int &qend, uint32_t freq, uint32_t node, int lane) {
     const int q0 = qend++;
-    int i = q0, j;
-    while ((j = i >> 1)) {
-        const uint32_t fj = h.ldf(j);
-        if (fj <= freq) break;
-        h.stf(i, fj); i = j;
-    }
-    h.stf(i, freq);
-    Q.push(HQ_INSERT, (uint32_t)q0, (uint32_t)i, node);
+    const int p = q0 >> lane;                                   // lane 0: the new slot; lane k: its ancestor k levels up (0: above the root)
+    uint32_t fk = 0u, nk = 0u;
+    bool down = false;
+    if (lane >= 1 && p >= 1) { fk = h.ldf(p); if (WITH_N) nk = h.ldn(p); down = fk > freq; }
+    const int s = __popc(__ballot_sync(0xffffffffu, down)) + 1;  // ancestors 1 .. s-1 move down, the new element lands on ancestor s-1
+    const int fin = q0 >> (s - 1);
+    if (down) { h.stf(q0 >> (lane - 1), fk); if (WITH_N) h.stn(q0 >> (lane - 1), nk); }
+    if (lane == 0) { h.stf(fin, freq); if (WITH_N) h.stn(fin, node); }
+    __syncwarp();
+    return (uint32_t)fin;
 }
+// Removal (ref: Huffman.c:87-114), "hole" form: the element taken from the end sinks from the root while it is STRICTLY larger than
+// the smaller child (right child only if STRICTLY smaller).  THREE levels per trip: the children f[2i..2i+1], the grandchildren
+// f[4i..4i+3] and the great-grandchildren f[8i..8i+7] are fetched together (all addresses follow from i alone), so the serial chain
+// holds one shared-memory round trip per three levels; the three decisions are then taken in registers (compare, select, compare,
+// select, compare) and the trip ends in ONE branch: the stores of the trip are predicated on how far the element sinks.
 // LIM = false: the frequency array has room for the children of every position a sift can reach (cap >= 2 * (leaves + 2)), so the
-// "no child slots" test drops out of the level loop
+// "no child slots" tests drop out.  A quad that would start beyond the array is fetched from a clamped address and never used:
+// whenever a position is occupied its children's slots exist, and with them the whole aligned quad around them (cap is a
+// multiple of 4).  Returns the removed frequency; fin = final position of the moved element (0: heap now empty).
 template <bool LIM>
-__device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, HeapQueue &Q, int &qend, int cap, uint32_t out_code) {
+__device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, int &qend, int cap, uint32_t &fin) {
     const uint32_t topf = h.ldf(1);
     qend--;
     const uint32_t mf = h.ldf(qend);
     h.stf(qend, HEAP_FINF);
-    if (qend == 1) { Q.push(HQ_REMOVE, 0u, 1u, out_code); return topf; }
-    const int lim = cap >> 1;
-    const int qmax = cap - 4;
+    if (qend == 1) { fin = 0u; return topf; }
+    const int lim = cap >> 1;                                   // positions >= lim have no child slots
+    const int qmax = cap - 4, pmax = cap - 2;
     int i = 1;
-    uint2 pr = h.ldf2(2);
-    uint4 qa = h.ldf4(4), qb;
-#define SZB_SIFT2_LEVEL(QCUR, QNEXT)                                                       \
-    {                                                                                      \
-        const bool r = pr.y < pr.x;                                                        \
-        const uint32_t fc = min(pr.x, pr.y);                                               \
-        if (!(mf > fc)) break;                                                             \
-        h.stf(i, fc);                                                                      \
-        i = 2 * i + (r ? 1 : 0);                                                           \
-        pr = r ? make_uint2(QCUR.z, QCUR.w) : make_uint2(QCUR.x, QCUR.y);                  \
-        if (LIM && i >= lim) pr = make_uint2(HEAP_FINF, HEAP_FINF);                        \
-        QNEXT = h.ldf4(min(4 * i, qmax));                                                  \
-    }
     for (;;) {
-        SZB_SIFT2_LEVEL(qa, qb)
-        SZB_SIFT2_LEVEL(qb, qa)
+        uint2 P = h.ldf2(LIM ? min(2 * i, pmax) : 2 * i);
+        const uint4 Q = h.ldf4(min(4 * i, qmax));
+        const uint4 O0 = h.ldf4(min(8 * i, qmax)), O1 = h.ldf4(min(8 * i + 4, qmax));
+        if (LIM && i >= lim) P = make_uint2(HEAP_FINF, HEAP_FINF);
+        const bool r1 = P.y < P.x;
+        const uint32_t c1 = min(P.x, P.y);
+        const int i1 = 2 * i + (r1 ? 1 : 0);
+        uint2 P2 = r1 ? make_uint2(Q.z, Q.w) : make_uint2(Q.x, Q.y);
+        const uint4 H = r1 ? O1 : O0;
+        if (LIM && i1 >= lim) P2 = make_uint2(HEAP_FINF, HEAP_FINF);
+        const bool r2 = P2.y < P2.x;
+        const uint32_t c2 = min(P2.x, P2.y);
+        const int i2 = 2 * i1 + (r2 ? 1 : 0);
+        uint2 P3 = r2 ? make_uint2(H.z, H.w) : make_uint2(H.x, H.y);
+        if (LIM && i2 >= lim) P3 = make_uint2(HEAP_FINF, HEAP_FINF);
+        const bool r3 = P3.y < P3.x;
+        const uint32_t c3 = min(P3.x, P3.y);
+        const int i3 = 2 * i2 + (r3 ? 1 : 0);
+        const bool g1 = mf > c1, g2 = g1 && mf > c2, g3 = g2 && mf > c3;      // sinks below level 1 / 2 / 3 of this trip
+        if (g1) h.stf(i, c1);
+        if (g2) h.stf(i1, c2);
+        if (g3) h.stf(i2, c3);
+        if (!g3) { i = g2 ? i2 : (g1 ? i1 : i); break; }
+        i = i3;
     }
-#undef SZB_SIFT2_LEVEL
     h.stf(i, mf);
-    Q.push(HQ_REMOVE, (uint32_t)i, (uint32_t)qend, out_code);
+    fin = (uint32_t)i;
     return topf;
 }
-template <bool LIM>
-__device__ __forceinline__ void heap2_thread_a(const HeapSmem &h, HeapQueue &Q, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
+// LEAFN: n[] is in shared memory and the producer fills it during the leaf phase itself (no queue traffic until the first merge)
+template <bool LIM, bool LEAFN>
+__device__ __forceinline__ void heap2_warp_a(const HeapSmem &h, HeapQueue &Q, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
+    int lane = threadIdx.x & 31;
+    asm volatile("mov.u32 %0, %0;" : "+r"(lane));                // kept in a register (the special register is not re-read per use)
+    Q.lane0 = lane == 0;
     int qend = 1;
-    uint32_t k = 0;
-    for (; k + 4 <= leaves; k += 4) {
-        uint32_t f0 = lfreq[k], f1 = lfreq[k + 1], f2 = lfreq[k + 2], f3 = lfreq[k + 3];
-        heap2_insert(h, Q, qend, f0, k); heap2_insert(h, Q, qend, f1, k + 1); heap2_insert(h, Q, qend, f2, k + 2); heap2_insert(h, Q, qend, f3, k + 3);
+    // leaf frequencies: one coalesced load per 32 leaves, the next group in flight while this one is inserted
+    uint32_t cur = (uint32_t)lane < leaves ? lfreq[lane] : 0u;
+    for (uint32_t k0 = 0; k0 < leaves; k0 += 32) {
+        const uint32_t nxt = k0 + 32u + (uint32_t)lane < leaves ? lfreq[k0 + 32u + lane] : 0u;
+        const int cnt = (int)min(32u, leaves - k0);
+        for (int j = 0; j < cnt; j++) {
+            const uint32_t f = __shfl_sync(0xffffffffu, cur, j);
+            const uint32_t fin = heap2_insert_warp<LEAFN>(h, qend, f, k0 + (uint32_t)j, lane);
+            if (!LEAFN) Q.push(HQ_LEAF, 0u, 0u, fin);
+        }
+        cur = nxt;
     }
-    for (; k < leaves; k++) heap2_insert(h, Q, qend, lfreq[k], k);
-    D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
-    uint32_t nn = leaves;
+    if (LEAFN) __threadfence_block();                           // n[] as left by the leaf phase, before the first queue entry
+    if (lane == 0) D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
     while (qend > 2) {
-        const uint32_t fb = heap2_remove<LIM>(h, Q, qend, hcap, (nn << 1) | 1u);   // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
-        const uint32_t fa = heap2_remove<LIM>(h, Q, qend, hcap, (nn << 1) | 0u);   // second removed -> left
-        heap2_insert(h, Q, qend, fa + fb, nn);
-        nn++;
+        uint32_t p1, p2;
+        const uint32_t fb = heap2_remove<LIM>(h, qend, hcap, p1);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+        const uint32_t fa = heap2_remove<LIM>(h, qend, hcap, p2);    // second removed -> left
+        const uint32_t p3 = heap2_insert_warp<false>(h, qend, fa + fb, 0u, lane);
+        Q.push(HQ_MERGE, p1, p2, p3);
     }
     Q.push(HQ_FIN, 0u, 0u, 0u);
-    D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
-}
-// thread B: node ids.  Returns the root node.
-__device__ __forceinline__ uint32_t heap2_thread_b(const HeapSmem &h, unsigned int qaddr, unsigned int *done, const HuffTreeDesc &D) {
-    for (uint32_t t = 0;; t++) {
-        const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
-        unsigned long long e;
-        do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 52) != ((t + 1) & 4095u));
-        const uint32_t kind = (uint32_t)(e >> 50) & 3u;
-        const uint32_t a = (uint32_t)e & 0xffffu, b = ((uint32_t)e >> 16) & 0xffffu, c = (uint32_t)(e >> 32) & 0x3ffffu;
-        if (kind == HQ_FIN) break;
-        if (kind == HQ_REMOVE) {
-            // a = final position of the moved element (0: the heap became empty), b = position it was taken from
-            const uint32_t topn = h.ldn(1);
-            if (c & 1u) D.n_right[c >> 1] = topn; else D.n_left[c >> 1] = topn;
-            if (a != 0) {
-                const uint32_t mn = h.ldn((int)b);
-                const int depth = 31 - __clz(a);
-                // the path is the chain of ancestors of a; every node moves up one level, top-down (each source is still intact)
-                uint32_t v = depth > 0 ? h.ldn((int)(a >> (depth - 1))) : 0u;
-                for (int j = 1; j <= depth; j++) {
-                    const uint32_t src = a >> (depth - j);
-                    const uint32_t vn = (j < depth) ? h.ldn((int)(a >> (depth - j - 1))) : 0u;      // next source, fetched before the store
-                    h.stn((int)(src >> 1), v);
-                    v = vn;
-                }
-                h.stn((int)a, mn);
-            }
-        } else {
-            // insertion: a = position appended at, b = final position, c = node id; ancestors move down one level, bottom-up
-            uint32_t pos = a;
-            while (pos != b) { h.stn((int)pos, h.ldn((int)(pos >> 1))); pos >>= 1; }
-            h.stn((int)b, c);
-        }
-        if ((t & 63u) == 63u) *(volatile unsigned int *)done = t + 1;
-    }
-    return h.ldn(1);
+    if (lane == 0) D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
 }
 
-// the node-id side for trees whose two arrays do not both fit into shared memory: f[] keeps all of it (up to ~54 k entries)
-// and n[] lives in global memory.  One WARP replays each operation: every lane fetches one node of the ancestor chain (all the
-// loads of an operation are in flight together: one L2 round trip), the warp synchronises, every lane stores its value one
-// level up.  Returns the root node (lane 0).
-__device__ __forceinline__ uint32_t heap2_warp_b_global(uint32_t *ng, unsigned int qaddr, unsigned int *done, const HuffTreeDesc &D) {
+// The consumer (warp 1): node ids.  The warp replays each operation with one lane per node of the ancestor chain: all the loads of
+// an operation are in flight together, the warp synchronises, every lane stores its value one level up (removal) or down
+// (insertion).  NA is where n[] lives: shared memory (16- or 32-bit ids), or -- for trees whose two arrays do not both fit; f[]
+// then keeps all of the shared memory, up to ~54 k entries -- global memory.  Returns the root node.
+struct NodeIdsSmem {
+    HeapSmem h;
+    __device__ __forceinline__ uint32_t ld(uint32_t i) const { return h.ldn((int)i); }
+    __device__ __forceinline__ void st(uint32_t i, uint32_t v) const { h.stn((int)i, v); }
+};
+struct NodeIdsGmem {
+    uint32_t *ng;
+    __device__ __forceinline__ uint32_t ld(uint32_t i) const { return __ldcg(ng + i); }
+    __device__ __forceinline__ void st(uint32_t i, uint32_t v) const { ng[i] = v; }
+};
+// removal: a = final position of the moved element (0: the heap became empty), b = position it was taken from; the path is the
+// chain of ancestors of a, every node of it moves up one level; the old root goes to *out
+template <typename NA>
+__device__ __forceinline__ void heap2_replay_remove(const NA &na, uint32_t a, uint32_t b, uint32_t *out, int lane) {
+    const int depth = a ? 31 - __clz(a) : 0;
+    const bool on_path = a != 0u && lane >= 1 && lane <= depth;
+    const bool last = a != 0u && lane == 31;
+    const uint32_t src = last ? b : (on_path ? a >> (depth - lane) : 1u);                // lane 0: the root
+    uint32_t v = 0u;
+    if (lane == 0 || on_path || last) v = na.ld(src);
+    __syncwarp();
+    if (on_path || last) na.st(last ? a : src >> 1, v);
+    if (lane == 0) *out = v;
+    __syncwarp();
+}
+// insertion: a = position appended at, b = final position, c = node id; the ancestors in between move down one level
+template <typename NA>
+__device__ __forceinline__ void heap2_replay_insert(const NA &na, uint32_t a, uint32_t b, uint32_t c, int lane) {
+    const int k = __clz(b) - __clz(a);                                                   // depth(a) - depth(b)
+    uint32_t v = c;
+    if (lane < k) v = na.ld(a >> (lane + 1));
+    __syncwarp();
+    if (lane < k) na.st(a >> lane, v);
+    if (lane == 31) na.st(b, c);
+    __syncwarp();
+}
+template <typename NA>
+__device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qaddr, unsigned int *done, uint32_t leaves, bool leaves_done, const HuffTreeDesc &D) {
     const int lane = threadIdx.x & 31;
+    uint32_t qend = leaves_done ? leaves + 1u : 1u, nn = leaves, kleaf = 0u;              // counted along with the producer
+    unsigned long long ahead;                                                            // the next entry, fetched while the current one is replayed
+    asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(ahead) : "r"(qaddr) : "memory");
     for (uint32_t t = 0;; t++) {
-        unsigned long long e = 0;
-        if (lane == 0) {
-            const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
-            do { asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory"); } while ((uint32_t)(e >> 52) != ((t + 1) & 4095u));
-        }
-        e = __shfl_sync(0xffffffffu, e, 0);
-        const uint32_t kind = (uint32_t)(e >> 50) & 3u;
-        const uint32_t a = (uint32_t)e & 0xffffu, b = ((uint32_t)e >> 16) & 0xffffu, c = (uint32_t)(e >> 32) & 0x3ffffu;
+        const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
+        unsigned long long e = ahead;                                                     // every lane polls the same word: one broadcast load, uniform exit
+        while ((uint32_t)(e >> 52) != ((t + 1) & 4095u)) asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory");
+        asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(ahead) : "r"(qaddr + 8u * ((t + 1) & (HQ_CAP - 1))) : "memory");
+        const uint32_t kind = (uint32_t)(e >> 48) & 3u;
+        const uint32_t p1 = (uint32_t)e & 0xffffu, p2 = ((uint32_t)e >> 16) & 0xffffu, p3 = (uint32_t)(e >> 32) & 0xffffu;
         if (kind == HQ_FIN) break;
-        if (kind == HQ_REMOVE) {
-            const int depth = a ? 31 - __clz(a) : 0;
-            uint32_t v = 0;
-            if (lane == 0) v = __ldcg(ng + 1);                                           // the removed root
-            else if (a != 0 && lane <= depth) v = __ldcg(ng + (a >> (depth - lane)));    // path node p_lane
-            else if (a != 0 && lane == 31) v = __ldcg(ng + b);                           // the element that was taken from the end
-            __syncwarp();
-            if (lane == 0) { if (c & 1u) D.n_right[c >> 1] = v; else D.n_left[c >> 1] = v; }
-            else if (a != 0 && lane <= depth) ng[(a >> (depth - lane)) >> 1] = v;        // p_lane moves up to p_(lane-1)
-            else if (a != 0 && lane == 31) ng[a] = v;
-            __syncwarp();
+        if (kind == HQ_MERGE) {
+            qend--; heap2_replay_remove(na, p1, qend, D.n_right + nn, lane);
+            qend--; heap2_replay_remove(na, p2, qend, D.n_left + nn, lane);
+            heap2_replay_insert(na, qend, p3, nn, lane); qend++; nn++;
         } else {
-            const int k = (31 - __clz(a)) - (31 - __clz(b));                             // ancestors that move down
-            uint32_t v = 0;
-            if (lane < k) v = __ldcg(ng + (a >> (lane + 1)));
-            __syncwarp();
-            if (lane < k) ng[a >> lane] = v;
-            else if (lane == 31) ng[b] = c;
-            __syncwarp();
+            heap2_replay_insert(na, qend, p3, kleaf, lane); qend++; kleaf++;
         }
         if (lane == 0 && (t & 63u) == 63u) *(volatile unsigned int *)done = t + 1;
     }
     __syncwarp();
-    return __ldcg(ng + 1);
+    return na.ld(1u);
 }
 
 constexpr int HUFF_TB = 256;
@@ -453,14 +479,14 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
             for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
             if (t == 0) s_qdone = 0u;
             __syncthreads();
-            if (t == 0 || t == 32) {
+            if (t < 64) {
                 HeapSmem h;
                 const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * fcap_c, qa0 = na0 + n16_bytes;
                 unsigned int qaddr;
                 asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
                 h.n16 = true;
-                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a<false>(h, Q, (int)fcap_c, leaves, lfreq, D, tk1); }
-                else s_root = heap2_thread_b(h, qaddr, &s_qdone, D);
+                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<false, true>(h, Q, (int)fcap_c, leaves, lfreq, D, tk1); }
+                else { NodeIdsSmem na; na.h = h; const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, true, D); if (t == 32) s_root = root; }
             }
         } else if (in_smem) {
             uint32_t *s_queue = s_heap + 2 * scap;
@@ -468,15 +494,15 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
             for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
             if (t == 0) s_qdone = 0u;
             __syncthreads();
-            if (t == 0 || t == 32) {
+            if (t < 64) {
                 // the addresses pass through an opaque asm so that the compiler keeps them in registers instead of
                 // re-deriving the shared window base (S2R + LEA) at every use inside the sift loops
                 HeapSmem h;
                 const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * (unsigned)scap, qa0 = na0 + 4u * (unsigned)scap;
                 unsigned int qaddr;
                 asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
-                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a<true>(h, Q, scap, leaves, lfreq, D, tk1); }
-                else s_root = heap2_thread_b(h, qaddr, &s_qdone, D);
+                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<true, true>(h, Q, scap, leaves, lfreq, D, tk1); }
+                else { NodeIdsSmem na; na.h = h; const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, true, D); if (t == 32) s_root = root; }
             }
         } else if (leaves + 8 <= (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u)) {
             // f[] alone fills the shared memory, n[] lives in global memory and is maintained by warp 1
@@ -486,14 +512,14 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
             for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
             if (t == 0) s_qdone = 0u;
             __syncthreads();
-            if (t == 0 || (t >= 32 && t < 64)) {
+            if (t < 64) {
                 HeapSmem h;
                 const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), qa0 = fa0 + 4u * (unsigned)fcap;
                 unsigned int qaddr;
                 asm volatile("mov.u32 %0, %2;\n\tmov.u32 %1, %3;" : "=r"(h.fa), "=r"(qaddr) : "r"(fa0), "r"(qa0));
                 h.na = 0;
-                if (t == 0) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_thread_a<true>(h, Q, fcap, leaves, lfreq, D, tk1); }
-                else { const uint32_t root = heap2_warp_b_global(reinterpret_cast<uint32_t *>(D.heap_g), qaddr, &s_qdone, D); if (t == 32) s_root = root; }
+                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<true, false>(h, Q, fcap, leaves, lfreq, D, tk1); }
+                else { NodeIdsGmem na; na.ng = reinterpret_cast<uint32_t *>(D.heap_g); const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, false, D); if (t == 32) s_root = root; }
             }
         } else {
             uint32_t *hg = reinterpret_cast<uint32_t *>(D.heap_g);       // capacity 64-bit words = two 32-bit arrays of that length
