@@ -136,6 +136,10 @@ struct HeapSmem {
     }
     __device__ __forceinline__ uint2 ldf2(int i) const { uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(fa + 4u * (unsigned)i)); return v; }
     __device__ __forceinline__ uint4 ldf4(int i) const { uint4 v; asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(fa + 4u * (unsigned)i)); return v; }
+    // the same on byte addresses (the removal keeps the hole's ADDRESS, not its index: no index-to-address step per access)
+    static __device__ __forceinline__ uint2 ld2a(unsigned a) { uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }
+    static __device__ __forceinline__ uint4 ld4a(unsigned a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
+    static __device__ __forceinline__ void sta(unsigned a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 };
 struct HeapGmem {
     uint32_t *f, *n;
@@ -296,36 +300,40 @@ __device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, int &qend, i
     const uint32_t mf = h.ldf(qend);
     h.stf(qend, HEAP_FINF);
     if (qend == 1) { fin = 0u; return topf; }
-    const int lim = cap >> 1;                                   // positions >= lim have no child slots
-    const int qmax = cap - 4, pmax = cap - 2;
-    int i = 1;
+    // byte addresses throughout: a = address of f[i]; the children of f[i] start at 2a - base, and so on
+    const unsigned fa = h.fa;
+    const unsigned alim = fa + 4u * (unsigned)(cap >> 1);       // positions from here on have no child slots
+    const unsigned aqmax = fa + 4u * (unsigned)(cap - 4), apmax = fa + 4u * (unsigned)(cap - 2);
+    unsigned a = fa + 4u;
     for (;;) {
-        uint2 P = h.ldf2(LIM ? min(2 * i, pmax) : 2 * i);
-        const uint4 Q = h.ldf4(min(4 * i, qmax));
-        const uint4 O0 = h.ldf4(min(8 * i, qmax)), O1 = h.ldf4(min(8 * i + 4, qmax));
-        if (LIM && i >= lim) P = make_uint2(HEAP_FINF, HEAP_FINF);
+        const unsigned ap = 2u * a - fa, aq = 2u * ap - fa, ao = 2u * aq - fa;
+        uint2 P = HeapSmem::ld2a(LIM ? min(ap, apmax) : ap);
+        const uint4 Q = HeapSmem::ld4a(min(aq, aqmax));
+        const uint4 O0 = HeapSmem::ld4a(min(ao, aqmax)), O1 = HeapSmem::ld4a(min(ao + 16u, aqmax));
+        if (LIM && a >= alim) P = make_uint2(HEAP_FINF, HEAP_FINF);
         const bool r1 = P.y < P.x;
         const uint32_t c1 = min(P.x, P.y);
-        const int i1 = 2 * i + (r1 ? 1 : 0);
+        unsigned a1 = ap; if (r1) a1 += 4u;
         uint2 P2 = r1 ? make_uint2(Q.z, Q.w) : make_uint2(Q.x, Q.y);
         const uint4 H = r1 ? O1 : O0;
-        if (LIM && i1 >= lim) P2 = make_uint2(HEAP_FINF, HEAP_FINF);
+        if (LIM && a1 >= alim) P2 = make_uint2(HEAP_FINF, HEAP_FINF);
         const bool r2 = P2.y < P2.x;
         const uint32_t c2 = min(P2.x, P2.y);
-        const int i2 = 2 * i1 + (r2 ? 1 : 0);
+        unsigned a2 = 2u * a1 - fa; if (r2) a2 += 4u;
         uint2 P3 = r2 ? make_uint2(H.z, H.w) : make_uint2(H.x, H.y);
-        if (LIM && i2 >= lim) P3 = make_uint2(HEAP_FINF, HEAP_FINF);
+        if (LIM && a2 >= alim) P3 = make_uint2(HEAP_FINF, HEAP_FINF);
         const bool r3 = P3.y < P3.x;
         const uint32_t c3 = min(P3.x, P3.y);
-        const int i3 = 2 * i2 + (r3 ? 1 : 0);
+        unsigned a3 = 2u * a2 - fa; if (r3) a3 += 4u;
         const bool g1 = mf > c1, g2 = g1 && mf > c2, g3 = g2 && mf > c3;      // sinks below level 1 / 2 / 3 of this trip
-        if (g1) h.stf(i, c1);
-        if (g2) h.stf(i1, c2);
-        if (g3) h.stf(i2, c3);
-        if (!g3) { i = g2 ? i2 : (g1 ? i1 : i); break; }
-        i = i3;
+        if (g1) HeapSmem::sta(a, c1);
+        if (g2) HeapSmem::sta(a1, c2);
+        if (g3) HeapSmem::sta(a2, c3);
+        if (!g3) { a = g2 ? a2 : (g1 ? a1 : a); break; }
+        a = a3;
     }
-    h.stf(i, mf);
+    HeapSmem::sta(a, mf);
+    const int i = (int)((a - fa) >> 2);
     fin = (uint32_t)i;
     return topf;
 }
