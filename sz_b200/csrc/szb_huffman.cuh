@@ -105,14 +105,13 @@ struct HuffTreeDesc {           // per-tree I/O, all pointers to global memory
 // frequencies decide the path of a sift; the node ids just follow it.  Slots at or beyond qend always hold HEAP_FINF, so
 // "child does not exist" falls out of the ordinary comparisons.
 //
-// One thread runs the whole thing (the final array layout of every operation must equal the reference's, ties included), so
-// the cost is the length of the dependent chain per heap level.  The sift-down therefore
-//   * reads the four GRANDCHILDREN f[4i..4i+3] with one 128-bit load one level ahead: when the smaller child is known, its
-//     children are already in registers, and the shared-memory round trip is off the chain;
-//   * moves the node ids one level late (load at level L, store at level L+1), so that no store waits for its load.
-// What remains per level is compare -> select -> compare -> branch.
-// (Measured slower, and dropped: a warp-cooperative variant with a speculative 5-level descent; a multi-warp pipelined heap;
-//  fully unrolled predicated sifts; grandchild prefetch on packed 64-bit entries, where the extra 64-bit selects ate the gain.)
+// The final array layout of every operation must equal the reference's, ties included, so the operations run one after the other
+// and the cost is the instruction count and the dependent chain per heap level.  The single-thread form below (heap_insert /
+// heap_remove / heap_build_tree) serves the trees that do not fit into shared memory: its sift-down reads the four GRANDCHILDREN
+// f[4i..4i+3] one level ahead and moves the node ids one level late.  Trees whose frequencies fit into shared memory use the
+// two-warp form further down (vote-based insertion, three levels per removal trip, node ids replayed by a second warp).
+// (Measured slower, and dropped: a lane-per-node removal over 5-level subtrees -- votes on the dependent chain cost more than the
+//  levels they save; a multi-warp pipelined heap; fully unrolled predicated sifts; grandchild prefetch on packed 64-bit entries.)
 constexpr uint32_t HEAP_FINF = 0xffffffffu;
 struct HeapTop { uint32_t f, n; };
 
