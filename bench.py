@@ -345,7 +345,7 @@ def run_ours(args):
                          "unit": "GB/s", "frac": algo_bytes / (wave * 1e-3) / 1e9 / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes": algo_bytes, "kernel_ms": wave, "job_frac": algo_bytes / (ms_step * 1e-3) / 1e9 / peak,
                          "note": "the wavefront is bound by its dependency chain (latency), not by HBM; the largest share of the step is the wait "
-                                 "for the four coefficient Huffman trees (exact emulation of the reference's sequential heap, one thread per tree, side stream): "
+                                 "for the four coefficient Huffman trees (exact emulation of the reference's sequential heap, two warps per tree, side stream): "
                                  "%.2f ms of %.2f ms" % (side, ms_step)},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": len(s_host), "ms_per_step": e_ms},
             "gpu_launches": int(launches), "clocks": clocks}
