@@ -479,6 +479,8 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         const uint32_t fcap_c = (2u * (leaves + 2u) + 3u) & ~3u;
         const uint32_t n16_bytes = ((leaves + 8u) * 2u + 7u) & ~7u;
         const bool compact = 2u * leaves < 65536u && (unsigned long long)fcap_c * 4u + n16_bytes + 8u * HQ_CAP <= (unsigned long long)smem_heap_capacity * 8u;
+        const uint32_t fcap_t16 = (leaves + 8u + 3u) & ~3u;
+        const bool tight16 = 2u * leaves < 65536u && (unsigned long long)fcap_t16 * 4u + n16_bytes + 8u * HQ_CAP <= (unsigned long long)smem_heap_capacity * 8u;
         if (compact) {
             unsigned char *s_bytes = reinterpret_cast<unsigned char *>(s_heap);
             uint32_t *s_queue = reinterpret_cast<uint32_t *>(s_bytes + (size_t)fcap_c * 4u + n16_bytes);
@@ -495,9 +497,15 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
                 if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<false, true>(h, Q, (int)fcap_c, leaves, lfreq, D, tk1); }
                 else { NodeIdsSmem na; na.h = h; const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, true, D); if (t == 32) s_root = root; }
             }
-        } else if (in_smem) {
-            uint32_t *s_queue = s_heap + 2 * scap;
-            for (int q = t; q < scap; q += blockDim.x) s_heap[q] = HEAP_FINF;
+        } else if (tight16 || in_smem) {
+            // tight layout: f gets leaves + 8 entries ("no child slots" tests in the level loop); the node ids are 16-bit values for
+            // trees with fewer than 32768 leaves (up to ~37 k entries fit), 32-bit ones otherwise (never reached today: 32-bit ids
+            // fit up to ~27 k leaves only; kept for other shared-memory sizes)
+            const uint32_t fcap_t = tight16 ? fcap_t16 : (uint32_t)scap;
+            const uint32_t nbytes = tight16 ? n16_bytes : 4u * (uint32_t)scap;
+            unsigned char *s_bytes = reinterpret_cast<unsigned char *>(s_heap);
+            uint32_t *s_queue = reinterpret_cast<uint32_t *>(s_bytes + (size_t)fcap_t * 4u + nbytes);
+            for (int q = t; q < (int)fcap_t; q += blockDim.x) s_heap[q] = HEAP_FINF;
             for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
             if (t == 0) s_qdone = 0u;
             __syncthreads();
@@ -505,10 +513,11 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
                 // the addresses pass through an opaque asm so that the compiler keeps them in registers instead of
                 // re-deriving the shared window base (S2R + LEA) at every use inside the sift loops
                 HeapSmem h;
-                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * (unsigned)scap, qa0 = na0 + 4u * (unsigned)scap;
+                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * fcap_t, qa0 = na0 + nbytes;
                 unsigned int qaddr;
                 asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
-                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<true, true>(h, Q, scap, leaves, lfreq, D, tk1); }
+                h.n16 = tight16;
+                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<true, true>(h, Q, (int)fcap_t, leaves, lfreq, D, tk1); }
                 else { NodeIdsSmem na; na.h = h; const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, true, D); if (t == 32) s_root = root; }
             }
         } else if (leaves + 8 <= (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u)) {
