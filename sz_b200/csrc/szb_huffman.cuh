@@ -237,6 +237,7 @@ __device__ __forceinline__ uint32_t heap_build_tree(const H &h, int hcap, uint32
 // consumer counts along -- and the consumer replays the node-id moves on n[] and writes the children of every merged node.  The
 // producer never reads n[], so the queue is one-way: single producer, single consumer, entries tagged with their sequence number.
 constexpr int HQ_CAP = 512;                                   // queue entries (one 64-bit word each)
+constexpr unsigned HQ_SPIN_LIMIT = 1u << 24;                  // polls before a waiting side gives up (a merge takes ~40 of them)
 enum { HQ_MERGE = 0, HQ_LEAF = 1, HQ_FIN = 2 };
 // entry = {low word: p1:16 | p2:16, high word: p3:16 | kind:2 | -:2 | tag:12}, written and read with ONE 64-bit shared-memory
 // access (single-copy atomic), so the consumer sees either the old or the new entry, never a mixture, and no fence is needed:
@@ -248,17 +249,30 @@ struct HeapQueue {
     unsigned int *done;                                       // consumer progress (generic pointer into shared memory)
     uint32_t t;                                               // producer: next sequence number
     bool lane0;                                               // every lane of the producer runs push(), lane 0 stores
+    bool remote = false;                                      // the ring lives in the partner CTA of the cluster (qa is a shared::cluster address)
+    bool dead = false;                                        // the consumer stopped answering (never seen; keeps a fault from hanging the GPU)
     __device__ __forceinline__ void push(uint32_t kind, uint32_t p1, uint32_t p2, uint32_t p3) {
-        if ((t & 127u) == 0 && t >= HQ_CAP - 128) {           // back-pressure, checked every 128 entries
-            while (t - *(volatile unsigned int *)done > HQ_CAP - 128) { }
+        if ((t & 127u) == 0 && t >= HQ_CAP - 128 && !dead) {  // back-pressure, checked every 128 entries
+            unsigned spins = 0;
+            while (t - *(volatile unsigned int *)done > HQ_CAP - 128) { if (++spins > HQ_SPIN_LIMIT) { dead = true; break; } }
         }
         const uint32_t lo = p1 | (p2 << 16), hi = p3 | (kind << 16) | (((t + 1) & 4095u) << 20);
         unsigned long long e;
         asm volatile("mov.b64 %0, {%1, %2};" : "=l"(e) : "r"(lo), "r"(hi));
-        if (lane0) asm volatile("st.volatile.shared.u64 [%0], %1;" ::"r"(qa + 8u * (t & (HQ_CAP - 1))), "l"(e) : "memory");
+        const unsigned slot = qa + 8u * (t & (HQ_CAP - 1));
+        if (lane0) {
+            if (remote) asm volatile("st.relaxed.cluster.shared::cluster.u64 [%0], %1;" ::"r"(slot), "l"(e) : "memory");
+            else asm volatile("st.volatile.shared.u64 [%0], %1;" ::"r"(slot), "l"(e) : "memory");
+        }
         t++;
     }
 };
+// thread-block cluster helpers (the two CTAs of a tree: rank 0 holds the frequencies, rank 1 the node ids when both do not fit one SM)
+__device__ __forceinline__ unsigned cluster_rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ unsigned cluster_addr(unsigned saddr, unsigned rank) { unsigned r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 
 // The producer is a WARP whose 32 lanes run the same code on the same values (the removals are simply executed redundantly: same
 // addresses, same data).  The lanes serve the insertion: the positions an inserted element can pass are the ancestors of the slot
@@ -370,17 +384,12 @@ __device__ __forceinline__ void heap2_warp_a(const HeapSmem &h, HeapQueue &Q, in
 
 // The consumer (warp 1): node ids.  The warp replays each operation with one lane per node of the ancestor chain: all the loads of
 // an operation are in flight together, the warp synchronises, every lane stores its value one level up (removal) or down
-// (insertion).  NA is where n[] lives: shared memory (16- or 32-bit ids), or -- for trees whose two arrays do not both fit; f[]
-// then keeps all of the shared memory, up to ~54 k entries -- global memory.  Returns the root node.
+// (insertion).  n[] is in the shared memory of the CTA the consumer runs in (16- or 32-bit ids).  Returns the root node, or
+// 0xffffffff if the producer stopped feeding the queue.
 struct NodeIdsSmem {
     HeapSmem h;
     __device__ __forceinline__ uint32_t ld(uint32_t i) const { return h.ldn((int)i); }
     __device__ __forceinline__ void st(uint32_t i, uint32_t v) const { h.stn((int)i, v); }
-};
-struct NodeIdsGmem {
-    uint32_t *ng;
-    __device__ __forceinline__ uint32_t ld(uint32_t i) const { return __ldcg(ng + i); }
-    __device__ __forceinline__ void st(uint32_t i, uint32_t v) const { ng[i] = v; }
 };
 // removal: a = final position of the moved element (0: the heap became empty), b = position it was taken from; the path is the
 // chain of ancestors of a, every node of it moves up one level; the old root goes to *out
@@ -409,7 +418,7 @@ __device__ __forceinline__ void heap2_replay_insert(const NA &na, uint32_t a, ui
     __syncwarp();
 }
 template <typename NA>
-__device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qaddr, unsigned int *done, uint32_t leaves, bool leaves_done, const HuffTreeDesc &D) {
+__device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qaddr, unsigned int done_addr, bool done_remote, uint32_t leaves, bool leaves_done, const HuffTreeDesc &D) {
     const int lane = threadIdx.x & 31;
     uint32_t qend = leaves_done ? leaves + 1u : 1u, nn = leaves, kleaf = 0u;              // counted along with the producer
     unsigned long long ahead;                                                            // the next entry, fetched while the current one is replayed
@@ -417,7 +426,11 @@ __device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qadd
     for (uint32_t t = 0;; t++) {
         const unsigned int slot = qaddr + 8u * (t & (HQ_CAP - 1));
         unsigned long long e = ahead;                                                     // every lane polls the same word: one broadcast load, uniform exit
-        while ((uint32_t)(e >> 52) != ((t + 1) & 4095u)) asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory");
+        unsigned spins = 0;
+        while ((uint32_t)(e >> 52) != ((t + 1) & 4095u)) {
+            asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(e) : "r"(slot) : "memory");
+            if (++spins > HQ_SPIN_LIMIT) return 0xffffffffu;                             // the producer stopped: report, do not hang
+        }
         asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(ahead) : "r"(qaddr + 8u * ((t + 1) & (HQ_CAP - 1))) : "memory");
         const uint32_t kind = (uint32_t)(e >> 48) & 3u;
         const uint32_t p1 = (uint32_t)e & 0xffffu, p2 = ((uint32_t)e >> 16) & 0xffffu, p3 = (uint32_t)(e >> 32) & 0xffffu;
@@ -429,7 +442,10 @@ __device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qadd
         } else {
             heap2_replay_insert(na, qend, p3, kleaf, lane); qend++; kleaf++;
         }
-        if (lane == 0 && (t & 63u) == 63u) *(volatile unsigned int *)done = t + 1;
+        if (lane == 0 && (t & 63u) == 63u) {
+            if (done_remote) asm volatile("st.relaxed.cluster.shared::cluster.u32 [%0], %1;" ::"r"(done_addr), "r"(t + 1) : "memory");
+            else asm volatile("st.volatile.shared.u32 [%0], %1;" ::"r"(done_addr), "r"(t + 1) : "memory");
+        }
     }
     __syncwarp();
     return na.ld(1u);
@@ -438,7 +454,10 @@ __device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qadd
 constexpr int HUFF_TB = 256;
 __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
     extern __shared__ __align__(16) uint32_t s_heap[];          // f[cap] then n[cap]
-    const HuffTreeDesc D = descs[blockIdx.x];
+    // launched as clusters of two CTAs per tree: rank 0 builds the tree; rank 1 only works for a tree whose frequencies and node
+    // ids do not both fit one SM's shared memory -- it then keeps the node ids and runs the consumer (see "pair layout" below)
+    const unsigned rank = cluster_rank();
+    const HuffTreeDesc D = descs[blockIdx.x >> 1];
     __shared__ uint32_t s_scan[HUFF_TB];
     __shared__ uint32_t s_root, s_leaves, s_cnt, s_err, s_lvl[72];
     const int t = threadIdx.x;
@@ -454,89 +473,86 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         __syncthreads();
         for (int o = 1; o < HUFF_TB; o <<= 1) { uint32_t v = (t >= o) ? s_scan[t - o] : 0; __syncthreads(); s_scan[t] += v; __syncthreads(); }
         uint32_t k = s_scan[t] - cnt;
-        for (uint32_t i = lo; i < hi; i++) {
+        if (rank == 0) for (uint32_t i = lo; i < hi; i++) {
             uint32_t f = D.hist[i];
             if (f) { D.n_sym[k] = i; lfreq[k] = f; D.n_left[k] = 0xffffffffu; D.n_right[k] = 0xffffffffu; k++; }
         }
         if (t == HUFF_TB - 1) { s_leaves = s_scan[HUFF_TB - 1]; s_err = 0; }
-        for (uint32_t i = t; i < D.nbins; i += blockDim.x) { D.code[i] = 0; D.clen[i] = 0; }
+        if (rank == 0) for (uint32_t i = t; i < D.nbins; i += blockDim.x) { D.code[i] = 0; D.clen[i] = 0; }
         __syncthreads();
     }
     const uint32_t leaves = s_leaves;
     const uint32_t nodeCount = leaves ? 2 * leaves - 1 : 0;
-    if (leaves == 0) { if (t == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = 0; D.out[3] = 0; } return; }
+    if (leaves == 0) { if (t == 0 && rank == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = 0; D.out[3] = 0; } return; }
     // ---- phase B (serial): exact emulation of the reference's heap ----
     const long long tk1 = clock64();
     {
-        // two inlined copies of the heap loop, so that the shared-memory one compiles to LDS/STS with 32-bit addresses instead
-        // of generic loads (a pointer that may be shared OR global forces the slower generic path)
-        // shared memory: f[scap], n[scap], then the queue of the two-thread form
-        const int scap = (int)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 8u) & ~3u);      // entries per array (multiple of 4: 128-bit loads stay aligned)
-        const bool in_smem = leaves + 8 <= (uint32_t)scap;
+        // separate inlined copies of the heap loops per layout, so that the shared-memory ones compile to LDS/STS with 32-bit
+        // addresses instead of generic loads (a pointer that may be shared OR global forces the slower generic path)
         __shared__ unsigned int s_qdone;
-        // compact layout for trees with fewer than 32768 leaves (node ids fit 16 bits): f gets 2*(leaves+2) entries -- child slots exist
-        // for every position a sift can reach, so the level loop needs no "no child slots" test -- and n is an array of 16-bit ids
+        // compact layout (trees with fewer than 32768 leaves: node ids fit 16 bits): f gets 2*(leaves+2) entries -- child slots exist for
+        // every position a sift can reach, so the level loop needs no "no child slots" test; up to ~22.8 k leaves.
+        // tight layout: f gets leaves + 8 entries ("no child slots" tests in the level loop); up to 32767 leaves.
         const uint32_t fcap_c = (2u * (leaves + 2u) + 3u) & ~3u;
         const uint32_t n16_bytes = ((leaves + 8u) * 2u + 7u) & ~7u;
         const bool compact = 2u * leaves < 65536u && (unsigned long long)fcap_c * 4u + n16_bytes + 8u * HQ_CAP <= (unsigned long long)smem_heap_capacity * 8u;
         const uint32_t fcap_t16 = (leaves + 8u + 3u) & ~3u;
         const bool tight16 = 2u * leaves < 65536u && (unsigned long long)fcap_t16 * 4u + n16_bytes + 8u * HQ_CAP <= (unsigned long long)smem_heap_capacity * 8u;
-        if (compact) {
+        // pair layout (neither of the above fits, up to ~54 k leaves): rank 0 keeps the queue-sized gap and f[], rank 1 the queue and
+        // n[] at the same offsets; the producer writes its queue entries into rank 1's shared memory (one 64-bit remote store per
+        // merge, nothing waits for it), the consumer works on its own SM's memory and sends its progress counter and the root back
+        const uint32_t fcap_p = (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u);
+        const bool pair = !compact && !tight16 && leaves + 8u <= fcap_p;
+        if (rank != 0 && !pair) return;
+        if (compact || tight16) {
+            // one CTA: f[fcap], n[leaves + 8] as 16-bit ids, the queue
+            const uint32_t fcap = compact ? fcap_c : fcap_t16;
             unsigned char *s_bytes = reinterpret_cast<unsigned char *>(s_heap);
-            uint32_t *s_queue = reinterpret_cast<uint32_t *>(s_bytes + (size_t)fcap_c * 4u + n16_bytes);
-            for (int q = t; q < (int)fcap_c; q += blockDim.x) s_heap[q] = HEAP_FINF;
+            uint32_t *s_queue = reinterpret_cast<uint32_t *>(s_bytes + (size_t)fcap * 4u + n16_bytes);
+            for (int q = t; q < (int)fcap; q += blockDim.x) s_heap[q] = HEAP_FINF;
             for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
             if (t == 0) s_qdone = 0u;
             __syncthreads();
             if (t < 64) {
+                // the addresses pass through an opaque asm so that the compiler keeps them in registers instead of re-deriving the
+                // shared window base (S2R + LEA) at every use inside the sift loops
                 HeapSmem h;
-                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * fcap_c, qa0 = na0 + n16_bytes;
+                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * fcap, qa0 = na0 + n16_bytes;
                 unsigned int qaddr;
                 asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
                 h.n16 = true;
-                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<false, true>(h, Q, (int)fcap_c, leaves, lfreq, D, tk1); }
-                else { NodeIdsSmem na; na.h = h; const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, true, D); if (t == 32) s_root = root; }
+                if (t < 32) {
+                    HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0;
+                    if (compact) heap2_warp_a<false, true>(h, Q, (int)fcap, leaves, lfreq, D, tk1);
+                    else heap2_warp_a<true, true>(h, Q, (int)fcap, leaves, lfreq, D, tk1);
+                } else { NodeIdsSmem na; na.h = h; const uint32_t root = heap2_warp_b(na, qaddr, (unsigned)__cvta_generic_to_shared(&s_qdone), false, leaves, true, D); if (t == 32) s_root = root; }
             }
-        } else if (tight16 || in_smem) {
-            // tight layout: f gets leaves + 8 entries ("no child slots" tests in the level loop); the node ids are 16-bit values for
-            // trees with fewer than 32768 leaves (up to ~37 k entries fit), 32-bit ones otherwise (never reached today: 32-bit ids
-            // fit up to ~27 k leaves only; kept for other shared-memory sizes)
-            const uint32_t fcap_t = tight16 ? fcap_t16 : (uint32_t)scap;
-            const uint32_t nbytes = tight16 ? n16_bytes : 4u * (uint32_t)scap;
-            unsigned char *s_bytes = reinterpret_cast<unsigned char *>(s_heap);
-            uint32_t *s_queue = reinterpret_cast<uint32_t *>(s_bytes + (size_t)fcap_t * 4u + nbytes);
-            for (int q = t; q < (int)fcap_t; q += blockDim.x) s_heap[q] = HEAP_FINF;
+        } else if (pair) {
+            uint32_t *s_queue = s_heap, *s_arr = s_heap + 2 * HQ_CAP;                      // rank 0: f[fcap_p]; rank 1: n[fcap_p]
+            if (rank == 0) for (int q = t; q < (int)fcap_p; q += blockDim.x) s_arr[q] = HEAP_FINF;
             for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
             if (t == 0) s_qdone = 0u;
-            __syncthreads();
-            if (t < 64) {
-                // the addresses pass through an opaque asm so that the compiler keeps them in registers instead of
-                // re-deriving the shared window base (S2R + LEA) at every use inside the sift loops
+            cluster_sync_all();                                                          // the ring in rank 1 is clear before the first entry
+            if (t < 32) {
+                const unsigned int qa0 = (unsigned int)__cvta_generic_to_shared(s_queue), aa0 = (unsigned int)__cvta_generic_to_shared(s_arr);
+                unsigned int qaddr, aaddr;
+                asm volatile("mov.u32 %0, %2;\n\tmov.u32 %1, %3;" : "=r"(qaddr), "=r"(aaddr) : "r"(qa0), "r"(aa0));
                 HeapSmem h;
-                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), na0 = fa0 + 4u * fcap_t, qa0 = na0 + nbytes;
-                unsigned int qaddr;
-                asm volatile("mov.u32 %0, %3;\n\tmov.u32 %1, %4;\n\tmov.u32 %2, %5;" : "=r"(h.fa), "=r"(h.na), "=r"(qaddr) : "r"(fa0), "r"(na0), "r"(qa0));
-                h.n16 = tight16;
-                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<true, true>(h, Q, (int)fcap_t, leaves, lfreq, D, tk1); }
-                else { NodeIdsSmem na; na.h = h; const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, true, D); if (t == 32) s_root = root; }
+                if (rank == 0) {
+                    h.fa = aaddr; h.na = 0;
+                    HeapQueue Q; Q.qa = cluster_addr(qaddr, 1u); Q.remote = true; Q.done = &s_qdone; Q.t = 0;
+                    heap2_warp_a<true, false>(h, Q, (int)fcap_p, leaves, lfreq, D, tk1);
+                    if (Q.dead && t == 0) s_err = 2;
+                } else {
+                    h.fa = 0; h.na = aaddr;
+                    NodeIdsSmem na; na.h = h;
+                    const uint32_t root = heap2_warp_b(na, qaddr, cluster_addr((unsigned)__cvta_generic_to_shared(&s_qdone), 0u), true, leaves, false, D);
+                    if (t == 0) asm volatile("st.relaxed.cluster.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr((unsigned)__cvta_generic_to_shared(&s_root), 0u)), "r"(root) : "memory");
+                }
             }
-        } else if (leaves + 8 <= (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u)) {
-            // f[] alone fills the shared memory, n[] lives in global memory and is maintained by warp 1
-            const int fcap = (int)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u);
-            uint32_t *s_queue = s_heap + fcap;
-            for (int q = t; q < fcap; q += blockDim.x) s_heap[q] = HEAP_FINF;
-            for (int q = t; q < 2 * HQ_CAP; q += blockDim.x) s_queue[q] = 0u;
-            if (t == 0) s_qdone = 0u;
-            __syncthreads();
-            if (t < 64) {
-                HeapSmem h;
-                const unsigned int fa0 = (unsigned int)__cvta_generic_to_shared(s_heap), qa0 = fa0 + 4u * (unsigned)fcap;
-                unsigned int qaddr;
-                asm volatile("mov.u32 %0, %2;\n\tmov.u32 %1, %3;" : "=r"(h.fa), "=r"(qaddr) : "r"(fa0), "r"(qa0));
-                h.na = 0;
-                if (t < 32) { HeapQueue Q; Q.qa = qaddr; Q.done = &s_qdone; Q.t = 0; heap2_warp_a<true, false>(h, Q, fcap, leaves, lfreq, D, tk1); }
-                else { NodeIdsGmem na; na.ng = reinterpret_cast<uint32_t *>(D.heap_g); const uint32_t root = heap2_warp_b(na, qaddr, &s_qdone, leaves, false, D); if (t == 32) s_root = root; }
-            }
+            if (rank != 0) __threadfence();                                              // the children written by the consumer, for rank 0's passes
+            cluster_sync_all();
+            if (rank != 0) return;
         } else {
             uint32_t *hg = reinterpret_cast<uint32_t *>(D.heap_g);       // capacity 64-bit words = two 32-bit arrays of that length
             const int gcap = (int)(D.capacity & ~3u);
@@ -546,6 +562,10 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         }
     }
     __syncthreads();
+    if (s_root >= nodeCount || s_err == 2) {                    // a side of the two-warp build gave up waiting for the other (never seen)
+        if (t == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = leaves; D.out[3] = 2; }
+        return;
+    }
     const long long tk2 = clock64();
     // ---- serialised layout (ref: Huffman.c:503-585): [endian:1][L: w*n][R: w*n][C: 4*n][t: n], native endian ----
     const uint32_t w = nodeCount <= 256 ? 1u : (nodeCount <= 65536 ? 2u : 4u);

@@ -521,6 +521,16 @@ extern "C" size_t szb200_body_capacity(const szb200_job *job) {
     return 8 + 4 + st + 12 + 5ull * (16 + 13ull * 2 * 65536) + 1 + st + g.num_blocks * (4 * 4 + 2 + 2 + st) + 8 + g.N * st + g.N * 4 + 4096;
 }
 
+// one cluster of two CTAs per tree (the second one only works for trees too large for one SM's shared memory, see huff_build_kernel)
+static cudaError_t launch_huff_build(cudaStream_t st, const HuffTreeDesc *d_desc, int ntrees, size_t heap_sm, uint32_t heap_cap) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2u * (unsigned)ntrees); cfg.blockDim = dim3(HUFF_TB); cfg.dynamicSmemBytes = heap_sm; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, huff_build_kernel, d_desc, heap_cap);
+}
+
 template <typename T>
 static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst, int dst_on_device, size_t dst_cap, size_t *body_size, szb200_stats *stats) {
     const Geom g = make_geom(job.dim, job.n0, job.n1, job.n2);
@@ -671,7 +681,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
         for (int e = 0; e < ntrees - 1; e++)
             if (launch_hist(c, c.stream2, d_ctype + (size_t)e * nb, reg_count, 65536, tw[1 + e].hist)) return SZ_NSCS;
-        huff_build_kernel<<<ntrees - 1, HUFF_TB, heap_sm, c.stream2>>>(d_desc + 1, heap_cap); KCHECK();
+        CU(launch_huff_build(c.stream2, d_desc + 1, ntrees - 1, heap_sm, heap_cap)); KCHECK();
         for (int e = 0; e < ntrees - 1; e++) {
             const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
             enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream2>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
@@ -691,7 +701,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     // ---- main histogram, main tree, main bit lengths ----
     if (launch_hist(c, c.stream, d_codes, N, intervals, tw[0].hist)) return SZ_NSCS;
     if (mark(ST_HIST)) return SZ_NSCS;
-    huff_build_kernel<<<1, HUFF_TB, heap_sm, c.stream>>>(d_desc, heap_cap); KCHECK();
+    CU(launch_huff_build(c.stream, d_desc, 1, heap_sm, heap_cap)); KCHECK();
     if (mark(ST_TREE)) return SZ_NSCS;
     enc_len_kernel<true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.clen, d_cb, d_cz); KCHECK();
     if (launch_scan(c, c.stream, 0, d_cb, nchunk_main, d_cbo, d_tot + 1)) return SZ_NSCS;
@@ -723,7 +733,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     CU(cudaStreamSynchronize(c.stream));
     if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
         fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
-    for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err("Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
+    for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err(h_tree[i][3] == 2 ? "Huffman tree build gave up (tree %d)" : "Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
     uint64_t cbytes[4] = {0, 0, 0, 0};
     for (int e = 0; e < ntrees - 1; e++) cbytes[e] = (h_tot[3 + e] + 7) / 8;
     uint32_t *d_cbits[4] = {nullptr, nullptr, nullptr, nullptr};
