@@ -451,7 +451,7 @@ __device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qadd
     return na.ld(1u);
 }
 
-constexpr int HUFF_TB = 256;
+constexpr int HUFF_TB = 1024;                                 // the breadth-first passes after the heap use the threads; the heap itself two warps
 __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
     extern __shared__ __align__(16) uint32_t s_heap[];          // f[cap] then n[cap]
     // launched as clusters of two CTAs per tree: rank 0 builds the tree; rank 1 only works for a tree whose frequencies and node
