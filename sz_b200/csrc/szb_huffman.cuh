@@ -268,6 +268,7 @@ struct HeapQueue {
     }
 };
 // thread-block cluster helpers (the two CTAs of a tree: rank 0 holds the frequencies, rank 1 the node ids when both do not fit one SM)
+__device__ __forceinline__ unsigned cluster_size() { unsigned r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ unsigned cluster_rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ unsigned cluster_addr(unsigned saddr, unsigned rank) { unsigned r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank)); return r; }
 __device__ __forceinline__ void cluster_sync_all() {
@@ -456,8 +457,10 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     extern __shared__ __align__(16) uint32_t s_heap[];          // f[cap] then n[cap]
     // launched as clusters of two CTAs per tree: rank 0 builds the tree; rank 1 only works for a tree whose frequencies and node
     // ids do not both fit one SM's shared memory -- it then keeps the node ids and runs the consumer (see "pair layout" below)
-    const unsigned rank = cluster_rank();
-    const HuffTreeDesc D = descs[blockIdx.x >> 1];
+    // (the host launches plain one-CTA-per-tree grids when no tree of the launch can have 32768 leaves or more)
+    const unsigned csize = cluster_size();
+    const unsigned rank = csize > 1 ? cluster_rank() : 0u;
+    const HuffTreeDesc D = descs[blockIdx.x / csize];
     __shared__ uint32_t s_scan[HUFF_TB];
     __shared__ uint32_t s_root, s_leaves, s_cnt, s_err, s_lvl[72];
     const int t = threadIdx.x;
@@ -502,7 +505,7 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         // n[] at the same offsets; the producer writes its queue entries into rank 1's shared memory (one 64-bit remote store per
         // merge, nothing waits for it), the consumer works on its own SM's memory and sends its progress counter and the root back
         const uint32_t fcap_p = (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u);
-        const bool pair = !compact && !tight16 && leaves + 8u <= fcap_p;
+        const bool pair = csize > 1 && !compact && !tight16 && leaves + 8u <= fcap_p;
         if (rank != 0 && !pair) return;
         if (compact || tight16) {
             // one CTA: f[fcap], n[leaves + 8] as 16-bit ids, the queue

@@ -522,11 +522,14 @@ extern "C" size_t szb200_body_capacity(const szb200_job *job) {
 }
 
 // one cluster of two CTAs per tree (the second one only works for trees too large for one SM's shared memory, see huff_build_kernel)
-static cudaError_t launch_huff_build(cudaStream_t st, const HuffTreeDesc *d_desc, int ntrees, size_t heap_sm, uint32_t heap_cap) {
+// max_leaves: upper bound of the leaves of any tree of the launch.  Below 32768 every tree fits one SM's shared memory and the grid is
+// one plain CTA per tree (a cluster needs two free SMs of one GPC at the same moment: under several worker lanes that wait costs).
+static cudaError_t launch_huff_build(cudaStream_t st, const HuffTreeDesc *d_desc, int ntrees, size_t heap_sm, uint32_t heap_cap, uint64_t max_leaves) {
+    const unsigned csize = max_leaves >= 32768u ? 2u : 1u;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2u * (unsigned)ntrees); cfg.blockDim = dim3(HUFF_TB); cfg.dynamicSmemBytes = heap_sm; cfg.stream = st;
+    cfg.gridDim = dim3(csize * (unsigned)ntrees); cfg.blockDim = dim3(HUFF_TB); cfg.dynamicSmemBytes = heap_sm; cfg.stream = st;
     cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, huff_build_kernel, d_desc, heap_cap);
 }
@@ -681,7 +684,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
         for (int e = 0; e < ntrees - 1; e++)
             if (launch_hist(c, c.stream2, d_ctype + (size_t)e * nb, reg_count, 65536, tw[1 + e].hist)) return SZ_NSCS;
-        CU(launch_huff_build(c.stream2, d_desc + 1, ntrees - 1, heap_sm, heap_cap)); KCHECK();
+        CU(launch_huff_build(c.stream2, d_desc + 1, ntrees - 1, heap_sm, heap_cap, std::min<uint64_t>(65536u, reg_count))); KCHECK();
         for (int e = 0; e < ntrees - 1; e++) {
             const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
             enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream2>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
@@ -701,7 +704,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     // ---- main histogram, main tree, main bit lengths ----
     if (launch_hist(c, c.stream, d_codes, N, intervals, tw[0].hist)) return SZ_NSCS;
     if (mark(ST_HIST)) return SZ_NSCS;
-    CU(launch_huff_build(c.stream, d_desc, 1, heap_sm, heap_cap)); KCHECK();
+    CU(launch_huff_build(c.stream, d_desc, 1, heap_sm, heap_cap, std::min<uint64_t>(intervals, N))); KCHECK();
     if (mark(ST_TREE)) return SZ_NSCS;
     enc_len_kernel<true><<<(unsigned)nchunk_main, ENC_THREADS, 0, c.stream>>>(d_codes, N, g, tw[0].d.clen, d_cb, d_cz); KCHECK();
     if (launch_scan(c, c.stream, 0, d_cb, nchunk_main, d_cbo, d_tot + 1)) return SZ_NSCS;
