@@ -289,11 +289,12 @@ __device__ __forceinline__ uint32_t heap2_insert_warp(const HeapSmem &h, int &qe
     const int q0 = qend++;
     const int p = q0 >> lane;                                   // lane 0: the new slot; lane k: its ancestor k levels up (0: above the root)
     uint32_t fk = 0u, nk = 0u;
-    bool down = false;
-    if (lane >= 1 && p >= 1) { fk = h.ldf(p); if (WITH_N) nk = h.ldn(p); down = fk > freq; }
-    const int s = __popc(__ballot_sync(0xffffffffu, down)) + 1;  // ancestors 1 .. s-1 move down, the new element lands on ancestor s-1
+    const bool anc = lane >= 1 && p >= 1;
+    if (anc) { fk = h.ldf(p); if (WITH_N) nk = h.ldn(p); }
+    const unsigned mv = __ballot_sync(0xffffffffu, anc && fk > freq);
+    const int s = __popc(mv) + 1;                               // ancestors 1 .. s-1 move down, the new element lands on ancestor s-1
     const int fin = q0 >> (s - 1);
-    if (down) { h.stf(q0 >> (lane - 1), fk); if (WITH_N) h.stn(q0 >> (lane - 1), nk); }
+    if ((mv >> lane) & 1u) { h.stf(q0 >> (lane - 1), fk); if (WITH_N) h.stn(q0 >> (lane - 1), nk); }
     if (lane == 0) { h.stf(fin, freq); if (WITH_N) h.stn(fin, node); }
     __syncwarp();
     return (uint32_t)fin;
