@@ -285,8 +285,7 @@ __device__ __forceinline__ void cluster_sync_all() {
 // number is a population count.  The removals before an insertion need no barrier (every lane ran all of their stores itself); the
 // insertion's stores come from different lanes, hence the barrier after it.
 template <bool WITH_N>
-__device__ __forceinline__ uint32_t heap2_insert_warp(const HeapSmem &h, int &qend, uint32_t freq, uint32_t node, int lane) {
-    const int q0 = qend++;
+__device__ __forceinline__ uint32_t heap2_insert_warp(const HeapSmem &h, const int q0, uint32_t freq, uint32_t node, int lane) {
     const int p = q0 >> lane;                                   // lane 0: the new slot; lane k: its ancestor k levels up (0: above the root)
     uint32_t fk = 0u, nk = 0u;
     const bool anc = lane >= 1 && p >= 1;
@@ -352,6 +351,23 @@ __device__ __forceinline__ uint32_t heap2_remove(const HeapSmem &h, int &qend, i
     fin = (uint32_t)i;
     return topf;
 }
+// The merge loop is a function of its own, not inlined: the code the compiler makes of it then does not depend on what surrounds
+// it (the same loop measured between 21.7 and 25.9 M cycles for the 19 k-leaf tree as part of differently shaped callers).
+// Everything travels by value in registers.  Returns the queue's sequence number.
+template <bool LIM>
+__device__ __noinline__ uint32_t heap2_merge_phase(unsigned fa, unsigned qa, bool remote, unsigned int *done, uint32_t qt, int hcap, int qend, int lane) {
+    HeapSmem h; h.fa = fa; h.na = 0u;
+    HeapQueue Q; Q.qa = qa; Q.remote = remote; Q.done = done; Q.t = qt; Q.lane0 = lane == 0;
+    while (qend > 2) {
+        uint32_t p1, p2;
+        const uint32_t fb = heap2_remove<LIM>(h, qend, hcap, p1);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
+        const uint32_t fa2 = heap2_remove<LIM>(h, qend, hcap, p2);   // second removed -> left
+        const uint32_t p3 = heap2_insert_warp<false>(h, qend, fa2 + fb, 0u, lane); qend++;
+        Q.push(HQ_MERGE, p1, p2, p3);
+    }
+    Q.push(HQ_FIN, 0u, 0u, 0u);
+    return Q.t | (Q.dead ? 0x80000000u : 0u);
+}
 // LEAFN: n[] is in shared memory and the producer fills it during the leaf phase itself (no queue traffic until the first merge)
 template <bool LIM, bool LEAFN>
 __device__ __forceinline__ void heap2_warp_a(const HeapSmem &h, HeapQueue &Q, int hcap, uint32_t leaves, const uint32_t *lfreq, const HuffTreeDesc &D, long long tk1) {
@@ -364,23 +380,39 @@ __device__ __forceinline__ void heap2_warp_a(const HeapSmem &h, HeapQueue &Q, in
     for (uint32_t k0 = 0; k0 < leaves; k0 += 32) {
         const uint32_t nxt = k0 + 32u + (uint32_t)lane < leaves ? lfreq[k0 + 32u + lane] : 0u;
         const int cnt = (int)min(32u, leaves - k0);
-        for (int j = 0; j < cnt; j++) {
-            const uint32_t f = __shfl_sync(0xffffffffu, cur, j);
-            const uint32_t fin = heap2_insert_warp<LEAFN>(h, qend, f, k0 + (uint32_t)j, lane);
-            if (!LEAFN) Q.push(HQ_LEAF, 0u, 0u, fin);
+        // The 32 leaves of a group go to the slots q0 .. q0+cnt-1, whose parents all lie below q0 (q0 >= 32).  A leaf that is not
+        // smaller than its parent stays where it is appended; a sift of another leaf of the group only LOWERS the values on its
+        // ancestors, so a test against the parent as it is before the group holds for the leaf's turn as well.  Those leaves are
+        // therefore stored all at once, and only the others (bit set in `sift`) take the serial route, in order.
+        const int q0 = qend;
+        unsigned sift = cnt == 32 ? 0xffffffffu : (1u << cnt) - 1u;
+        if (q0 >= 32) {
+            const bool mine = lane < cnt;
+            const uint32_t fp = mine ? h.ldf((q0 + lane) >> 1) : 0u;
+            sift = __ballot_sync(0xffffffffu, mine && fp > cur);
+            if (mine && ((sift >> lane) & 1u) == 0u) { h.stf(q0 + lane, cur); if (LEAFN) h.stn(q0 + lane, k0 + (uint32_t)lane); }
+            __syncwarp();
         }
+        if (LEAFN) {
+            while (sift) {
+                const int j = __ffs((int)sift) - 1; sift &= sift - 1u;
+                heap2_insert_warp<true>(h, q0 + j, __shfl_sync(0xffffffffu, cur, j), k0 + (uint32_t)j, lane);
+            }
+        } else {
+            for (int j = 0; j < cnt; j++) {                     // the consumer replays every leaf: one entry each, in order
+                uint32_t fin = (uint32_t)(q0 + j);
+                const uint32_t f = __shfl_sync(0xffffffffu, cur, j);
+                if ((sift >> j) & 1u) fin = heap2_insert_warp<false>(h, q0 + j, f, 0u, lane);
+                Q.push(HQ_LEAF, 0u, 0u, fin);
+            }
+        }
+        qend = q0 + cnt;
         cur = nxt;
     }
     if (LEAFN) __threadfence_block();                           // n[] as left by the leaf phase, before the first queue entry
     if (lane == 0) D.out[5] = (uint32_t)((clock64() - tk1) >> 10);
-    while (qend > 2) {
-        uint32_t p1, p2;
-        const uint32_t fb = heap2_remove<LIM>(h, qend, hcap, p1);    // first removed  -> right (gcc evaluates Huffman.c:181's arguments right to left)
-        const uint32_t fa = heap2_remove<LIM>(h, qend, hcap, p2);    // second removed -> left
-        const uint32_t p3 = heap2_insert_warp<false>(h, qend, fa + fb, 0u, lane);
-        Q.push(HQ_MERGE, p1, p2, p3);
-    }
-    Q.push(HQ_FIN, 0u, 0u, 0u);
+    const uint32_t qt = heap2_merge_phase<LIM>(h.fa, Q.qa, Q.remote, Q.done, Q.t, hcap, qend, lane);
+    Q.t = qt & 0x7fffffffu; if (qt >> 31) Q.dead = true;
     if (lane == 0) D.out[6] = (uint32_t)((clock64() - tk1) >> 10);
 }
 
