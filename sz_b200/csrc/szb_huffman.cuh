@@ -120,7 +120,7 @@ struct HeapTop { uint32_t f, n; };
 // sift loop (a dozen uniform-datapath instructions per level).
 struct HeapSmem {
     unsigned int fa, na;                 // shared addresses of f[0] and n[0]
-    bool n16 = false;                    // node ids stored as 16-bit values (two-thread form, trees with fewer than 32768 leaves)
+    bool n16 = false;                    // node ids stored as 16-bit values (single-CTA layouts of the two-warp form, trees with fewer than 32768 leaves)
     __device__ __forceinline__ uint32_t ldf(int i) const { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(fa + 4u * (unsigned)i)); return v; }
     __device__ __forceinline__ uint32_t ldn(int i) const {
         uint32_t v;
