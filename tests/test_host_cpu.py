@@ -35,7 +35,9 @@ def declared_symbols():
     for h in ("sz.h", "szb200.h"):
         txt = open(os.path.join(ROOT, "include", h)).read()
         txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-        for m in re.finditer(r"\b(SZ_\w+|szb200_\w+|computeDataLength|computeDimension|filterDimension|convertSZParamsToBytes|convertBytesToSZParams)\s*\(", txt):
+        for m in re.finditer(r"\b(SZ_\w+|szb200_\w+|computeDataLength|computeDimension|filterDimension|convertSZParamsToBytes|convertBytesToSZParams|"
+                             r"readByteData|readFloatData|readDoubleData|writeByteData|writeFloatData_inBytes|writeDoubleData_inBytes|checkFileExistance|"
+                             r"writeStrings|writeFloatData|writeDoubleData|detransposeData|is_lossless_compressed_data|sz_lossless_decompress65536bytes)\s*\(", txt):
             names.add(m.group(1))
     return sorted(names)
 
@@ -135,3 +137,77 @@ def test_no_gpu_means_loud_failure_not_a_cpu_fallback():
     with pytest.raises(RuntimeError):
         ours.compress(a, szref.ABS, 1e-3, 0)
     ours.finalize()
+
+
+def _io_lib(path):
+    L = C.CDLL(path)
+    L.detransposeData.restype = C.c_void_p
+    L.detransposeData.argtypes = [C.c_void_p, C.c_int] + [C.c_size_t] * 5
+    L.is_lossless_compressed_data.argtypes = [C.c_char_p, C.c_size_t]
+    L.writeFloatData.argtypes = [C.c_void_p, C.c_size_t, C.c_char_p, C.POINTER(C.c_int)]
+    L.writeDoubleData.argtypes = [C.c_void_p, C.c_size_t, C.c_char_p, C.POINTER(C.c_int)]
+    L.writeStrings.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.c_char_p, C.POINTER(C.c_int)]
+    L.checkFileExistance.argtypes = [C.c_char_p]
+    return L
+
+
+def test_command_line_helpers_standalone(tmp_path):
+    """The rw.h / utility.h helpers the reference's command-line tool links against (sz_io.c): text writers, existence test,
+    magic-number test, and detransposeData as the transpose it is (ref: sz/src/utility.c:236-330)."""
+    L = _io_lib(LIB)
+    libc = C.CDLL(None)
+    libc.free.argtypes = [C.c_void_p]
+    st = C.c_int(-7)
+    a = np.array([1.5, -2.25, 3.0e-8], dtype=np.float32)
+    L.writeFloatData(a.ctypes.data, a.size, str(tmp_path / "f.txt").encode(), C.byref(st))
+    assert st.value == 0 and (tmp_path / "f.txt").read_text().split() == ["%.30G" % float(v) for v in a]
+    d = np.array([0.1, -1e300], dtype=np.float64)
+    L.writeDoubleData(d.ctypes.data, d.size, str(tmp_path / "d.txt").encode(), C.byref(st))
+    assert st.value == 0 and (tmp_path / "d.txt").read_text().split() == ["%.20G" % float(v) for v in d]
+    strs = (C.c_char_p * 2)(b"first line", b"second")
+    L.writeStrings(2, strs, str(tmp_path / "s.txt").encode(), C.byref(st))
+    assert st.value == 0 and (tmp_path / "s.txt").read_text() == "first line\nsecond\n"
+    assert L.checkFileExistance(str(tmp_path / "s.txt").encode()) == 1 and L.checkFileExistance(str(tmp_path / "nope").encode()) == 0
+    assert L.is_lossless_compressed_data(bytes([0x28, 0xB5, 0x2F, 0xFD, 0, 0]), 6) == 1       # a zstd frame
+    assert L.is_lossless_compressed_data(bytes([120, 156, 1, 2]), 4) == 0                    # a zlib stream
+    assert L.is_lossless_compressed_data(bytes([2, 1, 12, 0xC0]), 4) == -1                   # an SZ_BEST_SPEED stream: neither
+    for dtype, code in ((np.float32, 0), (np.float64, 1)):
+        for dims in ((0, 0, 0, 3, 5), (0, 0, 4, 3, 5), (0, 2, 4, 3, 5), (0, 0, 0, 0, 7)):
+            r5, r4, r3, r2, r1 = dims
+            n = int(np.prod([v for v in dims if v]))
+            x = np.arange(n, dtype=dtype)
+            ptr = L.detransposeData(x.ctypes.data, code, *dims)
+            got = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float if code == 0 else C.c_double)), (n,)).copy()
+            libc.free(ptr)
+            fast = {1: 1, 2: r1, 3: r3, 4: r4}[sum(1 for v in dims if v)]   # extent of the input's fastest axis
+            want = x.reshape(n // fast, fast).T.reshape(-1) if fast > 1 else x
+            assert np.array_equal(got, want), (dtype, dims)
+
+
+@pytest.mark.skipif(not szref.have_ref(), reason="needs oracle/_ref/libSZ_ref.so")
+def test_command_line_helpers_match_reference(tmp_path):
+    ref, ours = _io_lib(szref.REF_SO), _io_lib(LIB)
+    libc = C.CDLL(None)
+    libc.free.argtypes = [C.c_void_p]
+    rng = np.random.default_rng(5)
+    for dims in ((0, 0, 0, 6, 4), (0, 0, 5, 6, 4), (0, 3, 5, 6, 4)):
+        n = int(np.prod([v for v in dims if v]))
+        for dtype, code, ct in ((np.float32, 0, C.c_float), (np.float64, 1, C.c_double)):
+            x = rng.standard_normal(n).astype(dtype)
+            outs = []
+            for L in (ref, ours):
+                ptr = L.detransposeData(x.ctypes.data, code, *dims)
+                outs.append(np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ct)), (n,)).copy())
+                libc.free(ptr)
+            assert outs[0].tobytes() == outs[1].tobytes(), (dims, dtype)
+    for head in ([0x28, 0xB5, 0x2F, 0xFD], [104, 5], [104, 129], [104, 222], [120, 1], [120, 94], [120, 156], [120, 218], [120, 2], [2, 1, 12, 0xC0], [0, 0, 0, 0]):
+        b = bytes(head + [0] * 8)
+        assert ref.is_lossless_compressed_data(b, len(b)) == ours.is_lossless_compressed_data(b, len(b)), head
+    st = C.c_int(0)
+    a = rng.standard_normal(50).astype(np.float32)
+    d = rng.standard_normal(50)
+    for nm, L in (("ref", ref), ("ours", ours)):
+        L.writeFloatData(a.ctypes.data, a.size, str(tmp_path / (nm + "_f.txt")).encode(), C.byref(st))
+        L.writeDoubleData(d.ctypes.data, d.size, str(tmp_path / (nm + "_d.txt")).encode(), C.byref(st))
+    assert (tmp_path / "ref_f.txt").read_bytes() == (tmp_path / "ours_f.txt").read_bytes()
+    assert (tmp_path / "ref_d.txt").read_bytes() == (tmp_path / "ours_d.txt").read_bytes()
