@@ -4,6 +4,7 @@
 //      :656-788 (reconstruct); call sites sz/src/sz_float.c:7379-7471.
 #pragma once
 #include "szb_common.cuh"
+#include "szb_heap_pipe.cuh"
 
 namespace szb {
 
@@ -486,7 +487,9 @@ __device__ __forceinline__ uint32_t heap2_warp_b(const NA &na, unsigned int qadd
 }
 
 constexpr int HUFF_TB = 1024;                                 // the breadth-first passes after the heap use the threads; the heap itself two warps
-__global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity) {
+// heap_form: 0 = the pipelined one-warp heap (szb_heap_pipe.cuh) whenever the tree fits one SM's shared memory as 8-byte entries, 1 = never (the
+// two-warp forms below, which also serve the larger trees)
+__global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc *descs, uint32_t smem_heap_capacity, uint32_t heap_form) {
     extern __shared__ __align__(16) uint32_t s_heap[];          // f[cap] then n[cap]
     // launched as clusters of two CTAs per tree: rank 0 builds the tree; rank 1 only works for a tree whose frequencies and node
     // ids do not both fit one SM's shared memory -- it then keeps the node ids and runs the consumer (see "pair layout" below)
@@ -538,9 +541,16 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         // n[] at the same offsets; the producer writes its queue entries into rank 1's shared memory (one 64-bit remote store per
         // merge, nothing waits for it), the consumer works on its own SM's memory and sends its progress counter and the root back
         const uint32_t fcap_p = (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u);
-        const bool pair = csize > 1 && !compact && !tight16 && leaves + 8u <= fcap_p;
+        const bool piped = heap_form == 0u && leaves + 2u <= smem_heap_capacity;
+        const bool pair = csize > 1 && !piped && !compact && !tight16 && leaves + 8u <= fcap_p;
         if (rank != 0 && !pair) return;
-        if (compact || tight16) {
+        if (piped) {
+            // several heap operations in flight in one warp, {frequency, node} entries of 8 bytes (szb_heap_pipe.cuh)
+            if (t < 32) {
+                const uint32_t root = hp_build((unsigned int)__cvta_generic_to_shared(s_heap), leaves, lfreq, D.n_left, D.n_right, D.out, tk1);
+                if (t == 0) s_root = root;
+            }
+        } else if (compact || tight16) {
             // one CTA: f[fcap], n[leaves + 8] as 16-bit ids, the queue
             const uint32_t fcap = compact ? fcap_c : fcap_t16;
             unsigned char *s_bytes = reinterpret_cast<unsigned char *>(s_heap);

@@ -549,7 +549,9 @@ static cudaError_t launch_huff_build(cudaStream_t st, const HuffTreeDesc *d_desc
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, huff_build_kernel, d_desc, heap_cap);
+    static int form = -1;                                        // SZB200_HEAP=twowarp: the older two-warp heap for every tree (A/B runs)
+    if (form < 0) { const char *e = getenv("SZB200_HEAP"); form = (e && strcmp(e, "twowarp") == 0) ? 1 : 0; }
+    return cudaLaunchKernelEx(&cfg, huff_build_kernel, d_desc, heap_cap, (uint32_t)form);
 }
 
 template <typename T>
