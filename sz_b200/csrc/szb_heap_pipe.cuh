@@ -38,34 +38,42 @@ static __device__ __forceinline__ void hp_st2(unsigned a, uint32_t x, uint32_t y
 // h is x or one of its ancestors (1-based heap positions)
 static __device__ __forceinline__ bool hp_anc(uint32_t h, uint32_t x) { const int d = __clz(h) - __clz(x); return d >= 0 && (x >> (d & 31)) == h; }
 
+// A lane that holds no removal has ek = 0 (never larger than a child: frequencies are >= 1) and its hole at the unused slot 0: it
+// runs the same instructions as the others and changes nothing.
 struct HpLane {
-    unsigned ha, pa, ba;    // address of the hole, of its two children, of the last slot this removal may use
+    unsigned ha, pa;        // address of the hole, of its two children
     uint32_t ek, en;        // the element that sinks
-    bool act;               // the removal is still sinking
-    bool in;                // the children's slot pair exists (address not beyond the last slot); kept one step ahead, see hp_tick
+    uint32_t t0;            // tick count at launch: a sinking element goes down one level per tick, so its hole's level is ticks - t0
 };
-static __device__ __forceinline__ void hp_launch(HpLane &S, const unsigned base, const uint32_t last, const uint2 e) {
-    S.act = true; S.ha = base + 8u; S.pa = base + 16u; S.ba = base + 8u * last; S.in = 2u <= last; S.ek = e.x; S.en = e.y;
-}
+constexpr uint32_t HP_INF = 0xffffffffu;
 
-// One level for every removal in flight.  The dependent chain from one load to the next is: which child is smaller -> select the
-// next pair address.  Everything else is kept off it: the next pair address of BOTH children and whether those pairs exist are
-// computed while the load is in flight, and the load is issued for every lane that was sinking before this step (the comparison
-// with the sinking element, which decides whether it goes on, is not waited for: a lane that stops has loaded a pair it ignores).
-static __device__ __forceinline__ void hp_tick(const unsigned base, HpLane &S) {
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (S.in) v = hp_ld4(S.pa);
-    const unsigned pl = 2u * S.pa - base;                       // children pair of the left child; the right child's is 16 bytes on
-    const bool in_l = pl <= S.ba, in_r = pl + 16u <= S.ba;
-    const bool right = S.pa + 8u <= S.ba && v.z < v.x;          // right child only if STRICTLY smaller (Huffman.c:98)
+// One level for every removal in flight, without a branch or a predicate: slots beyond the heap's current end hold HP_INF (every
+// removal marks the slot it empties), and a children pair beyond the array is read from `capa`, a pair of HP_INF entries behind it,
+// so "no such child" is an ordinary comparison.  The dependent chain from one load to the next is: which child is smaller -> its
+// address -> its children's address -> clamp; whether the element goes on sinking is not waited for (a lane that stops has ek = 0
+// from then on and whatever it loads is ignored).
+// CHK: the tick also answers "does some removal have its hole on the ancestor chain of slot x (x included) after this tick?"
+// (cx = level of x minus the tick count after this tick: a sinking element goes down one level per tick, so its hole's level is
+// ticks - t0 and the chain's node at that level is x >> (cx + t0); a lane without a removal has its hole at slot 0, which the
+// max() keeps out of the comparison).  Asked inside the tick, the vote's latency is hidden behind the tick's own tail.
+template <bool CHK>
+static __device__ __forceinline__ bool hp_tick_finish(const unsigned base, const unsigned capa, HpLane &S, const uint4 v, const uint32_t x = 0u, const int cx = 0) {
+    const bool right = v.z < v.x;                               // right child only if STRICTLY smaller (Huffman.c:98)
     const uint32_t kc = right ? v.z : v.x, nc = right ? v.w : v.y;
-    const bool move = S.act && S.in && S.ek > kc;               // sinks only while STRICTLY larger (Huffman.c:101)
-    if (S.act) hp_st2(S.ha, move ? kc : S.ek, move ? nc : S.en);
-    if (move) S.ha = S.pa + (right ? 8u : 0u);
-    S.in = S.act && (right ? in_r : in_l);
-    S.pa = right ? pl + 16u : pl;
-    S.act = move;
-    __syncwarp();
+    const unsigned hc = S.pa + (right ? 8u : 0u);
+    const bool move = S.ek > kc;                                // sinks only while STRICTLY larger (Huffman.c:101)
+    hp_st2(S.ha, move ? kc : S.ek, move ? nc : S.en);
+    S.ha = move ? hc : base;
+    S.pa = min(2u * hc - base, capa);
+    S.ek = move ? S.ek : 0u;
+    bool busy = false;
+    if (CHK) busy = __any_sync(0xffffffffu, base + 8u * max(x >> ((cx + (int)S.t0) & 31), 1u) == S.ha);
+    return busy;
+}
+template <bool CHK>
+static __device__ __forceinline__ bool hp_tick(const unsigned base, const unsigned capa, HpLane &S, const uint32_t x = 0u, const int cx = 0) {
+    const uint4 v = hp_ld4(S.pa);
+    return hp_tick_finish<CHK>(base, capa, S, v, x, cx);
 }
 
 // leaf phase: bottom-up insertion by the lanes (lane k looks at the ancestor k levels above the new slot q0)
@@ -82,7 +90,7 @@ static __device__ __forceinline__ void hp_insert_warp(const unsigned base, const
 }
 
 // Leaf inserts, merges, and the root: the whole heap part of one tree, run by ONE warp (all 32 lanes call it).
-//   base: shared address of the heap, 8 (leaves + 2) bytes; lfreq: leaf frequencies in increasing symbol order (global memory)
+//   base: shared address of the heap, 16-byte aligned, 8 (leaves + 4) bytes; lfreq: leaf frequencies in increasing symbol order (global memory)
 //   n_left / n_right: children of the internal nodes (global memory), node ids: leaves 0 .. leaves-1, internal nodes in merge order
 static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t leaves, const uint32_t *__restrict__ lfreq, uint32_t *n_left, uint32_t *n_right,
                                                  uint32_t *prof_out, const long long tk1) {
@@ -117,49 +125,89 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
     }
     if (lane == 0) prof_out[5] = (uint32_t)((clock64() - tk1) >> 10);
     // ---- merges ----
-    HpLane S; S.act = false; S.in = false; S.ha = base + 8u; S.pa = base + 16u; S.ba = base; S.ek = 0u; S.en = 0u;
-    uint32_t m = leaves, k = 0;                                   // m: elements in the heap; the last one travels in e1, not in its slot
-    uint2 e1 = make_uint2(0u, 0u), a = make_uint2(0u, 0u);
+    const uint32_t cap = (leaves + 2u) & ~1u;                     // an even slot behind the heap: slots cap, cap + 1 = the HP_INF pair
+    const unsigned capa = base + 8u * cap;
+    if (lane < 3) hp_st2(base + 8u * (leaves + 1u + (uint32_t)lane), HP_INF, 0u);      // leaves + 1 .. cap + 1 (at most three slots)
+    __syncwarp();
+    HpLane S; S.ha = base; S.pa = capa; S.ek = 0u; S.en = 0u; S.t0 = 0u;
+    uint32_t m = leaves, k = 0, ticks = 0;                        // m: elements in the heap (the last one travels in registers, not in its slot)
+#ifdef HP_COUNT
+    uint32_t n_wait_e = 0, n_wait_c = 0;
+#define HP_CNT(x) (x)++
+#else
+#define HP_CNT(x)
+#endif
     const bool piped = m >= HP_TAIL;
-    if (piped) { e1 = hp_ld2(base + 8u * m); a = hp_ld2(base + 8u); }
-    for (; m >= HP_TAIL; m--, k++) {
-        const int la = (int)((2u * k) & 31u);
-        // first removal: takes the root `a`, the last element e1 sinks from the root among slots 1 .. m-1
-        if (lane == la) hp_launch(S, base, m - 1u, e1);
-        hp_tick(base, S);
-        hp_tick(base, S);
-        // second removal: its element is the one in slot m-1, once no older removal can still end there
-        const uint32_t x = m - 1u;
-        while (__ballot_sync(0xffffffffu, S.act && hp_anc((S.ha - base) >> 3, x))) hp_tick(base, S);
-        const uint2 b = hp_ld2(base + 8u), e2 = hp_ld2(base + 8u * x);
-        if (lane == la + 1) hp_launch(S, base, m - 2u, e2);
-        hp_tick(base, S);
-        hp_tick(base, S);
-        // the merged node: first removed -> right, second removed -> left (gcc evaluates the arguments of Huffman.c:181 right to left)
-        const uint32_t nn = leaves + k, kn = a.x + b.x;
-        if (lane == 0) { n_left[nn] = b.y; n_right[nn] = a.y; }
-        // its insertion at slot x (Huffman.c:76-85), by the lanes, once the ancestor chain of x is nobody's
-        while (__ballot_sync(0xffffffffu, S.act && hp_anc((S.ha - base) >> 3, x))) hp_tick(base, S);
-        const int d = 31 - __clz(x);                              // ancestors: x >> 1 .. x >> d (= the root)
-        const int j = lane + 1;
-        const bool valid = j <= d;
-        uint2 v = make_uint2(0u, 0u);
-        if (valid) v = hp_ld2(base + 8u * (x >> j));
-        const uint2 root = hp_ld2(base + 8u), par = hp_ld2(base + 8u * (x >> 1));
-        const int cnt = __popc(__ballot_sync(0xffffffffu, valid && v.x > kn));     // the ancestors 1 .. cnt levels up move down one level
-        if (j >= 2 && j <= cnt) hp_st2(base + 8u * (x >> (j - 1)), v.x, v.y);
-        if (lane == 0 && cnt >= 1) hp_st2(base + 8u * (x >> cnt), kn, nn);
-        // what would now sit in slot x is what the next first removal takes from there: handed over, never stored
-        e1 = cnt >= 1 ? par : make_uint2(kn, nn);
-        a = cnt == d ? make_uint2(kn, nn) : root;
+    uint2 pend = make_uint2(0u, 0u);                              // the merged node whose insertion is still to be done when the loop ends
+    if (piped) {
+        uint32_t *pl = n_left + leaves, *pr = n_right + leaves;
+        // first removal of the first merge: takes the root `a`, the last element sinks from the root
+        uint2 a = hp_ld2(base + 8u);
+        { const uint2 e1 = hp_ld2(base + 8u * m); __syncwarp(); hp_st2(base + 8u * m, HP_INF, 0u);
+          if (lane == 0) { S.ha = base + 8u; S.pa = base + 16u; S.ek = e1.x; S.en = e1.y; S.t0 = ticks; } }
         __syncwarp();
+        hp_tick<false>(base, capa, S); ticks++;
+        for (;; m--, k++) {
+            const int la = (int)((2u * k) & 31u);
+            // second removal: its element is the one in slot x = m - 1, once no older removal can still end there (hole on x's chain).
+            const uint32_t x = m - 1u;
+            const int lvx = 31 - __clz(x);
+            ticks++;
+            bool busy = hp_tick<true>(base, capa, S, x, lvx - (int)ticks);             // the first removal's second level: level 1 is final again
+            while (busy) { ticks++; busy = hp_tick<true>(base, capa, S, x, lvx - (int)ticks); HP_CNT(n_wait_e); }
+            // Launch and first level in one round trip: the root, slot x and the lanes' children pairs are loaded together.
+            if (lane == la + 1) { S.ha = base + 8u; S.pa = base + 16u; S.t0 = ticks; }
+            uint4 v = hp_ld4(S.pa);
+            const uint2 b = hp_ld2(base + 8u), e2 = hp_ld2(base + 8u * x);
+            hp_st2(base + 8u * x, HP_INF, 0u);                    // the heap ends one slot earlier (every lane stores the same)
+            if (lane == la + 1) { S.ek = e2.x; S.en = e2.y; }
+            hp_tick_finish<false>(base, capa, S, v); ticks++;
+            ticks++;
+            busy = hp_tick<true>(base, capa, S, x, lvx - (int)ticks);
+            // the merged node: first removed -> right, second removed -> left (gcc evaluates the arguments of Huffman.c:181 right to left)
+            const uint32_t nn = leaves + k, kn = a.x + b.x;
+#ifndef HP_NO_GST
+            if (lane == 0) { *pl = b.y; *pr = a.y; }
+#endif
+            pl++; pr++;
+            if (m - 1u < HP_TAIL) { pend = make_uint2(kn, nn); break; }
+            // its insertion at slot x (Huffman.c:76-85), once the ancestor chain of x is nobody's, in one round trip with the launch and
+            // first level of the next merge's first removal, which takes what the insertion would leave in slot x out of it again:
+            // mostly the new node itself (its parent is not larger), which therefore never touches the heap.
+            while (busy) { ticks++; busy = hp_tick<true>(base, capa, S, x, lvx - (int)ticks); HP_CNT(n_wait_c); }
+            const int ln = (la + 2) & 31;
+            if (lane == ln) { S.ha = base + 8u; S.pa = base + 16u; S.t0 = ticks; }
+            v = hp_ld4(S.pa);
+            const uint2 par = hp_ld2(base + 8u * (x >> 1));
+            a = hp_ld2(base + 8u);
+            uint2 e1 = make_uint2(kn, nn);
+            if (par.x > kn) {
+                // the lanes move the chain: lane j-1 looks at the ancestor j levels up, the larger ones (a bottom prefix) go down a level,
+                // the parent's element is the one that leaves
+                const int j = lane + 1;
+                const bool valid = j <= lvx;                      // ancestors: x >> 1 .. x >> lvx (= the root)
+                uint2 w = make_uint2(0u, 0u);
+                if (valid) w = hp_ld2(base + 8u * (x >> j));
+                const int cnt = __popc(__ballot_sync(0xffffffffu, valid && w.x > kn));
+                __syncwarp();
+                if (j >= 2 && j <= cnt) hp_st2(base + 8u * (x >> (j - 1)), w.x, w.y);
+                if (lane == 0) hp_st2(base + 8u * (x >> cnt), kn, nn);
+                e1 = par;
+                __syncwarp();
+                v = hp_ld4(S.pa);                                 // the top of the heap may have changed
+                a = hp_ld2(base + 8u);
+            }
+            if (lane == ln) { S.ek = e1.x; S.en = e1.y; }
+            hp_tick_finish<false>(base, capa, S, v); ticks++;
+        }
+        m--; k++;                                                 // the merge whose node is still in `pend`
     }
-    while (__ballot_sync(0xffffffffu, S.act)) hp_tick(base, S);
+    while (__any_sync(0xffffffffu, S.ek != 0u)) hp_tick<false>(base, capa, S);
     // ---- the last few merges, one operation after the other (lane 0) ----
     uint32_t rootn = 0u;
     if (lane == 0) {
-        if (piped) hp_st2(base + 8u * m, e1.x, e1.y);
-        uint32_t qend = m + 1u, nn = leaves + k;
+        // m elements; if the loop above ran, its last merged node `pend` still has to be inserted (then the heap holds m - 1 in slots 1 .. m-1)
+        uint32_t qend = piped ? m : m + 1u, nn = leaves + k;
         auto ld = [&](uint32_t i) { return hp_ld2(base + 8u * i); };
         auto st = [&](uint32_t i, uint2 e) { hp_st2(base + 8u * i, e.x, e.y); };
         auto rem = [&]() {
@@ -174,19 +222,25 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
             st(i, mm);
             return top;
         };
-        while (qend > 2u) {
-            const uint2 rb = rem(), ra = rem();
-            n_left[nn] = ra.y; n_right[nn] = rb.y;
-            const uint2 e = make_uint2(ra.x + rb.x, nn);
+        auto ins = [&](const uint2 e) {
             uint32_t i = qend++, jj;
             while ((jj = i >> 1)) { const uint2 pj = ld(jj); if (pj.x <= e.x) break; st(i, pj); i = jj; }
             st(i, e);
+        };
+        if (piped) ins(pend);
+        while (qend > 2u) {
+            const uint2 rb = rem(), ra = rem();
+            n_left[nn] = ra.y; n_right[nn] = rb.y;
+            ins(make_uint2(ra.x + rb.x, nn));
             nn++;
         }
         rootn = ld(1u).y;
     }
     rootn = __shfl_sync(0xffffffffu, rootn, 0);
     if (lane == 0) prof_out[6] = (uint32_t)((clock64() - tk1) >> 10);
+#ifdef HP_COUNT
+    if (lane == 0) { prof_out[8] = ticks; prof_out[9] = n_wait_e; prof_out[10] = n_wait_c; }
+#endif
     return rootn;
 }
 

@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         // n[] at the same offsets; the producer writes its queue entries into rank 1's shared memory (one 64-bit remote store per
         // merge, nothing waits for it), the consumer works on its own SM's memory and sends its progress counter and the root back
         const uint32_t fcap_p = (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u);
-        const bool piped = heap_form == 0u && leaves + 2u <= smem_heap_capacity;
+        const bool piped = heap_form == 0u && leaves + 4u <= smem_heap_capacity;
         const bool pair = csize > 1 && !piped && !compact && !tight16 && leaves + 8u <= fcap_p;
         if (rank != 0 && !pair) return;
         if (piped) {
