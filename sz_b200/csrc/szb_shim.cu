@@ -756,6 +756,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     CU(cudaStreamSynchronize(c.stream));
     if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
         fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
+    if (h_chain.err) { set_err("coefficient chain: a step left its tabulated interval (internal error)"); return SZ_NSCS; }
     for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err(h_tree[i][3] == 2 ? "Huffman tree build gave up (tree %d)" : "Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
     uint64_t cbytes[4] = {0, 0, 0, 0};
     for (int e = 0; e < ntrees - 1; e++) cbytes[e] = (h_tot[3 + e] + 7) / 8;

@@ -502,7 +502,7 @@ __global__ void reg_gather_kernel(const unsigned char *__restrict__ indicator, c
 // recurrence, so each coefficient is ONE serial lane; the ncoef lanes run side by side in one warp.  The whole warp
 // stages 256 steps at a time through shared memory so that global loads/stores are coalesced and off the chain.
 // =====================================================================================================================
-struct ChainOut { unsigned int unpred_count[4]; };
+struct ChainOut { unsigned int unpred_count[4]; unsigned int err; };
 
 // one step of the reference's coefficient quantiser as a function of `last` (exact formula, ref: sz_float.c:7130-7150)
 template <typename T>
@@ -532,13 +532,13 @@ __device__ __forceinline__ int chain_step_exact(T cur, T last, T prec, T rprec, 
 // the serial kernel then only compares, selects and adds.  Anything outside the prepared interval / piece budget takes
 // the exact formula in the serial kernel, so the result is bit-identical by construction.
 template <typename T> struct __align__(16) ChainStep {
-    T lo, hi;            // interval of `last` covered by the table; not tabulated: lo = +inf, hi = -inf (no `last` is inside)
-    T thr1, thr2;        // piece 0: last <= thr1; piece 1: thr1 < last <= thr2; piece 2: last > thr2
+    T thr1, thr2;        // piece 0: last <= thr1; piece 1: thr1 < last <= thr2; piece 2: last > thr2 (a threshold that is not needed
+                         // lies beyond the interval `last` can be in)
     T d0, d1, d2;        // increment fl(fl(2k) * prec) of each piece; +inf for a piece beyond the code capacity, which makes
                          // the serial kernel's verification fail and the coefficient itself the new `last`, as the reference does
     T cur;               // the coefficient being quantised
-    uint16_t c0, c1, c2; // code (k + 32768) of each piece; 0 = beyond the 65536-interval capacity (unpredictable)
-    uint16_t np;         // number of pieces (0 = not tabulated: use the exact formula)
+    uint32_t np;         // number of pieces (0 = not tabulated: the serial kernel uses the exact formula for this step)
+    uint32_t pad_[sizeof(T) == 4 ? 1 : 3];                   // 32 bytes (float) / 64 bytes (double)
 };
 
 template <typename T> struct Ord;
@@ -575,7 +575,8 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
     const T rprec = (T)1 / prec;
     const T cur = reg_c[(size_t)e * nb + r];
     ChainStep<T> st;
-    st.cur = cur; st.np = 0; st.c0 = st.c1 = st.c2 = 0; st.d0 = st.d1 = st.d2 = (T)0; st.thr1 = st.thr2 = (T)0;
+    st.cur = cur; st.np = 0; st.d0 = st.d1 = st.d2 = (T)0; st.thr1 = st.thr2 = (T)0;
+    for (auto &w : st.pad_) w = 0u;
     T lo, hi;
     if (r == 0) { lo = (T)0; hi = (T)0; }
     else {
@@ -584,7 +585,6 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
         lo = prev - w; hi = prev + w;
         lo = Ord<T>::from(Ord<T>::to(lo) - 2); hi = Ord<T>::from(Ord<T>::to(hi) + 2);
     }
-    st.lo = lo; st.hi = hi;
     const U olo = Ord<T>::to(lo), ohi = Ord<T>::to(hi);
     bool finite = (lo == lo) && (hi == hi) && TT<T>::abs(lo) < (T)1e30 && TT<T>::abs(hi) < (T)1e30 && TT<T>::abs(cur) < (T)1e30 && prec > (T)0;
     if (finite) {
@@ -606,18 +606,16 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
             a = l + 1;
         }
         if (okp) {
-            auto code_of = [](int k) -> uint16_t { return (k == (1 << 20) || k == -(1 << 20)) ? (uint16_t)0 : (uint16_t)(k + 32768); };
             auto delta_of = [&](int k) -> T { if (k == (1 << 20) || k == -(1 << 20)) return (T)INFINITY; T dq = (T)(2 * k); return dq * prec; };
-            st.np = (uint16_t)np;
-            st.c0 = code_of(pk[0]); st.d0 = delta_of(pk[0]);
+            st.np = (uint32_t)np;
+            st.d0 = delta_of(pk[0]);
             const T big = hi;                               // thresholds beyond hi are never exceeded inside the interval
             st.thr1 = np > 1 ? Ord<T>::from(pend[0]) : big;
             st.thr2 = np > 2 ? Ord<T>::from(pend[1]) : big;
-            if (np > 1) { st.c1 = code_of(pk[1]); st.d1 = delta_of(pk[1]); }
-            if (np > 2) { st.c2 = code_of(pk[2]); st.d2 = delta_of(pk[2]); }
+            if (np > 1) st.d1 = delta_of(pk[1]);
+            if (np > 2) st.d2 = delta_of(pk[2]);
         }
     }
-    if (st.np == 0) { st.lo = (T)INFINITY; st.hi = -(T)INFINITY; }
     steps[(size_t)e * reg_count + r] = st;
 }
 
@@ -625,8 +623,11 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
 // K5: coefficient DPCM chain (S1; ref: sz_float.c:7126-7152 no-mean "/precision", :6792-6812 mean "*recip", 2D :6035-6055;
 // double always "*recip").  last[e] threads through every regression block in raster order: one serial lane per
 // coefficient, the ncoef lanes side by side in one warp.  Per step: two compares select the prepared piece, one add
-// applies it, one subtract + compare verifies it (the reference's "machine-epsilon" guard).  128 steps at a time are
-// staged through shared memory by the whole warp so that global traffic is coalesced and off the chain.
+// applies it, one subtract + compare verifies it (the reference's "machine-epsilon" guard): seven dependent operations, ten
+// instructions with the loads and the store.  `last` entering a step lies inside the interval its table was made for by
+// construction (the step before verified |c - last| <= prec or set last = c, and chain_prep covers that with slack).
+// Nothing relies on that argument alone: the helper warps recompute EVERY step from the `last` the serial warp stored with the
+// exact formula -- that gives the codes -- and compare the next `last`; a difference raises ChainOut::err and the job fails.
 // =====================================================================================================================
 constexpr int CHAIN_THREADS = 192;
 template <typename T>
@@ -635,57 +636,52 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
                                                           uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/,
                                                           T *__restrict__ coeff_unpred /*[ncoef][nb]*/, ChainOut *out) {
     // A three-stage software pipeline over chunks of CH steps, one __syncthreads per chunk:
-    //   warp 0, lanes 0..ncoef-1 : (A) the serial part proper of chunk c -- only the sequence of `last` values.  All three
-    //                              pieces of the step table are evaluated speculatively (three independent add / verify
-    //                              chains) and selected at the end, so the dependent chain is add -> subtract -> compare -> select;
-    //   warps 1, 2, 3, 5 (one per coefficient; warp 4 would share warp 0's scheduler and only idles) : (B) codes and the ordered unpredictable list of chunk c-1, recomputed from the
-    //                              stored `last` sequence in parallel and written back coalesced; and the prefetch of the step
-    //                              tables of chunk c+1.
+    //   warp 0, lanes 0..ncoef-1 : (A) the serial part proper of chunk c -- only the sequence of `last` values;
+    //   warps 1, 2, 3, 5 (one per coefficient; warp 4 would share warp 0's scheduler and only idles) : the fetch of the step
+    //                              tables of chunk c+1, then (B) codes and the ordered unpredictable list of chunk c-1, computed from
+    //                              the stored `last` sequence in parallel and written back coalesced.
     // The serial warp therefore never waits for anything but its own arithmetic.
     constexpr int CH = sizeof(T) == 4 ? 64 : 32;
-    constexpr int WORDS = sizeof(ChainStep<T>) / 4;
     __shared__ __align__(16) ChainStep<T> s_step[3][4][CH + 1];
+    __shared__ int s_untab[3][4];                          // the chunk holds a step without a table
     __shared__ T s_last[2][4][CH + 1];                     // s_last[.][e][i] = value of last ENTERING step i (slot cnt: leaving the chunk)
     __shared__ uint32_t s_blk[3][CH];
     __shared__ unsigned int s_ucnt[4];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid < 4) s_ucnt[tid] = 0;
-    // all loads of a chunk are issued before the first store (one L2 round trip per chunk, not one per coefficient)
-    auto load_chunk = [&](uint32_t chunk, int t0, int nt) {
+    // a helper warp fetches the step tables of its coefficient for one chunk: every lane whole steps, all loads issued before the
+    // first store
+    auto load_chunk = [&](uint32_t chunk, int e, int ln) {
         const uint32_t r0 = chunk * CH;
-        if (r0 >= reg_count) return;
+        if (r0 >= reg_count || e >= ncoef) return;
         const int buf = (int)(chunk % 3u);
         const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        const int per = cnt * WORDS;
-        constexpr int MAXQ = (CH * WORDS + 127) / 128;
-        uint32_t v[4][MAXQ];
+        constexpr int PER = CH / 32;
+        ChainStep<T> st[PER];
+        uint32_t blk[PER];
 #pragma unroll
-        for (int e = 0; e < 4; e++) {
-            const uint32_t *src = reinterpret_cast<const uint32_t *>(steps + (size_t)e * reg_count + r0);
+        for (int q = 0; q < PER; q++) {
+            const int i = ln + 32 * q;
+            if (i < cnt) { st[q] = steps[(size_t)e * reg_count + r0 + i]; blk[q] = e == 0 ? reg_list[r0 + i] : 0u; }
+        }
+        bool untab = false;
 #pragma unroll
-            for (int q = 0; q < MAXQ; q++) {
-                const int w = t0 + q * nt;
-                if (e < ncoef && w < per) v[e][q] = __ldg(src + w);
+        for (int q = 0; q < PER; q++) {
+            const int i = ln + 32 * q;
+            if (i < cnt) {
+                s_step[buf][e][i] = st[q];
+                untab = untab || st[q].np == 0u;
+                if (e == 0) s_blk[buf][i] = blk[q];
             }
         }
-        const uint32_t blk = (t0 < cnt) ? reg_list[r0 + t0] : 0u;
-#pragma unroll
-        for (int e = 0; e < 4; e++) {
-            uint32_t *dst = reinterpret_cast<uint32_t *>(&s_step[buf][e][0]);
-#pragma unroll
-            for (int q = 0; q < MAXQ; q++) {
-                const int w = t0 + q * nt;
-                if (e < ncoef && w < per) dst[w] = v[e][q];
-            }
-        }
-        if (t0 < cnt) s_blk[buf][t0] = blk;
+        untab = __any_sync(0xffffffffu, untab);
+        if (ln == 0) s_untab[buf][e] = untab ? 1 : 0;
     };
     T last = (T)0;                                          // carried by warp 0, lane e
     const T precA = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : p3;
     const T rprecA = (T)1 / precA;
     const int eB = warp == 5 ? 3 : ((warp == 4 || warp == 0) ? 99 : warp - 1);     // helper warps 1,2,3,5 <-> coefficient 0..3; warps 0 and 4: none
-    const int tB = eB * 32 + lane;                                   // thread index among the 128 helper threads
-    if (eB < 4 && eB >= 0) load_chunk(0, tB, 128);
+    if (eB < 4 && eB >= 0) load_chunk(0, eB, lane);
     const T precB = eB == 0 ? p0 : eB == 1 ? p1 : eB == 2 ? p2 : p3;
     const T rprecB = (T)1 / precB;
     const uint32_t nchunks = (reg_count + CH - 1) / CH;
@@ -696,49 +692,38 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
             if (it < nchunks && lane < ncoef) {
                 const int e = lane, buf = (int)(it % 3u), lb = (int)(it & 1u);
                 const int cnt = (int)min((uint32_t)CH, reg_count - it * CH);
-                // The chunk is first run on the tables alone, without a branch in the step; `allin` records whether every `last`
-                // fell inside its tabulated interval.  If one did not (rare: a table is missing or the slack around the previous
-                // coefficient was not enough) the chunk is run again with the exact formula available at every step.
-                const T last0 = last;
-                bool allin = true;
-                {
-                    ChainStep<T> nxt = s_step[buf][e][0];
+                const ChainStep<T> *sp = &s_step[buf][e][0];
+                T *lp = &s_last[lb][e][0];
+                if (s_untab[buf][e] == 0) {
+#pragma unroll 8
                     for (int i = 0; i < cnt; i++) {
-                        const ChainStep<T> st = nxt;
-                        nxt = s_step[buf][e][i + 1];           // fetched while this step computes (slot CH is padding)
-                        s_last[lb][e][i] = last;
-                        allin = allin && (last >= st.lo) && (last <= st.hi);
-                        const bool g1 = last > st.thr1, g2 = last > st.thr2;
-                        T d = g1 ? st.d1 : st.d0;
-                        d = g2 ? st.d2 : d;
+                        const ChainStep<T> st = sp[i];
+                        lp[i] = last;
+                        T d = last > st.thr1 ? st.d1 : st.d0;
+                        d = last > st.thr2 ? st.d2 : d;
                         const T v = last + d;
                         const T k = st.cur - v;
                         last = TT<T>::abs(k) > precA ? st.cur : v;
                     }
-                }
-                if (!allin) {
-                    last = last0;
-                    ChainStep<T> nxt = s_step[buf][e][0];
+                } else {
+                    // a step without a table in this chunk (non-finite input, or more than three pieces): the exact formula there
                     for (int i = 0; i < cnt; i++) {
-                        const ChainStep<T> st = nxt;
-                        nxt = s_step[buf][e][i + 1];
-                        s_last[lb][e][i] = last;
-                        const bool in = last >= st.lo && last <= st.hi;
-                        const bool g1 = last > st.thr1, g2 = last > st.thr2;
-                        T d = g1 ? st.d1 : st.d0;
-                        d = g2 ? st.d2 : d;
+                        const ChainStep<T> st = sp[i];
+                        lp[i] = last;
+                        T d = last > st.thr1 ? st.d1 : st.d0;
+                        d = last > st.thr2 ? st.d2 : d;
                         const T v = last + d;
                         const T k = st.cur - v;
                         T nl = TT<T>::abs(k) > precA ? st.cur : v;
-                        if (!in) (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
+                        if (st.np == 0u) (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
                         last = nl;
                     }
                 }
-                s_last[lb][e][cnt] = last;
+                lp[cnt] = last;
             }
         } else {
-            // ---- prefetch chunk it+1, then (B) chunk it-1 ----
-            if (it + 1 < nchunks && eB < 4) load_chunk(it + 1, tB, 128);
+            // ---- fetch chunk it+1, then (B) chunk it-1 ----
+            if (it + 1 < nchunks && eB < 4) load_chunk(it + 1, eB, lane);
             if (it >= 1 && eB < ncoef) {
                 const uint32_t cb = it - 1, r0 = cb * CH;
                 const int e = eB, buf = (int)(cb % 3u), lb = (int)(cb & 1u);
@@ -747,20 +732,13 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
                     const int i = i0 + lane;
                     int ct = 1; T cur = (T)0;
                     if (i < cnt) {
-                        const ChainStep<T> st = s_step[buf][e][i];
-                        const T lin = s_last[lb][e][i];
-                        cur = st.cur;
+                        cur = s_step[buf][e][i].cur;
+                        const T lin = s_last[lb][e][i], lout = s_last[lb][e][i + 1];
                         T nl;
-                        if (st.np != 0 && lin >= st.lo && lin <= st.hi) {
-                            const bool g1 = lin > st.thr1, g2 = lin > st.thr2;
-                            const T d = g2 ? st.d2 : (g1 ? st.d1 : st.d0);
-                            const int c = g2 ? st.c2 : (g1 ? st.c1 : st.c0);
-                            const T v = lin + d;
-                            const T chk = st.cur - v;
-                            ct = ((c == 0) || (TT<T>::abs(chk) > precB)) ? 0 : c;
-                        } else ct = chain_step_exact<T>(st.cur, lin, precB, rprecB, use_div, nl);
+                        ct = chain_step_exact<T>(cur, lin, precB, rprecB, use_div, nl);
+                        if (!(nl == lout)) out->err = 1u;          // the serial warp's table step and the exact formula disagree: never seen
                         coeff_type[(size_t)e * nb + r0 + i] = (uint16_t)ct;
-                        coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_last[lb][e][i + 1];
+                        coeff_last[(size_t)e * nb + s_blk[buf][i]] = lout;
                     }
                     const unsigned int zmask = __ballot_sync(0xffffffffu, i < cnt && ct == 0);
                     const unsigned int base = s_ucnt[e];
