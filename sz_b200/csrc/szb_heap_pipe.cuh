@@ -91,8 +91,12 @@ static __device__ __forceinline__ void hp_insert_warp(const unsigned base, const
 
 // Leaf inserts, merges, and the root: the whole heap part of one tree, run by ONE warp (all 32 lanes call it).
 //   base: shared address of the heap, 16-byte aligned, 8 (leaves + 4) bytes; lfreq: leaf frequencies in increasing symbol order (global memory)
-//   n_left / n_right: children of the internal nodes (global memory), node ids: leaves 0 .. leaves-1, internal nodes in merge order
-static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t leaves, const uint32_t *__restrict__ lfreq, uint32_t *n_left, uint32_t *n_right,
+//   up: what the passes after the heap need, per node (global memory, written as the merges happen, never read here):
+//       {parent:16 | 1 + nodes of the left sibling's subtree if this node is a right child, else 1 : 16}; the root keeps HP_ROOT.
+//   Node ids: leaves 0 .. leaves-1 in symbol order, internal nodes in merge order; fewer than 32768 leaves (ids and subtree sizes fit
+//   16 bits: the node word of a heap entry is {id:16 | nodes in its subtree:16}, so a merge knows its subtree size without a lookup).
+constexpr uint32_t HP_ROOT = 0xffffffffu;
+static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t leaves, const uint32_t *__restrict__ lfreq, uint32_t *up,
                                                  uint32_t *prof_out, const long long tk1) {
     int lane = threadIdx.x & 31;
     asm volatile("mov.u32 %0, %0;" : "+r"(lane));
@@ -112,12 +116,12 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
                 const bool mine = lane < cnt;
                 const uint32_t fp = mine ? hp_ld2(base + 8u * (unsigned)((q0 + lane) >> 1)).x : 0u;
                 sift = __ballot_sync(0xffffffffu, mine && fp > cur);
-                if (mine && ((sift >> lane) & 1u) == 0u) hp_st2(base + 8u * (unsigned)(q0 + lane), cur, k0 + (uint32_t)lane);
+                if (mine && ((sift >> lane) & 1u) == 0u) hp_st2(base + 8u * (unsigned)(q0 + lane), cur, (k0 + (uint32_t)lane) | 0x10000u);
                 __syncwarp();
             }
             while (sift) {
                 const int j = __ffs((int)sift) - 1; sift &= sift - 1u;
-                hp_insert_warp(base, q0 + j, __shfl_sync(0xffffffffu, cur, j), k0 + (uint32_t)j, lane);
+                hp_insert_warp(base, q0 + j, __shfl_sync(0xffffffffu, cur, j), (k0 + (uint32_t)j) | 0x10000u, lane);
             }
             qend = q0 + cnt;
             cur = nxt;
@@ -139,8 +143,8 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
 #endif
     const bool piped = m >= HP_TAIL;
     uint2 pend = make_uint2(0u, 0u);                              // the merged node whose insertion is still to be done when the loop ends
+    uint32_t nid1 = leaves + 0x10000u, ra = 0u, rb = 0u;        // next node id (+ the 1 of its subtree size); lane's pending records
     if (piped) {
-        uint32_t *pl = n_left + leaves, *pr = n_right + leaves;
         // first removal of the first merge: takes the root `a`, the last element sinks from the root
         uint2 a = hp_ld2(base + 8u);
         { const uint2 e1 = hp_ld2(base + 8u * m); __syncwarp(); hp_st2(base + 8u * m, HP_INF, 0u);
@@ -165,11 +169,15 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
             ticks++;
             busy = hp_tick<true>(base, capa, S, x, lvx - (int)ticks);
             // the merged node: first removed -> right, second removed -> left (gcc evaluates the arguments of Huffman.c:181 right to left)
-            const uint32_t nn = leaves + k, kn = a.x + b.x;
-#ifndef HP_NO_GST
-            if (lane == 0) { *pl = b.y; *pr = a.y; }
-#endif
-            pl++; pr++;
+            const uint32_t kn = a.x + b.x;
+            const uint32_t nn = (a.y & 0xffff0000u) + (b.y & 0xffff0000u) + nid1;      // {id, nodes of both subtrees + 1}
+            nid1++;
+            // the two `up` records of this merge are kept by lane k mod 32 and written 32 merges at a time
+            if (lane == (int)(k & 31u)) { ra = a.y; rb = b.y; }
+            if ((k & 31u) == 31u) {
+                const uint32_t nid = leaves + k - 31u + (uint32_t)lane;
+                up[rb & 0xffffu] = nid | 0x10000u; up[ra & 0xffffu] = nid | ((rb & 0xffff0000u) + 0x10000u);
+            }
             if (m - 1u < HP_TAIL) { pend = make_uint2(kn, nn); break; }
             // its insertion at slot x (Huffman.c:76-85), once the ancestor chain of x is nobody's, in one round trip with the launch and
             // first level of the next merge's first removal, which takes what the insertion would leave in slot x out of it again:
@@ -201,13 +209,17 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
             hp_tick_finish<false>(base, capa, S, v); ticks++;
         }
         m--; k++;                                                 // the merge whose node is still in `pend`
+        if ((k & 31u) != 0u && (uint32_t)lane < (k & 31u)) {      // the records of the last, incomplete group of merges
+            const uint32_t nid = leaves + (k & ~31u) + (uint32_t)lane;
+            up[rb & 0xffffu] = nid | 0x10000u; up[ra & 0xffffu] = nid | ((rb & 0xffff0000u) + 0x10000u);
+        }
     }
     while (__any_sync(0xffffffffu, S.ek != 0u)) hp_tick<false>(base, capa, S);
     // ---- the last few merges, one operation after the other (lane 0) ----
     uint32_t rootn = 0u;
     if (lane == 0) {
         // m elements; if the loop above ran, its last merged node `pend` still has to be inserted (then the heap holds m - 1 in slots 1 .. m-1)
-        uint32_t qend = piped ? m : m + 1u, nn = leaves + k;
+        uint32_t qend = piped ? m : m + 1u, nid = leaves + k;
         auto ld = [&](uint32_t i) { return hp_ld2(base + 8u * i); };
         auto st = [&](uint32_t i, uint2 e) { hp_st2(base + 8u * i, e.x, e.y); };
         auto rem = [&]() {
@@ -229,12 +241,14 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
         };
         if (piped) ins(pend);
         while (qend > 2u) {
-            const uint2 rb = rem(), ra = rem();
-            n_left[nn] = ra.y; n_right[nn] = rb.y;
-            ins(make_uint2(ra.x + rb.x, nn));
-            nn++;
+            const uint2 rb = rem(), ra = rem();                  // first removed -> right, second -> left
+            const uint32_t sl = ra.y >> 16;
+            up[ra.y & 0xffffu] = nid | 0x10000u; up[rb.y & 0xffffu] = nid | ((sl + 1u) << 16);
+            ins(make_uint2(ra.x + rb.x, nid | ((sl + (rb.y >> 16) + 1u) << 16)));
+            nid++;
         }
-        rootn = ld(1u).y;
+        rootn = ld(1u).y & 0xffffu;
+        up[rootn] = HP_ROOT;
     }
     rootn = __shfl_sync(0xffffffffu, rootn, 0);
     if (lane == 0) prof_out[6] = (uint32_t)((clock64() - tk1) >> 10);

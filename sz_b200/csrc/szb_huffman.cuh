@@ -501,30 +501,52 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
     __shared__ uint32_t s_root, s_leaves, s_cnt, s_err, s_lvl[72];
     const int t = threadIdx.x;
     const long long tk0 = clock64();
-    // ---- phase A (parallel): ordered compaction of the non-empty bins -> leaf nodes 0..leaves-1 in increasing symbol order ----
+    // ---- phase A (parallel): ordered compaction of the non-empty bins -> leaf nodes 0..leaves-1 in increasing symbol order.
+    //      Every warp takes a contiguous range of bins, 32 at a time (coalesced), one vote per row counts and places them ----
     uint32_t *lfreq = D.n_pre;                                  // scratch until phase E
     {
-        const uint32_t per = (D.nbins + blockDim.x - 1) / blockDim.x;
-        const uint32_t lo = min(D.nbins, t * per), hi = min(D.nbins, lo + per);
+        const int warp = t >> 5, lane = t & 31;
+        const uint32_t rows = (D.nbins + HUFF_TB - 1) / HUFF_TB;                   // rows of 32 bins per warp
+        const uint32_t bin0 = (uint32_t)warp * rows * 32u;
         uint32_t cnt = 0;
-        for (uint32_t i = lo; i < hi; i++) cnt += (D.hist[i] != 0);
-        s_scan[t] = cnt;
-        __syncthreads();
-        for (int o = 1; o < HUFF_TB; o <<= 1) { uint32_t v = (t >= o) ? s_scan[t - o] : 0; __syncthreads(); s_scan[t] += v; __syncthreads(); }
-        uint32_t k = s_scan[t] - cnt;
-        if (rank == 0) for (uint32_t i = lo; i < hi; i++) {
-            uint32_t f = D.hist[i];
-            if (f) { D.n_sym[k] = i; lfreq[k] = f; D.n_left[k] = 0xffffffffu; D.n_right[k] = 0xffffffffu; k++; }
+#pragma unroll 8
+        for (uint32_t r = 0; r < rows; r++) {
+            const uint32_t bin = bin0 + 32u * r + (uint32_t)lane;
+            const uint32_t f = bin < D.nbins ? D.hist[bin] : 0u;
+            cnt += __popc(__ballot_sync(0xffffffffu, f != 0u));
         }
-        if (t == HUFF_TB - 1) { s_leaves = s_scan[HUFF_TB - 1]; s_err = 0; }
-        if (rank == 0) for (uint32_t i = t; i < D.nbins; i += blockDim.x) { D.code[i] = 0; D.clen[i] = 0; }
+        if (lane == 0) s_scan[warp] = cnt;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t c = s_scan[lane];
+            uint32_t inc = c;
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+            s_scan[32 + lane] = inc - c;
+            if (lane == 31) { s_leaves = inc; s_err = 0; }
+        }
+        __syncthreads();
+        uint32_t k = s_scan[32 + warp];
+        if (rank == 0) {
+#pragma unroll 8
+            for (uint32_t r = 0; r < rows; r++) {                                  // the counts again (cache hits)
+                const uint32_t bin = bin0 + 32u * r + (uint32_t)lane;
+                const uint32_t f = bin < D.nbins ? D.hist[bin] : 0u;
+                const unsigned mk = __ballot_sync(0xffffffffu, f != 0u);
+                if (f != 0u) { const uint32_t idx = k + __popc(mk & ((1u << lane) - 1u)); D.n_sym[idx] = bin; lfreq[idx] = f; }
+                k += __popc(mk);
+            }
+        }
         __syncthreads();
     }
     const uint32_t leaves = s_leaves;
     const uint32_t nodeCount = leaves ? 2 * leaves - 1 : 0;
     if (leaves == 0) { if (t == 0 && rank == 0) { D.out[0] = 0; D.out[1] = 0; D.out[2] = 0; D.out[3] = 0; } return; }
+    // the code table of the absent symbols (never looked up by the encoder; kept defined) -- by the threads that would otherwise
+    // only wait for the heap
+    if (rank == 0 && t >= 64) for (uint32_t i = t - 64; i < D.nbins; i += blockDim.x - 64) { D.code[i] = 0; D.clen[i] = 0; }
     // ---- phase B (serial): exact emulation of the reference's heap ----
     const long long tk1 = clock64();
+    bool piped_tree = false;
     {
         // separate inlined copies of the heap loops per layout, so that the shared-memory ones compile to LDS/STS with 32-bit
         // addresses instead of generic loads (a pointer that may be shared OR global forces the slower generic path)
@@ -541,13 +563,15 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         // n[] at the same offsets; the producer writes its queue entries into rank 1's shared memory (one 64-bit remote store per
         // merge, nothing waits for it), the consumer works on its own SM's memory and sends its progress counter and the root back
         const uint32_t fcap_p = (uint32_t)(((smem_heap_capacity * 8u - 8u * HQ_CAP) / 4u) & ~3u);
-        const bool piped = heap_form == 0u && leaves + 4u <= smem_heap_capacity;
+        const bool piped = heap_form == 0u && leaves + 4u <= smem_heap_capacity && leaves < 32768u;
+        piped_tree = piped;
         const bool pair = csize > 1 && !piped && !compact && !tight16 && leaves + 8u <= fcap_p;
         if (rank != 0 && !pair) return;
+        if (!piped && rank == 0) { for (uint32_t q = t; q < leaves; q += blockDim.x) { D.n_left[q] = 0xffffffffu; D.n_right[q] = 0xffffffffu; } __syncthreads(); }
         if (piped) {
             // several heap operations in flight in one warp, {frequency, node} entries of 8 bytes (szb_heap_pipe.cuh)
             if (t < 32) {
-                const uint32_t root = hp_build((unsigned int)__cvta_generic_to_shared(s_heap), leaves, lfreq, D.n_left, D.n_right, D.out, tk1);
+                const uint32_t root = hp_build((unsigned int)__cvta_generic_to_shared(s_heap), leaves, lfreq, D.n_left, D.out, tk1);
                 if (t == 0) s_root = root;
             }
         } else if (compact || tight16) {
@@ -622,6 +646,55 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         else if (w == 2) { base[2 * idx] = (unsigned char)v; base[2 * idx + 1] = (unsigned char)(v >> 8); }
         else { base[4 * idx] = (unsigned char)v; base[4 * idx + 1] = (unsigned char)(v >> 8); base[4 * idx + 2] = (unsigned char)(v >> 16); base[4 * idx + 3] = (unsigned char)(v >> 24); }
     };
+    if (piped_tree) {
+        // ---- the pipelined heap left, per node, {parent, 1 + size of the left sibling's subtree if it is a right child, else 1}.  The
+        //      pre-order index of a node (pad_tree_*, Huffman.c:443-501) is the sum of the second field along its ancestor chain, its code
+        //      (build_code, :122-157) the "is a right child" bits along the chain, deepest bit last.  Every node walks its own chain, in
+        //      shared memory (the heap's, free now): no level-by-level passes, no frontier ----
+        uint32_t *ups = s_heap;
+        uint32_t *pre_g = D.n_pre;                                  // pre-order index per node (the leaf frequencies kept there are done with)
+        for (uint32_t n = t; n < nodeCount; n += blockDim.x) ups[n] = D.n_left[n];
+        if (t == 0) tb[0] = 0;
+        __syncthreads();
+        for (uint32_t n = t; n < nodeCount; n += blockDim.x) {
+            uint32_t e = ups[n], pre = 0, len = 0; uint64_t code = 0;
+            while (e != HP_ROOT) {
+                const uint32_t step = e >> 16;
+                pre += step;
+                if (len < 64 && step > 1u) code |= 1ULL << len;
+                len++;
+                e = ups[e & 0xffffu];
+            }
+            pre_g[n] = pre;
+            if (n < leaves) {
+                const uint32_t sym = D.n_sym[n];
+                if (len > 64) s_err = 1;
+                D.code[sym] = code; D.clen[sym] = (uint8_t)len;
+            }
+        }
+        __syncthreads();
+        // the serialised arrays are written in THEIR order (consecutive threads, consecutive records): inv[] = node of a pre-order
+        // index, rch[] = pre-order index of the right child (the left child's is the record's own + 1), both in shared memory
+        uint16_t *inv = reinterpret_cast<uint16_t *>(s_heap), *rch = inv + nodeCount + 1;
+        for (uint32_t n = t; n < nodeCount; n += blockDim.x) {
+            const uint32_t pre = pre_g[n], e0 = D.n_left[n];        // (the shared copy of the records is being overwritten)
+            inv[pre] = (uint16_t)n;
+            if (e0 != HP_ROOT && (e0 >> 16) > 1u) rch[pre - (e0 >> 16)] = (uint16_t)pre;
+        }
+        __syncthreads();
+        for (uint32_t q = t; q < nodeCount; q += blockDim.x) {
+            const uint32_t n = inv[q];
+            uint32_t l = 0, r = 0, c = 0, leaf = 0;
+            if (n < leaves) { c = D.n_sym[n]; leaf = 1; } else { l = q + 1; r = rch[q]; }
+            put_w(pl, q, l); put_w(pr, q, r);
+            pc[4 * q] = (unsigned char)c; pc[4 * q + 1] = (unsigned char)(c >> 8); pc[4 * q + 2] = (unsigned char)(c >> 16); pc[4 * q + 3] = (unsigned char)(c >> 24);
+            pt[q] = (unsigned char)leaf;
+        }
+        __syncthreads();
+        if (t == 0) { D.out[0] = 1 + 2 * w * nodeCount + 4 * nodeCount + nodeCount; D.out[1] = nodeCount; D.out[2] = leaves; D.out[3] = s_err;
+                      D.out[4] = (uint32_t)((tk1 - tk0) >> 10); D.out[7] = (uint32_t)((clock64() - tk2) >> 10); }
+        return;
+    }
     // ---- phase C (parallel): breadth-first order of the finished tree: order[] = nodes level by level, s_lvl[] = level starts ----
     uint32_t *order = D.frontier;                               // [capacity]
     uint32_t *nsize = D.frontier + D.capacity;                  // [capacity] subtree sizes (in nodes)

@@ -754,6 +754,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     for (int i = 1; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
+    if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u kcycles: serial warp busy=%u, helper warp busy=%u, total=%u\n", reg_count, h_chain.passes, h_chain.kcyc_serial, h_chain.kcyc_helper, h_chain.kcyc_total);
     if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
         fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
     if (h_chain.err) { set_err("coefficient chain: a step left its tabulated interval (internal error)"); return SZ_NSCS; }

@@ -2,6 +2,7 @@
 // sampling + finish (K3), use_mean mean (K4), regression fit + predictor selection (K2), regression-block
 // compaction and the coefficient DPCM chain (K5).  See DESIGN.md for the roofline of each.
 #pragma once
+#include <string.h>
 #include "szb_common.cuh"
 
 namespace szb {
@@ -502,7 +503,7 @@ __global__ void reg_gather_kernel(const unsigned char *__restrict__ indicator, c
 // recurrence, so each coefficient is ONE serial lane; the ncoef lanes run side by side in one warp.  The whole warp
 // stages 256 steps at a time through shared memory so that global loads/stores are coalesced and off the chain.
 // =====================================================================================================================
-struct ChainOut { unsigned int unpred_count[4]; unsigned int err; };
+struct ChainOut { unsigned int unpred_count[4]; unsigned int err; unsigned int passes, kcyc_serial, kcyc_total, kcyc_helper; };   // last four: profiling aid
 
 // one step of the reference's coefficient quantiser as a function of `last` (exact formula, ref: sz_float.c:7130-7150)
 template <typename T>
@@ -622,13 +623,27 @@ __global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ r
 // =====================================================================================================================
 // K5: coefficient DPCM chain (S1; ref: sz_float.c:7126-7152 no-mean "/precision", :6792-6812 mean "*recip", 2D :6035-6055;
 // double always "*recip").  last[e] threads through every regression block in raster order: one serial lane per
-// coefficient, the ncoef lanes side by side in one warp.  Per step: two compares select the prepared piece, one add
-// applies it, one subtract + compare verifies it (the reference's "machine-epsilon" guard): seven dependent operations, ten
-// instructions with the loads and the store.  `last` entering a step lies inside the interval its table was made for by
-// construction (the step before verified |c - last| <= prec or set last = c, and chain_prep covers that with slack).
-// Nothing relies on that argument alone: the helper warps recompute EVERY step from the `last` the serial warp stored with the
-// exact formula -- that gives the codes -- and compare the next `last`; a difference raises ChainOut::err and the job fails.
+// coefficient, the ncoef lanes side by side in one warp.
+//
+// The reference's step is: quantise (cur - last), add the de-quantised increment, and keep the result unless |cur - result| > prec
+// (its guard against rounding; then, and for a code beyond the capacity, last = cur and the coefficient is stored raw).  The guard
+// almost never fires, and it is the longer half of the dependent chain, so the serial warp runs a chunk WITHOUT it: which of the
+// (<= 3) prepared pieces, add its increment -- three additions side by side, two compares, two selects, a dependent chain of three
+// operations.  The helper warps then recompute every step of the chunk from the `last` values the serial warp stored, with the
+// exact formula: that gives the codes, and it proves the serial warp's sequence (each step's input is the stored value and its
+// output must equal the next stored value, bit for bit).  A chunk that fails the proof (the guard fired, a step had no table, a
+// `last` left its table's interval) is run again by the serial warp with the complete step, and the chunks after it are redone.
 // =====================================================================================================================
+// (x > thr) ? a : b without a predicate on the way: a compare that yields an all-ones / all-zeros word and a bitwise select.  On the
+// serial chain a predicate costs more than an ordinary result (it is produced late and the instruction it guards waits for it).
+__device__ __forceinline__ float pick_gt(float x, float thr, float a, float b) {
+    unsigned int m, r;
+    asm("set.gt.u32.f32 %0, %1, %2;" : "=r"(m) : "f"(x), "f"(thr));
+    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(r) : "r"(__float_as_uint(a)), "r"(__float_as_uint(b)), "r"(m));
+    return __uint_as_float(r);
+}
+__device__ __forceinline__ double pick_gt(double x, double thr, double a, double b) { return x > thr ? a : b; }
+
 constexpr int CHAIN_THREADS = 192;
 template <typename T>
 __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainStep<T> *__restrict__ steps, const uint32_t *__restrict__ reg_list, uint32_t nb,
@@ -638,17 +653,19 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
     // A three-stage software pipeline over chunks of CH steps, one __syncthreads per chunk:
     //   warp 0, lanes 0..ncoef-1 : (A) the serial part proper of chunk c -- only the sequence of `last` values;
     //   warps 1, 2, 3, 5 (one per coefficient; warp 4 would share warp 0's scheduler and only idles) : the fetch of the step
-    //                              tables of chunk c+1, then (B) codes and the ordered unpredictable list of chunk c-1, computed from
-    //                              the stored `last` sequence in parallel and written back coalesced.
+    //                              tables of chunk c+1, then (B) proof, codes and ordered unpredictable list of chunk c-1.
     // The serial warp therefore never waits for anything but its own arithmetic.
+    typedef typename TT<T>::bits_t bits_t;
     constexpr int CH = sizeof(T) == 4 ? 64 : 32;
+    constexpr int PER = CH / 32;
     __shared__ __align__(16) ChainStep<T> s_step[3][4][CH + 1];
-    __shared__ int s_untab[3][4];                          // the chunk holds a step without a table
     __shared__ T s_last[2][4][CH + 1];                     // s_last[.][e][i] = value of last ENTERING step i (slot cnt: leaving the chunk)
     __shared__ uint32_t s_blk[3][CH];
     __shared__ unsigned int s_ucnt[4];
+    __shared__ unsigned int s_redo[2];                     // slot pass & 1 = the pass number in which (B) found that its chunk failed the proof
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid < 4) s_ucnt[tid] = 0;
+    if (tid < 2) s_redo[tid] = 0u;
     // a helper warp fetches the step tables of its coefficient for one chunk: every lane whole steps, all loads issued before the
     // first store
     auto load_chunk = [&](uint32_t chunk, int e, int ln) {
@@ -656,7 +673,6 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
         if (r0 >= reg_count || e >= ncoef) return;
         const int buf = (int)(chunk % 3u);
         const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        constexpr int PER = CH / 32;
         ChainStep<T> st[PER];
         uint32_t blk[PER];
 #pragma unroll
@@ -664,18 +680,11 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
             const int i = ln + 32 * q;
             if (i < cnt) { st[q] = steps[(size_t)e * reg_count + r0 + i]; blk[q] = e == 0 ? reg_list[r0 + i] : 0u; }
         }
-        bool untab = false;
 #pragma unroll
         for (int q = 0; q < PER; q++) {
             const int i = ln + 32 * q;
-            if (i < cnt) {
-                s_step[buf][e][i] = st[q];
-                untab = untab || st[q].np == 0u;
-                if (e == 0) s_blk[buf][i] = blk[q];
-            }
+            if (i < cnt) { s_step[buf][e][i] = st[q]; if (e == 0) s_blk[buf][i] = blk[q]; }
         }
-        untab = __any_sync(0xffffffffu, untab);
-        if (ln == 0) s_untab[buf][e] = untab ? 1 : 0;
     };
     T last = (T)0;                                          // carried by warp 0, lane e
     const T precA = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : p3;
@@ -685,8 +694,12 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
     const T precB = eB == 0 ? p0 : eB == 1 ? p1 : eB == 2 ? p2 : p3;
     const T rprecB = (T)1 / precB;
     const uint32_t nchunks = (reg_count + CH - 1) / CH;
+    uint32_t committed = 0;                                 // helper warps: chunks of their coefficient proven and written out
+    uint32_t complete = 0xffffffffu;                        // the chunk the serial warp runs with the complete step (none)
+    long long cyc_a = 0, cyc_h = 0; const long long cyc_0 = clock64(); uint32_t npass = 0;
     __syncthreads();
-    for (uint32_t it = 0; it <= nchunks; it++) {
+    for (uint32_t it = 0, pass = 1; it <= nchunks; pass++) {
+        const long long cyc_1 = clock64(); npass++;
         if (warp == 0) {
             // ---- (A) chunk `it` ----
             if (it < nchunks && lane < ncoef) {
@@ -694,19 +707,50 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
                 const int cnt = (int)min((uint32_t)CH, reg_count - it * CH);
                 const ChainStep<T> *sp = &s_step[buf][e][0];
                 T *lp = &s_last[lb][e][0];
-                if (s_untab[buf][e] == 0) {
-#pragma unroll 8
-                    for (int i = 0; i < cnt; i++) {
-                        const ChainStep<T> st = sp[i];
-                        lp[i] = last;
-                        T d = last > st.thr1 ? st.d1 : st.d0;
-                        d = last > st.thr2 ? st.d2 : d;
-                        const T v = last + d;
-                        const T k = st.cur - v;
-                        last = TT<T>::abs(k) > precA ? st.cur : v;
+                if (it != complete) {
+                    // groups of four steps; the tables of the next group are fetched (explicit shared-memory loads, which the
+                    // compiler keeps where they are) before the current group is computed, so no step waits for its table
+                    struct Tab { T thr1, thr2, d0, d1, d2; };
+                    auto fetch = [&](Tab (&g)[4], int i0) {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            const unsigned a = (unsigned)__cvta_generic_to_shared(sp + min(i0 + q, CH));      // slot CH is padding
+                            if (sizeof(T) == 4) {
+                                uint32_t w0, w1, w2, w3, w4;
+                                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(a));
+                                asm volatile("ld.shared.u32 %0, [%1+16];" : "=r"(w4) : "r"(a));
+                                g[q].thr1 = (T)__uint_as_float(w0); g[q].thr2 = (T)__uint_as_float(w1); g[q].d0 = (T)__uint_as_float(w2);
+                                g[q].d1 = (T)__uint_as_float(w3); g[q].d2 = (T)__uint_as_float(w4);
+                            } else {
+                                unsigned long long w0, w1, w2, w3, w4;
+                                asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(w0), "=l"(w1) : "r"(a));
+                                asm volatile("ld.shared.v2.u64 {%0,%1}, [%2+16];" : "=l"(w2), "=l"(w3) : "r"(a));
+                                asm volatile("ld.shared.u64 %0, [%1+32];" : "=l"(w4) : "r"(a));
+                                g[q].thr1 = (T)__longlong_as_double((long long)w0); g[q].thr2 = (T)__longlong_as_double((long long)w1);
+                                g[q].d0 = (T)__longlong_as_double((long long)w2); g[q].d1 = (T)__longlong_as_double((long long)w3);
+                                g[q].d2 = (T)__longlong_as_double((long long)w4);
+                            }
+                        }
+                    };
+                    auto run = [&](const Tab (&g)[4], int i0) {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            if (i0 + q < cnt) {
+                                lp[i0 + q] = last;
+                                const T d = pick_gt(last, g[q].thr1, g[q].d1, g[q].d0);
+                                last = last + pick_gt(last, g[q].thr2, g[q].d2, d);
+                            }
+                        }
+                    };
+                    Tab ga[4], gb[4];
+                    fetch(ga, 0);
+                    for (int i0 = 0; i0 < cnt; i0 += 8) {
+                        fetch(gb, i0 + 4);
+                        run(ga, i0);
+                        fetch(ga, i0 + 8);
+                        run(gb, i0 + 4);
                     }
                 } else {
-                    // a step without a table in this chunk (non-finite input, or more than three pieces): the exact formula there
                     for (int i = 0; i < cnt; i++) {
                         const ChainStep<T> st = sp[i];
                         lp[i] = last;
@@ -715,7 +759,11 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
                         const T v = last + d;
                         const T k = st.cur - v;
                         T nl = TT<T>::abs(k) > precA ? st.cur : v;
-                        if (st.np == 0u) (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
+                        // no table for this step, or `last` not within prec of the previous coefficient, where the table was made for
+                        // (which the step before guarantees; the first step of the chunk is not worth looking the neighbour up):
+                        // the reference's arithmetic itself
+                        if (i == 0 || st.np == 0u || !(TT<T>::abs(sp[i - 1].cur - last) <= precA))
+                            (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
                         last = nl;
                     }
                 }
@@ -724,34 +772,60 @@ __global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainS
         } else {
             // ---- fetch chunk it+1, then (B) chunk it-1 ----
             if (it + 1 < nchunks && eB < 4) load_chunk(it + 1, eB, lane);
-            if (it >= 1 && eB < ncoef) {
+            if (it >= 1 && eB < ncoef && it - 1 == committed) {
                 const uint32_t cb = it - 1, r0 = cb * CH;
                 const int e = eB, buf = (int)(cb % 3u), lb = (int)(cb & 1u);
                 const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-                for (int i0 = 0; i0 < cnt; i0 += 32) {
-                    const int i = i0 + lane;
-                    int ct = 1; T cur = (T)0;
+                int ct[PER]; T cur[PER], lout[PER];
+                bool ok = true;
+#pragma unroll
+                for (int q = 0; q < PER; q++) {
+                    const int i = lane + 32 * q;
+                    ct[q] = 1; cur[q] = (T)0; lout[q] = (T)0;
                     if (i < cnt) {
-                        cur = s_step[buf][e][i].cur;
-                        const T lin = s_last[lb][e][i], lout = s_last[lb][e][i + 1];
+                        cur[q] = s_step[buf][e][i].cur;
+                        const T lin = s_last[lb][e][i];
+                        lout[q] = s_last[lb][e][i + 1];
                         T nl;
-                        ct = chain_step_exact<T>(cur, lin, precB, rprecB, use_div, nl);
-                        if (!(nl == lout)) out->err = 1u;          // the serial warp's table step and the exact formula disagree: never seen
-                        coeff_type[(size_t)e * nb + r0 + i] = (uint16_t)ct;
-                        coeff_last[(size_t)e * nb + s_blk[buf][i]] = lout;
+                        ct[q] = chain_step_exact<T>(cur[q], lin, precB, rprecB, use_div, nl);
+                        bits_t bn, bo; memcpy(&bn, &nl, sizeof(T)); memcpy(&bo, &lout[q], sizeof(T));
+                        ok = ok && bn == bo;
                     }
-                    const unsigned int zmask = __ballot_sync(0xffffffffu, i < cnt && ct == 0);
-                    const unsigned int base = s_ucnt[e];
-                    if (i < cnt && ct == 0) coeff_unpred[(size_t)e * nb + base + __popc(zmask & ((1u << lane) - 1u))] = cur;
-                    __syncwarp();
-                    if (lane == 0) s_ucnt[e] = base + __popc(zmask);
-                    __syncwarp();
+                }
+                ok = __all_sync(0xffffffffu, ok);
+                if (!ok && cb == complete) { if (lane == 0) out->err = 1u; ok = true; }     // the complete step itself disagrees: never seen
+                if (!ok) { if (lane == 0) s_redo[pass & 1u] = pass; }
+                else {
+                    committed = cb + 1;
+#pragma unroll
+                    for (int q = 0; q < PER; q++) {
+                        const int i = lane + 32 * q;
+                        if (i < cnt) {
+                            coeff_type[(size_t)e * nb + r0 + i] = (uint16_t)ct[q];
+                            coeff_last[(size_t)e * nb + s_blk[buf][i]] = lout[q];
+                        }
+                        const unsigned int zmask = __ballot_sync(0xffffffffu, i < cnt && ct[q] == 0);
+                        const unsigned int base = s_ucnt[e];
+                        if (i < cnt && ct[q] == 0) coeff_unpred[(size_t)e * nb + base + __popc(zmask & ((1u << lane) - 1u))] = cur[q];
+                        __syncwarp();
+                        if (lane == 0) s_ucnt[e] = base + __popc(zmask);
+                        __syncwarp();
+                    }
                 }
             }
         }
+        if (warp == 0) cyc_a += clock64() - cyc_1; else cyc_h += clock64() - cyc_1;
         __syncthreads();
+        if (s_redo[pass & 1u] == pass) {
+            // chunk it-1 again, with the complete step, from the value it was entered with (the chunks before it are proven)
+            it = it - 1;
+            complete = it;
+            if (warp == 0 && lane < ncoef) last = s_last[it & 1u][lane][0];
+        } else it++;
     }
     if (tid < 4) out->unpred_count[tid] = (tid < ncoef) ? s_ucnt[tid] : 0u;
+    if (tid == 0) { out->passes = npass; out->kcyc_serial = (unsigned int)(cyc_a >> 10); out->kcyc_total = (unsigned int)((clock64() - cyc_0) >> 10); }
+    if (tid == 5 * 32) out->kcyc_helper = (unsigned int)(cyc_h >> 10);
 }
 
 }  // namespace szb

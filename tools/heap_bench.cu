@@ -1,7 +1,7 @@
 // heap_bench.cu -- stand-alone timing and check of the pipelined Huffman heap (sz_b200/csrc/szb_heap_pipe.cuh) on one histogram.
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -I sz_b200/csrc -o /tmp/heap_bench tools/heap_bench.cu
 //   /tmp/heap_bench hist.bin [threads per CTA]        (hist.bin: uint32 counts per symbol; without a file: a synthetic bell)
-// Prints cycles per phase and per merge, and compares the children of every internal node with the sequential heap on the host.
+// Prints cycles per phase and per merge, and compares every node's {parent, pre-order step} record with the sequential heap on the host.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -14,11 +14,11 @@
 
 using namespace szb;
 
-__global__ void bench_kernel(const uint32_t *lfreq, uint32_t leaves, uint32_t *n_left, uint32_t *n_right, uint32_t *out, unsigned long long *cyc) {
+__global__ void bench_kernel(const uint32_t *lfreq, uint32_t leaves, uint32_t *up, uint32_t *out, unsigned long long *cyc) {
     extern __shared__ __align__(16) uint32_t s_heap[];
     if (threadIdx.x < 32) {
         const long long t0 = clock64();
-        const uint32_t root = hp_build((unsigned)__cvta_generic_to_shared(s_heap), leaves, lfreq, n_left, n_right, out, t0);
+        const uint32_t root = hp_build((unsigned)__cvta_generic_to_shared(s_heap), leaves, lfreq, up, out, t0);
         if (threadIdx.x == 0) { cyc[0] = (unsigned long long)(clock64() - t0); out[0] = root; }
     }
     __syncthreads();
@@ -55,20 +55,23 @@ int main(int argc, char **argv) {
     const int threads = argc > 2 ? atoi(argv[2]) : 1024;
     const uint32_t L = (uint32_t)f.size();
     std::vector<uint32_t> l0, r0; uint32_t root0; ref_build(f, l0, r0, root0);
-    uint32_t *d_f, *d_l, *d_r, *d_out; unsigned long long *d_c;
-    cudaMalloc(&d_f, 4 * L); cudaMalloc(&d_l, 8 * L); cudaMalloc(&d_r, 8 * L); cudaMalloc(&d_out, 64); cudaMalloc(&d_c, 64);
+    // the records hp_build leaves: {parent:16 | 1 (left child) or 1 + nodes of the left sibling's subtree (right child) : 16}
+    std::vector<uint32_t> size(2 * L, 1), up0(2 * L, 0xffffffffu);
+    for (uint32_t n = L; n + 1 < 2 * L; n++) { size[n] = 1 + size[l0[n]] + size[r0[n]]; up0[l0[n]] = n | (1u << 16); up0[r0[n]] = n | ((1 + size[l0[n]]) << 16); }
+    uint32_t *d_f, *d_l, *d_out; unsigned long long *d_c;
+    cudaMalloc(&d_f, 4 * L); cudaMalloc(&d_l, 8 * L); cudaMalloc(&d_out, 64); cudaMalloc(&d_c, 64);
     cudaMemcpy(d_f, f.data(), 4 * L, cudaMemcpyHostToDevice);
     const size_t smem = 8ull * (L + 4);
     cudaFuncSetAttribute(bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     for (int rep = 0; rep < 3; rep++) {
-        cudaMemset(d_l, 0xff, 8 * L); cudaMemset(d_r, 0xff, 8 * L); cudaMemset(d_out, 0, 64);
-        bench_kernel<<<1, threads, smem>>>(d_f, L, d_l, d_r, d_out, d_c);
+        cudaMemset(d_l, 0xee, 8 * L); cudaMemset(d_out, 0, 64);
+        bench_kernel<<<1, threads, smem>>>(d_f, L, d_l, d_out, d_c);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("CUDA error: %s\n", cudaGetErrorString(e)); return 1; }
-        std::vector<uint32_t> l1(2 * L), r1(2 * L); uint32_t out[16]; unsigned long long c[8];
-        cudaMemcpy(l1.data(), d_l, 8 * L, cudaMemcpyDeviceToHost); cudaMemcpy(r1.data(), d_r, 8 * L, cudaMemcpyDeviceToHost);
+        std::vector<uint32_t> up1(2 * L); uint32_t out[16]; unsigned long long c[8];
+        cudaMemcpy(up1.data(), d_l, 8 * L, cudaMemcpyDeviceToHost);
         cudaMemcpy(out, d_out, 64, cudaMemcpyDeviceToHost); cudaMemcpy(c, d_c, 64, cudaMemcpyDeviceToHost);
-        size_t bad = 0; for (uint32_t n = L; n + 1 < 2 * L; n++) if (l0[n] != l1[n] || r0[n] != r1[n]) bad++;
+        size_t bad = 0; for (uint32_t n = 0; n + 1 < 2 * L; n++) if (up0[n] != up1[n]) bad++;
         const double leafc = out[5] * 1024.0, allc = out[6] * 1024.0;
         printf("leaves %u threads %d: %s (root %u/%u, %zu nodes differ)  leaf phase %.0f cycles (%.1f per leaf), merges %.0f cycles (%.1f per merge), total %llu\n",
                L, threads, bad == 0 && out[0] == root0 ? "ok" : "MISMATCH", out[0], root0, bad, leafc, leafc / L, allc - leafc, (allc - leafc) / (L - 1), c[0]);
