@@ -113,6 +113,15 @@ int szb200_copy(void *dst, const void *src, size_t bytes, int kind /*0 h2d, 1 d2
 int szb200_sync(void);
 /* CUDA stream of the current context as an opaque handle (cudaStream_t) -- lets a caller order its own work */
 void *szb200_stream(void);
+/* Stream ordering for the device-pointer calls (no counterpart in the reference, whose data lives in host memory).  Every job runs
+ * on the context's own non-blocking stream; nothing orders that stream after the stream on which the caller produced d_data (or on
+ * which a collective still reads a buffer the next job will overwrite).  Contract: either the caller synchronises its producer
+ * stream before the call, or it records an event (cudaEvent_t, passed as an opaque handle) on that stream and hands it to
+ * szb200_wait_event(): the jobs submitted afterwards on this context wait for it on the device.  The device-pointer calls return
+ * after their job has finished (the stream length is a host value), so results need no event; szb200_record_event() records one
+ * on the library's stream for callers that enqueue asynchronous work through szb200_stream() themselves. */
+int szb200_wait_event(void *cuda_event);
+int szb200_record_event(void *cuda_event);
 
 /* ---- device-pointer variants of the public API (same semantics as SZ_compress_args / SZ_decompress_args,
  * ref: sz/src/sz.c:294, :584, but data and stream live in device memory; implemented in sz_host.c) ---- */

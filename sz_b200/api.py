@@ -183,6 +183,20 @@ def compress_bound(dtype, shape):
     return int(lib().szb200_compress_bound(_code(dtype), *_dims5(shape)))
 
 
+def _order_after_current_stream():
+    """The library works on its own stream: make it wait (on the device) for everything already enqueued on torch's current
+    stream -- the kernel that is still writing the input, a collective that still reads the output buffer."""
+    import torch
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream())
+    L = lib()
+    L.szb200_wait_event.argtypes = [C.c_void_p]
+    L.szb200_wait_event.restype = C.c_int
+    rc = L.szb200_wait_event(C.c_void_p(ev.cuda_event))
+    if rc != 0:
+        raise SZError("szb200_wait_event rc=%d: %s" % (rc, L.szb200_last_error().decode()))
+
+
 def compress_device(x, out, mode, abs_eb=0.0, rel=0.0):
     """Device-resident compress: x is a contiguous torch CUDA tensor (float32/float64), out a uint8 CUDA tensor of at least
     compress_bound() bytes.  Returns the stream length."""
@@ -191,6 +205,7 @@ def compress_device(x, out, mode, abs_eb=0.0, rel=0.0):
     code = SZ_FLOAT if x.dtype == torch.float32 else SZ_DOUBLE
     n = C.c_size_t(0)
     L = lib()
+    _order_after_current_stream()
     rc = L.szb200_compress_args_device(code, x.data_ptr(), out.data_ptr(), out.numel(), C.byref(n), int(mode), float(abs_eb), float(rel), *_dims5(tuple(x.shape)))
     if rc != 0:
         raise SZError("szb200_compress_args_device rc=%d: %s" % (rc, L.szb200_last_error().decode()))
@@ -203,6 +218,7 @@ def decompress_device(stream, nbytes, out):
     assert stream.is_cuda and out.is_cuda and out.is_contiguous()
     code = SZ_FLOAT if out.dtype == torch.float32 else SZ_DOUBLE
     L = lib()
+    _order_after_current_stream()
     rc = L.szb200_decompress_device(code, stream.data_ptr(), int(nbytes), out.data_ptr(), *_dims5(tuple(out.shape)))
     if rc != 0:
         raise SZError("szb200_decompress_device rc=%d: %s" % (rc, L.szb200_last_error().decode()))
@@ -229,6 +245,7 @@ def compress_batch_device(xs, outs, mode, abs_eb=0.0, rel=0.0, lanes=4):
     L.szb200_compress_batch_device.argtypes = [C.c_int, C.POINTER(BatchItem), C.c_int, C.c_int, C.c_int, C.c_double, C.c_double] + [C.c_size_t] * 5
     L.szb200_compress_batch_device.restype = C.c_int
     code = SZ_FLOAT if dt == torch.float32 else SZ_DOUBLE
+    torch.cuda.current_stream().synchronize()        # the worker lanes have streams of their own: inputs must be complete
     rc = L.szb200_compress_batch_device(code, items, len(xs), int(lanes), int(mode), float(abs_eb), float(rel), *_dims5(shape))
     if rc != 0:
         raise SZError("szb200_compress_batch_device rc=%d (items: %s)" % (rc, [it.rc for it in items]))
@@ -248,6 +265,7 @@ def decompress_batch_device(streams, sizes, outs, lanes=4):
     L.szb200_decompress_batch_device.argtypes = [C.c_int, C.POINTER(BatchItem), C.c_int, C.c_int] + [C.c_size_t] * 5
     L.szb200_decompress_batch_device.restype = C.c_int
     code = SZ_FLOAT if dt == torch.float32 else SZ_DOUBLE
+    torch.cuda.current_stream().synchronize()
     rc = L.szb200_decompress_batch_device(code, items, len(outs), int(lanes), *_dims5(shape))
     if rc != 0:
         raise SZError("szb200_decompress_batch_device rc=%d (items: %s)" % (rc, [it.rc for it in items]))

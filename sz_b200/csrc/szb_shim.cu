@@ -137,6 +137,20 @@ extern "C" int szb200_set_device(int device) { CU(cudaSetDevice(device)); return
 extern "C" const char *szb200_last_error(void) { return g_err; }
 extern "C" void szb200_release(void) { Ctx *c = ctx(); if (c) { cudaStreamSynchronize(c->stream); c->release(); } }
 extern "C" void *szb200_stream(void) { Ctx *c = ctx(); return c ? (void *)c->stream : nullptr; }
+// Ordering against the caller's own streams: the library's work runs on its private non-blocking stream, which nothing orders
+// against the stream a caller's producer kernel (or an NCCL collective) was launched on.
+extern "C" int szb200_wait_event(void *cuda_event) {
+    Ctx *c = ctx(); if (!c) return SZ_NSCS;
+    if (!cuda_event) return 0;
+    CU(cudaStreamWaitEvent(c->stream, (cudaEvent_t)cuda_event, 0));
+    return 0;
+}
+extern "C" int szb200_record_event(void *cuda_event) {
+    Ctx *c = ctx(); if (!c) return SZ_NSCS;
+    if (!cuda_event) return SZ_NSCS;
+    CU(cudaEventRecord((cudaEvent_t)cuda_event, c->stream));
+    return 0;
+}
 extern "C" int szb200_sync(void) { Ctx *c = ctx(); if (!c) return SZ_NSCS; CU(cudaStreamSynchronize(c->stream)); return 0; }
 extern "C" int szb200_last_stats(szb200_stats *out) { Ctx *c = ctx(); if (!c || !c->have_last) return SZ_NSCS; *out = c->last; return 0; }
 

@@ -41,5 +41,29 @@ def main():
         json.dump(out, f, indent=1, sort_keys=True)
 
 
+def full_size():
+    """BASELINE.json configs[1] at its own size (512^3 fp32, REL 1e-3, the field of bench.make_field): digests of the reference's
+    stream and reconstruction -> tests/golden/full_size.json (the GPU test compares against them when the box generates the very
+    same input bytes, and runs the compiled reference itself otherwise)."""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    import bench
+    ref = szref.SZLib(szref.REF_SO)
+    out = {}
+    a = bench.make_field((512, 512, 512))
+    ref.init(dict(errorBoundMode="REL", relBoundRatio=1e-3))
+    s = ref.compress(a, szref.REL, 1e-4, 1e-3)
+    rec = ref.decompress(s, a.dtype, a.shape)
+    ref.finalize()
+    out["cfg2_nyx_512_rel"] = dict(input_md5=hashlib.md5(a.tobytes()).hexdigest(), size=len(s), md5=hashlib.md5(s).hexdigest(),
+                                   dec_md5=hashlib.md5(rec.tobytes()).hexdigest(),
+                                   max_err=float(np.max(np.abs(rec.astype(np.float64) - a.astype(np.float64)))))
+    print(out)
+    with open(os.path.join(HERE, "full_size.json"), "w") as f:
+        json.dump(out, f, indent=1, sort_keys=True)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "--full":
+        full_size()
+    else:
+        main()

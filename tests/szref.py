@@ -328,3 +328,21 @@ def blocky_field(n, dtype, seed=7):
     up = lambda X: np.repeat(np.repeat(np.repeat(X, 6, 0), 6, 1), 6, 2)
     f = up(A) * ii[:, None, None] + up(B) * ii[None, :, None] + up(Cc) * ii[None, None, :] + 10 * up(D)
     return np.ascontiguousarray(f.astype(dtype))
+
+
+def ref_compress_file(path, dtype, shape, cfg, mode, abs_eb, rel, want_dec=False):
+    """Worker for process pools: run the compiled reference on an array stored as .npy; returns (size, md5, dec_md5 or None,
+    seconds inside SZ_compress_args).  The array is memory-mapped, the reference gets a private contiguous copy."""
+    import hashlib
+    import time
+    a = np.ascontiguousarray(np.load(path, mmap_mode="r")).astype(dtype, copy=False).reshape(shape)
+    ref = SZLib(REF_SO)
+    ref.init(cfg)
+    t0 = time.perf_counter()
+    s = ref.compress(a, mode, abs_eb, rel)
+    dt = time.perf_counter() - t0
+    dec = None
+    if want_dec:
+        dec = hashlib.md5(ref.decompress(s, a.dtype, a.shape).tobytes()).hexdigest()
+    ref.finalize()
+    return len(s), hashlib.md5(s).hexdigest(), dec, dt

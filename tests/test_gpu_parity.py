@@ -302,28 +302,111 @@ def test_device_pointer_api_roundtrip_and_determinism(sz):
     sz.finalize()
 
 
-def test_full_size_nyx_512_properties(sz):
-    """BASELINE.json configs[1] at full size: size-independent properties (the byte-for-byte check against the reference at
-    this size is part of bench.py's cpu_baseline leg, which runs the reference on the same field)."""
+FULL = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "full_size.json")))
+
+
+def test_full_size_nyx_512_stream_equals_reference(sz):
+    """BASELINE.json configs[1] at full size (512^3 fp32, REL 1e-3, the field bench.py times): the stream and the reconstruction
+    equal the reference's, byte for byte -- against the digests tests/golden/make_golden.py --full took from the compiled
+    reference when this box generates the very same input bytes, against the compiled reference run here otherwise."""
     import torch
     import bench
     a = bench.make_field((512, 512, 512))
+    gold = FULL["cfg2_nyx_512_rel"]
     sz.init(dict(errorBoundMode="REL", relBoundRatio=1e-3))
     x = torch.from_numpy(a).cuda()
     buf = torch.empty(sz.compress_bound(np.float32, a.shape), dtype=torch.uint8, device="cuda")
     n = sz.compress_device(x, buf, sz.REL, 1e-4, 1e-3)
     st = sz.last_stats()
     assert st.num_blocks == 85 ** 3 and st.intervals >= 32
-    h1 = hashlib.md5(buf[:n].cpu().numpy().tobytes()).hexdigest()
+    s_gpu = buf[:n].cpu().numpy().tobytes()
     out = torch.empty_like(x)
     sz.decompress_device(buf, n, out)
+    dec_md5 = hashlib.md5(out.cpu().numpy().tobytes()).hexdigest()
+    if hashlib.md5(a.tobytes()).hexdigest() == gold["input_md5"]:
+        assert n == gold["size"] and hashlib.md5(s_gpu).hexdigest() == gold["md5"], "GPU stream differs from the reference stream at 512^3"
+        assert dec_md5 == gold["dec_md5"], "GPU reconstruction differs from the reference's at 512^3"
+    else:
+        assert szref.have_ref(), "this box's numpy makes a different field and the compiled reference is not here to compare with"
+        ref = szref.SZLib(szref.REF_SO)
+        ref.init(dict(errorBoundMode="REL", relBoundRatio=1e-3))
+        s_ref = ref.compress(a, szref.REL, 1e-4, 1e-3)
+        assert s_gpu == s_ref
+        assert dec_md5 == hashlib.md5(ref.decompress(s_ref, a.dtype, a.shape).tobytes()).hexdigest()
+        ref.finalize()
     rng = float((x.max() - x.min()).item())
     eb = float(np.float32(1e-3 * np.float64(np.float32(rng))))
     assert float((out.double() - x.double()).abs().max().item()) <= eb
-    # idempotence of the round trip at the stream level: recompressing gives the same bytes
-    n2 = sz.compress_device(x, buf, sz.REL, 1e-4, 1e-3)
-    assert n2 == n and hashlib.md5(buf[:n2].cpu().numpy().tobytes()).hexdigest() == h1
-    assert 8 < a.nbytes / n < 30
+    n2 = sz.compress_device(x, buf, sz.REL, 1e-4, 1e-3)          # deterministic
+    assert n2 == n and buf[:n2].cpu().numpy().tobytes() == s_gpu
+    sz.finalize()
+
+
+def _cfg5_slab(r, lo, hi, dev):
+    """rows [lo, hi) of the flattened (5500, 500, 500) fp64 S3D-shape field of BASELINE.json configs[4] (4D: 11 x 500 x 500 x 500;
+    the reference flattens r4 * r3 itself, sz_float.c:3010), generated on the device"""
+    import torch
+    g = [torch.linspace(0, 8 * np.pi, 500, dtype=torch.float64, device=dev) for _ in range(3)]
+    rows = torch.arange(lo, hi, device=dev)
+    s4, z = (rows // 500).double()[:, None, None], g[0][rows % 500][:, None, None]
+    y, xx = g[1][None, :, None], g[2][None, None, :]
+    x = torch.sin(xx) * torch.cos(1.3 * y) * torch.sin(0.7 * z + 0.3 + 0.37 * s4) + 0.25 * torch.sin(3.1 * xx + 1.7 * y) * torch.cos(2.3 * z)
+    x += 1e-3 * torch.randn(x.shape, dtype=torch.float64, device=dev, generator=torch.Generator(device=dev).manual_seed(4321 + r))
+    return x.contiguous()
+
+
+@pytest.mark.slow
+@pytest.mark.skipif(not szref.have_ref(), reason="compiled reference (oracle/_ref) not present")
+def test_config5_full_size_slabs_equal_reference(sz, tmp_path):
+    """BASELINE.json configs[4] at its own size and dtype: the 11 GB fp64 ABS_AND_REL array cut into 8 slabs along the slowest
+    dimension (sz_b200.slabs.slab_bounds, the reference's own pattern: example/test_threadsafe.c:40-58).  Every slab's GPU stream
+    equals the stream of the compiled reference called on that slab (one host process per slab), the GPU reconstructs every slab
+    within the bound, and the reference's reconstruction of one slab equals the GPU's bit for bit.  First evidence at this scale
+    for the fp64 coefficient trees (tens of thousands of leaves) and a 688-row slow axis."""
+    import concurrent.futures as cf
+    import multiprocessing as mp
+    import shutil
+    import torch
+    from sz_b200 import slabs
+    G = 8
+    free, _ = torch.cuda.mem_get_info()
+    if free < 12e9:
+        pytest.skip("needs 12 GB of device memory")
+    shm = "/dev/shm" if os.path.isdir("/dev/shm") and shutil.disk_usage("/dev/shm").free > 13e9 else str(tmp_path)
+    if shutil.disk_usage(shm).free < 13e9:
+        pytest.skip("needs 13 GB of scratch space for the slabs handed to the reference processes")
+    cfg = dict(errorBoundMode="ABS_AND_REL", absErrBound=1e-3, relBoundRatio=1e-3)
+    sz.init(cfg)
+    bounds = slabs.slab_bounds(5500, G)
+    paths, futs, gpu = [], [], []
+    workers = max(1, min(G, (os.cpu_count() or 8)))
+    with cf.ProcessPoolExecutor(max_workers=workers, mp_context=mp.get_context("spawn")) as pool:
+        for r, (lo, hi) in enumerate(bounds):
+            x = _cfg5_slab(r, lo, hi, "cuda")
+            shape = (hi - lo, 500, 500)
+            path = os.path.join(shm, "szb200_cfg5_slab%d.npy" % r)
+            np.save(path, x.cpu().numpy())
+            paths.append(path)
+            futs.append(pool.submit(szref.ref_compress_file, path, np.float64, shape, cfg, szref.ABS_AND_REL, 1e-3, 1e-3, r == 0))
+            buf = torch.empty(sz.compress_bound(np.float64, shape), dtype=torch.uint8, device="cuda")
+            n = sz.compress_device(x, buf, sz.ABS_AND_REL, 1e-3, 1e-3)
+            out = torch.empty_like(x)
+            sz.decompress_device(buf, n, out)
+            eb = min(1e-3, 1e-3 * float(x.max() - x.min()))
+            assert float((out - x).abs().max()) <= eb
+            gpu.append((n, hashlib.md5(buf[:n].cpu().numpy().tobytes()).hexdigest(),
+                        hashlib.md5(out.cpu().numpy().tobytes()).hexdigest() if r == 0 else None))
+            del x, buf, out
+        try:
+            for r, f in enumerate(futs):
+                size, md5, dec, _ = f.result(timeout=600)
+                assert gpu[r][0] == size and gpu[r][1] == md5, "slab %d: GPU stream differs from the reference stream" % r
+                if dec is not None:
+                    assert gpu[r][2] == dec, "slab %d: GPU reconstruction differs from the reference's" % r
+        finally:
+            for p in paths:
+                if os.path.exists(p):
+                    os.remove(p)
     sz.finalize()
 
 
