@@ -44,7 +44,8 @@ static void set_err(const char *fmt, ...) {
 
 enum Stage { ST_OPT = 0, ST_MEAN, ST_FIT, ST_CHAIN, ST_WAVE, ST_HIST, ST_TREE, ST_ENC, ST_EMIT, ST_PARSE, ST_DECODE, ST_DCHAIN, ST_RECON, ST_JOIN, ST_COUNT };
 static const char *k_stage_names[16] = {"opt_intervals", "use_mean_mean", "fit_select", "coeff_chain", "wavefront_quant", "histogram", "huffman_tree",
-                                        "encode", "emit", "d_parse", "d_huffman_decode", "d_coeff_chain", "d_wavefront_recon", "wait_coeff_trees_side_stream", "", ""};
+                                        "encode", "emit", "d_parse", "d_huffman_decode", "d_coeff_chain", "d_wavefront_recon", "wait_coeff_trees_side_stream",
+                                        "coeff_trees_kernel_side_stream", ""};   // [14]: duration of the coefficient huff_build_kernel itself (overlaps the main stream's stages; not part of their sum)
 extern "C" const char *szb200_stage_name(int i) { return (i >= 0 && i < 16) ? k_stage_names[i] : ""; }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -54,6 +55,7 @@ struct Ctx {
     int dev = -1;
     cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: side branch (coefficient histograms / trees / bit lengths)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_tree0 = nullptr, ev_tree1 = nullptr;  // around the coefficient-tree kernel on the side stream
     std::map<std::string, Buf> bufs;
     uint32_t wf_epoch = 0;                               // tag of the most recent wavefront launch (see szb_wavefront.cuh)
     void *pinned = nullptr; size_t pinned_cap = 0;
@@ -79,6 +81,7 @@ struct Ctx {
         { int lo_p = 0, hi_p = 0; CU(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p)); CU(cudaStreamCreateWithPriority(&stream2, cudaStreamNonBlocking, hi_p)); }
         CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
         for (auto &e : ev) CU(cudaEventCreate(&e));
+        CU(cudaEventCreate(&ev_tree0)); CU(cudaEventCreate(&ev_tree1));
         ev_ok = true;
         cudaDeviceProp pr; CU(cudaGetDeviceProperties(&pr, d));
         sm_count = pr.multiProcessorCount; smem_optin = pr.sharedMemPerBlockOptin;
@@ -718,7 +721,9 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
         for (int e = 0; e < ntrees - 1; e++)
             if (launch_hist(c, c.stream2, d_ctype + (size_t)e * nb, reg_count, 65536, tw[1 + e].hist)) return SZ_NSCS;
+        CU(cudaEventRecord(c.ev_tree0, c.stream2));
         CU(launch_huff_build(c.stream2, d_desc + 1, ntrees - 1, heap_sm, heap_cap, std::min<uint64_t>(65536u, reg_count))); KCHECK();
+        CU(cudaEventRecord(c.ev_tree1, c.stream2));
         for (int e = 0; e < ntrees - 1; e++) {
             const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
             enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream2>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
@@ -816,6 +821,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     st.tree_bytes = h_tree[0][0]; st.node_count = h_tree[0][1]; st.type_bits_bytes = main_bytes; st.body_bytes = E.total; st.launches = c.launches;
     for (int i = 1; i < evi; i++) { float ms = 0; cudaEventElapsedTime(&ms, c.ev[i - 1], c.ev[i]); st.ms_stage[stage_of_ev[i]] += ms; }
     cudaEventElapsedTime(&st.ms_total, c.ev[0], c.ev[evi - 1]);
+    if (ntrees > 1) cudaEventElapsedTime(&st.ms_stage[14], c.ev_tree0, c.ev_tree1);
     c.last = st; c.have_last = true;
     c.dbg_g = g; c.dbg_dtype = job.dtype; c.dbg_intervals = intervals; c.dbg_reg_count = reg_count;
     if (stats) *stats = st;
