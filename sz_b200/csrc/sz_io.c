@@ -118,11 +118,10 @@ int is_lossless_compressed_data(unsigned char *compressedBytes, size_t cmpSize) 
 }
 
 /* ref: sz/src/utility.c:203-234.  The lossless back-end is outside this library (szMode = SZ_BEST_SPEED only): such a file is
- * refused, loudly, instead of being decoded. */
+ * refused -- a message, *oriData = NULL and 0 bytes -- instead of being decoded. */
 unsigned long sz_lossless_decompress65536bytes(int losslessCompressor, unsigned char *compressBytes, unsigned long cmpSize, unsigned char **oriData) {
     (void)losslessCompressor; (void)compressBytes; (void)cmpSize;
     printf("Error: this file was written with a zstd/gzip pass (szMode != SZ_BEST_SPEED); libSZ_b200 reads SZ_BEST_SPEED streams only.\n");
-    *oriData = NULL;
-    exit(1);
+    *oriData = NULL;                     /* nothing decoded: 0 bytes, no buffer -- the caller decides (a library does not end the process) */
     return 0;
 }

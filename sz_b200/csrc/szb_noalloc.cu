@@ -13,11 +13,16 @@
 // All calls on a device share the array: it still holds the previous call's partials (harmless, every slot a launch reads
 // is rewritten by that launch first) and the completion counter, which is cleared before every launch.  Two calls whose
 // kernels overlap on the GPU (different streams, or different host threads) race on it -- serialise them.
+// Every system / CUDA header the kernel headers below include is included HERE first, at global scope: the kernel headers are
+// pulled into an anonymous namespace further down, and a system header that had not been seen yet would be declared inside it.
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "../../include/szb200.h"
 

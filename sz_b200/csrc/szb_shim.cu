@@ -689,7 +689,8 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
         ChainStep<T> *d_steps = (ChainStep<T> *)c.get("chain_steps", sizeof(ChainStep<T>) * (size_t)ncoef * reg_count + 256); if (!d_steps) return SZ_NSCS;
         chain_prep_kernel<T><<<dim3((reg_count + 255) / 256, ncoef), 256, 0, c.stream>>>(d_regc, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_steps); KCHECK();
-        coeff_chain_kernel<T><<<1, CHAIN_THREADS, 0, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
+        CU(cudaFuncSetAttribute(coeff_chain_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ChainCfg<T>::SMEM));
+        coeff_chain_kernel<T><<<1, CHAIN_THREADS, ChainCfg<T>::SMEM, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
     }
     if (mark(ST_CHAIN)) return SZ_NSCS;
 
@@ -773,7 +774,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     for (int i = 1; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
-    if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u kcycles: serial warp busy=%u, helper warp busy=%u, total=%u\n", reg_count, h_chain.passes, h_chain.kcyc_serial, h_chain.kcyc_helper, h_chain.kcyc_total);
+    if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u (complete: %u) kcycles: serial warp busy=%u, helper warp busy=%u, total=%u\n", reg_count, h_chain.passes, h_chain.slow_chunks, h_chain.kcyc_serial, h_chain.kcyc_helper, h_chain.kcyc_total);
     if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
         fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
     if (h_chain.err) { set_err("coefficient chain: a step left its tabulated interval (internal error)"); return SZ_NSCS; }
