@@ -90,6 +90,7 @@ int szb200_range_noalloc(int dtype, const void *d_data, size_t n, void *d_minmax
 /* replaces the body of SZ_compress_*_MDQ_nonblocked_with_blocked_regression (see szb200_job) from the element-count
  * field onwards (offset 4+MD): writes [N:8][block_size:4][eb:T][intervals:4]...[type bits].
  * d_data: DEVICE pointer to the original array.  dst: destination of the body (device pointer if dst_on_device). */
+#define SZB200_BODY_TOO_LARGE (-100)   /* szb200_compress_blocked: the body does not fit dst_capacity; *body_size = the size it would have had */
 int szb200_compress_blocked(const szb200_job *job, const void *d_data, void *dst, int dst_on_device,
                             size_t dst_capacity, size_t *body_size, szb200_stats *stats);
 /* upper bound of the body size for a job (the reference's calloc size, ref: sz_float.c:7394) */
@@ -134,7 +135,7 @@ int szb200_decompress_device(int dataType, const void *d_stream, size_t byteLeng
 /* ---- batches of independent fields (BASELINE configs 3 and 4: 13 and 77 calls of the same shape) --------------------------
  * No counterpart in the reference, whose callers loop over SZ_compress_args; the closest precedent is the one-thread-per-slab
  * pattern of example/test_threadsafe.c:40-58.  Every item is compressed exactly as szb200_compress_args_device would compress it
- * (same stream, byte for byte); `lanes` worker threads (1..16), each with its own streams and workspace, pull items from a
+ * (same stream, byte for byte); `lanes` worker threads (1..8), each with its own streams and workspace, pull items from a
  * queue, so the serial stages of one field (coefficient chain, Huffman trees) overlap the bandwidth stages of the others.
  * The exported parameter globals are read once at entry and not modified. */
 typedef struct szb200_batch_item {
@@ -149,6 +150,19 @@ int szb200_compress_batch_device(int dataType, szb200_batch_item *items, int n_i
                                  double relBoundRatio, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
 int szb200_decompress_batch_device(int dataType, szb200_batch_item *items, int n_items, int lanes,
                                    size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+/* ---- one host array over several GPUs of the node (BASELINE config 5: an 11 GB array, one slab per GPU) ----------------------
+ * The precedent in the reference is the slab-parallel pattern of example/test_threadsafe.c:40-58 (slabs of one array through
+ * SZ_compress_customize_threadsafe, sz/src/sz.c:1399); it has no multi-slab container, the framing is ours:
+ *   [n_slabs : u32 LE][size_s : u64 LE x n_slabs][stream_0 ... stream_{n_slabs-1}]
+ * The slowest dimension (r4 * r3 for a 4D array) is cut into n_slabs contiguous slabs (0: one per device); slab s is compressed on
+ * device s mod n_devices (0: all visible devices) by a worker thread with its own context, and is byte for byte the stream
+ * SZ_compress_args gives for that slab -- under REL / ABS_AND_REL with the slab's own value range, as in the reference's example.
+ * data / out are HOST arrays; *container is malloc'ed (caller frees).  One process, no MPI / NCCL: the slabs travel over PCIe.
+ * Calls from several threads are safe (they share a pool of eight worker contexts per device). */
+int szb200_compress_slabs(int dataType, const void *data, int n_slabs, int n_devices, unsigned char **container, size_t *containerSize,
+                          int errBoundMode, double absErrBound, double relBoundRatio, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
+int szb200_decompress_slabs(int dataType, const unsigned char *container, size_t containerSize, int n_devices, void *out,
+                            size_t r5, size_t r4, size_t r3, size_t r2, size_t r1);
 /* worker-lane selection of the calling thread (0 = the default context); used by the batch entry points */
 int szb200_set_lane(int lane);
 int szb200_current_device(void);

@@ -6,7 +6,8 @@ tests, bench.py and multi-GPU slab sharding.  There is NO CPU fallback: if the l
 is present, the calls fail loudly.
 """
 from .api import (ABS, ABS_AND_REL, ABS_OR_REL, REL, SZ_DOUBLE, SZ_FLOAT, LIB_PATH, SZError, Stats, compress, compress_device,
-                  compress_view, compress_bound, compress_batch_device, decompress_batch_device, decompress, decompress_device, finalize, init, last_stats, lib, set_device, stage_names)
+                  compress_view, compress_bound, compress_batch_device, decompress_batch_device, decompress, decompress_device, finalize, init, last_stats, lib, set_device, stage_names,
+                  compress_slabs, decompress_slabs, SzParams)
 
 __all__ = ["ABS", "REL", "ABS_AND_REL", "ABS_OR_REL", "SZ_FLOAT", "SZ_DOUBLE", "LIB_PATH", "SZError", "Stats", "compress", "compress_device",
-           "compress_view", "compress_bound", "compress_batch_device", "decompress_batch_device", "decompress", "decompress_device", "finalize", "init", "last_stats", "lib", "set_device", "stage_names"]
+           "compress_view", "compress_bound", "compress_batch_device", "decompress_batch_device", "decompress", "decompress_device", "finalize", "init", "last_stats", "lib", "set_device", "stage_names", "compress_slabs", "decompress_slabs", "SzParams"]

@@ -225,6 +225,16 @@ def decompress_device(stream, nbytes, out):
     return out
 
 
+class SzParams(C.Structure):
+    """sz_params (include/sz.h:87-118 == reference sz/include/sz.h:164-198), for the customize / thread-safe calls"""
+    _fields_ = [("dataType", C.c_int), ("max_quant_intervals", C.c_uint), ("quantization_intervals", C.c_uint), ("maxRangeRadius", C.c_uint),
+                ("sol_ID", C.c_int), ("losslessCompressor", C.c_int), ("sampleDistance", C.c_int), ("predThreshold", C.c_float), ("szMode", C.c_int),
+                ("gzipMode", C.c_int), ("errorBoundMode", C.c_int), ("absErrBound", C.c_double), ("relBoundRatio", C.c_double), ("psnr", C.c_double),
+                ("normErr", C.c_double), ("pw_relBoundRatio", C.c_double), ("segment_size", C.c_int), ("pwr_type", C.c_int), ("protectValueRange", C.c_int),
+                ("fmin", C.c_float), ("fmax", C.c_float), ("dmin", C.c_double), ("dmax", C.c_double), ("snapshotCmprStep", C.c_int), ("predictionMode", C.c_int),
+                ("accelerate_pw_rel_compression", C.c_int), ("plus_bits", C.c_int), ("randomAccess", C.c_int), ("withRegression", C.c_int)]
+
+
 class BatchItem(C.Structure):
     """szb200_batch_item (include/szb200.h)"""
     _fields_ = [("d_data", C.c_void_p), ("d_stream", C.c_void_p), ("stream_capacity", C.c_size_t), ("out_size", C.c_size_t),
@@ -270,6 +280,36 @@ def decompress_batch_device(streams, sizes, outs, lanes=4):
     if rc != 0:
         raise SZError("szb200_decompress_batch_device rc=%d (items: %s)" % (rc, [it.rc for it in items]))
     return outs
+
+
+def compress_slabs(a, mode, abs_eb=0.0, rel=0.0, n_slabs=0, n_devices=0):
+    """szb200_compress_slabs: one HOST array cut into slabs along its slowest dimension, the slabs compressed side by side on the
+    GPUs of this node (one process, worker threads); returns the slab container as bytes."""
+    L = lib()
+    sz = C.c_size_t
+    L.szb200_compress_slabs.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(sz), C.c_int, C.c_double, C.c_double] + [sz] * 5
+    L.szb200_compress_slabs.restype = C.c_int
+    a = np.ascontiguousarray(a)
+    out, n = C.c_void_p(), sz(0)
+    rc = L.szb200_compress_slabs(_code(a.dtype), a.ctypes.data, int(n_slabs), int(n_devices), C.byref(out), C.byref(n), int(mode), float(abs_eb), float(rel), *_dims5(a.shape))
+    if rc != 0 or not out:
+        raise SZError("szb200_compress_slabs rc=%d: %s" % (rc, L.szb200_last_error().decode()))
+    res = C.string_at(out, n.value)
+    _libc.free(out)
+    return res
+
+
+def decompress_slabs(container, dtype, shape, n_devices=0):
+    """szb200_decompress_slabs: the inverse, into a fresh HOST array."""
+    L = lib()
+    sz = C.c_size_t
+    L.szb200_decompress_slabs.argtypes = [C.c_int, C.c_char_p, sz, C.c_int, C.c_void_p] + [sz] * 5
+    L.szb200_decompress_slabs.restype = C.c_int
+    out = np.empty(shape, dtype=dtype)
+    rc = L.szb200_decompress_slabs(_code(np.dtype(dtype)), container, len(container), int(n_devices), out.ctypes.data, *_dims5(tuple(shape)))
+    if rc != 0:
+        raise SZError("szb200_decompress_slabs rc=%d: %s" % (rc, L.szb200_last_error().decode()))
+    return out
 
 
 def last_stats():

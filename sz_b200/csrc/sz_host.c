@@ -261,6 +261,11 @@ static int sz_read_conf(const char *path) {
 int SZ_Init(const char *configFilePath) {
     if (sz_read_conf(configFilePath) == SZ_NSCS) return SZ_NSCS;
     exe_params->SZ_SIZE_TYPE = sizeof(size_t);
+    /* The reference's built-in configuration (SZ_Init(NULL), conf.c:114) asks for SZ_BEST_COMPRESSION, i.e. the zstd pass this
+     * library does not have, so a caller that never sets szMode (example/test_threadsafe.c) would only get refusals.
+     * SZB200_SZMODE=SZ_BEST_SPEED in the environment overrides the configured mode -- an explicit, outside decision. */
+    const char *m = getenv("SZB200_SZMODE");
+    if (m && strcmp(m, "SZ_BEST_SPEED") == 0) confparams_cpr->szMode = SZ_BEST_SPEED;
     return SZ_SCES;
 }
 
@@ -516,7 +521,7 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     if (to_dev) { if (dev_cap < lossless_total) { printf("Error: device stream buffer too small (need at least %zu bytes)\n", lossless_total); return SZ_NSCS; } cap = dev_cap; out = (unsigned char *)dev_out; }
     else { out = (unsigned char *)szb200_output_buffer(cap); if (!out) { printf("Error: %s\n", szb200_last_error()); return SZ_NSCS; } }
     size_t body = 0;
-    szb200_stats st;
+    szb200_stats st; memset(&st, 0, sizeof(st));
     const double hp1 = hprof ? now_ms() : 0.0;
     /* host destination: guess the size, allocate and pre-fault while the GPU works */
     unsigned char *early = NULL; size_t early_cap = 0; pthread_t pf_thread; int pf_started = 0; prefault_job pf;
@@ -531,8 +536,11 @@ static int compress_core(int dataType, const void *data, int data_on_device, uns
     int rc = szb200_compress_blocked(&job, d_in, out + 4 + md, 1, cap - 4 - md, &body, &st);
     if (pf_started) pthread_join(pf_thread, NULL);
     const double hp2 = hprof ? now_ms() : 0.0;
-    if (rc != SZ_SCES) { printf("Error: %s\n", szb200_last_error()); free(early); return rc; }
-    if (EXE()->optQuantMode == 1) { EXE()->intvCapacity = (int)st.intervals; EXE()->intvRadius = (int)st.intervals / 2; }   /* side effect of the reference (sz_float.c:6651) */
+    /* A body that does not fit the caller's buffer is, in a buffer that holds the raw copy, exactly the case in which the reference
+     * stores the original data instead (its trigger, sz_float.c:2979, is "stream at least as long as the raw copy"): not an error. */
+    const int too_large = rc == SZB200_BODY_TOO_LARGE && 4 + md + body >= N * ts + 3 + md + 8 + 1;
+    if (rc != SZ_SCES && !too_large) { printf("Error: %s\n", szb200_last_error()); free(early); return rc == SZB200_BODY_TOO_LARGE ? SZ_NSCS : rc; }
+    if (!too_large && EXE()->optQuantMode == 1) { EXE()->intvCapacity = (int)st.intervals; EXE()->intvRadius = (int)st.intervals / 2; }   /* side effect of the reference (sz_float.c:6651) */
     size_t total = 4 + md + body;
     unsigned char same = 0x80 | 0x40;                   /* initRandomAccessBytes, ref: dataCompression.c:686-709 */
     if (CPR()->protectValueRange) same |= 0x04;
@@ -738,6 +746,184 @@ int szb200_decompress_device(int dataType, const void *d_stream, size_t byteLeng
     return rc;
 }
 
+/* ---- worker lanes for calls that run beside each other ---------------------------------------------------------------------
+ * A lane is a context of the shim (streams + workspace) on the current device.  Lane 0 serves the ordinary calls, which the API
+ * mutex serialises like the reference's global state demands; lanes 0 .. 7 serve the workers of a batch (which holds that mutex);
+ * lanes 8 .. 15 are handed out here to the thread-safe calls (ref: sz/src/sz.c:1399, :1507) and to the slab workers: every such
+ * call works on private copies of the parameter blocks and does not hold the API mutex while the GPU works, so the five threads
+ * of example/test_threadsafe.c:40-58 really run beside each other. */
+#define BATCH_MAX_LANES 8
+#define POOL_FIRST_LANE 8
+#define POOL_LANES 8
+static pthread_mutex_t g_pool_mu = PTHREAD_MUTEX_INITIALIZER;
+static pthread_cond_t g_pool_cv = PTHREAD_COND_INITIALIZER;
+static int g_pool_busy[POOL_LANES];
+static int pool_acquire(void) {
+    pthread_mutex_lock(&g_pool_mu);
+    for (;;) {
+        for (int k = 0; k < POOL_LANES; k++) if (!g_pool_busy[k]) { g_pool_busy[k] = 1; pthread_mutex_unlock(&g_pool_mu); return POOL_FIRST_LANE + k; }
+        pthread_cond_wait(&g_pool_cv, &g_pool_mu);
+    }
+}
+static void pool_release(int lane) {
+    pthread_mutex_lock(&g_pool_mu);
+    g_pool_busy[lane - POOL_FIRST_LANE] = 0;
+    pthread_cond_signal(&g_pool_cv);
+    pthread_mutex_unlock(&g_pool_mu);
+}
+
+/* one compress / decompress on a pool lane with private parameter blocks (snapshots of the globals, taken under the API mutex) */
+static int lane_compress(int dataType, const void *data, unsigned char **out, size_t *outSize, int mode, double absb, double relb, const size_t *r) {
+    sz_params cpr; sz_exedata exe;
+    pthread_mutex_lock(&g_api_mu);
+    lazy_init();
+    cpr = *confparams_cpr; exe = *exe_params;
+    pthread_mutex_unlock(&g_api_mu);
+    const int lane = pool_acquire();
+    int rc = SZ_NSCS;
+    if (szb200_set_lane(lane) == 0) {
+        tl_cpr = &cpr; tl_exe = &exe;
+        rc = compress_core(dataType, data, 0, out, NULL, 0, outSize, mode, absb, relb, r);
+        tl_cpr = NULL; tl_exe = NULL;
+    }
+    szb200_set_lane(0);
+    pool_release(lane);
+    return rc;
+}
+static int lane_decompress(int dataType, unsigned char *bytes, size_t len, void *dst, void **made, const size_t *r) {
+    sz_params dec; sz_exedata exe;
+    memset(&dec, 0, sizeof(dec)); memset(&exe, 0, sizeof(exe)); exe.SZ_SIZE_TYPE = 8;           /* == reset_dec_state() */
+    const int lane = pool_acquire();
+    int rc = SZ_NSCS;
+    if (szb200_set_lane(lane) == 0) {
+        tl_dec = &dec; tl_exe = &exe;
+        rc = decompress_to_host(dataType, bytes, len, dst, made, r);
+        tl_dec = NULL; tl_exe = NULL;
+    }
+    szb200_set_lane(0);
+    pool_release(lane);
+    return rc;
+}
+
+/* ---- one array over several GPUs: slabs (include/szb200.h) ------------------------------------------------------------------
+ * The slowest dimension is cut into n_slabs contiguous pieces (sizes floor or floor + 1, the larger ones first); slab s is
+ * compressed on device s mod n_devices by a worker thread on a pool lane, as an independent SZ stream that equals the reference
+ * called on that slab (the reference's own pattern: example/test_threadsafe.c:40-58).  Container (ours; the reference has none):
+ *   [n_slabs : u32 LE][size_s : u64 LE x n_slabs][stream_0 ... stream_{n_slabs-1}]      -- the framing of sz_b200/slabs.py */
+typedef struct slab_shared {
+    int dataType, decompress, mode, n_slabs, n_devices;
+    double absb, relb;
+    size_t row_elems, n0;                       /* elements per row of the slowest dimension; its extent */
+    size_t rlow[2];                             /* r1, r2 of every slab (a 4D array is cut as (r4 * r3, r2, r1), which the reference makes of it anyway) */
+    const unsigned char *in;                    /* compress: the array; decompress: the container */
+    unsigned char *out;                         /* decompress: the array */
+    unsigned char **streams; size_t *sizes, *offs;
+    int next, failed;
+    pthread_mutex_t mu;
+} slab_shared;
+static void slab_range(const slab_shared *sh, int s, size_t *lo, size_t *hi) {
+    const size_t base = sh->n0 / (size_t)sh->n_slabs, extra = sh->n0 % (size_t)sh->n_slabs;
+    *lo = (size_t)s * base + ((size_t)s < extra ? (size_t)s : extra);
+    *hi = *lo + base + ((size_t)s < extra ? 1 : 0);
+}
+static void *slab_thread(void *arg) {
+    slab_shared *sh = (slab_shared *)arg;
+    const size_t ts = sh->dataType == SZ_FLOAT ? 4 : 8;
+    for (;;) {
+        pthread_mutex_lock(&sh->mu);
+        const int s = sh->next < sh->n_slabs ? sh->next++ : -1;
+        pthread_mutex_unlock(&sh->mu);
+        if (s < 0) break;
+        size_t lo, hi; slab_range(sh, s, &lo, &hi);
+        size_t r[5] = {sh->rlow[0], sh->rlow[1] ? sh->rlow[1] : hi - lo, sh->rlow[1] ? hi - lo : 0, 0, 0};   /* (r1, r2, rows) or, for a 2D array, (r1, rows) */
+        size_t rf[5]; filterDimension(r[4], r[3], r[2], r[1], r[0], rf);
+        int rc = SZ_NSCS;
+        if (szb200_set_device(s % sh->n_devices) == 0) {
+            if (!sh->decompress) rc = lane_compress(sh->dataType, sh->in + lo * sh->row_elems * ts, &sh->streams[s], &sh->sizes[s], sh->mode, sh->absb, sh->relb, rf);
+            else rc = lane_decompress(sh->dataType, (unsigned char *)sh->in + sh->offs[s], sh->sizes[s], sh->out + lo * sh->row_elems * ts, NULL, rf);
+        }
+        if (rc != SZ_SCES) { pthread_mutex_lock(&sh->mu); sh->failed = 1; pthread_mutex_unlock(&sh->mu); }
+    }
+    return NULL;
+}
+static int slab_setup(slab_shared *sh, int dataType, int n_slabs, int n_devices, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
+    if (dataType != SZ_FLOAT && dataType != SZ_DOUBLE) return SZ_NSCS;
+    size_t r[5]; filterDimension(r5, r4, r3, r2, r1, r);
+    if (r[4] != 0 || r[1] == 0) { printf("Error: slabs need a 2D, 3D or 4D array.\n"); return SZ_DERR; }
+    memset(sh, 0, sizeof(*sh));
+    sh->dataType = dataType;
+    if (r[2] == 0) { sh->n0 = r[1]; sh->rlow[0] = r[0]; sh->rlow[1] = 0; sh->row_elems = r[0]; }                       /* 2D: cut r2 */
+    else { sh->n0 = r[3] ? r[3] * r[2] : r[2]; sh->rlow[0] = r[0]; sh->rlow[1] = r[1]; sh->row_elems = r[0] * r[1]; }  /* 3D / 4D */
+    const int ndev = szb200_device_count();
+    if (ndev <= 0) { printf("Error: no CUDA device.\n"); return SZ_NSCS; }
+    sh->n_devices = (n_devices <= 0 || n_devices > ndev) ? ndev : n_devices;
+    sh->n_slabs = n_slabs <= 0 ? sh->n_devices : n_slabs;
+    if ((size_t)sh->n_slabs > sh->n0 / 12) sh->n_slabs = sh->n0 / 12 ? (int)(sh->n0 / 12) : 1;      /* at least two blocks of rows per slab */
+    pthread_mutex_init(&sh->mu, NULL);
+    return SZ_SCES;
+}
+static int slab_run(slab_shared *sh) {
+    const int device0 = szb200_current_device();
+    int workers = sh->n_slabs < POOL_LANES ? sh->n_slabs : POOL_LANES;
+    pthread_t th[POOL_LANES]; int started = 0;
+    for (int k = 0; k < workers; k++) { if (pthread_create(&th[k], NULL, slab_thread, sh) != 0) break; started++; }
+    for (int k = 0; k < started; k++) pthread_join(th[k], NULL);
+    pthread_mutex_destroy(&sh->mu);
+    if (device0 >= 0) szb200_set_device(device0);
+    return (started > 0 && !sh->failed && sh->next >= sh->n_slabs) ? SZ_SCES : SZ_NSCS;
+}
+
+int szb200_compress_slabs(int dataType, const void *data, int n_slabs, int n_devices, unsigned char **container, size_t *containerSize,
+                          int errBoundMode, double absErrBound, double relBoundRatio, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
+    slab_shared sh;
+    if (!data || !container || !containerSize) return SZ_NSCS;
+    int rc = slab_setup(&sh, dataType, n_slabs, n_devices, r5, r4, r3, r2, r1);
+    if (rc != SZ_SCES) return rc;
+    sh.mode = errBoundMode; sh.absb = absErrBound; sh.relb = relBoundRatio; sh.in = (const unsigned char *)data;
+    sh.streams = (unsigned char **)calloc((size_t)sh.n_slabs, sizeof(unsigned char *));
+    sh.sizes = (size_t *)calloc((size_t)sh.n_slabs, sizeof(size_t));
+    rc = (sh.streams && sh.sizes) ? slab_run(&sh) : SZ_NSCS;
+    if (rc == SZ_SCES) {
+        size_t total = 4 + 8 * (size_t)sh.n_slabs;
+        for (int s = 0; s < sh.n_slabs; s++) total += sh.sizes[s];
+        unsigned char *c = (unsigned char *)host_alloc_result(total);
+        if (!c) rc = SZ_NSCS;
+        else {
+            const uint32_t g = (uint32_t)sh.n_slabs;
+            memcpy(c, &g, 4);                                     /* little endian, like sz_b200/slabs.py */
+            size_t off = 4 + 8 * (size_t)sh.n_slabs;
+            for (int s = 0; s < sh.n_slabs; s++) { const uint64_t z = sh.sizes[s]; memcpy(c + 4 + 8 * (size_t)s, &z, 8); memcpy(c + off, sh.streams[s], sh.sizes[s]); off += sh.sizes[s]; }
+            *container = c; *containerSize = total;
+        }
+    }
+    if (sh.streams) for (int s = 0; s < sh.n_slabs; s++) free(sh.streams[s]);
+    free(sh.streams); free(sh.sizes);
+    return rc;
+}
+
+int szb200_decompress_slabs(int dataType, const unsigned char *container, size_t containerSize, int n_devices, void *out,
+                            size_t r5, size_t r4, size_t r3, size_t r2, size_t r1) {
+    slab_shared sh;
+    if (!container || !out || containerSize < 4) return SZ_NSCS;
+    uint32_t g; memcpy(&g, container, 4);
+    if (g == 0 || g > 65536 || containerSize < 4 + 8 * (size_t)g) { printf("Error: not a slab container.\n"); return SZ_NSCS; }
+    int rc = slab_setup(&sh, dataType, (int)g, n_devices, r5, r4, r3, r2, r1);
+    if (rc != SZ_SCES) return rc;
+    if (sh.n_slabs != (int)g) { printf("Error: the container holds %u slabs, which does not fit these dimensions.\n", g); pthread_mutex_destroy(&sh.mu); return SZ_DERR; }
+    sh.decompress = 1; sh.in = container; sh.out = (unsigned char *)out;
+    sh.sizes = (size_t *)calloc(g, sizeof(size_t)); sh.offs = (size_t *)calloc(g, sizeof(size_t));
+    rc = (sh.sizes && sh.offs) ? SZ_SCES : SZ_NSCS;
+    size_t off = 4 + 8 * (size_t)g;
+    for (uint32_t s = 0; rc == SZ_SCES && s < g; s++) {
+        uint64_t z; memcpy(&z, container + 4 + 8 * (size_t)s, 8);
+        if (z > containerSize || off + z > containerSize) { printf("Error: truncated slab container.\n"); rc = SZ_NSCS; break; }
+        sh.sizes[s] = (size_t)z; sh.offs[s] = off; off += (size_t)z;
+    }
+    if (rc == SZ_SCES) rc = slab_run(&sh); else pthread_mutex_destroy(&sh.mu);
+    free(sh.sizes); free(sh.offs);
+    return rc;
+}
+
 /* ---- batches (include/szb200.h) ------------------------------------------------------------------------------------------- */
 typedef struct batch_shared {
     int dataType, decompress, mode, device;
@@ -779,7 +965,7 @@ static void *batch_thread(void *arg) {
 
 static int run_batch(batch_shared *sh, int lanes) {
     if (lanes < 1) lanes = 1;
-    if (lanes > 16) lanes = 16;
+    if (lanes > BATCH_MAX_LANES) lanes = BATCH_MAX_LANES;     /* lanes 0 .. 7; 8 .. 15 belong to the thread-safe calls and the slab workers */
     if (lanes > sh->n_items) lanes = sh->n_items;
     pthread_t th[16]; batch_worker wk[16];
     pthread_mutex_init(&sh->mu, NULL);
@@ -894,12 +1080,15 @@ unsigned char *SZ_compress_customize(const char *cmprName, void *userPara, int d
 }
 
 unsigned char *SZ_compress_customize_threadsafe(const char *cmprName, void *userPara, int dataType, void *data, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1, size_t *outSize, int *status) {
-    if (!is_sz2_name(cmprName) || userPara == NULL) { *status = SZ_NSCS; return NULL; }
+    if (!is_sz2_name(cmprName) || userPara == NULL || (dataType != SZ_FLOAT && dataType != SZ_DOUBLE)) { *status = SZ_NSCS; return NULL; }
     sz_params *para = (sz_params *)userPara;
-    /* the reference bypasses SZ_compress_args and its dimension filter here (sz.c:1399-1417); the global state it still
-     * writes is serialised by the API mutex inside SZ_compress_args */
-    if (confparams_cpr == NULL) SZ_Init(NULL);
-    unsigned char *res = SZ_compress_args(dataType, data, outSize, para->errorBoundMode, para->absErrBound, para->relBoundRatio, para->pw_relBoundRatio, r5, r4, r3, r2, r1);
+    /* ref: sz/src/sz.c:1399-1417 -- mode and bounds from the caller's block, everything else from the global configuration; the
+     * call runs on a worker lane of its own with private parameter blocks (see "worker lanes" above), beside other such calls */
+    size_t r[5];
+    filterDimension(r5, r4, r3, r2, r1, r);
+    unsigned char *res = NULL;
+    const int rc = lane_compress(dataType, data, &res, outSize, para->errorBoundMode, para->absErrBound, para->relBoundRatio, r);
+    if (rc != SZ_SCES) res = NULL;
     *status = res ? SZ_SCES : SZ_NSCS;
     return res;
 }
@@ -913,5 +1102,12 @@ void *SZ_decompress_customize(const char *cmprName, void *userPara, int dataType
 }
 
 void *SZ_decompress_customize_threadsafe(const char *cmprName, void *userPara, int dataType, unsigned char *bytes, size_t byteLength, size_t r5, size_t r4, size_t r3, size_t r2, size_t r1, int *status) {
-    return SZ_decompress_customize(cmprName, userPara, dataType, bytes, byteLength, r5, r4, r3, r2, r1, status);
+    (void)userPara;
+    if (!(is_sz2_name(cmprName)) || (dataType != SZ_FLOAT && dataType != SZ_DOUBLE)) { *status = SZ_NSCS; return NULL; }
+    size_t r[5];
+    filterDimension(r5, r4, r3, r2, r1, r);
+    void *out = NULL;
+    if (lane_decompress(dataType, bytes, byteLength, NULL, &out, r) != SZ_SCES) out = NULL;
+    *status = out ? SZ_SCES : SZ_NSCS;
+    return out;
 }

@@ -1154,6 +1154,17 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const DecJobList *__restr
 // its own symbols one by one touches a different 32-byte sector per lane and per symbol: ~0.7 ms of sector traffic at 512^3).
 // Unpredictable values (code 0, rare) are pre-placed into the output field at their raster position.
 constexpr int DECW_TB = 128, DECW_CAP = 4096;               // symbols a warp can stage; a longer run (codes < 2 bits on average) is stored directly
+// A main tree that is one leaf with symbol 0 (ref: Huffman.c:316-321 fills the type array with the root's symbol whatever it is):
+// every point is unpredictable, the list of raw values IS the field in block-major order -- each thread places 16 of them.
+template <typename T>
+__global__ void __launch_bounds__(256) unpred_all_kernel(uint64_t n, Geom g, const T *__restrict__ unpred, uint64_t unpred_count, T *field_out) {
+    const uint64_t p0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16u;
+    if (p0 >= n) return;
+    BMIter it; it.init(g, p0);
+    const int cnt = (int)min((uint64_t)16, n - p0);
+    for (int q = 0; q < cnt; q++) { if (p0 + q < unpred_count) field_out[it.raster] = unpred[p0 + q]; it.next(g); }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(DECW_TB) dec_write_bm_kernel(const uint32_t *__restrict__ words, uint64_t total_bits, uint64_t nsub, DecTree tr,
                                                               const unsigned long long *__restrict__ start_used,

@@ -811,7 +811,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     { unsigned char *p = E.h(8); uint64_t tu = total_unpred; memcpy(p, &tu, 8); }
     E.d(d_unp, sizeof(T) * total_unpred);
     E.d(d_bits, main_bytes);
-    if (E.total > dst_cap) { set_err("stream body (%zu bytes) exceeds the destination capacity (%zu)", E.total, dst_cap); return SZ_NSCS; }
+    if (E.total > dst_cap) { set_err("stream body (%zu bytes) exceeds the destination capacity (%zu)", E.total, dst_cap); *body_size = E.total; return SZB200_BODY_TOO_LARGE; }
     if (emit_all(c, E, dst, dst_on_device)) return SZ_NSCS;
     *body_size = E.total;
     if (mark(ST_EMIT)) return SZ_NSCS;
@@ -875,8 +875,10 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         DecJob &J = jobs[j];
         J.single_leaf = roots[j].leaf != 0; J.root_sym = roots[j].sym; J.converged = false;
         if (J.single_leaf) {            // constant symbol array, empty payload (ref: Huffman.c:316-321)
-            if (J.blockmajor && J.root_sym == 0) { set_err("all-unpredictable stream with a single-leaf tree is not supported"); return SZ_NSCS; }
             fill_u16_kernel<<<c.sm_count * 4, 256, 0, c.stream>>>(J.d_out, J.nsym, (uint16_t)J.root_sym); KCHECK();
+            if (J.blockmajor && J.root_sym == 0 && d_field) {       // every point unpredictable: the raw values are the field
+                unpred_all_kernel<T><<<(unsigned)((J.nsym + 4095) / 4096), 256, 0, c.stream>>>(J.nsym, g, d_unpred, unpred_count, d_field); KCHECK();
+            }
             J.converged = true;
             continue;
         }
@@ -1024,7 +1026,17 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     const uint64_t total_unpred = H.total_unpred;
     const size_t o_unp = (size_t)H.o_unp, o_bits = (size_t)H.o_bits;
     const uint64_t main_bytes = body_len - o_bits;
-    (void)tree_size;
+    // Nothing read from the stream sizes a copy or a loop before it has been checked against what the job and the buffer allow:
+    // a cut or corrupt stream is refused here instead of writing past a workspace (ref: the reference trusts these fields).
+    {
+        auto tree_bytes_of = [](uint32_t n) -> uint64_t { const uint64_t w = n <= 256 ? 1 : (n <= 65536 ? 2 : 4); return 1 + (uint64_t)n * (2 * w + 5); };
+        bool ok = reg_count <= nb && total_unpred <= N && o_bits <= body_len && o_unp <= body_len && o_unp + (uint64_t)sizeof(T) * total_unpred <= body_len
+                  && tree_bytes_of(nodeCount) <= tree_size && o_tree + (uint64_t)tree_size <= body_len && o_ind + (nb + 7) / 8 <= body_len;
+        for (int e = 0; ok && reg_count > 0 && e < ncoef; e++)
+            ok = cunp_cnt[e] <= reg_count && o_ctree[e] + tree_bytes_of(cnode[e]) <= body_len && o_cbits[e] + cbits_bytes[e] <= body_len
+                 && o_cunp[e] + (uint64_t)sizeof(T) * cunp_cnt[e] <= body_len;
+        if (!ok) { set_err("corrupt stream: a section header does not fit the stream or the array"); return SZ_NSCS; }
+    }
     if (mark(ST_PARSE)) return SZ_NSCS;
 
     // ---- aligned copies of the T-typed sections ----

@@ -410,6 +410,137 @@ def test_config5_full_size_slabs_equal_reference(sz, tmp_path):
     sz.finalize()
 
 
+def test_thread_safe_calls_run_side_by_side_and_equal_the_reference(sz):
+    """The reference's slab-parallel pattern (example/test_threadsafe.c:40-58): five threads, each SZ_compress_customize_threadsafe
+    on its slab of one array with its own REL bound, then SZ_decompress_customize_threadsafe.  Here every such call has a worker
+    context of its own, so the threads overlap on the GPU; every stream must equal the reference's SZ_compress_args on that slab."""
+    import ctypes as C
+    import threading
+    L = sz.lib()
+    sz.init(dict(errorBoundMode="ABS", absErrBound=1e-3))
+    full = szref.smooth_field((100, 120, 140), np.float32, span=6 * np.pi)
+    nthr, rows = 5, 20
+
+    cpr = C.c_void_p.in_dll(L, "confparams_cpr")
+    results = [None] * nthr
+    stsz = C.c_size_t
+    L.SZ_compress_customize_threadsafe.restype = C.c_void_p
+    L.SZ_compress_customize_threadsafe.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p] + [stsz] * 5 + [C.POINTER(stsz), C.POINTER(C.c_int)]
+    L.SZ_decompress_customize_threadsafe.restype = C.c_void_p
+    L.SZ_decompress_customize_threadsafe.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p, stsz] + [stsz] * 5 + [C.POINTER(C.c_int)]
+
+    def worker(i):
+        slab = np.ascontiguousarray(full[i * rows:(i + 1) * rows])
+        para = sz.SzParams()                                     # memcpy(&params, confparams_cpr, sizeof(sz_params)), as the example does
+        C.memmove(C.byref(para), cpr.value, C.sizeof(para))
+        para.errorBoundMode, para.relBoundRatio = sz.REL, 1e-4 * (i + 1)
+        n, status = stsz(0), C.c_int(0)
+        p = L.SZ_compress_customize_threadsafe(b"SZ", C.byref(para), 0, slab.ctypes.data, 0, 0, rows, 120, 140, C.byref(n), C.byref(status))
+        stream = C.string_at(p, n.value) if p else None
+        q = L.SZ_decompress_customize_threadsafe(b"SZ", C.byref(para), 0, p, n.value, 0, 0, rows, 120, 140, C.byref(status)) if p else None
+        rec = np.frombuffer(C.string_at(q, slab.nbytes), dtype=np.float32).reshape(slab.shape).copy() if q else None
+        results[i] = (stream, rec, slab)
+
+    for rep in range(2):
+        th = [threading.Thread(target=worker, args=(i,)) for i in range(nthr)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        orc = szref.Oracle()
+        for i in range(nthr):
+            stream, rec, slab = results[i]
+            assert stream is not None and rec is not None
+            orc.init(dict(errorBoundMode="ABS", absErrBound=1e-3))      # the global configuration (the header's rel field comes from it, ByteToolkit.c:924-929)
+            want = orc.compress(slab, szref.REL, 1e-3, 1e-4 * (i + 1))     # mode and bound from the caller's block
+            assert stream == want, "thread %d: stream differs from the oracle's on its slab" % i
+            assert rec.tobytes() == orc.decompress(want, np.float32, slab.shape).tobytes()
+    sz.finalize()
+
+
+def test_slab_entry_point_of_the_c_boundary(sz):
+    """szb200_compress_slabs / szb200_decompress_slabs: one host array, eight slabs, worker threads over the visible devices (all
+    on one device here).  Every slab stream in the container equals the oracle's stream for that slab; the array comes back."""
+    from sz_b200 import slabs
+    for dtype, shape, mode, ab, rl in ((np.float32, (130, 64, 80), szref.REL, 1e-4, 1e-3), (np.float64, (11, 12, 20, 24), szref.ABS_AND_REL, 1e-3, 1e-3),
+                                       (np.float32, (200, 333), szref.ABS, 1e-3, 1e-4)):
+        a = szref.smooth_field(shape, dtype, span=4 * np.pi)
+        cfg = cases.make_cfg(mode, ab, rl, {})
+        sz.init(cfg)
+        box = sz.compress_slabs(a, mode, ab, rl, n_slabs=8)
+        parts = slabs.unframe(box)
+        n0 = shape[0] if len(shape) < 4 else shape[0] * shape[1]
+        flat = a.reshape((n0,) + shape[-2:]) if len(shape) >= 3 else a
+        bounds = slabs.slab_bounds(n0, len(parts))
+        assert len(parts) == min(8, max(1, n0 // 12))
+        orc = szref.Oracle()
+        orc.init(cfg)
+        for (lo, hi), s in zip(bounds, parts):
+            assert s == orc.compress(np.ascontiguousarray(flat[lo:hi]), mode, ab, rl)
+        back = sz.decompress_slabs(box, dtype, shape)
+        for (lo, hi), s in zip(bounds, parts):
+            assert back.reshape(flat.shape)[lo:hi].tobytes() == orc.decompress(s, dtype, flat[lo:hi].shape).tobytes()
+        sz.finalize()
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(_DROPIN, "test_threadsafe")), reason="relinked example/test_threadsafe.c (make -C oracle dropin) not present")
+def test_reference_thread_safe_example_runs_unmodified_on_the_library(sz, tmp_path):
+    """example/test_threadsafe.c, compiled unmodified with OpenMP and linked against libSZ_b200.so: five threads, five slabs of a
+    100 x 500 x 500 field, REL 1e-4 .. 5e-4 per slab; every slab's maximum relative error stays within its bound.  (The example
+    never sets szMode and the built-in default is the zstd mode, which this library refuses: SZB200_SZMODE overrides it.)"""
+    import re
+    import subprocess
+    a = szref.smooth_field((100, 500, 500), np.float32, span=8 * np.pi)
+    a.tofile(tmp_path / "CLOUDf48.bin.f32")
+    r = subprocess.run([os.path.join(_DROPIN, "test_threadsafe")], cwd=tmp_path, capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, OMP_NUM_THREADS="5", SZB200_SZMODE="SZ_BEST_SPEED"))     # the example takes SZ_Init(NULL)'s mode, the zstd one
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    rel = [float(x) for x in re.findall(r"Max relative error = ([0-9.eE+-]+)", r.stdout)]
+    assert len(rel) == 5 and max(rel) <= 5e-4 * 1.0001 and min(rel) > 0, r.stdout[-2000:]
+    assert re.search(r"max_error=", r.stdout)
+
+
+def test_incompressible_field_fits_a_raw_sized_device_buffer(sz):
+    """white noise with a tight bound: the reference stores the original data (lossless container, sz_float.c:526-559, :2979).  A
+    device buffer of just that size must be enough -- the Huffman body that does not fit it is the very trigger of that container --
+    and the stream equals the host-pointer call's."""
+    import torch
+    a = szref.random_field((40, 36, 44), np.float32)
+    sz.init(dict(errorBoundMode="ABS", absErrBound=1e-7))
+    s_host = sz.compress(a, sz.ABS, 1e-7, 0)
+    assert s_host[3] == 80 and len(s_host) == a.nbytes + 3 + 28 + 8 + 1
+    x = torch.from_numpy(a).cuda()
+    buf = torch.empty(len(s_host), dtype=torch.uint8, device="cuda")
+    n = sz.compress_device(x, buf, sz.ABS, 1e-7, 0)
+    assert n == len(s_host) and buf[:n].cpu().numpy().tobytes() == s_host
+    sz.finalize()
+
+
+def test_corrupt_section_headers_are_refused_without_damage(sz):
+    """every count and size a stream carries is checked before it sizes a copy: a stream with a damaged section header is refused
+    (or, if the damage happens to be harmless, decoded), and the next valid call still gives the right answer"""
+    a = szref.plane_field((30, 26, 40), np.float32)              # regression blocks: coefficient sections present
+    sz.init(dict(errorBoundMode="ABS", absErrBound=1e-1))
+    s = sz.compress(a, sz.ABS, 1e-1, 0)
+    good = sz.decompress(s, a.dtype, a.shape)
+    rng = np.random.default_rng(5)
+    head = 4 + 28 + 8                                            # version + flags, parameter block, element count
+    refused = 0
+    for trial in range(60):
+        b = bytearray(s)
+        off = head + int(rng.integers(0, min(len(s) - head, 400 + 40 * trial)))
+        for q in range(int(rng.integers(1, 5))):
+            if off + q < len(b):
+                b[off + q] = 0xff if trial % 2 else int(rng.integers(0, 256))
+        try:
+            sz.decompress(bytes(b), a.dtype, a.shape)
+        except sz.SZError:
+            refused += 1
+    assert refused > 0
+    assert sz.decompress(s, a.dtype, a.shape).tobytes() == good.tobytes()
+    sz.finalize()
+
+
 def test_unsupported_requests_fail_loudly(sz):
     a = szref.smooth_field((32, 32, 32), np.float32)
     sz.init(dict(szMode="SZ_BEST_COMPRESSION"))
