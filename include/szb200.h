@@ -102,6 +102,14 @@ size_t szb200_body_capacity(const szb200_job *job);
 int szb200_decompress_blocked(const szb200_job *job, const void *body, size_t body_len, int body_on_device,
                               void *d_out, szb200_stats *stats);
 
+/* replace encode_withTree / decode_withTree (ref: sz/src/Huffman.c:790-816, :865-889), the Huffman container of the reference's SZ 1.4
+ * storage (TightDataPointStorageF.c:296-301):  [nodeCount : 4 BE][stateNum / 2 : 4 BE][tree bytes][Huffman bits].
+ * d_symbols: DEVICE array of n 16-bit symbols < stateNum (<= 65536), linear order.  The container equals the reference's byte for
+ * byte for the same symbols (the reference takes them as int[]); dst / container may be host or device memory. */
+int szb200_encode_with_tree(const void *d_symbols_u16, size_t n, unsigned int stateNum, void *dst, int dst_on_device,
+                            size_t dst_capacity, size_t *out_size);
+int szb200_decode_with_tree(const void *container, size_t len, int on_device, size_t n, void *d_symbols_out_u16);
+
 /* replaces the big-endian copy loops of SZ_compress_args_*_StoreOriData (ref: sz_float.c:526-559) and of the
  * isLossless branch of SZ_decompress_args_* (ref: szd_float.c:106-119): element-wise byte swap on the device */
 int szb200_swap_copy(int dtype, const void *src, int src_on_device, void *dst, int dst_on_device, size_t n);

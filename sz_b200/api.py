@@ -312,6 +312,39 @@ def decompress_slabs(container, dtype, shape, n_devices=0):
     return out
 
 
+def encode_with_tree(sym, stateNum):
+    """szb200_encode_with_tree on a uint16 CUDA tensor -> container bytes ([nodeCount][stateNum/2][tree][bits], Huffman.c:790-816)."""
+    import torch
+    assert sym.is_cuda and sym.dtype in (torch.uint16, torch.int16) and sym.is_contiguous()
+    L = lib()
+    sz = C.c_size_t
+    L.szb200_encode_with_tree.argtypes = [C.c_void_p, sz, C.c_uint, C.c_void_p, C.c_int, sz, C.POINTER(sz)]
+    L.szb200_encode_with_tree.restype = C.c_int
+    cap = 8 + 16 + 13 * 2 * int(stateNum) + 8 * sym.numel() + 64
+    out = np.empty(cap, dtype=np.uint8)
+    n = sz(0)
+    _order_after_current_stream()
+    rc = L.szb200_encode_with_tree(sym.data_ptr(), sym.numel(), int(stateNum), out.ctypes.data, 0, cap, C.byref(n))
+    if rc != 0:
+        raise SZError("szb200_encode_with_tree rc=%d: %s" % (rc, L.szb200_last_error().decode()))
+    return out[:n.value].tobytes()
+
+
+def decode_with_tree(container, n):
+    """szb200_decode_with_tree: container bytes -> uint16 CUDA tensor of n symbols (Huffman.c:865-889)."""
+    import torch
+    L = lib()
+    sz = C.c_size_t
+    L.szb200_decode_with_tree.argtypes = [C.c_char_p, sz, C.c_int, sz, C.c_void_p]
+    L.szb200_decode_with_tree.restype = C.c_int
+    out = torch.empty(int(n), dtype=torch.int16, device="cuda")
+    _order_after_current_stream()
+    rc = L.szb200_decode_with_tree(container, len(container), 0, int(n), out.data_ptr())
+    if rc != 0:
+        raise SZError("szb200_decode_with_tree rc=%d: %s" % (rc, L.szb200_last_error().decode()))
+    return out
+
+
 def last_stats():
     s = Stats()
     if lib().szb200_last_stats(C.byref(s)) != 0:

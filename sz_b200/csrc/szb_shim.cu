@@ -984,6 +984,80 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// The SZ 1.4 Huffman container, stand-alone (ref: Huffman.c:790-816 encode_withTree, :865-889 decode_withTree; used by the
+// reference's 1D / withLinearRegression = NO storage, TightDataPointStorageF.c:296-301):
+//     [nodeCount : 4 BE][stateNum / 2 : 4 BE][tree bytes][Huffman bits of the n symbols]
+// Same kernels as the blocked path: histogram, exact heap, code table + serialised tree, bit lengths, prefix sum, bit scatter; and the
+// marker-less parallel decode on the way back.  Symbols are 16-bit (stateNum <= 65536) in device memory, in their own (linear) order.
+extern "C" int szb200_encode_with_tree(const void *d_symbols_u16, size_t n, unsigned int stateNum, void *dst, int dst_on_device,
+                                       size_t dst_capacity, size_t *out_size) {
+    Ctx *cp = ctx(); if (!cp) return SZ_NSCS;
+    Ctx &c = *cp;
+    if (!d_symbols_u16 || !dst || !out_size || n == 0 || stateNum == 0 || stateNum > 65536 || n >= (1ull << 32)) { set_err("encode_with_tree: bad arguments"); return SZ_NSCS; }
+    const uint16_t *d_sym = (const uint16_t *)d_symbols_u16;
+    TreeWs tw;
+    if (tree_ws(c, 0, stateNum, tw)) return SZ_NSCS;
+    HuffTreeDesc *d_desc = (HuffTreeDesc *)c.get("tree_desc", sizeof(HuffTreeDesc) * 8); if (!d_desc) return SZ_NSCS;
+    const uint32_t heap_cap = (uint32_t)((c.smem_optin - 8192) / 8);
+    const size_t heap_sm = 8ull * heap_cap;
+    CU(cudaFuncSetAttribute(huff_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heap_sm));
+    CU(cudaMemcpyAsync(d_desc, &tw.d, sizeof(HuffTreeDesc), cudaMemcpyHostToDevice, c.stream));
+    if (launch_hist(c, c.stream, d_sym, n, stateNum, tw.hist)) return SZ_NSCS;
+    CU(launch_huff_build(c.stream, d_desc, 1, heap_sm, heap_cap, std::min<uint64_t>(stateNum, n))); KCHECK();
+    const uint64_t nchunk = (n + ENC_CHUNK - 1) / ENC_CHUNK;
+    uint32_t *d_cb = (uint32_t *)c.get("enc_cb", 4 * (nchunk + 8)), *d_cz = (uint32_t *)c.get("enc_cz", 4 * (nchunk + 8));
+    unsigned long long *d_cbo = (unsigned long long *)c.get("enc_cbo", 8 * (nchunk + 8)), *d_czo = (unsigned long long *)c.get("enc_czo", 8 * (nchunk + 8));
+    unsigned long long *d_tot = (unsigned long long *)c.get("totals", 256);
+    if (!d_cb || !d_cz || !d_cbo || !d_czo || !d_tot) return SZ_NSCS;
+    Geom g = make_geom(2, 1, 1, 1);
+    enc_len_kernel<false><<<(unsigned)nchunk, ENC_THREADS, 0, c.stream>>>(d_sym, n, g, tw.d.clen, d_cb, d_cz); KCHECK();
+    if (launch_scan(c, c.stream, 0, d_cb, nchunk, d_cbo, d_tot + 1)) return SZ_NSCS;
+    unsigned long long h_bits = 0; uint32_t h_tree[8];
+    CU(cudaMemcpyAsync(&h_bits, d_tot + 1, 8, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaMemcpyAsync(h_tree, tw.d.out, 32, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    if (h_tree[3]) { set_err(h_tree[3] == 2 ? "Huffman tree build gave up" : "Huffman code longer than 64 bits"); return SZ_NSCS; }
+    const uint64_t nbytes = (h_bits + 7) / 8;
+    uint32_t *d_bits = (uint32_t *)c.get("enc_bits", nbytes + 64); if (!d_bits) return SZ_NSCS;
+    CU(cudaMemsetAsync(d_bits, 0, nbytes + 64, c.stream));
+    enc_write_kernel<float, false><<<(unsigned)nchunk, ENC_THREADS, 0, c.stream>>>(d_sym, n, g, tw.d.code, tw.d.clen, d_cbo, d_czo, d_bits, (const float *)nullptr, (float *)nullptr); KCHECK();
+    Emitter E;
+    { unsigned char *p = E.h(8); put_be32(p, h_tree[1]); put_be32(p + 4, stateNum / 2); }
+    E.d(tw.d.tree_bytes, h_tree[0]);
+    E.d(d_bits, nbytes);
+    if (E.total > dst_capacity) { set_err("encode_with_tree: %zu bytes do not fit the destination (%zu)", E.total, dst_capacity); *out_size = E.total; return SZB200_BODY_TOO_LARGE; }
+    if (emit_all(c, E, dst, dst_on_device)) return SZ_NSCS;
+    *out_size = E.total;
+    return 0;
+}
+
+extern "C" int szb200_decode_with_tree(const void *container, size_t len, int on_device, size_t n, void *d_symbols_out_u16) {
+    Ctx *cp = ctx(); if (!cp) return SZ_NSCS;
+    Ctx &c = *cp;
+    if (!container || !d_symbols_out_u16 || len < 8 || n == 0 || n >= (1ull << 32)) { set_err("decode_with_tree: bad arguments"); return SZ_NSCS; }
+    unsigned char *d_body = (unsigned char *)c.get("dec_body", len + 256); if (!d_body) return SZ_NSCS;
+    CU(cudaMemcpyAsync(d_body, container, len, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c.stream));
+    unsigned char head[8];
+    CU(cudaMemcpyAsync(head, d_body, 8, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    const uint32_t nodeCount = ((uint32_t)head[0] << 24) | ((uint32_t)head[1] << 16) | ((uint32_t)head[2] << 8) | head[3];
+    const uint64_t w = nodeCount <= 256 ? 1 : (nodeCount <= 65536 ? 2 : 4), tree_bytes = 1 + (uint64_t)nodeCount * (2 * w + 5);   // ref: Huffman.c:881-886
+    if (nodeCount == 0 || nodeCount > 2 * 65536 || 8 + tree_bytes > len) { set_err("decode_with_tree: not a Huffman container (nodeCount %u)", nodeCount); return SZ_NSCS; }
+    DecJob job; memset(&job, 0, sizeof(job));
+    job.slot = 1; job.d_tree = d_body + 8; job.nodeCount = nodeCount; job.d_payload = d_body + 8 + tree_bytes; job.payload_bytes = len - 8 - tree_bytes;
+    job.nsym = n; job.blockmajor = false; job.d_out = (uint16_t *)d_symbols_out_u16;
+    unsigned long long *d_totals = nullptr; uint64_t expect[5] = {0, 0, 0, 0, 0};
+    const Geom g = make_geom(2, 1, 1, 1);
+    c.launches = 0;
+    if (huff_decode_all<float>(c, &job, 1, g, (const float *)nullptr, 0, (float *)nullptr, nullptr, &d_totals, expect)) return SZ_NSCS;
+    unsigned long long h_tot[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (d_totals) CU(cudaMemcpyAsync(h_tot, d_totals, 64, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    if (expect[0] && h_tot[0] < expect[0]) { set_err("decode_with_tree: the container holds %llu symbols, %zu expected", h_tot[0], n); return SZ_NSCS; }
+    return 0;
+}
+
 template <typename T>
 static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size_t body_len, int body_on_device, T *d_out, szb200_stats *stats) {
     const Geom g = make_geom(job.dim, job.n0, job.n1, job.n2);

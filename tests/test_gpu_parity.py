@@ -500,6 +500,48 @@ def test_reference_thread_safe_example_runs_unmodified_on_the_library(sz, tmp_pa
     assert re.search(r"max_error=", r.stdout)
 
 
+@pytest.mark.parametrize("kind", ["bell_1024", "two_symbols", "one_symbol", "wide_65536", "skewed_64"])
+def test_huffman_container_encode_with_tree_equals_the_reference(sz, orc, kind):
+    """encode_withTree / decode_withTree (Huffman.c:790-816, :865-889), the [nodeCount][stateNum/2][tree][bits]
+    container of the SZ 1.4 storage, stand-alone through the C-ABI: byte-equal to the compiled reference's encode_withTree where it
+    is present, to the container put together from the oracle's tree and bit stream otherwise; and back."""
+    import ctypes as C
+    import struct
+    import torch
+    from sz_b200 import api
+    rng = np.random.default_rng(11)
+    n = 200000
+    if kind == "bell_1024":
+        state, s = 1024, np.clip(np.rint(rng.normal(256, 40, n)), 0, 511).astype(np.int32)
+    elif kind == "two_symbols":
+        state, s = 64, rng.integers(7, 9, n).astype(np.int32)
+    elif kind == "one_symbol":
+        state, s = 64, np.full(n, 5, dtype=np.int32)
+    elif kind == "wide_65536":
+        state, s = 65536, np.clip(np.rint(rng.normal(16384, 3000, n)), 0, 32767).astype(np.int32)
+    else:
+        state, s = 128, np.minimum(rng.geometric(0.3, n), 63).astype(np.int32)
+    tree, nodes, code, clen = orc.huffman_build(s, state)
+    want = struct.pack(">II", nodes, state // 2) + tree + orc.huffman_encode(s, code, clen)
+    if szref.have_ref():                                        # the reference itself
+        R = C.CDLL(szref.REF_SO)
+        R.createHuffmanTree.restype = C.c_void_p
+        R.createHuffmanTree.argtypes = [C.c_int]
+        R.encode_withTree.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+        R.SZ_ReleaseHuffman.argtypes = [C.c_void_p]
+        t = R.createHuffmanTree(state)
+        out, osz = C.c_void_p(), C.c_size_t(0)
+        R.encode_withTree(t, s.ctypes.data, s.size, C.byref(out), C.byref(osz))
+        ref = C.string_at(out, osz.value)
+        R.SZ_ReleaseHuffman(t)
+        assert ref == want, "the oracle's container differs from the reference's"
+    d_sym = torch.from_numpy(s.astype(np.int16)).cuda()
+    got = api.encode_with_tree(d_sym, state)
+    assert got == want
+    back = api.decode_with_tree(got, n)
+    assert torch.equal(back, d_sym)
+
+
 def test_incompressible_field_fits_a_raw_sized_device_buffer(sz):
     """white noise with a tight bound: the reference stores the original data (lossless container, sz_float.c:526-559, :2979).  A
     device buffer of just that size must be enough -- the Huffman body that does not fit it is the very trigger of that container --
