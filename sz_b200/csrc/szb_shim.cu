@@ -3,6 +3,7 @@
 // the hot path is a kernel from szb_stage1.cuh / szb_wavefront.cuh / szb_huffman.cuh.
 //
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a --fmad=false -lineinfo -Xcompiler -ffp-contract=off ...
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdarg.h>
@@ -456,6 +457,35 @@ static int launch_hist(Ctx &c, cudaStream_t st, const uint16_t *s, uint64_t n, u
     return 0;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *p = nullptr; cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (EncodeTiledFn)p;
+        else cudaGetLastError();
+    });
+    return fn;
+}
+// the merged wavefront input `xin` ([rows = n0 * n1][pitch]) as a tensor {pitch, n1, n0} (2D: {pitch, n1}); box = what one warp's
+// pencil needs of it for two chunks: {2 CH, PJ, PI} (2D: {2 CH, PJ}).  This GPU's memory only; no swizzle, out-of-bounds = zero.
+template <typename T, int DIM>
+static int make_xin_map(CUtensorMap *tm, const T *d_xin, const Geom &g, uint32_t pitch) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) { set_err("cuTensorMapEncodeTiled is not available from this driver"); return SZ_NSCS; }
+    const cuuint64_t dims[3] = {pitch, g.ax[1].n, g.ax[0].n};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch * sizeof(T), (cuuint64_t)pitch * sizeof(T) * g.ax[1].n};
+    const cuuint32_t box[3] = {(cuuint32_t)WfSmem<T, DIM>::HALF, (cuuint32_t)Pencil<DIM>::PJ, (cuuint32_t)Pencil<DIM>::PI};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = enc(tm, sizeof(T) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64, DIM == 3 ? 3 : 2, (void *)d_xin, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_err("cuTensorMapEncodeTiled failed (%d) for xin %u x %u x pitch %u", (int)r, g.ax[0].n, g.ax[1].n, pitch); return SZ_NSCS; }
+    return 0;
+}
+
 template <typename T, int DIM>
 static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, int cap, const unsigned char *indicator, const T *x, uint16_t *codes,
                             T *recon, const T *coeff_last, T eb, T recip, T mean, int write_all) {
@@ -507,6 +537,8 @@ static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, in
         KCHECK();
     }
     P.given = d_given; P.given_wpr = wpr; P.pitch = pitch;
+    CUtensorMap xin_map;
+    if (make_xin_map<T, DIM>(&xin_map, d_xin, g, pitch)) return SZ_NSCS;
     const size_t per_warp = wf_smem_per_warp<T>(DIM);
     int warps = sizeof(T) == 4 ? 4 : 2;
     while (warps > 1 && per_warp * warps > c.smem_optin) warps--;
@@ -516,7 +548,7 @@ static int launch_wavefront(Ctx &c, const Geom &g, bool decomp, int use_mean, in
     int grid = (int)std::min<uint32_t>(need_ctas, (uint32_t)(c.sm_count * ctas_per_sm));
     auto run = [&](auto kern) -> int {
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<grid, warps * 32, smem, c.stream>>>(P, (const T *)d_xin, codes, recon, eb, recip); KCHECK();
+        kern<<<grid, warps * 32, smem, c.stream>>>(P, xin_map, codes, recon, eb, recip); KCHECK();
         return 0;
     };
     int rc;

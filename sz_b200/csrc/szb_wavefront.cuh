@@ -26,6 +26,7 @@
 // wavefront step is then: one input (staged by bulk-asynchronous copies half a ring ahead), three ring loads, the Lorenzo sum, the
 // branch-free quantiser (compress) or one add (decompress), one select on the given bit.
 #pragma once
+#include <cuda.h>          // CUtensorMap (the tensor map itself is encoded on the host, szb_shim.cu)
 #include "szb_common.cuh"
 
 namespace szb {
@@ -66,15 +67,18 @@ template <int DIM> struct WfBnd { static constexpr int NR = (DIM == 3) ? Pencil<
 template <typename T, int DIM>
 inline size_t wf_bnd_bytes(uint32_t num_pencils, uint32_t n2) { return (size_t)num_pencils * WfBnd<DIM>::NR * n2 * (sizeof(T) / 4) * 8; }
 
-// Per-warp shared memory: [reconstruction ring incl. halo rows | input ring, one row per lane | one mbarrier per chunk slot].
-// The input ring is indexed by POSITION (k mod IW) and its rows are 16-byte aligned with a 16-byte pad (bank spread): every
-// chunk of every row is the destination of one bulk-asynchronous copy.
+// Per-warp shared memory: [reconstruction ring incl. halo rows | input ring | one mbarrier per half of the input ring].
+// The input ring holds two HALVES of two chunks each; a half is the destination of ONE tensor-map tile load (TMA): the box
+// {2 CH points, PJ rows, PI planes} of the merged input `xin` lands as [lane = li * PJ + lj][2 CH], rows beyond the array are
+// zero-filled by the TMA unit.  Lane l reads its point k at half (k / 2CH) & 1, offset l * 2CH + k mod 2CH: the lanes of a warp
+// are at different k (their delays differ), which spreads them over the banks without padding.  128-byte aligned (TMA destination).
 template <typename T, int DIM> struct WfSmem {
-    static constexpr int IS = WfCfg<DIM>::IW + 16 / (int)sizeof(T);                                   // input row stride (elements)
-    static constexpr size_t RING = (((size_t)WfCfg<DIM>::ROWS * WfCfg<DIM>::S * sizeof(T)) + 15) & ~(size_t)15;
-    static constexpr size_t INR = (size_t)32 * IS * sizeof(T);
+    static constexpr int HALF = 2 * WfCfg<DIM>::CH;                                                   // points per lane and half
+    static constexpr size_t RING = (((size_t)WfCfg<DIM>::ROWS * WfCfg<DIM>::S * sizeof(T)) + 127) & ~(size_t)127;
+    static constexpr size_t HALF_BYTES = (size_t)32 * HALF * sizeof(T);
+    static constexpr size_t INR = 2 * HALF_BYTES;
     static constexpr size_t BARS = 8 * WfCfg<DIM>::NSLOT;
-    static constexpr size_t TOTAL = RING + INR + BARS;
+    static constexpr size_t TOTAL = (RING + INR + BARS + 127) & ~(size_t)127;
 };
 template <typename T>
 __host__ __device__ constexpr size_t wf_smem_per_warp(int dim) { return dim == 3 ? WfSmem<T, 3>::TOTAL : WfSmem<T, 2>::TOTAL; }
@@ -94,6 +98,15 @@ __device__ __forceinline__ bool mbar_try_wait(unsigned int bar, unsigned int par
 // one contiguous run of `bytes` (multiple of 16, both addresses 16-byte aligned) global -> shared; completion is counted on `bar`
 __device__ __forceinline__ void bulk_g2s(unsigned int smem_dst, const void *gmem_src, unsigned int bytes, unsigned int bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst), "l"(gmem_src), "r"(bytes), "r"(bar) : "memory");
+}
+// one tile of a tensor map (this GPU's memory, no multicast) global -> shared; the box's bytes are counted on `bar`
+__device__ __forceinline__ void tma_tile_3d(unsigned int smem_dst, const CUtensorMap *tm, int c0, int c1, int c2, unsigned int bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_tile_2d(unsigned int smem_dst, const CUtensorMap *tm, int c0, int c1, unsigned int bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -255,13 +268,15 @@ __global__ void __launch_bounds__(256) prepass_decompress_kernel(Geom g, const u
 // over one ring period (U = 2 chunks) every shared-memory offset and the chunk boundaries are compile-time constants and the
 // step body is straight-line code: 4 LDS, the 6-add Lorenzo chain, the quantiser, 1 STS, 1 warp barrier.
 template <typename T, int DIM, bool MEAN, bool DECOMP>
-__global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__restrict__ xin /*merged input of the pre-pass*/,
+__global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const __grid_constant__ CUtensorMap xin_map /*the merged input of the pre-pass, `xin`,
+                                                        as a tensor {pitch, n1, n0} (2D: {pitch, n1}) with box {2 CH, PJ, PI}*/,
                                                         uint16_t *codes /*raster; compress: codes of the not-given points are written here*/,
                                                         T *recon /*raster; decompress: output; compress: only with write_all_recon*/,
                                                         T eb, T recip_eb) {
     constexpr int PI = Pencil<DIM>::PI, PJ = Pencil<DIM>::PJ;
-    constexpr int CH = WfCfg<DIM>::CH, W = WfCfg<DIM>::W, S = WfCfg<DIM>::S, IW = WfCfg<DIM>::IW, IS = WfSmem<T, DIM>::IS, NSLOT = WfCfg<DIM>::NSLOT;
-    constexpr unsigned int CHUNK_BYTES = CH * sizeof(T);
+    constexpr int CH = WfCfg<DIM>::CH, W = WfCfg<DIM>::W, S = WfCfg<DIM>::S, IW = WfCfg<DIM>::IW, HALF = WfSmem<T, DIM>::HALF, NSLOT = WfCfg<DIM>::NSLOT;
+    constexpr unsigned int HALF_BYTES = (unsigned int)WfSmem<T, DIM>::HALF_BYTES;
+    static_assert(IW == 2 * HALF && (HALF & (HALF - 1)) == 0, "the input ring is two halves of two chunks");
     constexpr int U = W;                               // steps per unrolled period (two chunks)
     constexpr int RJ = PJ + 1;                         // ring rows per li (incl. halo lj = -1)
     constexpr int DMAX = PI - 1 + PJ - 1;
@@ -270,10 +285,10 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
     static_assert(U % 32 == 0, "given-bit windows are whole words");
     static_assert(U - 6 >= DMAX, "the next half of the input ring is requested at step U-6, when every lane has left the previous one");
     constexpr int NW = U / 32;                         // given-bit words per period
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     T *ring = reinterpret_cast<T *>(smem_raw + (size_t)warp * wf_smem_per_warp<T>(DIM));
-    T *inr = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(ring) + WfSmem<T, DIM>::RING);       // input ring [32][IS], position-indexed
+    T *inr = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(ring) + WfSmem<T, DIM>::RING);       // input ring [2 halves][32 lanes][2 CH]
     const unsigned int inr_s32 = (unsigned int)__cvta_generic_to_shared(inr);
     const unsigned int bars_s32 = inr_s32 + (unsigned int)WfSmem<T, DIM>::INR;                          // NSLOT mbarriers
     if (lane == 0) {
@@ -294,7 +309,7 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
     const T *row_b = ring + ((size_t)(li + 1) * RJ + lj) * S;        // (li, lj-1)
     const T *row_c = ring + ((size_t)li * RJ + (lj + 1)) * S;        // (li-1, lj)
     const T *row_f = ring + ((size_t)li * RJ + lj) * S;              // (li-1, lj-1)
-    const T *my_in = inr + (size_t)lane * IS;
+    const T *my_in = inr + (size_t)lane * HALF;                      // this lane's row of half 0; half 1 is 32 * HALF elements on
     const int radius = P.radius;
     const T caplf = (T)P.cap_l;
     const uint32_t wpr = P.given_wpr;
@@ -330,22 +345,19 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
         bool ok = true;
         __syncwarp();
 
-        // staging of the input: every lane issues ONE bulk-asynchronous copy per PAIR of chunks (pair h = chunks 2h, 2h+1 = one half
-        // of its ring row); lane 0 first tells the half's barrier how many bytes to expect.  A warp-wide bulk-copy instruction is 32
-        // separate requests and costs ~2000 cycles of issue whatever their size, so they are made as large as the ring allows and
-        // issued late in a period (step U-6), when the slowest lane has left the half that is overwritten and the neighbour
-        // pencils have already been handed what they wait for.  Rows of xin are padded to whole chunks.
-        const unsigned int nrows = (unsigned int)__popc(__ballot_sync(0xffffffffu, active));
-        const T *xrow = xin + rowid * pitch;
-        const unsigned int my_in_s32 = inr_s32 + (unsigned int)(lane * IS * sizeof(T));
+        // staging of the input: ONE tensor-map tile load per PAIR of chunks (pair h = chunks 2h, 2h+1 = one half of the input ring)
+        // brings the 2 CH points of all PI x PJ rows of the pencil; lane 0 tells the half's barrier how many bytes to expect and issues
+        // the request.  It is issued late in a period (step U-6), when the slowest lane has left the half that is overwritten.
+        // Rows of xin are padded to whole chunks; what lies beyond the array reads as zero.
         auto stage_pair = [&](uint32_t h) {
             const uint32_t k0 = 2 * h * CH;
             if (k0 >= n2) return;
-            const unsigned int bytes = (unsigned int)min((uint32_t)(2 * CH), pitch - k0) * (unsigned int)sizeof(T);
             const unsigned int half = h & 1u, bar = bars_s32 + 8u * half;
-            if (lane == 0) mbar_expect_tx(bar, nrows * bytes);
-            __syncwarp();
-            if (active) bulk_g2s(my_in_s32 + half * 2u * CHUNK_BYTES, xrow + k0, bytes, bar);
+            if (lane == 0) {
+                mbar_expect_tx(bar, HALF_BYTES);
+                if (DIM == 3) tma_tile_3d(inr_s32 + half * HALF_BYTES, &xin_map, (int)k0, (int)j0, (int)i0, bar);
+                else tma_tile_2d(inr_s32 + half * HALF_BYTES, &xin_map, (int)k0, (int)j0, bar);
+            }
         };
         auto wait_pair = [&](uint32_t h) {
             const unsigned int half = h & 1u, bar = bars_s32 + 8u * half, parity = (phases >> half) & 1u;
@@ -528,7 +540,8 @@ __global__ void __launch_bounds__(128) wavefront_kernel(WfParams P, const T *__r
                 const T rb = row_b[(s + W - 1) & (W - 1)];
                 const T rc = (DIM == 3) ? row_c[(s + W - 1) & (W - 1)] : (T)0;
                 const T rf = (DIM == 3) ? row_f[(s + W - 2) & (W - 1)] : (T)0;
-                const T in = my_in[(kin + s) & (IW - 1)];
+                const uint32_t ipos = (kin + s) & (IW - 1);
+                const T in = my_in[(ipos & (HALF - 1)) + (ipos & HALF) * 32u];         // half (ipos / HALF) starts 32 * HALF elements on
                 T pred;
                 if (DIM == 3) {   // main-loop term order (ref: sz_float.c:7268-7269)
                     pred = ra + rb; pred = pred + rc; pred = pred - rd; pred = pred - re; pred = pred - rf; pred = pred + rg;
