@@ -24,6 +24,7 @@
 #include "szb_common.cuh"
 #include "szb_huffman.cuh"
 #include "szb_stage1.cuh"
+#include "szb_chain.cuh"
 #include "szb_wavefront.cuh"
 
 using namespace szb;
@@ -719,10 +720,16 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     if (reg_count > 0) {
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, ncoef, d_reg, d_regc, d_list); KCHECK();
         const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
-        ChainStep<T> *d_steps = (ChainStep<T> *)c.get("chain_steps", sizeof(ChainStep<T>) * (size_t)ncoef * reg_count + 256); if (!d_steps) return SZ_NSCS;
-        chain_prep_kernel<T><<<dim3((reg_count + 255) / 256, ncoef), 256, 0, c.stream>>>(d_regc, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_steps); KCHECK();
-        CU(cudaFuncSetAttribute(coeff_chain_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ChainCfg<T>::SMEM));
-        coeff_chain_kernel<T><<<1, CHAIN_THREADS, ChainCfg<T>::SMEM, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
+        static const int chain_form = [] { const char *e = getenv("SZB200_CHAIN"); return e && !strcmp(e, "tables") ? 1 : e && !strcmp(e, "exact") ? 2 : 0; }();
+        if (chain_form != 1) {
+            // one CTA per coefficient: lattice guess, add chain, exact proof (szb_chain.cuh); "exact" runs every step with the complete formula
+            coeff_lattice_kernel<T><<<ncoef, LAT_THREADS, 0, c.stream>>>(d_regc, d_list, nb, reg_count, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain, chain_form == 2 ? 2 : 0, getenv("SZB200_LAT_BAND") ? (float)atof(getenv("SZB200_LAT_BAND")) : LAT_BAND); KCHECK();
+        } else {
+            ChainStep<T> *d_steps = (ChainStep<T> *)c.get("chain_steps", sizeof(ChainStep<T>) * (size_t)ncoef * reg_count + 256); if (!d_steps) return SZ_NSCS;
+            chain_prep_kernel<T><<<dim3((reg_count + 255) / 256, ncoef), 256, 0, c.stream>>>(d_regc, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_steps); KCHECK();
+            CU(cudaFuncSetAttribute(coeff_chain_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ChainCfg<T>::SMEM));
+            coeff_chain_kernel<T><<<1, CHAIN_THREADS, ChainCfg<T>::SMEM, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
+        }
     }
     if (mark(ST_CHAIN)) return SZ_NSCS;
 
@@ -806,7 +813,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     for (int i = 1; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
-    if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u (complete: %u) kcycles: serial warp busy=%u, helper warp busy=%u, total=%u\n", reg_count, h_chain.passes, h_chain.slow_chunks, h_chain.kcyc_serial, h_chain.kcyc_helper, h_chain.kcyc_total);
+    if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u (reruns: %u) kcycles: serial thread busy=%u, total=%u; last coefficient: pair steps=%u, full steps=%u\n", reg_count, h_chain.passes, h_chain.slow_chunks, h_chain.kcyc_serial, h_chain.kcyc_total, h_chain.kcyc_helper, h_chain.n_full);
     if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
         fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
     if (h_chain.err) { set_err("coefficient chain: a step left its tabulated interval (internal error)"); return SZ_NSCS; }

@@ -503,7 +503,7 @@ __global__ void reg_gather_kernel(const unsigned char *__restrict__ indicator, c
 // recurrence, so each coefficient is ONE serial lane; the ncoef lanes run side by side in one warp.  The whole warp
 // stages 256 steps at a time through shared memory so that global loads/stores are coalesced and off the chain.
 // =====================================================================================================================
-struct ChainOut { unsigned int unpred_count[4]; unsigned int err; unsigned int passes, kcyc_serial, kcyc_total, kcyc_helper, slow_chunks; };   // last four: profiling aid
+struct ChainOut { unsigned int unpred_count[4]; unsigned int err; unsigned int passes, kcyc_serial, kcyc_total, kcyc_helper, slow_chunks, n_full; };   // last four: profiling aid
 
 // one step of the reference's coefficient quantiser as a function of `last` (exact formula, ref: sz_float.c:7130-7150)
 template <typename T>
