@@ -341,7 +341,7 @@ def run_ours(args):
     per_step = {k: v / args.steps for k, v in stage_ms.items() if v > 0}
     # the kernels (or launch groups) a stage consists of, for the roofline line: the one with the largest measured share
     kernels = {"coeff_trees_kernel_side_stream": "huff_build_kernel (four coefficient Huffman trees: the reference's binary heap replayed operation by operation, side stream)",
-               "coeff_chain": "coeff_chain_kernel (+ reg_gather, chain_prep: the coefficient DPCM recurrence)",
+               "coeff_chain": "coeff_lattice_kernel (+ reg_gather: the coefficient DPCM recurrence)",
                "wavefront_quant": "prepass_compress_kernel + wavefront_kernel<float,3> (predict + quantise)",
                "encode": "enc_len_kernel + scans + enc_write_kernel (Huffman bit packing)",
                "fit_select": "fit_select_kernel (regression fit + predictor selection)",

@@ -10,26 +10,31 @@
 // off the lattice by a few ulps; that matters for the code when cur_i lies within this drift of the midpoint of two lattice
 // points, and it always matters for the bits of last_i.  One CTA per coefficient, windows of LAT_W steps, three stages that run
 // side by side on consecutive windows (one __syncthreads per window):
-//   (G) helper thread h guesses the code of step h from the closed form (double arithmetic, relative to the exact `last` that
-//       entered the window before) and classes the step: SURE; PAIR when the guess is within a drift band of a midpoint or follows
-//       such a step -- two candidate codes, told apart by an exact threshold D on |cur - last| that the thread finds by evaluating
-//       the reference's own quotient at the floats around (2n+1) prec; FULL when neither form is safe (two pairs in a row, near the
-//       code range, not finite).  Increments fl(2 dk * prec) are formed here.
-//   (S) ONE thread runs the recurrence: a SURE step is one add, a PAIR step a subtraction, a compare, a select, an add and the
-//       reference's check, a FULL step the reference's complete formula.  An unpredictable coefficient (new base) ends the window.
+//   (G1) helper thread h guesses the code of step h of the NEXT window from the closed form (double arithmetic, relative to the exact
+//       `last` that entered the window (S) is running) and prepares the step in up to three forms: SURE (one increment
+//       fl(2 dk * prec)); PAIR when cur_h may lie within the drift band of a midpoint -- two candidate codes of magnitudes n, n+1,
+//       told apart by an exact threshold on |cur - last| that the thread finds by evaluating the reference's own quotient at the
+//       floats around (2n+1) prec -- or when it follows such a step (two codes again, any threshold between them);
+//   (G2) at the top of the next tick, when the exact `last` entering the window is known, the same thread subtracts the measured
+//       drift, settles the class with the band of its own window only and writes the step's table entry; FULL when no prepared
+//       form is safe (two midpoint steps in a row, near the code range, not finite);
+//   (S) ONE thread runs the recurrence: 32 or 8 SURE steps are that many adds; a group of 8 with PAIR steps runs branch-free as
+//       subtraction, compare, select, add per step plus the reference's check; a FULL step is the reference's complete formula.  An
+//       unpredictable coefficient (new base) ends the window.
 //   (V) helper thread h proves step h with the complete formula on the exact `last` that entered it: code and bits of the new
 //       `last`.  A window that fails is rerun from its exact entry value with a wider band, then with every step FULL, i.e. as the
 //       reference's own loop.
 // The output is the reference's sequence by induction over the proved steps, not by the quality of the guess, which only decides
 // the speed.
 #pragma once
+
 #include "szb_stage1.cuh"
 
 namespace szb {
 
 constexpr int LAT_W = 256;                    // steps per window = helper threads
 constexpr int LAT_THREADS = LAT_W + 32;       // warp 0: the serial thread; warps 1..8: helpers
-constexpr float LAT_BAND = 0.75f;             // drift band in units of mag eps sqrt(steps), see (G)
+constexpr float LAT_BAND = 0.35f;             // drift band in units of mag eps sqrt(steps), see (G1)
 template <typename T> struct LatEps;
 template <> struct LatEps<float> { static constexpr double eps = 1.0 / 8388608.0; };              // 2^-23: ulp(x) <= eps |x|
 template <> struct LatEps<double> { static constexpr double eps = 1.0 / 4503599627370496.0; };    // 2^-52
@@ -37,9 +42,10 @@ template <> struct LatEps<double> { static constexpr double eps = 1.0 / 45035996
 template <typename T> struct __align__(16) LatSlot {        // one window in shared memory
     T cur[LAT_W], inc[LAT_W], incB[LAT_W], thr[LAT_W], out[LAT_W];     // out[i]: last after step i
     int q[LAT_W], qB[LAT_W];
-    unsigned int hm[LAT_W / 32], xm[LAT_W / 32];                        // one bit per step: PAIR or FULL / FULL
+    unsigned int hm[LAT_W / 32], xm[LAT_W / 32];                        // one bit per step: PAIR form / FULL
+    unsigned char bigm[LAT_W / 8];                                      // written by (S): PAIR steps that took their second candidate
     unsigned int wend; T exit;                                          // written by (S): steps done, last after them
-    float maxmag;                                                       // written by (G): largest magnitude the window's values can have
+    float maxmag;                                                       // written by (G1): largest magnitude the window's values can have
 };
 
 __device__ __forceinline__ void lat_helper_bar() { asm volatile("bar.sync 1, %0;" ::"n"(LAT_W) : "memory"); }
@@ -50,37 +56,6 @@ __device__ __forceinline__ int lat_mag(T d, T prec, T rprec, int use_div) {
     T itv = use_div ? d / prec : d * rprec;
     itv = itv + (T)1;
     return itv < (T)65536 ? (int)(itv / (T)2) : 65536;
-}
-
-// A FULL step: the reference's complete formula; `ended`: the coefficient is unpredictable (the window ends with it).  The running
-// `last` goes in and out by value (a reference parameter would put it into local memory).
-template <typename T> struct LatStep { T s; int ended; };
-template <typename T>
-__device__ __noinline__ LatStep<T> lat_full_step(LatSlot<T> &L, int i, T prec, T rprec, int use_div, T s) {
-    T nl;
-    const int ct = chain_step_exact<T>(L.cur[i], s, prec, rprec, use_div, nl);
-    L.q[i] = ct; L.out[i] = nl;
-    LatStep<T> r; r.s = nl; r.ended = ct == 0;
-    return r;
-}
-// A PAIR step: the code has magnitude n0 or n0 + 1, told apart by |cur - last| against the exact threshold; then the reference's check.
-// When it takes its second candidate, the step behind it starts from the other lattice point: its increment and code are replaced.
-template <typename T>
-__device__ __forceinline__ LatStep<T> lat_pair_step(LatSlot<T> &L, int i, T prec, T s) {
-    const T cur = L.cur[i], thr = L.thr[i], iA = L.inc[i], iB = L.incB[i];
-    const T diff = cur - s;
-    const bool big = !(TT<T>::abs(diff) < thr);
-    const T v = s + (big ? iB : iA);
-    const T chk = cur - v;
-    const bool unp = TT<T>::abs(chk) > prec;
-    if (big) {
-        L.q[i] = L.qB[i];
-        if (i + 1 < LAT_W) { L.inc[i + 1] = L.incB[i + 1]; L.q[i + 1] = L.qB[i + 1]; }
-    }
-    LatStep<T> r;
-    if (unp) { L.q[i] = 0; r.s = cur; r.ended = 1; } else { r.s = v; r.ended = 0; }
-    L.out[i] = r.s;
-    return r;
 }
 
 __device__ __forceinline__ void lat_ld8(const float *p, float v[8]) {
@@ -99,33 +74,123 @@ __device__ __forceinline__ void lat_st8(double *p, const double v[8]) {
     for (int t = 0; t < 4; t++) *reinterpret_cast<double2 *>(p + 2 * t) = make_double2(v[2 * t], v[2 * t + 1]);
 }
 
-// Eight steps of which at least one is PAIR or FULL (ONE copy of this code: the serial thread runs alone on its scheduler and pays for
-// every instruction-cache miss).  ended: index in the group of the first unpredictable coefficient, or -1; the steps behind such a
-// coefficient are computed for nothing (no exit from the unrolled steps).
-template <typename T> struct LatGroup { T s; int ended; };
+// The running `last` goes in and out of these by value (a reference parameter would put it into local memory).
+template <typename T> struct LatStep { T s; int ended; };
+
+// Eight steps of which some are PAIR and none FULL, without a branch: every step in the PAIR form (a SURE step has an infinite
+// threshold).  ended = 1: some step failed the reference's check (unpredictable coefficient); the caller reruns the group step by step.
 template <typename T>
-__device__ __noinline__ LatGroup<T> lat_mixed_group(LatSlot<T> &L, int i0, unsigned int hm8, unsigned int xm8, T prec, T rprec, int use_div, T s) {
-    T v[8];
-    lat_ld8(&L.inc[i0], v);
-    int ended = -1;
+__device__ __noinline__ LatStep<T> lat_pair_group(LatSlot<T> &L, int i0, T prec, T s) {
+    T cur[8], thr[8], iA[8], iB[8], o[8];
+    lat_ld8(&L.cur[i0], cur); lat_ld8(&L.thr[i0], thr); lat_ld8(&L.inc[i0], iA); lat_ld8(&L.incB[i0], iB);
+    unsigned int bigm = 0u; bool unp = false;
 #pragma unroll
     for (int t = 0; t < 8; t++) {
-        if ((hm8 >> t) & 1u) {
-            LatStep<T> r;
-            if ((xm8 >> t) & 1u) r = lat_full_step<T>(L, i0 + t, prec, rprec, use_div, s);
-            else {
-                r = lat_pair_step<T>(L, i0 + t, prec, s);
-                if (t + 1 < 8) v[t + 1] = L.inc[i0 + t + 1];       // it may have replaced the increment of the step behind it
+        const T diff = cur[t] - s;
+        const bool big = !(TT<T>::abs(diff) < thr[t]);
+        s = s + (big ? iB[t] : iA[t]);
+        o[t] = s;
+        const T chk = cur[t] - s;
+        unp = unp || TT<T>::abs(chk) > prec;
+        bigm |= big ? (1u << t) : 0u;
+    }
+    lat_st8(&L.out[i0], o);
+    L.bigm[i0 >> 3] = (unsigned char)bigm;
+    LatStep<T> r; r.s = s; r.ended = unp ? 1 : 0;
+    return r;
+}
+
+// Eight steps one by one: SURE an add, PAIR with the reference's check, FULL the reference's complete formula.  ended: index of the
+// first unpredictable coefficient (the window ends with it; the steps behind it are not run), or -1.
+template <typename T>
+__device__ __noinline__ LatStep<T> lat_slow_group(LatSlot<T> &L, int i0, unsigned int hm8, unsigned int xm8, T prec, T rprec, int use_div, T s) {
+    unsigned int bigm = 0u; int ended = -1;
+    for (int t = 0; t < 8 && ended < 0; t++) {
+        const int i = i0 + t;
+        const T cur = L.cur[i];
+        if ((xm8 >> t) & 1u) {
+            T nl;
+            const int ct = chain_step_exact<T>(cur, s, prec, rprec, use_div, nl);
+            L.q[i] = ct; s = nl;
+            if (ct == 0) ended = t;
+        } else if ((hm8 >> t) & 1u) {
+            const T diff = cur - s;
+            const bool big = !(TT<T>::abs(diff) < L.thr[i]);
+            const T v = s + (big ? L.incB[i] : L.inc[i]);
+            const T chk = cur - v;
+            if (TT<T>::abs(chk) > prec) { L.q[i] = 0; L.qB[i] = 0; s = cur; ended = t; }
+            else { s = v; bigm |= big ? (1u << t) : 0u; }
+        } else s = s + L.inc[i];
+        L.out[i] = s;
+    }
+    L.bigm[i0 >> 3] = (unsigned char)bigm;
+    LatStep<T> r; r.s = s; r.ended = ended;
+    return r;
+}
+
+// 32 steps with their increments in registers; returns true when the window ends in this word (wend set)
+template <typename T>
+__device__ __forceinline__ bool lat_word(LatSlot<T> &L, int w, const T (&v)[32], unsigned int hmw, unsigned int xmw, T prec, T rprec, int use_div, T &s, int &wend, unsigned int *prof) {
+#ifdef LAT_PROF
+    const long long pc0 = clock64();
+#define LAT_PROF_ADD(k) { prof[2 * (k)] += 1u; prof[2 * (k) + 1] += (unsigned int)(clock64() - pc1); }
+#else
+#define LAT_PROF_ADD(k)
+#endif
+    if ((hmw | xmw) == 0u) {                                  // 32 SURE steps (steps past the window's end add zero)
+        T o[32];
+#pragma unroll
+        for (int t = 0; t < 32; t++) { s = s + v[t]; o[t] = s; }
+#pragma unroll
+        for (int g = 0; g < 4; g++) lat_st8(&L.out[32 * w + 8 * g], &o[8 * g]);
+#ifdef LAT_PROF
+        { const long long pc1 = pc0; LAT_PROF_ADD(0) }
+#endif
+        return false;
+    }
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+        const int i0 = 32 * w + 8 * g;
+        const unsigned int h8 = (hmw >> (8 * g)) & 0xffu, x8 = (xmw >> (8 * g)) & 0xffu;
+#ifdef LAT_PROF
+        const long long pc1 = clock64();
+#endif
+        if ((h8 | x8) == 0u) {
+            T o[8];
+#pragma unroll
+            for (int t = 0; t < 8; t++) { s = s + v[8 * g + t]; o[t] = s; }
+            lat_st8(&L.out[i0], o);
+            LAT_PROF_ADD(1)
+        } else {
+            LatStep<T> r; r.ended = 1;
+            if (x8 == 0u) r = lat_pair_group<T>(L, i0, prec, s);
+            if (r.ended) {
+                r = lat_slow_group<T>(L, i0, h8, x8, prec, rprec, use_div, s);
+                if (r.ended >= 0) { wend = i0 + r.ended + 1; return true; }
             }
             s = r.s;
-            if (r.ended && ended < 0) ended = t;
-        } else { s = s + v[t]; L.out[i0 + t] = s; }
+            LAT_PROF_ADD(x8 ? 3 : 2)
+        }
     }
-    LatGroup<T> g; g.s = s; g.ended = ended;
-    return g;
+    return false;
+}
+__device__ __forceinline__ void lat_ld32(const float *p, float (&v)[32]) {
+#pragma unroll
+    for (int g = 0; g < 4; g++) lat_ld8(p + 8 * g, &v[8 * g]);
+}
+__device__ __forceinline__ void lat_ld32(const double *p, double (&v)[32]) {
+#pragma unroll
+    for (int g = 0; g < 4; g++) lat_ld8(p + 8 * g, &v[8 * g]);
 }
 
 template <typename T> struct LatWin { uint32_t p; int cnt, slot, mode; T entry; bool valid, fresh; };
+// what (G1) leaves in the registers of helper h for (G2), one tick later
+template <typename T> struct LatPrep {
+    double base, frac, adk, band;          // the exact `last` the guess is relative to; cur's offset from its lattice point; |dk|; the band of (G2)
+    int kprev0;                            // lattice index of the step before the window under `base`
+    bool in, valid, pairok, followok;      // step inside the window; numbers finite; PAIR data of a midpoint step / of a step behind one prepared
+    int q0, qA, qB, fqA, fqB; T inc0, incA, incB, thr, fincA, fincB, fthr;
+};
 
 template <typename T>
 __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__restrict__ reg_c /*[ncoef][nb], compacted*/, const uint32_t *__restrict__ reg_list,
@@ -134,71 +199,84 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                                                                     T *__restrict__ coeff_unpred /*[ncoef][nb]*/, ChainOut *out, int first_mode, float band_scale) {
     typedef typename TT<T>::bits_t bits_t;
     constexpr int W = LAT_W;
-    __shared__ __align__(16) LatSlot<T> s_slot[2];
+    __shared__ LatSlot<T> s_slot[2];
     __shared__ int s_k[W];
-    __shared__ unsigned char s_tie[W];            // bit 0: within the band of a midpoint; bit 1: cur above the guessed lattice point
+    __shared__ unsigned char s_tie[W];            // (G1) bit 0: may be at a midpoint, bit 1: cur above its lattice point, bit 2: PAIR data ready; (G2) bit 3: at a midpoint
     __shared__ float s_wmag[W / 32];
-    __shared__ unsigned int s_wcnt[2][W / 32];      // by tick parity: read after the tick's barrier, written again one tick later
+    __shared__ unsigned int s_wcnt[2][W / 32];    // by tick parity: read after the tick's barrier, written again one tick later
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, h = tid - 32;
     const int e = blockIdx.x;
     const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
     const T rprec = (T)1 / prec;
     const double inv2p = 1.0 / (2.0 * (double)prec);
     const T *cur_e = reg_c + (size_t)e * nb;
+    T t_inf; { const bits_t b = sizeof(T) == 4 ? (bits_t)0x7f800000u : (bits_t)0x7ff0000000000000ull; memcpy(&t_inf, &b, sizeof(T)); }
+    const double sqrt_h1 = (double)sqrtf((float)(h > 0 ? h + 1 : 1)) * 1.000001;
     uint32_t ucount = 0;
     unsigned int n_ticks = 0, n_redo = 0, n_pair = 0, n_full = 0;
-    long long cyc_s = 0; const long long cyc_0 = clock64();
+    long long cyc_s = 0, cyc_h = 0; const long long cyc_0 = clock64();
+    unsigned int prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // LAT_PROF builds: {count, cycles} of clean words, clean groups, PAIR groups, groups run step by step
     LatWin<T> vw, sw, gw;
+    LatPrep<T> P; P.in = false;
     vw.valid = false; sw.valid = false;
     gw.p = 0; gw.cnt = (int)min((uint32_t)W, reg_count); gw.slot = 0; gw.mode = first_mode; gw.entry = (T)0; gw.valid = reg_count > 0; gw.fresh = true;
     while (vw.valid || sw.valid || gw.valid) {
+        // ======================== (G2): the window (S) runs in this tick gets its final table ========================
+        if (sw.valid) {
+            if (warp != 0) {
+                LatSlot<T> &L = s_slot[sw.slot];
+                // measured drift: where the exact `last` entering the window lies relative to the lattice the guess used
+                const double y = ((double)sw.entry - P.base) * inv2p, yk = rint(y), rho = y - yk;
+                const bool mismatch = !(fabs(y) < 1073741824.0) || (int)yk != P.kprev0;      // the step before went to another lattice point
+                const bool tie = P.in && !(0.5 - fabs(P.frac - rho) > P.band);
+                s_tie[h] = (unsigned char)((s_tie[h] & 7) | (tie ? 8 : 0));
+                lat_helper_bar();
+                const bool tie1 = h >= 1 && (s_tie[h - 1] & 8) != 0, tie2 = h >= 2 && (s_tie[h - 2] & 8) != 0;
+                const bool pred_pairok = h >= 1 && (s_tie[h - 1] & 4) != 0;
+                bool full = P.in && (sw.mode >= 2 || !P.valid || P.adk >= 32760.0 || (h == 0 && mismatch) ||
+                                     (tie && (tie1 || !P.pairok)) || (!tie && tie1 && (tie2 || !pred_pairok || !P.followok)));
+                const bool pairform = P.in && !full && (tie || tie1);
+                T inc = P.inc0, incB = (T)0, thr = t_inf; int q = P.q0, qB = 0;
+                if (pairform && tie) { inc = P.incA; incB = P.incB; thr = P.thr; q = P.qA; qB = P.qB; }
+                else if (pairform) { inc = P.fincA; incB = P.fincB; thr = P.fthr; q = P.fqA; qB = P.fqB; }
+                if (full || !P.in) { inc = (T)0; q = 0; }
+                const unsigned int hm = __ballot_sync(0xffffffffu, pairform), xm = __ballot_sync(0xffffffffu, full);
+                if (lane == 0) { L.hm[warp - 1] = hm; L.xm[warp - 1] = xm; }
+                L.inc[h] = inc; L.incB[h] = incB; L.thr[h] = thr; L.q[h] = q; L.qB[h] = qB;
+                n_pair += __popc(hm); n_full += __popc(xm);
+            }
+            __syncthreads();
+        }
         bool my_fail = false;
         if (warp == 0) {
-            // ---------------------------------------- (S) ----------------------------------------
+            // ================================================ (S) ================================================
             if (lane == 0 && sw.valid) {
                 const long long c0 = clock64();
                 LatSlot<T> &L = s_slot[sw.slot];
                 T s = sw.entry;
                 int wend = sw.cnt;
                 const int nwords = (sw.cnt + 31) >> 5;
-                T nv[8];                                             // increments of the next group, fetched one group ahead
-                lat_ld8(&L.inc[0], nv);
-                unsigned int hm_n = L.hm[0], xm_n = L.xm[0];
-                for (int w = 0; w < nwords; w++) {
-                    const unsigned int hmw = hm_n, xmw = xm_n;
-                    if (w + 1 < nwords) { hm_n = L.hm[w + 1]; xm_n = L.xm[w + 1]; }
-                    int ended_at = -1;
-#pragma unroll
-                    for (int gg = 0; gg < 4; gg++) {
-                        const int i0 = 32 * w + 8 * gg;
-                        T v[8];
-#pragma unroll
-                        for (int t = 0; t < 8; t++) v[t] = nv[t];
-                        if (i0 + 8 < LAT_W) lat_ld8(&L.inc[i0 + 8], nv);
-                        const unsigned int hm8 = (hmw >> (8 * gg)) & 0xffu;
-                        if (hm8 == 0u) {                             // eight SURE steps (steps past the window's end add zero)
-#pragma unroll
-                            for (int t = 0; t < 8; t++) { s = s + v[t]; v[t] = s; }
-                            lat_st8(&L.out[i0], v);
-                        } else {
-                            const LatGroup<T> r = lat_mixed_group<T>(L, i0, hm8, (xmw >> (8 * gg)) & 0xffu, prec, rprec, use_div, s);
-                            s = r.s;
-                            if (r.ended >= 0 && ended_at < 0) ended_at = 8 * gg + r.ended;
-                            if (i0 + 8 < LAT_W) lat_ld8(&L.inc[i0 + 8], nv);      // a PAIR step at the group's end replaces the next increment
-                        }
-                    }
-                    if (ended_at >= 0) { wend = 32 * w + ended_at + 1; break; }
+                T a[32], b[32];                                      // increments of two words: one in use, one being fetched
+                lat_ld32(&L.inc[0], a);
+                unsigned int hm_a = L.hm[0], xm_a = L.xm[0], hm_b = 0u, xm_b = 0u;
+                for (int w = 0; w < nwords; w += 2) {
+                    if (w + 1 < nwords) { lat_ld32(&L.inc[32 * (w + 1)], b); hm_b = L.hm[w + 1]; xm_b = L.xm[w + 1]; }
+                    if (lat_word<T>(L, w, a, hm_a, xm_a, prec, rprec, use_div, s, wend, prof)) break;
+                    if (w + 1 >= nwords) break;
+                    if (w + 2 < nwords) { lat_ld32(&L.inc[32 * (w + 2)], a); hm_a = L.hm[w + 2]; xm_a = L.xm[w + 2]; }
+                    if (lat_word<T>(L, w + 1, b, hm_b, xm_b, prec, rprec, use_div, s, wend, prof)) break;
                 }
                 L.wend = (unsigned int)wend;
                 L.exit = L.out[wend - 1];
                 cyc_s += clock64() - c0;
             }
         } else {
+            const long long c0 = clock64();
             // global loads of this tick first: their latency hides behind (V)
             T cur_g = (T)0; uint32_t blk_v = 0;
             if (gw.valid && h < gw.cnt) cur_g = cur_e[gw.p + h];
             if (vw.valid && h < vw.cnt) blk_v = reg_list[vw.p + h];
-            // ---------------------------------------- (V) ----------------------------------------
+            // ================================================ (V) ================================================
             int ct = 1; T lout = (T)0, vcur = (T)0; unsigned int zmask = 0;
             if (vw.valid) {
                 LatSlot<T> &L = s_slot[vw.slot];
@@ -209,7 +287,8 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                     T nl;
                     ct = chain_step_exact<T>(vcur, lin, prec, rprec, use_div, nl);
                     bits_t bn, bo; memcpy(&bn, &nl, sizeof(T)); memcpy(&bo, &lout, sizeof(T));
-                    my_fail = ct != L.q[h] || bn != bo;
+                    const bool pairform = (L.hm[h >> 5] >> (h & 31)) & 1u, big = pairform && ((L.bigm[h >> 3] >> (h & 7)) & 1u);
+                    my_fail = ct != (big ? L.qB[h] : L.q[h]) || bn != bo;
                 }
                 zmask = __ballot_sync(0xffffffffu, h < vw.cnt && ct == 0);
                 if (lane == 0) s_wcnt[n_ticks & 1u][warp - 1] = __popc(zmask);
@@ -224,40 +303,36 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                     coeff_unpred[(size_t)e * nb + ucount + before + __popc(zmask & ((1u << lane) - 1u))] = vcur;
                 }
             }
-            // ---------------------------------------- (G) ----------------------------------------
+            // ================================================ (G1) ================================================
             if (gw.valid) {
                 LatSlot<T> &L = s_slot[gw.slot];
                 // the guess is relative to an exact `last`: the window's own entry value (fresh), or the entry value of the window
                 // that (S) is running now, one window back
                 const double base = (double)(gw.fresh ? gw.entry : sw.entry);
                 const int m0 = gw.fresh ? 0 : sw.cnt;
-                const double bandscale = gw.mode == 0 ? (double)band_scale : 16.0 * (double)band_scale;
+                const bool in = h < gw.cnt;
                 const double x = ((double)cur_g - base) * inv2p;
                 const double kr = rint(x);
-                const bool valid = h < gw.cnt && fabs(x) < 1073741824.0;            // false for NaN/inf too
-                const double tiedist = 0.5 - fabs(x - kr);
+                const bool valid = in && fabs(x) < 1073741824.0;            // false for NaN/inf too
                 const int k = valid ? (int)kr : 0;
+                const bool up = x > kr;
                 L.cur[h] = cur_g; s_k[h] = k;
                 {
-                    float m = h < gw.cnt ? fabsf((float)cur_g) : 0.0f;
+                    float m = in ? fabsf((float)cur_g) : 0.0f;
                     if (!(m <= 3.0e38f)) m = 3.0e38f;
 #pragma unroll
                     for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
                     if (lane == 0) s_wmag[warp - 1] = m;
                 }
-                // the step before the window (pipelined windows only): its lattice index and midpoint status under the same base
-                int kprev0 = 0; bool tie_prev0 = false, up_prev0 = false, valid_prev0 = true;
+                // the step before the window (pipelined windows only): its lattice index under the same base
+                int kprev0 = 0; bool valid_prev0 = true;
                 double magp = fabs(base);
                 if (!gw.fresh) {
                     magp = fmax(magp, (double)s_slot[sw.slot].maxmag);      // the drift is run up in that window too
                     const T pc = s_slot[sw.slot].cur[sw.cnt - 1];
-                    const double xp = ((double)pc - base) * inv2p, kp = rint(xp);
+                    const double xp = ((double)pc - base) * inv2p;
                     valid_prev0 = fabs(xp) < 1073741824.0;
-                    kprev0 = valid_prev0 ? (int)kp : 0;
-                    up_prev0 = xp > kp;
-                    magp = fmax(magp, fabs((double)pc));
-                    // its own band needs the step before it; the widest quotient stands in
-                    tie_prev0 = !(0.5 - fabs(xp - kp) > bandscale * (magp * LatEps<T>::eps) * sqrt((double)m0) * inv2p + 32770.0 * (8.0 * LatEps<T>::eps) + (fabs(xp) + 1.0) * 1e-15);
+                    kprev0 = valid_prev0 ? (int)rint(xp) : 0;
                 }
                 lat_helper_bar();
                 const int kprev = h ? s_k[h - 1] : kprev0;
@@ -268,81 +343,75 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                 for (int w = 1; w < W / 32; w++) wm = fmaxf(wm, s_wmag[w]);
                 const double mag = fmax((double)wm * 1.0000002, magp);
                 if (h == 0) L.maxmag = (float)fmin(mag * 1.0000002, 3.0e38);
-                // Drift of `last` after m steps from the exact base: two roundings per step (product, sum), each uniform within half an ulp
-                // of a value no larger than ~mag: a random walk with sigma ~ 0.25 mag eps per step.  LAT_BAND = 0.75 is three sigma; a
-                // window that leaves the band is caught by (V) and rerun with a wider one, so the band is set for speed, in lattice
-                // units.  Plus the formula's own roundings (difference, quotient, +1; the reciprocal), relative to the quotient |dk|, and
-                // the error of this double-precision estimate.
-                const double band = bandscale * (mag * LatEps<T>::eps) * sqrt((double)(m0 + h + 1)) * inv2p + (adk + 2.0) * (8.0 * LatEps<T>::eps) + (fabs(x) + 1.0) * 1e-15;
-                const bool tie = !(tiedist > band);
-                const bool up = x > kr;
-                s_tie[h] = (unsigned char)((tie ? 1 : 0) | (up ? 2 : 0));
-                lat_helper_bar();
-                // midpoint status of the two steps before this one (before a pipelined window: the step before it stands for both)
-                const unsigned char tp0 = (unsigned char)((tie_prev0 ? 1 : 0) | (up_prev0 ? 2 : 0));
-                const unsigned char tp = h ? s_tie[h - 1] : tp0;
-                const bool tie1 = (tp & 1) != 0;
-                const bool tie2 = h >= 2 ? (s_tie[h - 2] & 1) != 0 : tie_prev0;
+                // may this step be at a midpoint when (G2) looks?  The band of both windows, with a margin.
+                const double pband = 1.5 * (gw.mode == 0 ? (double)band_scale : 16.0 * (double)band_scale) * (mag * LatEps<T>::eps) * (double)sqrtf((float)(m0 + h + 1)) * inv2p
+                                     + (adk + 2.0) * (2.5 * LatEps<T>::eps) + (fabs(x) + 1.0) * 1e-15;
+                const bool ptie = valid && !(0.5 - fabs(x - kr) > pband);
                 const bool valid_prev = h ? (fabs(((double)L.cur[h - 1] - base) * inv2p) < 1073741824.0) : valid_prev0;
-                const bool in = h < gw.cnt;
-                // FULL: nothing safe to prepare.  A step at a midpoint whose predecessor is at one too; the step behind such a step.
-                bool full = in && (gw.mode >= 2 || !valid || !valid_prev || adk >= 32760.0 || (tie1 && (tie || tie2 || h == 0)));
-                bool pair = in && !full && tie;                      // at a midpoint, predecessor sure: two candidate codes, one threshold
-                const bool follow = in && !full && !tie && tie1;     // behind a PAIR step: two candidate increments, chosen by that step
-                int qA = (int)dk + 32768, qB = 0; T incA = (T)0, incB = (T)0, thr = (T)0;
-                if (pair) {
+                // Drift of `last` after m steps from an exact value: two roundings per step (product, sum), each uniform within half an
+                // ulp of a value no larger than mag -- a random walk with sigma <= 0.25 mag eps per step, in practice less (values
+                // are rarely at the window's maximum).  A window that leaves the band is caught by (V) and rerun with a wider one, so
+                // the band is set for speed: LAT_BAND = 0.35 (the 512^3 field: no rerun at 0.35, one in 409 windows at 0.25).
+                // Plus the formula's own roundings (difference, quotient, +1 and the reciprocal: at most four half ulps of the
+                // quotient 2|dk|, i.e. 2 eps |dk| lattice units) and the error of this double-precision estimate.  (G2) measures the
+                // drift up to the window's entry: m = h + 1.
+                const double bscale = (gw.mode == 0 ? (double)band_scale : 16.0 * (double)band_scale) * (mag * LatEps<T>::eps) * inv2p;
+                const double bfix = (adk + 2.0) * (2.5 * LatEps<T>::eps) + (fabs(x) + 1.0) * 1e-15;
+                P.base = base; P.frac = x - kr; P.adk = adk; P.band = bscale * sqrt_h1 + bfix;
+                P.kprev0 = kprev0; P.in = in; P.valid = valid && valid_prev;
+                P.q0 = (int)dk + 32768; { const T dq = (T)(2 * (int)dk); P.inc0 = dq * prec; }
+                P.pairok = false; P.followok = false;
+                if (ptie && P.valid && adk < 32760.0) {
                     // the candidates: magnitudes n0 (A) and n0 + 1 (B) with one sign
                     long long dA = dk, dB = dk + (up ? 1 : -1);       // the lattice point on the other side of the midpoint
                     long long aA = dA < 0 ? -dA : dA, aB = dB < 0 ? -dB : dB;
                     if (aA > aB) { long long t = dA; dA = dB; dB = t; t = aA; aA = aB; aB = t; }
-                    if (aB >= 32760) { full = true; pair = false; }
-                    else {
-                        // exact threshold: the smallest float d with lat_mag(d) >= aB, looked for among the floats around (2 aB - 1) prec
-                        const T d0 = (T)((double)(2 * aB - 1) * (double)prec);
-                        bits_t b0; memcpy(&b0, &d0, sizeof(T));
-                        int first = 99;
+                    // exact threshold: the smallest float d with lat_mag(d) >= aB, looked for among the floats around (2 aB - 1) prec
+                    const T d0 = (T)((double)(2 * aB - 1) * (double)prec);
+                    bits_t b0; memcpy(&b0, &d0, sizeof(T));
+                    int first = 99;
 #pragma unroll
-                        for (int o = 4; o >= -4; o--) {
-                            const bits_t b = b0 + (bits_t)(long long)o; T d; memcpy(&d, &b, sizeof(T));
-                            if (lat_mag<T>(d, prec, rprec, use_div) >= (int)aB) first = o;
-                        }
-                        bool mono_ok = first != 99;
-                        {   // below the found float the magnitude must be smaller (monotone function: one more evaluation settles it)
-                            const bits_t b = b0 + (bits_t)(long long)(first - 1); T d; memcpy(&d, &b, sizeof(T));
-                            if (mono_ok && lat_mag<T>(d, prec, rprec, use_div) >= (int)aB) mono_ok = false;
-                        }
-                        if (!mono_ok || !(d0 > (T)0) || b0 < (bits_t)16) { full = true; pair = false; }
-                        else {
-                            const bits_t b = b0 + (bits_t)(long long)first; memcpy(&thr, &b, sizeof(T));
-                            qA = (int)dA + 32768; qB = (int)dB + 32768;
-                            const T dqA = (T)(2 * (int)dA), dqB = (T)(2 * (int)dB);
-                            incA = dqA * prec; incB = dqB * prec;
-                        }
+                    for (int o = 4; o >= -4; o--) {
+                        const bits_t b = b0 + (bits_t)(long long)o; T d; memcpy(&d, &b, sizeof(T));
+                        if (lat_mag<T>(d, prec, rprec, use_div) >= (int)aB) first = o;
+                    }
+                    bool ok = first != 99 && d0 > (T)0 && b0 >= (bits_t)16;
+                    {   // below the found float the magnitude must be smaller (monotone function: one more evaluation settles it)
+                        const bits_t b = b0 + (bits_t)(long long)(first - 1); T d; memcpy(&d, &b, sizeof(T));
+                        if (ok && lat_mag<T>(d, prec, rprec, use_div) >= (int)aB) ok = false;
+                    }
+                    if (ok) {
+                        const bits_t b = b0 + (bits_t)(long long)first; memcpy(&P.thr, &b, sizeof(T));
+                        P.qA = (int)dA + 32768; P.qB = (int)dB + 32768;
+                        const T dqA = (T)(2 * (int)dA), dqB = (T)(2 * (int)dB);
+                        P.incA = dqA * prec; P.incB = dqB * prec;
+                        P.pairok = true;
                     }
                 }
-                if (follow) {
-                    // the predecessor's candidates in ITS order (A = smaller magnitude of its own code): this step's increment for either
+                s_tie[h] = (unsigned char)((ptie ? 1 : 0) | (up ? 2 : 0) | (P.pairok ? 4 : 0));
+                lat_helper_bar();
+                if (h >= 1 && (s_tie[h - 1] & 1) && P.valid) {
+                    // behind a step that may be at a midpoint: that step's candidates in ITS order (A = smaller magnitude of its own
+                    // code), this step's code from either, and any threshold between the two magnitudes (they differ by 2 prec in
+                    // |cur - last|, the midpoint is a whole prec from both)
+                    const unsigned char tp = s_tie[h - 1];
                     const long long kpp = h >= 2 ? (long long)s_k[h - 2] : (long long)kprev0;
                     long long kA = kprev, kB = (long long)kprev + ((tp & 2) ? 1 : -1);
                     const long long pA = kA - kpp, pB = kB - kpp;
                     if ((pA < 0 ? -pA : pA) > (pB < 0 ? -pB : pB)) { const long long t = kA; kA = kB; kB = t; }
-                    const long long fA = (long long)k - kA, fB = (long long)k - kB;
-                    qA = (int)fA + 32768; qB = (int)fB + 32768;
-                    const T dqA = (T)(2 * (int)fA), dqB = (T)(2 * (int)fB);
-                    incA = dqA * prec; incB = dqB * prec;
+                    long long fA = (long long)k - kA, fB = (long long)k - kB;
+                    long long aA = fA < 0 ? -fA : fA, aB = fB < 0 ? -fB : fB;
+                    if (aA > aB) { long long t = fA; fA = fB; fB = t; t = aA; aA = aB; aB = t; }
+                    if (aB < 32760) {
+                        P.fqA = (int)fA + 32768; P.fqB = (int)fB + 32768;
+                        const T dqA = (T)(2 * (int)fA), dqB = (T)(2 * (int)fB);
+                        P.fincA = dqA * prec; P.fincB = dqB * prec;
+                        P.fthr = (T)((double)(2 * aB - 1) * (double)prec);
+                        P.followok = true;
+                    }
                 }
-                if (in && !pair && !full && !follow) { const T dq = (T)(2 * (int)dk); incA = dq * prec; }
-                // a midpoint step that could not be prepared as a PAIR is FULL, and then so is the step behind it
-                if (in && tie && !pair) s_tie[h] = (unsigned char)(s_tie[h] | 4);
-                lat_helper_bar();
-                if (follow && h && (s_tie[h - 1] & 4)) full = true;
-                if (full) { qA = 0; incA = (T)0; }
-                const bool handler = pair || full;
-                const unsigned int hm = __ballot_sync(0xffffffffu, handler), xm = __ballot_sync(0xffffffffu, full);
-                if (lane == 0) { L.hm[warp - 1] = hm; L.xm[warp - 1] = xm; }
-                L.inc[h] = in ? incA : (T)0; L.incB[h] = incB; L.thr[h] = thr; L.q[h] = qA; L.qB[h] = qB;
-                n_pair += __popc(hm & ~xm); n_full += __popc(xm);
             }
+            cyc_h += clock64() - c0;
         }
         const int fail = __syncthreads_or(my_fail ? 1 : 0);
         const unsigned int par = n_ticks & 1u;
@@ -386,9 +455,10 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
         if (e == (int)gridDim.x - 1) {
             out->passes = n_ticks; out->slow_chunks = n_redo; out->kcyc_serial = (unsigned int)(cyc_s >> 10);
             out->kcyc_total = (unsigned int)((clock64() - cyc_0) >> 10);
+            for (int i = 0; i < 8; i++) out->prof[i] = prof[i];
         }
     }
-    if (e == (int)gridDim.x - 1 && warp >= 1 && lane == 0) { atomicAdd(&out->kcyc_helper, n_pair); atomicAdd(&out->n_full, n_full); }
+    if (e == (int)gridDim.x - 1 && warp >= 1 && lane == 0) { atomicAdd(&out->n_pair, n_pair); atomicAdd(&out->n_full, n_full); if (warp == 1) out->kcyc_helper = (unsigned int)(cyc_h >> 10); }
 }
 
 }  // namespace szb

@@ -715,21 +715,16 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     if (mark(ST_FIT)) return SZ_NSCS;
 
     // ---- coefficient chain ----
-    ChainOut *d_chain = (ChainOut *)c.get("chain_out", 64); if (!d_chain) return SZ_NSCS;
-    CU(cudaMemsetAsync(d_chain, 0, 64, c.stream));
+    ChainOut *d_chain = (ChainOut *)c.get("chain_out", 128); if (!d_chain) return SZ_NSCS;
+    CU(cudaMemsetAsync(d_chain, 0, 128, c.stream));
     if (reg_count > 0) {
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, ncoef, d_reg, d_regc, d_list); KCHECK();
         const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
-        static const int chain_form = [] { const char *e = getenv("SZB200_CHAIN"); return e && !strcmp(e, "tables") ? 1 : e && !strcmp(e, "exact") ? 2 : 0; }();
-        if (chain_form != 1) {
-            // one CTA per coefficient: lattice guess, add chain, exact proof (szb_chain.cuh); "exact" runs every step with the complete formula
-            coeff_lattice_kernel<T><<<ncoef, LAT_THREADS, 0, c.stream>>>(d_regc, d_list, nb, reg_count, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain, chain_form == 2 ? 2 : 0, getenv("SZB200_LAT_BAND") ? (float)atof(getenv("SZB200_LAT_BAND")) : LAT_BAND); KCHECK();
-        } else {
-            ChainStep<T> *d_steps = (ChainStep<T> *)c.get("chain_steps", sizeof(ChainStep<T>) * (size_t)ncoef * reg_count + 256); if (!d_steps) return SZ_NSCS;
-            chain_prep_kernel<T><<<dim3((reg_count + 255) / 256, ncoef), 256, 0, c.stream>>>(d_regc, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_steps); KCHECK();
-            CU(cudaFuncSetAttribute(coeff_chain_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ChainCfg<T>::SMEM));
-            coeff_chain_kernel<T><<<1, CHAIN_THREADS, ChainCfg<T>::SMEM, c.stream>>>(d_steps, d_list, nb, reg_count, ncoef, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain); KCHECK();
-        }
+        // one CTA per coefficient: lattice guess, add chain, exact proof (szb_chain.cuh); SZB200_CHAIN=exact runs every step with the
+        // reference's complete formula (the form a failed window falls back to), for tests and timing
+        static const int chain_mode = [] { const char *e = getenv("SZB200_CHAIN"); return e && !strcmp(e, "exact") ? 2 : 0; }();
+        static const float chain_band = [] { const char *e = getenv("SZB200_LAT_BAND"); return e ? (float)atof(e) : LAT_BAND; }();
+        coeff_lattice_kernel<T><<<ncoef, LAT_THREADS, 0, c.stream>>>(d_regc, d_list, nb, reg_count, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain, chain_mode, chain_band); KCHECK();
     }
     if (mark(ST_CHAIN)) return SZ_NSCS;
 
@@ -813,7 +808,8 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     for (int i = 1; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
-    if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u (reruns: %u) kcycles: serial thread busy=%u, total=%u; last coefficient: pair steps=%u, full steps=%u\n", reg_count, h_chain.passes, h_chain.slow_chunks, h_chain.kcyc_serial, h_chain.kcyc_total, h_chain.kcyc_helper, h_chain.n_full);
+    if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u (reruns: %u) kcycles: serial thread busy=%u, helper busy=%u, total=%u; last coefficient: pair-form steps=%u, full steps=%u\n", reg_count, h_chain.passes, h_chain.slow_chunks, h_chain.kcyc_serial, h_chain.kcyc_helper, h_chain.kcyc_total, h_chain.n_pair, h_chain.n_full);
+    if (getenv("SZB200_TREE_PROFILE") && h_chain.prof[0] + h_chain.prof[2]) fprintf(stderr, "[chain-prof] serial thread {count, cycles}: clean words %u %u, clean groups %u %u, pair groups %u %u, step-by-step groups %u %u\n", h_chain.prof[0], h_chain.prof[1], h_chain.prof[2], h_chain.prof[3], h_chain.prof[4], h_chain.prof[5], h_chain.prof[6], h_chain.prof[7]);
     if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
         fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
     if (h_chain.err) { set_err("coefficient chain: a step left its tabulated interval (internal error)"); return SZ_NSCS; }

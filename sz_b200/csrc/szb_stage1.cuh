@@ -500,10 +500,9 @@ __global__ void reg_gather_kernel(const unsigned char *__restrict__ indicator, c
 // =====================================================================================================================
 // K5: coefficient DPCM chain (S1; ref: sz_float.c:7126-7152 no-mean "/precision", :6792-6812 mean "*recip", 2D :6035-6055;
 // double always "*recip").  last[e] threads through every regression block in raster order: a nonlinear float
-// recurrence, so each coefficient is ONE serial lane; the ncoef lanes run side by side in one warp.  The whole warp
-// stages 256 steps at a time through shared memory so that global loads/stores are coalesced and off the chain.
+// recurrence.  The kernel is in szb_chain.cuh; here its result block and the reference's step.
 // =====================================================================================================================
-struct ChainOut { unsigned int unpred_count[4]; unsigned int err; unsigned int passes, kcyc_serial, kcyc_total, kcyc_helper, slow_chunks, n_full; };   // last four: profiling aid
+struct ChainOut { unsigned int unpred_count[4]; unsigned int err; unsigned int passes, kcyc_serial, kcyc_total, kcyc_helper, slow_chunks, n_full, n_pair, prof[8]; };   // from `passes` on: profiling aid
 
 // one step of the reference's coefficient quantiser as a function of `last` (exact formula, ref: sz_float.c:7130-7150)
 template <typename T>
@@ -524,374 +523,6 @@ __device__ __forceinline__ int chain_step_exact(T cur, T last, T prec, T rprec, 
     }
     nl = cur;
     return 0;
-}
-
-// The chain is serial in `last`, but `last` entering step r is confined to a tiny interval around the previous
-// coefficient (the previous step verified |c[r-1] - last| <= prec, or reset last = c[r-1]).  Over that interval the
-// quantisation index is a monotone step function of `last` with at most a few pieces.  chain_prep_kernel finds, in
-// parallel and with the EXACT float formula, the interval, the (<= 3) pieces, their breakpoints and their increments;
-// the serial kernel then only compares, selects and adds.  Anything outside the prepared interval / piece budget takes
-// the exact formula in the serial kernel, so the result is bit-identical by construction.
-template <typename T> struct __align__(16) ChainStep {
-    T thr1, thr2;        // piece 0: last <= thr1; piece 1: thr1 < last <= thr2; piece 2: last > thr2 (a threshold that is not needed
-                         // lies beyond the interval `last` can be in)
-    T d0, d1, d2;        // increment fl(fl(2k) * prec) of each piece; +inf for a piece beyond the code capacity, which makes
-                         // the serial kernel's verification fail and the coefficient itself the new `last`, as the reference does
-    T cur;               // the coefficient being quantised
-    uint32_t np;         // number of pieces (0 = not tabulated: the serial kernel uses the exact formula for this step)
-    uint32_t pad_[3];    // 64 bytes
-    __device__ __forceinline__ void set_thresholds(T t1, T t2, T, T) { thr1 = t1; thr2 = t2; }
-    __device__ __forceinline__ bool has_thresholds() const { return np != 0u; }
-    __device__ __forceinline__ bool integer_form() const { return np != 0u; }
-    __device__ __forceinline__ T get_thr1() const { return thr1; }
-    __device__ __forceinline__ T get_thr2() const { return thr2; }
-};
-// float: the thresholds are kept in the form the serial warp compares with, integers.  When every value `last` can take at this step
-// and both thresholds have the same sign (and are not zero), "last > thr" is a comparison of the bit patterns as integers -- reversed
-// for negative numbers -- i.e. the sign of  bits(last) * a + b  with (a, b) = (-1, bits(thr)) or (+1, -bits(thr)): one integer
-// multiply-add and a shift give an all-ones / all-zeros mask, where a floating-point compare gives a predicate the select has to wait
-// for.  a = 0: no such form for this step (its interval straddles zero; b1, b2 then hold the thresholds' own bit patterns): the serial
-// warp does the group of steps it belongs to with floating-point compares.
-template <> struct __align__(16) ChainStep<float> {
-    int32_t a, b1, b2;
-    float d0, d1, d2, cur;
-    uint32_t np;
-    __device__ __forceinline__ void set_thresholds(float t1, float t2, float lo, float hi) {
-        const bool pos = lo > 0.0f && t1 > 0.0f && t2 > 0.0f, neg = hi < 0.0f && t1 < 0.0f && t2 < 0.0f;
-        const int32_t i1 = __float_as_int(t1), i2 = __float_as_int(t2);
-        a = pos ? -1 : (neg ? 1 : 0);
-        b1 = neg ? -i1 : i1;
-        b2 = neg ? -i2 : i2;
-    }
-    __device__ __forceinline__ bool has_thresholds() const { return np != 0u; }
-    __device__ __forceinline__ bool integer_form() const { return np != 0u && a != 0; }
-    __device__ __forceinline__ float get_thr1() const { return __int_as_float(a > 0 ? -b1 : b1); }
-    __device__ __forceinline__ float get_thr2() const { return __int_as_float(a > 0 ? -b2 : b2); }
-};
-
-template <typename T> struct Ord;
-template <> struct Ord<float> {
-    typedef uint32_t U;
-    static __device__ __forceinline__ U to(float x) { uint32_t b = __float_as_uint(x); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
-    static __device__ __forceinline__ float from(U o) { uint32_t b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o; return __uint_as_float(b); }
-};
-template <> struct Ord<double> {
-    typedef unsigned long long U;
-    static __device__ __forceinline__ U to(double x) { unsigned long long b = (unsigned long long)__double_as_longlong(x); return (b >> 63) ? ~b : (b | 0x8000000000000000ULL); }
-    static __device__ __forceinline__ double from(U o) { unsigned long long b = (o >> 63) ? (o & 0x7fffffffffffffffULL) : ~o; return __longlong_as_double((long long)b); }
-};
-
-// piece id at `last` = x: the quantisation index k, or +-(1<<20) beyond the capacity (keeps the function monotone)
-template <typename T>
-__device__ __forceinline__ int chain_piece(T cur, T x, T prec, T rprec, int use_div) {
-    T diff = cur - x;
-    T itv = use_div ? TT<T>::abs(diff) / prec : TT<T>::abs(diff) * rprec;
-    itv = itv + (T)1;
-    if (!(itv < (T)65536)) return diff < (T)0 ? -(1 << 20) : (1 << 20);
-    if (diff < (T)0) itv = -itv;
-    return (int)(itv / (T)2);
-}
-
-template <typename T>
-__global__ void __launch_bounds__(256) chain_prep_kernel(const T *__restrict__ reg_c, uint32_t nb, uint32_t reg_count, int ncoef,
-                                                         T p0, T p1, T p2, T p3, int use_div, ChainStep<T> *__restrict__ steps /*[ncoef][reg_count]*/) {
-    typedef typename Ord<T>::U U;
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    const int e = blockIdx.y;
-    if (r >= reg_count || e >= ncoef) return;
-    const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
-    const T rprec = (T)1 / prec;
-    const T cur = reg_c[(size_t)e * nb + r];
-    ChainStep<T> st;
-    memset(&st, 0, sizeof(st));
-    st.cur = cur;
-    T lo, hi;
-    if (r == 0) { lo = (T)0; hi = (T)0; }
-    else {
-        const T prev = reg_c[(size_t)e * nb + r - 1];
-        const T w = prec + prec * (T)0.015625;           // |prev - last| <= prec (1 + 2^-23): 1/64 of slack is plenty
-        lo = prev - w; hi = prev + w;
-        lo = Ord<T>::from(Ord<T>::to(lo) - 2); hi = Ord<T>::from(Ord<T>::to(hi) + 2);
-    }
-    const U olo = Ord<T>::to(lo), ohi = Ord<T>::to(hi);
-    bool finite = (lo == lo) && (hi == hi) && TT<T>::abs(lo) < (T)1e30 && TT<T>::abs(hi) < (T)1e30 && TT<T>::abs(cur) < (T)1e30 && prec > (T)0;
-    if (finite) {
-        int pk[3]; U pend[3];
-        U a = olo;
-        int np = 0;
-        bool okp = true;
-        for (;;) {
-            const int k = chain_piece<T>(cur, Ord<T>::from(a), prec, rprec, use_div);
-            // largest ordinal b in [a, ohi] with piece(b) == k  (piece is monotone non-increasing in x)
-            U l = a, h = ohi;
-            while (l < h) {
-                const U m = l + (h - l + 1) / 2;
-                if (chain_piece<T>(cur, Ord<T>::from(m), prec, rprec, use_div) == k) l = m; else h = m - 1;
-            }
-            if (np == 3) { okp = false; break; }
-            pk[np] = k; pend[np] = l; np++;
-            if (l == ohi) break;
-            a = l + 1;
-        }
-        if (okp) {
-            auto delta_of = [&](int k) -> T { if (k == (1 << 20) || k == -(1 << 20)) return (T)INFINITY; T dq = (T)(2 * k); return dq * prec; };
-            st.np = (uint32_t)np;
-            st.d0 = delta_of(pk[0]);
-            const T big = hi;                               // thresholds beyond hi are never exceeded inside the interval
-            st.set_thresholds(np > 1 ? Ord<T>::from(pend[0]) : big, np > 2 ? Ord<T>::from(pend[1]) : big, lo, hi);
-            if (np > 1) st.d1 = delta_of(pk[1]);
-            if (np > 2) st.d2 = delta_of(pk[2]);
-        }
-    }
-    steps[(size_t)e * reg_count + r] = st;
-}
-
-// =====================================================================================================================
-// K5: coefficient DPCM chain (S1; ref: sz_float.c:7126-7152 no-mean "/precision", :6792-6812 mean "*recip", 2D :6035-6055;
-// double always "*recip").  last[e] threads through every regression block in raster order: one serial lane per
-// coefficient, the ncoef lanes side by side in one warp.
-//
-// The reference's step is: quantise (cur - last), add the de-quantised increment, and keep the result unless |cur - result| > prec
-// (its guard against rounding; then, and for a code beyond the capacity, last = cur and the coefficient is stored raw).  The guard
-// almost never fires, and it is the longer half of the dependent chain, so the serial warp runs a chunk WITHOUT it: which of the
-// (<= 3) prepared pieces, add its increment -- three additions side by side, two compares, two selects, a dependent chain of three
-// operations.  The helper warps then recompute every step of the chunk from the `last` values the serial warp stored, with the
-// exact formula: that gives the codes, and it proves the serial warp's sequence (each step's input is the stored value and its
-// output must equal the next stored value, bit for bit).  A chunk that fails the proof (the guard fired, a step had no table, a
-// `last` left its table's interval) is run again by the serial warp with the complete step, and the chunks after it are redone.
-// =====================================================================================================================
-// (x > thr) ? a : b without a predicate on the way: a compare that yields an all-ones / all-zeros word and a bitwise select.  On the
-// serial chain a predicate costs more than an ordinary result (it is produced late and the instruction it guards waits for it).
-__device__ __forceinline__ float pick_gt(float x, float thr, float a, float b) {
-    unsigned int m, r;
-    asm("set.gt.u32.f32 %0, %1, %2;" : "=r"(m) : "f"(x), "f"(thr));
-    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(r) : "r"(__float_as_uint(a)), "r"(__float_as_uint(b)), "r"(m));
-    return __uint_as_float(r);
-}
-__device__ __forceinline__ double pick_gt(double x, double thr, double a, double b) { return x > thr ? a : b; }
-
-// steps per chunk and the dynamic shared memory of the step-table ring (three chunks x four coefficients)
-template <typename T> struct ChainCfg { static constexpr int CH = sizeof(T) == 4 ? 64 : 32; static constexpr size_t SMEM = 3ull * 4 * (CH + 1) * sizeof(ChainStep<T>); };
-constexpr int CHAIN_THREADS = 192;
-template <typename T>
-__global__ void __launch_bounds__(CHAIN_THREADS) coeff_chain_kernel(const ChainStep<T> *__restrict__ steps, const uint32_t *__restrict__ reg_list, uint32_t nb,
-                                                          uint32_t reg_count, int ncoef, T p0, T p1, T p2, T p3, int use_div,
-                                                          uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/,
-                                                          T *__restrict__ coeff_unpred /*[ncoef][nb]*/, ChainOut *out) {
-    // A three-stage software pipeline over chunks of CH steps, one __syncthreads per chunk:
-    //   warp 0, lanes 0..ncoef-1 : (A) the serial part proper of chunk c -- only the sequence of `last` values;
-    //   warps 1, 2, 3, 5 (one per coefficient; warp 4 would share warp 0's scheduler and only idles) : the fetch of the step
-    //                              tables of chunk c+1, then (B) proof, codes and ordered unpredictable list of chunk c-1.
-    // The serial warp therefore never waits for anything but its own arithmetic.
-    typedef typename TT<T>::bits_t bits_t;
-    constexpr int CH = ChainCfg<T>::CH;
-    constexpr int PER = CH / 32;
-    extern __shared__ __align__(16) unsigned char s_dyn[];   // the step tables: ChainCfg<T>::SMEM bytes, three chunks deep
-    typedef ChainStep<T> (*StepRing)[4][CH + 1];
-    StepRing s_step = reinterpret_cast<StepRing>(s_dyn);
-    __shared__ T s_last[2][4][CH + 1];                     // s_last[.][e][i] = value of last ENTERING step i (slot cnt: leaving the chunk)
-    __shared__ uint32_t s_blk[3][CH];
-    __shared__ unsigned int s_ucnt[4];
-    __shared__ int s_slow[3][4];                           // the chunk holds a step without a table (the fast pass cannot do it)
-    __shared__ unsigned int s_fpgroups[3][4];              // the chunk holds a step whose thresholds have no integer form: floating-point compares for this chunk
-    __shared__ unsigned int s_redo[2];                     // slot pass & 1 = the pass number in which (B) found that its chunk failed the proof
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (tid < 4) s_ucnt[tid] = 0;
-    if (tid < 2) s_redo[tid] = 0u;
-    // a helper warp fetches the step tables of its coefficient for one chunk: every lane whole steps; the loads are issued at the
-    // top of a pass and their values stored into the ring at its end, after stage (B), so nobody waits for global memory
-    ChainStep<T> ld_st[PER];
-    uint32_t ld_blk[PER];
-    auto load_issue = [&](uint32_t chunk, int e, int ln) {
-        const uint32_t r0 = chunk * CH;
-        if (r0 >= reg_count || e >= ncoef) return;
-        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-#pragma unroll
-        for (int q = 0; q < PER; q++) {
-            const int i = ln + 32 * q;
-            if (i < cnt) { ld_st[q] = steps[(size_t)e * reg_count + r0 + i]; ld_blk[q] = e == 0 ? reg_list[r0 + i] : 0u; }
-        }
-    };
-    auto load_store = [&](uint32_t chunk, int e, int ln) {
-        const uint32_t r0 = chunk * CH;
-        if (r0 >= reg_count || e >= ncoef) return;
-        const int buf = (int)(chunk % 3u);
-        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        bool slow = false, fp = false;
-#pragma unroll
-        for (int q = 0; q < PER; q++) {
-            const int i = ln + 32 * q;
-            if (i < cnt) { s_step[buf][e][i] = ld_st[q]; slow = slow || !ld_st[q].has_thresholds(); fp = fp || !ld_st[q].integer_form(); if (e == 0) s_blk[buf][i] = ld_blk[q]; }
-        }
-        slow = __any_sync(0xffffffffu, slow); fp = __any_sync(0xffffffffu, fp);
-        if (ln == 0) { s_slow[buf][e] = slow ? 1 : 0; s_fpgroups[buf][e] = fp ? 1u : 0u; }
-    };
-    T last = (T)0;                                          // carried by warp 0, lane e
-    const T precA = lane == 0 ? p0 : lane == 1 ? p1 : lane == 2 ? p2 : p3;
-    const T rprecA = (T)1 / precA;
-    const int eB = warp == 5 ? 3 : ((warp == 4 || warp == 0) ? 99 : warp - 1);     // helper warps 1,2,3,5 <-> coefficient 0..3; warps 0 and 4: none
-    if (eB < 4 && eB >= 0) { load_issue(0, eB, lane); load_store(0, eB, lane); }
-    const T precB = eB == 0 ? p0 : eB == 1 ? p1 : eB == 2 ? p2 : p3;
-    const T rprecB = (T)1 / precB;
-    const uint32_t nchunks = (reg_count + CH - 1) / CH;
-    uint32_t committed = 0;                                 // helper warps: chunks of their coefficient proven and written out
-    uint32_t complete = 0xffffffffu;                        // the chunk the serial warp runs with the complete step (none)
-    long long cyc_a = 0, cyc_h = 0; const long long cyc_0 = clock64(); uint32_t npass = 0, nslow = 0;
-    __syncthreads();
-    for (uint32_t it = 0, pass = 1; it <= nchunks; pass++) {
-        const long long cyc_1 = clock64(); npass++;
-        if (warp == 0) {
-            // ---- (A) chunk `it` ----
-            if (it < nchunks && lane < ncoef) {
-                const int e = lane, buf = (int)(it % 3u), lb = (int)(it & 1u);
-                const int cnt = (int)min((uint32_t)CH, reg_count - it * CH);
-                const ChainStep<T> *sp = &s_step[buf][e][0];
-                T *lp = &s_last[lb][e][0];
-                // a chunk with a step the fast pass cannot do is run with the complete step at once (cheaper than failing the proof)
-                const bool fast = it != complete && (s_slow[buf][0] | s_slow[buf][1] | s_slow[buf][2] | (ncoef > 3 ? s_slow[buf][3] : 0)) == 0;
-                const unsigned int fpgroups = s_fpgroups[buf][0] | s_fpgroups[buf][1] | s_fpgroups[buf][2] | (ncoef > 3 ? s_fpgroups[buf][3] : 0u);
-                if (!fast && lane == 0) nslow++;
-                if (fast) {
-                    // groups of four steps; the tables of the next group are fetched (explicit shared-memory loads, which the
-                    // compiler keeps where they are) before the current group is computed, so no step waits for its table
-                    struct Tab { T thr1, thr2, d0, d1, d2; int32_t a, b1, b2; };
-                    auto fetch = [&](Tab (&g)[4], int i0) {
-#pragma unroll
-                        for (int q = 0; q < 4; q++) {
-                            const unsigned ad = (unsigned)__cvta_generic_to_shared(sp + min(i0 + q, CH));      // slot CH is padding
-                            if (sizeof(T) == 4) {
-                                uint32_t w0, w1, w2, w3, w4, w5;
-                                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3) : "r"(ad));
-                                asm volatile("ld.shared.v2.u32 {%0,%1}, [%2+16];" : "=r"(w4), "=r"(w5) : "r"(ad));
-                                g[q].a = (int32_t)w0; g[q].b1 = (int32_t)w1; g[q].b2 = (int32_t)w2;
-                                g[q].d0 = (T)__uint_as_float(w3); g[q].d1 = (T)__uint_as_float(w4); g[q].d2 = (T)__uint_as_float(w5);
-                            } else {
-                                unsigned long long w0, w1, w2, w3, w4;
-                                asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(w0), "=l"(w1) : "r"(ad));
-                                asm volatile("ld.shared.v2.u64 {%0,%1}, [%2+16];" : "=l"(w2), "=l"(w3) : "r"(ad));
-                                asm volatile("ld.shared.u64 %0, [%1+32];" : "=l"(w4) : "r"(ad));
-                                g[q].thr1 = (T)__longlong_as_double((long long)w0); g[q].thr2 = (T)__longlong_as_double((long long)w1);
-                                g[q].d0 = (T)__longlong_as_double((long long)w2); g[q].d1 = (T)__longlong_as_double((long long)w3);
-                                g[q].d2 = (T)__longlong_as_double((long long)w4);
-                            }
-                        }
-                    };
-                    auto run = [&](const Tab (&g)[4], int i0, const bool whole, const bool fp) {
-#pragma unroll
-                        for (int q = 0; q < 4; q++) {
-                            if (whole || i0 + q < cnt) {
-                                lp[i0 + q] = last;
-                                if (sizeof(T) == 4 && fp) {
-                                    const float t1 = __int_as_float(g[q].a > 0 ? -g[q].b1 : g[q].b1), t2 = __int_as_float(g[q].a > 0 ? -g[q].b2 : g[q].b2);
-                                    const float lf = (float)last;
-                                    const float d = lf > t1 ? (float)g[q].d1 : (float)g[q].d0;
-                                    last = (T)(lf + (lf > t2 ? (float)g[q].d2 : d));
-                                } else if (sizeof(T) == 4) {
-                                    // all three sums side by side; which one: sign of bits(last) * a + b, as a mask (see ChainStep<float>).
-                                    // In assembly: written in C the compiler turns the masks back into predicates.
-                                    const float lf = (float)last;
-                                    float nl;
-                                    asm volatile("{\n\t.reg .s32 l, x1, x2, m1, m2;\n\t.reg .f32 v0, v1, v2;\n\t.reg .b32 u0, u1, u2, u;\n\t"
-                                                 "mov.b32 l, %1;\n\tmad.lo.s32 x1, l, %2, %3;\n\tmad.lo.s32 x2, l, %2, %4;\n\t"
-                                                 "shr.s32 m1, x1, 31;\n\tshr.s32 m2, x2, 31;\n\t"
-                                                 "add.rn.f32 v0, %1, %5;\n\tadd.rn.f32 v1, %1, %6;\n\tadd.rn.f32 v2, %1, %7;\n\t"
-                                                 "mov.b32 u0, v0;\n\tmov.b32 u1, v1;\n\tmov.b32 u2, v2;\n\t"
-                                                 "lop3.b32 u, u1, u0, m1, 0xE4;\n\tlop3.b32 u, u2, u, m2, 0xE4;\n\tmov.b32 %0, u;\n\t}"
-                                                 : "=f"(nl) : "f"(lf), "r"(g[q].a), "r"(g[q].b1), "r"(g[q].b2), "f"((float)g[q].d0), "f"((float)g[q].d1), "f"((float)g[q].d2));
-                                    last = (T)nl;
-                                } else {
-                                    const T d = pick_gt(last, g[q].thr1, g[q].d1, g[q].d0);
-                                    last = last + pick_gt(last, g[q].thr2, g[q].d2, d);
-                                }
-                            }
-                        }
-                    };
-                    Tab ga[4], gb[4];
-                    fetch(ga, 0);
-                    if (cnt == CH && fpgroups == 0u) {
-                        for (int i0 = 0; i0 < CH; i0 += 8) { fetch(gb, i0 + 4); run(ga, i0, true, false); fetch(ga, i0 + 8); run(gb, i0 + 4, true, false); }
-                    } else if (cnt == CH) {
-                        for (int i0 = 0; i0 < CH; i0 += 8) { fetch(gb, i0 + 4); run(ga, i0, true, true); fetch(ga, i0 + 8); run(gb, i0 + 4, true, true); }
-                    } else {
-                        for (int i0 = 0; i0 < cnt; i0 += 8) { fetch(gb, i0 + 4); run(ga, i0, false, true); fetch(ga, i0 + 8); run(gb, i0 + 4, false, true); }
-                    }
-                } else {
-                    for (int i = 0; i < cnt; i++) {
-                        const ChainStep<T> st = sp[i];
-                        lp[i] = last;
-                        T d = last > st.get_thr1() ? st.d1 : st.d0;
-                        d = last > st.get_thr2() ? st.d2 : d;
-                        const T v = last + d;
-                        const T k = st.cur - v;
-                        T nl = TT<T>::abs(k) > precA ? st.cur : v;
-                        // no table for this step, or `last` not within prec of the previous coefficient, where the table was made for
-                        // (which the step before guarantees; the first step of the chunk is not worth looking the neighbour up):
-                        // the reference's arithmetic itself
-                        if (i == 0 || !st.has_thresholds() || !(TT<T>::abs(sp[i - 1].cur - last) <= precA))
-                            (void)chain_step_exact<T>(st.cur, last, precA, rprecA, use_div, nl);
-                        last = nl;
-                    }
-                }
-                lp[cnt] = last;
-            }
-        } else {
-            // ---- fetch chunk it+1, then (B) chunk it-1 ----
-            if (it + 1 < nchunks && eB < 4) load_issue(it + 1, eB, lane);
-            if (it >= 1 && eB < ncoef && it - 1 == committed) {
-                const uint32_t cb = it - 1, r0 = cb * CH;
-                const int e = eB, buf = (int)(cb % 3u), lb = (int)(cb & 1u);
-                const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-                int ct[PER]; T cur[PER], lout[PER];
-                bool ok = true;
-#pragma unroll
-                for (int q = 0; q < PER; q++) {
-                    const int i = lane + 32 * q;
-                    ct[q] = 1; cur[q] = (T)0; lout[q] = (T)0;
-                    if (i < cnt) {
-                        cur[q] = s_step[buf][e][i].cur;
-                        const T lin = s_last[lb][e][i];
-                        lout[q] = s_last[lb][e][i + 1];
-                        T nl;
-                        ct[q] = chain_step_exact<T>(cur[q], lin, precB, rprecB, use_div, nl);
-                        bits_t bn, bo; memcpy(&bn, &nl, sizeof(T)); memcpy(&bo, &lout[q], sizeof(T));
-                        ok = ok && bn == bo;
-                    }
-                }
-                ok = __all_sync(0xffffffffu, ok);
-                if (!ok && cb == complete) { if (lane == 0) out->err = 1u; ok = true; }     // the complete step itself disagrees: never seen
-                if (!ok) { if (lane == 0) s_redo[pass & 1u] = pass; }
-                else {
-                    committed = cb + 1;
-#pragma unroll
-                    for (int q = 0; q < PER; q++) {
-                        const int i = lane + 32 * q;
-                        if (i < cnt) {
-                            coeff_type[(size_t)e * nb + r0 + i] = (uint16_t)ct[q];
-                            coeff_last[(size_t)e * nb + s_blk[buf][i]] = lout[q];
-                        }
-                        const unsigned int zmask = __ballot_sync(0xffffffffu, i < cnt && ct[q] == 0);
-                        const unsigned int base = s_ucnt[e];
-                        if (i < cnt && ct[q] == 0) coeff_unpred[(size_t)e * nb + base + __popc(zmask & ((1u << lane) - 1u))] = cur[q];
-                        __syncwarp();
-                        if (lane == 0) s_ucnt[e] = base + __popc(zmask);
-                        __syncwarp();
-                    }
-                }
-            }
-        }
-        if (warp != 0 && it + 1 < nchunks && eB < 4) load_store(it + 1, eB, lane);
-        if (warp == 0) cyc_a += clock64() - cyc_1; else cyc_h += clock64() - cyc_1;
-        __syncthreads();
-        if (s_redo[pass & 1u] == pass) {
-            // chunk it-1 again, with the complete step, from the value it was entered with (the chunks before it are proven)
-            it = it - 1;
-            complete = it;
-            if (warp == 0 && lane < ncoef) last = s_last[it & 1u][lane][0];
-        } else it++;
-    }
-    if (tid < 4) out->unpred_count[tid] = (tid < ncoef) ? s_ucnt[tid] : 0u;
-    if (tid == 0) { out->slow_chunks = nslow; out->passes = npass; out->kcyc_serial = (unsigned int)(cyc_a >> 10); out->kcyc_total = (unsigned int)((clock64() - cyc_0) >> 10); }
-    if (tid == 5 * 32) out->kcyc_helper = (unsigned int)(cyc_h >> 10);
 }
 
 }  // namespace szb
