@@ -1,0 +1,48 @@
+"""Worker of tests/test_gpu_parity.py::test_coefficient_chain_forms_give_the_reference_stream (run in a fresh process because the
+library reads SZB200_CHAIN / SZB200_LAT_BAND once): compress fields with many regression blocks through the C-ABI and compare every
+stream byte for byte with the CPU oracle (the checker).  Prints one line per field and "chain forms check: ok" / "FAILED"."""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(HERE))
+
+
+def noisy_quadratic(shape, dtype, seed=3):
+    rng = np.random.default_rng(seed)
+    g = np.meshgrid(*[np.linspace(-1, 1, n) for n in shape], indexing="ij")
+    f = sum((i + 1) * x for i, x in enumerate(g)) + 0.7 * sum(x * x for x in g) + np.sin(3 * g[0]) * np.cos(2 * g[-1])
+    f = f + rng.normal(0, 4e-3 * (f.max() - f.min()), size=shape)
+    return np.ascontiguousarray(f.astype(dtype))
+
+
+def main():
+    import szref
+    import sz_b200
+    cfg = dict(errorBoundMode="REL", relBoundRatio=1e-3)
+    sz_b200.init(cfg)
+    orc = szref.Oracle()
+    orc.init(cfg)
+    fields = [("noisy quadratic f32 3D", noisy_quadratic((120, 96, 102), np.float32)),      # every block a regression block, ~1500 distinct codes
+              ("noisy quadratic f64 2D", noisy_quadratic((640, 700), np.float64)),
+              ("blocky f32", szref.blocky_field(120, np.float32)),           # coefficient codes spread over the whole range, unpredictable ones among them
+              ("blocky f64", szref.blocky_field(60, np.float64)),
+              ("plane f32", szref.plane_field((66, 70, 74), np.float32))]
+    bad = 0
+    for name, a in fields:
+        got = sz_b200.compress(a, sz_b200.REL, 1e-4, 1e-3)
+        want = orc.compress(a, szref.REL, 1e-4, 1e-3)
+        ok = bytes(got) == want
+        st = sz_b200.last_stats()
+        print("%s: %d bytes, regression blocks %d of %d, %s" % (name, len(want), st.reg_count, st.num_blocks, "equal" if ok else "DIFFERENT"), flush=True)
+        bad += 0 if ok else 1
+    sz_b200.finalize()
+    print("chain forms check: %s" % ("ok" if bad == 0 else "FAILED"), flush=True)
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -4,6 +4,7 @@ golden digests are only the checkers.  Bar: bit-exact streams and bit-exact reco
 import hashlib
 import json
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -498,6 +499,28 @@ def test_reference_thread_safe_example_runs_unmodified_on_the_library(sz, tmp_pa
     rel = [float(x) for x in re.findall(r"Max relative error = ([0-9.eE+-]+)", r.stdout)]
     assert len(rel) == 5 and max(rel) <= 5e-4 * 1.0001 and min(rel) > 0, r.stdout[-2000:]
     assert re.search(r"max_error=", r.stdout)
+
+
+@pytest.mark.parametrize("form", ["default", "exact", "narrow_band"])
+def test_coefficient_chain_forms_give_the_reference_stream(form):
+    """The coefficient chain (szb_chain.cuh) guesses codes and proves them; its fall-backs must give the same bytes: the default band,
+    every step with the reference's complete formula (SZB200_CHAIN=exact), and a band so narrow that the guesses near midpoints are
+    wrong and windows are rerun (SZB200_LAT_BAND=0.0005: the proof and both rerun levels run).  Fresh process per form: the
+    library reads the variables once."""
+    import re
+    import subprocess
+    env = dict(os.environ, SZB200_TREE_PROFILE="1")
+    if form == "exact":
+        env["SZB200_CHAIN"] = "exact"
+    if form == "narrow_band":
+        env["SZB200_LAT_BAND"] = "0.0005"
+    r = subprocess.run([sys.executable, os.path.join(os.path.dirname(os.path.abspath(__file__)), "chain_modes_check.py")],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "chain forms check: ok" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    reruns = [int(x) for x in re.findall(r"reruns: (\d+)", r.stderr)]
+    assert reruns, r.stderr[-2000:]
+    if form == "narrow_band":
+        assert max(reruns) > 0, "the narrow band was meant to make some window fail its proof: " + r.stderr[-2000:]
 
 
 @pytest.mark.parametrize("kind", ["bell_1024", "two_symbols", "one_symbol", "wide_65536", "skewed_64"])
