@@ -183,6 +183,8 @@ __device__ __forceinline__ void lat_ld32(const double *p, double (&v)[32]) {
     for (int g = 0; g < 4; g++) lat_ld8(p + 8 * g, &v[8 * g]);
 }
 
+struct LatHist { uint32_t *h[4]; };          // per coefficient: the histogram of its codes (65536 bins, zeroed), counted by the proof stage
+
 template <typename T> struct LatWin { uint32_t p; int cnt, slot, mode; T entry; bool valid, fresh; };
 // what (G1) leaves in the registers of helper h for (G2), one tick later
 template <typename T> struct LatPrep {
@@ -196,7 +198,7 @@ template <typename T>
 __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__restrict__ reg_c /*[ncoef][nb], compacted*/, const uint32_t *__restrict__ reg_list,
                                                                     uint32_t nb, uint32_t reg_count, T p0, T p1, T p2, T p3, int use_div,
                                                                     uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/,
-                                                                    T *__restrict__ coeff_unpred /*[ncoef][nb]*/, ChainOut *out, int first_mode, float band_scale) {
+                                                                    T *__restrict__ coeff_unpred /*[ncoef][nb]*/, LatHist hists, ChainOut *out, int first_mode, float band_scale) {
     typedef typename TT<T>::bits_t bits_t;
     constexpr int W = LAT_W;
     __shared__ LatSlot<T> s_slot[2];
@@ -210,6 +212,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
     const T rprec = (T)1 / prec;
     const double inv2p = 1.0 / (2.0 * (double)prec);
     const T *cur_e = reg_c + (size_t)e * nb;
+    uint32_t *hist_e = hists.h[e];
     T t_inf; { const bits_t b = sizeof(T) == 4 ? (bits_t)0x7f800000u : (bits_t)0x7ff0000000000000ull; memcpy(&t_inf, &b, sizeof(T)); }
     const double sqrt_h1 = (double)sqrtf((float)(h > 0 ? h + 1 : 1)) * 1.000001;
     uint32_t ucount = 0;
@@ -248,6 +251,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
             __syncthreads();
         }
         bool my_fail = false;
+        int v_ct = -1;                                     // helpers: the code of the step proved in this tick (counted once the window has passed)
         if (warp == 0) {
             // ================================================ (S) ================================================
             if (lane == 0 && sw.valid) {
@@ -289,6 +293,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                     bits_t bn, bo; memcpy(&bn, &nl, sizeof(T)); memcpy(&bo, &lout, sizeof(T));
                     const bool pairform = (L.hm[h >> 5] >> (h & 31)) & 1u, big = pairform && ((L.bigm[h >> 3] >> (h & 7)) & 1u);
                     my_fail = ct != (big ? L.qB[h] : L.q[h]) || bn != bo;
+                    v_ct = ct;
                 }
                 zmask = __ballot_sync(0xffffffffu, h < vw.cnt && ct == 0);
                 if (lane == 0) s_wcnt[n_ticks & 1u][warp - 1] = __popc(zmask);
@@ -424,6 +429,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                 vw.valid = false; sw.valid = false; n_redo++;
                 continue;
             }
+            if (v_ct >= 0) atomicAdd(hist_e + v_ct, 1u);   // the window has passed: its codes are final
             unsigned int tot = 0;
 #pragma unroll
             for (int w = 0; w < W / 32; w++) tot += s_wcnt[par][w];

@@ -97,7 +97,7 @@ static __device__ __forceinline__ void hp_insert_warp(const unsigned base, const
 //   16 bits: the node word of a heap entry is {id:16 | nodes in its subtree:16}, so a merge knows its subtree size without a lookup).
 constexpr uint32_t HP_ROOT = 0xffffffffu;
 static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t leaves, const uint32_t *__restrict__ lfreq, uint32_t *up,
-                                                 uint32_t *prof_out, const long long tk1) {
+                                                 uint32_t *loga, uint32_t *logb, uint32_t *prof_out, const long long tk1) {
     int lane = threadIdx.x & 31;
     asm volatile("mov.u32 %0, %0;" : "+r"(lane));
     asm volatile("mov.u32 %0, %0;" : "+r"(base));
@@ -144,6 +144,7 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
     const bool piped = m >= HP_TAIL;
     uint2 pend = make_uint2(0u, 0u);                              // the merged node whose insertion is still to be done when the loop ends
     uint32_t nid1 = leaves + 0x10000u, ra = 0u, rb = 0u;        // next node id (+ the 1 of its subtree size); lane's pending records
+    uint32_t nlog = 0u;                                           // merges logged (the last HP_TAIL ones write their `up` records directly)
     if (piped) {
         // first removal of the first merge: takes the root `a`, the last element sinks from the root
         uint2 a = hp_ld2(base + 8u);
@@ -172,12 +173,11 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
             const uint32_t kn = a.x + b.x;
             const uint32_t nn = (a.y & 0xffff0000u) + (b.y & 0xffff0000u) + nid1;      // {id, nodes of both subtrees + 1}
             nid1++;
-            // the two `up` records of this merge are kept by lane k mod 32 and written 32 merges at a time
+            // the children of this merge are kept by lane k mod 32 and logged 32 merges at a time, two coalesced stores (scattered
+            // `up` records from here cost the lone warp several hundred cycles per group when other kernels load the memory system);
+            // hp_apply_log turns the log into `up` records afterwards, with all threads
             if (lane == (int)(k & 31u)) { ra = a.y; rb = b.y; }
-            if ((k & 31u) == 31u) {
-                const uint32_t nid = leaves + k - 31u + (uint32_t)lane;
-                up[rb & 0xffffu] = nid | 0x10000u; up[ra & 0xffffu] = nid | ((rb & 0xffff0000u) + 0x10000u);
-            }
+            if ((k & 31u) == 31u) { loga[k - 31u + (uint32_t)lane] = ra; logb[k - 31u + (uint32_t)lane] = rb; }
             if (m - 1u < HP_TAIL) { pend = make_uint2(kn, nn); break; }
             // its insertion at slot x (Huffman.c:76-85), once the ancestor chain of x is nobody's, in one round trip with the launch and
             // first level of the next merge's first removal, which takes what the insertion would leave in slot x out of it again:
@@ -209,10 +209,8 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
             hp_tick_finish<false>(base, capa, S, v); ticks++;
         }
         m--; k++;                                                 // the merge whose node is still in `pend`
-        if ((k & 31u) != 0u && (uint32_t)lane < (k & 31u)) {      // the records of the last, incomplete group of merges
-            const uint32_t nid = leaves + (k & ~31u) + (uint32_t)lane;
-            up[rb & 0xffffu] = nid | 0x10000u; up[ra & 0xffffu] = nid | ((rb & 0xffff0000u) + 0x10000u);
-        }
+        if ((k & 31u) != 0u && (uint32_t)lane < (k & 31u)) { loga[(k & ~31u) + (uint32_t)lane] = ra; logb[(k & ~31u) + (uint32_t)lane] = rb; }   // the last, incomplete group
+        nlog = k;
     }
     while (__any_sync(0xffffffffu, S.ek != 0u)) hp_tick<false>(base, capa, S);
     // ---- the last few merges, one operation after the other (lane 0) ----
@@ -255,7 +253,13 @@ static __device__ __noinline__ uint32_t hp_build(unsigned base, const uint32_t l
 #ifdef HP_COUNT
     if (lane == 0) { prof_out[8] = ticks; prof_out[9] = n_wait_e; prof_out[10] = n_wait_c; }
 #endif
-    return rootn;
+    return rootn | (nlog << 16);                                  // both below 65536 (fewer than 32768 leaves)
+}
+
+// merge k of the log made node leaves + k out of a (left; second removed) and b (right): the children's {parent, pre-order step} records
+__device__ __forceinline__ void hp_apply_log(uint32_t *up, const uint32_t *loga, const uint32_t *logb, uint32_t leaves, uint32_t k) {
+    const uint32_t ra = loga[k], rb = logb[k], nid = leaves + k;
+    up[rb & 0xffffu] = nid | 0x10000u; up[ra & 0xffffu] = nid | ((rb & 0xffff0000u) + 0x10000u);
 }
 
 }  // namespace szb

@@ -571,8 +571,8 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         if (piped) {
             // several heap operations in flight in one warp, {frequency, node} entries of 8 bytes (szb_heap_pipe.cuh)
             if (t < 32) {
-                const uint32_t root = hp_build((unsigned int)__cvta_generic_to_shared(s_heap), leaves, lfreq, D.n_left, D.out, tk1);
-                if (t == 0) s_root = root;
+                const uint32_t r = hp_build((unsigned int)__cvta_generic_to_shared(s_heap), leaves, lfreq, D.n_left, D.n_right, D.n_sizeL, D.out, tk1);
+                if (t == 0) { s_root = r & 0xffffu; s_cnt = r >> 16; }
             }
         } else if (compact || tight16) {
             // one CTA: f[fcap], n[leaves + 8] as 16-bit ids, the queue
@@ -653,8 +653,12 @@ __global__ void __launch_bounds__(HUFF_TB) huff_build_kernel(const HuffTreeDesc 
         //      shared memory (the heap's, free now): no level-by-level passes, no frontier ----
         uint32_t *ups = s_heap;
         uint32_t *pre_g = D.n_pre;                                  // pre-order index per node (the leaf frequencies kept there are done with)
-        for (uint32_t n = t; n < nodeCount; n += blockDim.x) ups[n] = D.n_left[n];
+        for (uint32_t n = t; n < nodeCount; n += blockDim.x) ups[n] = D.n_left[n];       // the records of the last few merges and the root
         if (t == 0) tb[0] = 0;
+        __syncthreads();
+        for (uint32_t k = t; k < s_cnt; k += blockDim.x) hp_apply_log(ups, D.n_right, D.n_sizeL, leaves, k);   // all the others, from the merge log
+        __syncthreads();
+        for (uint32_t n = t; n < nodeCount; n += blockDim.x) D.n_left[n] = ups[n];
         __syncthreads();
         for (uint32_t n = t; n < nodeCount; n += blockDim.x) {
             uint32_t e = ups[n], pre = 0, len = 0; uint64_t code = 0;
@@ -859,6 +863,82 @@ __global__ void __launch_bounds__(ENC_THREADS) enc_write_kernel(const uint16_t *
         }
     }
     if (fill > 0 && cur != 0) atomicOr(out_words + widx, bswap32(cur));
+}
+
+// The coefficient streams (linear symbol arrays, one per coefficient) in ONE launch: bit lengths, their prefix over the chunks by
+// decoupled look-back, and the bit scatter.  grid = (chunks, coefficients); chunks are taken by ticket so that every chunk a CTA
+// waits for is already running.  state[e][chunk]: bits 63..62 = 1 the chunk's own bit count is in the low bits, 2 the count of all
+// chunks up to and including it; zeroed before the launch.
+struct CoefEnc { const uint16_t *syms; const uint64_t *code; const uint8_t *clen; uint32_t *out_words; unsigned long long *total_bits; };
+struct CoefEncArgs { CoefEnc c[4]; uint64_t n; unsigned long long *state; unsigned int *ticket; uint32_t nchunks; };
+__global__ void __launch_bounds__(ENC_THREADS) coef_encode_kernel(CoefEncArgs A) {
+    const int e = blockIdx.y, t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    const CoefEnc C = A.c[e];
+    __shared__ unsigned int s_chunk;
+    __shared__ uint32_t wb[ENC_THREADS / 32];
+    __shared__ unsigned long long s_excl;
+    if (t == 0) s_chunk = atomicAdd(A.ticket + e, 1u);
+    __syncthreads();
+    const uint32_t chunk = s_chunk;
+    unsigned long long *state = A.state + (size_t)e * A.nchunks;
+    const uint64_t p0 = ((uint64_t)chunk * ENC_THREADS + t) * ENC_PER_THREAD;
+    uint32_t syms[ENC_PER_THREAD], lens[ENC_PER_THREAD];
+    const int cnt = p0 < A.n ? (int)min((uint64_t)ENC_PER_THREAD, A.n - p0) : 0;
+    uint32_t bits = 0;
+#pragma unroll
+    for (int q = 0; q < ENC_PER_THREAD; q++) syms[q] = q < cnt ? C.syms[p0 + q] : 0u;
+#pragma unroll
+    for (int q = 0; q < ENC_PER_THREAD; q++) { lens[q] = q < cnt ? (uint32_t)C.clen[syms[q]] : 0u; bits += lens[q]; }
+    uint32_t ib = bits;
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t a = __shfl_up_sync(0xffffffffu, ib, o); if (lane >= o) ib += a; }
+    if (lane == 31) wb[wid] = ib;
+    __syncthreads();
+    uint32_t pb = 0, tot = 0;
+    for (int i = 0; i < ENC_THREADS / 32; i++) { if (i < wid) pb += wb[i]; tot += wb[i]; }
+    if (wid == 0) {
+        const unsigned long long F_AGG = 1ull << 62, F_PRE = 2ull << 62, VMASK = (1ull << 62) - 1ull;
+        if (lane == 0) { __threadfence(); atomicExch(state + chunk, (chunk == 0 ? F_PRE : F_AGG) | (unsigned long long)tot); }
+        unsigned long long excl = 0;
+        long long look = (long long)chunk - 1;
+        while (look >= 0) {                                 // 32 predecessors at a time, nearest first
+            const long long idx = look - lane;
+            unsigned long long v = F_PRE;                   // before the first chunk: a prefix of zero
+            if (idx >= 0) { do { v = *(volatile unsigned long long *)(state + idx); } while ((v >> 62) == 0ull); }
+            const unsigned int pre = __ballot_sync(0xffffffffu, (v >> 62) == 2ull);
+            const int stop = pre ? __ffs(pre) - 1 : 32;     // the nearest chunk that already knows its prefix
+            unsigned long long part = lane <= stop ? (v & VMASK) : 0ull;
+            for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+            excl += part;
+            if (pre) break;
+            look -= 32;
+        }
+        if (lane == 0) {
+            if (chunk != 0) { __threadfence(); atomicExch(state + chunk, F_PRE | (excl + tot)); }
+            s_excl = excl;
+            if (chunk == A.nchunks - 1) C.total_bits[0] = excl + tot;
+        }
+    }
+    __syncthreads();
+    if (cnt == 0) return;
+    const uint64_t pos = s_excl + pb + (ib - bits);
+    uint64_t widx = pos >> 5;
+    uint32_t fill = (uint32_t)(pos & 31), cur = 0;
+    uint64_t cd[ENC_PER_THREAD];
+#pragma unroll
+    for (int q = 0; q < ENC_PER_THREAD; q++) cd[q] = q < cnt ? C.code[syms[q]] : 0ull;
+#pragma unroll
+    for (int q = 0; q < ENC_PER_THREAD; q++) {
+        uint32_t len = lens[q];
+        const uint64_t cb = cd[q];
+        while (len > 0) {
+            const uint32_t take = min(32u - fill, len);
+            const uint32_t piece = (uint32_t)((cb >> (len - take)) & ((take == 32) ? 0xffffffffULL : ((1ULL << take) - 1ULL)));
+            cur |= piece << (32 - fill - take);
+            fill += take; len -= take;
+            if (fill == 32) { atomicOr(C.out_words + widx, bswap32(cur)); widx++; cur = 0; fill = 0; }
+        }
+    }
+    if (fill > 0 && cur != 0) atomicOr(C.out_words + widx, bswap32(cur));
 }
 
 // =====================================================================================================================

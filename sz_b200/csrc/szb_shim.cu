@@ -47,7 +47,7 @@ static void set_err(const char *fmt, ...) {
 enum Stage { ST_OPT = 0, ST_MEAN, ST_FIT, ST_CHAIN, ST_WAVE, ST_HIST, ST_TREE, ST_ENC, ST_EMIT, ST_PARSE, ST_DECODE, ST_DCHAIN, ST_RECON, ST_JOIN, ST_COUNT };
 static const char *k_stage_names[16] = {"opt_intervals", "use_mean_mean", "fit_select", "coeff_chain", "wavefront_quant", "histogram", "huffman_tree",
                                         "encode", "emit", "d_parse", "d_huffman_decode", "d_coeff_chain", "d_wavefront_recon", "wait_coeff_trees_side_stream",
-                                        "coeff_trees_kernel_side_stream", ""};   // [14]: duration of the coefficient huff_build_kernel itself (overlaps the main stream's stages; not part of their sum)
+                                        "coeff_trees_kernel_side_stream", "coeff_hist_and_encode_side_stream"};   // [14], [15]: the coefficient huff_build_kernel itself, and the histograms before / the encode launch behind it (they overlap the main stream's stages and are not part of their sum)
 extern "C" const char *szb200_stage_name(int i) { return (i >= 0 && i < 16) ? k_stage_names[i] : ""; }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -58,6 +58,7 @@ struct Ctx {
     cudaStream_t stream = nullptr, stream2 = nullptr;   // stream2: side branch (coefficient histograms / trees / bit lengths)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_tree0 = nullptr, ev_tree1 = nullptr;  // around the coefficient-tree kernel on the side stream
+    cudaEvent_t ev_side0 = nullptr, ev_side1 = nullptr;  // first and last thing on the side stream
     std::map<std::string, Buf> bufs;
     uint32_t wf_epoch = 0;                               // tag of the most recent wavefront launch (see szb_wavefront.cuh)
     void *pinned = nullptr; size_t pinned_cap = 0;
@@ -83,7 +84,7 @@ struct Ctx {
         { int lo_p = 0, hi_p = 0; CU(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p)); CU(cudaStreamCreateWithPriority(&stream2, cudaStreamNonBlocking, hi_p)); }
         CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
         for (auto &e : ev) CU(cudaEventCreate(&e));
-        CU(cudaEventCreate(&ev_tree0)); CU(cudaEventCreate(&ev_tree1));
+        CU(cudaEventCreate(&ev_tree0)); CU(cudaEventCreate(&ev_tree1)); CU(cudaEventCreate(&ev_side0)); CU(cudaEventCreate(&ev_side1));
         ev_ok = true;
         cudaDeviceProp pr; CU(cudaGetDeviceProperties(&pr, d));
         sm_count = pr.multiProcessorCount; smem_optin = pr.sharedMemPerBlockOptin;
@@ -714,26 +715,28 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     const uint32_t reg_count = (uint32_t)reg_count_ll;
     if (mark(ST_FIT)) return SZ_NSCS;
 
-    // ---- coefficient chain ----
+    // ---- coefficient chain (its proof stage also counts the codes: the histograms of the four coefficient trees) ----
+    TreeWs tw[5];
+    const int ntrees = 1 + (reg_count > 0 ? ncoef : 0);
+    if (tree_ws(c, 0, intervals, tw[0])) return SZ_NSCS;
+    for (int e = 0; e < ntrees - 1; e++) if (tree_ws(c, 1 + e, 65536, tw[1 + e])) return SZ_NSCS;
     ChainOut *d_chain = (ChainOut *)c.get("chain_out", 128); if (!d_chain) return SZ_NSCS;
     CU(cudaMemsetAsync(d_chain, 0, 128, c.stream));
     if (reg_count > 0) {
+        LatHist hists; memset(&hists, 0, sizeof(hists));
+        for (int e = 0; e < ncoef; e++) { hists.h[e] = tw[1 + e].hist; CU(cudaMemsetAsync(tw[1 + e].hist, 0, 4ull * 65536, c.stream)); }
         reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, ncoef, d_reg, d_regc, d_list); KCHECK();
         const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
         // one CTA per coefficient: lattice guess, add chain, exact proof (szb_chain.cuh); SZB200_CHAIN=exact runs every step with the
         // reference's complete formula (the form a failed window falls back to), for tests and timing
         static const int chain_mode = [] { const char *e = getenv("SZB200_CHAIN"); return e && !strcmp(e, "exact") ? 2 : 0; }();
         static const float chain_band = [] { const char *e = getenv("SZB200_LAT_BAND"); return e ? (float)atof(e) : LAT_BAND; }();
-        coeff_lattice_kernel<T><<<ncoef, LAT_THREADS, 0, c.stream>>>(d_regc, d_list, nb, reg_count, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, d_chain, chain_mode, chain_band); KCHECK();
+        coeff_lattice_kernel<T><<<ncoef, LAT_THREADS, 0, c.stream>>>(d_regc, d_list, nb, reg_count, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, hists, d_chain, chain_mode, chain_band); KCHECK();
     }
     if (mark(ST_CHAIN)) return SZ_NSCS;
 
     // ---- side branch on stream2 (needs only the chain's output): coefficient histograms, their Huffman trees (exact heap
     //      emulation, the longest serial stage) and bit lengths run concurrently with the wavefront / main-tree / main-length work ----
-    TreeWs tw[5];
-    const int ntrees = 1 + (reg_count > 0 ? ncoef : 0);
-    if (tree_ws(c, 0, intervals, tw[0])) return SZ_NSCS;
-    for (int e = 0; e < ntrees - 1; e++) if (tree_ws(c, 1 + e, 65536, tw[1 + e])) return SZ_NSCS;
     HuffTreeDesc *d_desc = (HuffTreeDesc *)c.get("tree_desc", sizeof(HuffTreeDesc) * 8); if (!d_desc) return SZ_NSCS;
     const uint32_t heap_cap = (uint32_t)((c.smem_optin - 8192) / 8);
     const size_t heap_sm = 8ull * heap_cap;
@@ -746,6 +749,20 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     const int write_all = getenv("SZB200_DEBUG_RECON") ? 1 : 0;      // debug: keep the full reconstructed field (szb200_debug_fetch(4))
     T *d_recon = write_all ? (T *)c.get("recon", sizeof(T) * N + 64) : nullptr;
     if (!d_cb || !d_cz || !d_cbo || !d_czo || !d_codes || (write_all && !d_recon)) return SZ_NSCS;
+    // The coefficient streams: ONE launch behind the tree kernel on the side stream (coef_encode_kernel: lengths, look-back prefix,
+    // bit scatter).  A Huffman code averages less than entropy + 1 <= 17 bits per symbol: that bounds the buffers, zeroed here.
+    uint32_t *d_cbits[4] = {nullptr, nullptr, nullptr, nullptr};
+    unsigned long long *d_cstate = nullptr;
+    if (ntrees > 1) {
+        const size_t bound = (17ull * reg_count + 7) / 8 + 64;
+        for (int e = 0; e < ntrees - 1; e++) {
+            char name[32]; snprintf(name, sizeof(name), "enc_cbits%d", e);
+            d_cbits[e] = (uint32_t *)c.get(name, bound); if (!d_cbits[e]) return SZ_NSCS;
+            CU(cudaMemsetAsync(d_cbits[e], 0, bound, c.stream));
+        }
+        d_cstate = (unsigned long long *)c.get("enc_cstate", 8 * (4 * nchunk_c + 8)); if (!d_cstate) return SZ_NSCS;
+        CU(cudaMemsetAsync(d_cstate, 0, 8 * (4 * nchunk_c + 8), c.stream));
+    }
     {
         HuffTreeDesc hd[8];
         for (int i = 0; i < ntrees; i++) hd[i] = tw[i].d;
@@ -754,16 +771,17 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     if (ntrees > 1) {
         CU(cudaEventRecord(c.ev_fork, c.stream));
         CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
-        for (int e = 0; e < ntrees - 1; e++)
-            if (launch_hist(c, c.stream2, d_ctype + (size_t)e * nb, reg_count, 65536, tw[1 + e].hist)) return SZ_NSCS;
+        CU(cudaEventRecord(c.ev_side0, c.stream2));
         CU(cudaEventRecord(c.ev_tree0, c.stream2));
         CU(launch_huff_build(c.stream2, d_desc + 1, ntrees - 1, heap_sm, heap_cap, std::min<uint64_t>(65536u, reg_count))); KCHECK();
         CU(cudaEventRecord(c.ev_tree1, c.stream2));
-        for (int e = 0; e < ntrees - 1; e++) {
-            const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
-            enc_len_kernel<false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream2>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.clen, d_cb + o, d_cz + o); KCHECK();
-            if (launch_scan(c, c.stream2, 1, d_cb + o, nchunk_c, d_cbo + o, d_tot + 3 + e)) return SZ_NSCS;
+        {
+            CoefEncArgs A; memset(&A, 0, sizeof(A));
+            for (int e = 0; e < ntrees - 1; e++) { A.c[e].syms = d_ctype + (size_t)e * nb; A.c[e].code = tw[1 + e].d.code; A.c[e].clen = tw[1 + e].d.clen; A.c[e].out_words = d_cbits[e]; A.c[e].total_bits = d_tot + 3 + e; }
+            A.n = reg_count; A.nchunks = (uint32_t)nchunk_c; A.state = d_cstate; A.ticket = (unsigned int *)(d_cstate + 4 * nchunk_c);
+            coef_encode_kernel<<<dim3((unsigned)nchunk_c, ntrees - 1), ENC_THREADS, 0, c.stream2>>>(A); KCHECK();
         }
+        CU(cudaEventRecord(c.ev_side1, c.stream2));
         CU(cudaEventRecord(c.ev_join, c.stream2));
     }
 
@@ -816,15 +834,6 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err(h_tree[i][3] == 2 ? "Huffman tree build gave up (tree %d)" : "Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
     uint64_t cbytes[4] = {0, 0, 0, 0};
     for (int e = 0; e < ntrees - 1; e++) cbytes[e] = (h_tot[3 + e] + 7) / 8;
-    uint32_t *d_cbits[4] = {nullptr, nullptr, nullptr, nullptr};
-    for (int e = 0; e < ntrees - 1; e++) {
-        char name[32]; snprintf(name, sizeof(name), "enc_cbits%d", e);
-        d_cbits[e] = (uint32_t *)c.get(name, cbytes[e] + 64); if (!d_cbits[e]) return SZ_NSCS;
-        CU(cudaMemsetAsync(d_cbits[e], 0, cbytes[e] + 64, c.stream));
-        const uint64_t o = nchunk_main + (uint64_t)e * nchunk_c;
-        enc_write_kernel<T, false><<<(unsigned)nchunk_c, ENC_THREADS, 0, c.stream>>>(d_ctype + (size_t)e * nb, reg_count, g, tw[1 + e].d.code, tw[1 + e].d.clen, d_cbo + o, d_czo + o,
-                                                                                      d_cbits[e], (const T *)nullptr, (T *)nullptr); KCHECK();
-    }
     if (mark(ST_ENC)) return SZ_NSCS;
 
     // ---- stream body (SURVEY.md Appendix A from offset 4+MD; ref: sz_float.c:7392-7489) ----
@@ -857,7 +866,10 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     st.tree_bytes = h_tree[0][0]; st.node_count = h_tree[0][1]; st.type_bits_bytes = main_bytes; st.body_bytes = E.total; st.launches = c.launches;
     for (int i = 1; i < evi; i++) { float ms = 0; cudaEventElapsedTime(&ms, c.ev[i - 1], c.ev[i]); st.ms_stage[stage_of_ev[i]] += ms; }
     cudaEventElapsedTime(&st.ms_total, c.ev[0], c.ev[evi - 1]);
-    if (ntrees > 1) cudaEventElapsedTime(&st.ms_stage[14], c.ev_tree0, c.ev_tree1);
+    if (ntrees > 1) {
+        cudaEventElapsedTime(&st.ms_stage[14], c.ev_tree0, c.ev_tree1);
+        float a = 0, b = 0; cudaEventElapsedTime(&a, c.ev_side0, c.ev_tree0); cudaEventElapsedTime(&b, c.ev_tree1, c.ev_side1); st.ms_stage[15] = a + b;
+    }
     c.last = st; c.have_last = true;
     c.dbg_g = g; c.dbg_dtype = job.dtype; c.dbg_intervals = intervals; c.dbg_reg_count = reg_count;
     if (stats) *stats = st;

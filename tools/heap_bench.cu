@@ -14,14 +14,16 @@
 
 using namespace szb;
 
-__global__ void bench_kernel(const uint32_t *lfreq, uint32_t leaves, uint32_t *up, uint32_t *out, unsigned long long *cyc) {
+__global__ void bench_kernel(const uint32_t *lfreq, uint32_t leaves, uint32_t *up, uint32_t *loga, uint32_t *logb, uint32_t *out, unsigned long long *cyc) {
     extern __shared__ __align__(16) uint32_t s_heap[];
     if (threadIdx.x < 32) {
         const long long t0 = clock64();
-        const uint32_t root = hp_build((unsigned)__cvta_generic_to_shared(s_heap), leaves, lfreq, up, out, t0);
-        if (threadIdx.x == 0) { cyc[0] = (unsigned long long)(clock64() - t0); out[0] = root; }
+        const uint32_t r = hp_build((unsigned)__cvta_generic_to_shared(s_heap), leaves, lfreq, up, loga, logb, out, t0);
+        if (threadIdx.x == 0) { cyc[0] = (unsigned long long)(clock64() - t0); out[0] = r & 0xffffu; out[1] = r >> 16; }
     }
     __syncthreads();
+    __threadfence();
+    for (uint32_t k = threadIdx.x; k < out[1]; k += blockDim.x) hp_apply_log(up, loga, logb, leaves, k);   // the logged merges -> `up` records
 }
 
 struct Ent { uint32_t k, n; };
@@ -58,14 +60,14 @@ int main(int argc, char **argv) {
     // the records hp_build leaves: {parent:16 | 1 (left child) or 1 + nodes of the left sibling's subtree (right child) : 16}
     std::vector<uint32_t> size(2 * L, 1), up0(2 * L, 0xffffffffu);
     for (uint32_t n = L; n + 1 < 2 * L; n++) { size[n] = 1 + size[l0[n]] + size[r0[n]]; up0[l0[n]] = n | (1u << 16); up0[r0[n]] = n | ((1 + size[l0[n]]) << 16); }
-    uint32_t *d_f, *d_l, *d_out; unsigned long long *d_c;
-    cudaMalloc(&d_f, 4 * L); cudaMalloc(&d_l, 8 * L); cudaMalloc(&d_out, 64); cudaMalloc(&d_c, 64);
+    uint32_t *d_f, *d_l, *d_la, *d_lb, *d_out; unsigned long long *d_c;
+    cudaMalloc(&d_f, 4 * L); cudaMalloc(&d_l, 8 * L); cudaMalloc(&d_la, 4 * L); cudaMalloc(&d_lb, 4 * L); cudaMalloc(&d_out, 64); cudaMalloc(&d_c, 64);
     cudaMemcpy(d_f, f.data(), 4 * L, cudaMemcpyHostToDevice);
     const size_t smem = 8ull * (L + 4);
     cudaFuncSetAttribute(bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     for (int rep = 0; rep < 3; rep++) {
         cudaMemset(d_l, 0xee, 8 * L); cudaMemset(d_out, 0, 64);
-        bench_kernel<<<1, threads, smem>>>(d_f, L, d_l, d_out, d_c);
+        bench_kernel<<<1, threads, smem>>>(d_f, L, d_l, d_la, d_lb, d_out, d_c);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("CUDA error: %s\n", cudaGetErrorString(e)); return 1; }
         std::vector<uint32_t> up1(2 * L); uint32_t out[16]; unsigned long long c[8];
