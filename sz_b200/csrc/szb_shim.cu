@@ -62,6 +62,7 @@ struct Ctx {
     std::map<std::string, Buf> bufs;
     uint32_t wf_epoch = 0;                               // tag of the most recent wavefront launch (see szb_wavefront.cuh)
     void *pinned = nullptr; size_t pinned_cap = 0;
+    unsigned long long *pinned_words = nullptr;          // 32 words of pinned memory for small read-backs that must not block the host
     unsigned char *bounce = nullptr;                     // 2 x BOUNCE_CHUNK pinned bytes: staging of device-to-host copies into pageable memory
     cudaEvent_t ev_bounce[2] = {nullptr, nullptr};
     cudaEvent_t ev[24];
@@ -112,6 +113,7 @@ struct Ctx {
         for (auto &kv : bufs) if (kv.second.p) cudaFree(kv.second.p);
         bufs.clear();
         if (pinned) { cudaFreeHost(pinned); pinned = nullptr; pinned_cap = 0; }
+        if (pinned_words) { cudaFreeHost(pinned_words); pinned_words = nullptr; }
         if (bounce) { cudaFreeHost(bounce); bounce = nullptr; }
     }
 };
@@ -659,9 +661,48 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     T mean = (T)0;
     const uint32_t maxRangeRadius = job.max_quant_intervals / 2;
 
+    // ---- precisions (ref: sz_float.c:6639-6645, 2D :5608-5612) and noise (:6697 / :5674) ----
+    T prec[4] = {0, 0, 0, 0};
+    {
+        const T rel = (job.dim == 3) ? (T)0.025 : (T)(0.15 / 3);
+        const T t = rel * eb;
+        if (job.dim == 3) { prec[0] = t / (T)g.ax[0].late; prec[1] = t / (T)g.ax[1].late; prec[2] = t / (T)g.ax[2].late; prec[3] = t; }
+        else { prec[0] = t / (T)g.ax[1].late; prec[1] = t / (T)g.ax[2].late; prec[2] = t; }
+    }
+    const T noise = (job.dim == 3) ? (T)((double)eb * 1.22) : (T)((double)eb * 0.81);
+
+    // ---- fit + selection, started beside the interval optimiser (which goes to the side stream): it needs nothing of the optimiser but the answer
+    //      to "predict blocks from the mean too?", which is almost always no; when it is yes, the stage is run again below ----
+    T *d_reg = (T *)c.get("reg", sizeof(T) * 4ull * nb), *d_regc = (T *)c.get("reg_c", sizeof(T) * 4ull * nb), *d_clast = (T *)c.get("coeff_last", sizeof(T) * 4ull * nb),
+      *d_cunp = (T *)c.get("coeff_unpred", sizeof(T) * 4ull * nb);
+    uint16_t *d_ctype = (uint16_t *)c.get("coeff_type", 2ull * 4 * nb + 64);
+    unsigned char *d_ind = (unsigned char *)c.get("indicator", nb + 64);
+    uint32_t *d_flags = (uint32_t *)c.get("reg_flags", 4ull * nb + 64), *d_list = (uint32_t *)c.get("reg_list", 4ull * nb + 64);
+    unsigned long long *d_rank = (unsigned long long *)c.get("reg_rank", 8ull * nb + 64);
+    unsigned long long *d_tot = (unsigned long long *)c.get("totals", 256);
+    if (!d_reg || !d_regc || !d_clast || !d_cunp || !d_ctype || !d_ind || !d_flags || !d_list || !d_rank || !d_tot) return SZ_NSCS;
+    if (!c.pinned_words && cudaMallocHost((void **)&c.pinned_words, 256) != cudaSuccess) { c.pinned_words = nullptr; cudaGetLastError(); set_err("pinned alloc failed"); return SZ_NSCS; }
+    auto launch_fit = [&](cudaStream_t st, int scan_slot, int um, T mn) -> int {
+        int grid = (nb + 127) / 128;
+        if (job.dim == 3) fit_select_kernel<T, 3><<<grid, 128, 0, st>>>(d_x, g, noise, um, mn, d_reg, d_ind);
+        else fit_select_kernel<T, 2><<<grid, 128, 0, st>>>(d_x, g, noise, um, mn, d_reg, d_ind);
+        KCHECK();
+        reg_flag_kernel<<<(nb + 255) / 256, 256, 0, st>>>(d_ind, nb, d_flags); KCHECK();
+        if (launch_scan(c, st, scan_slot, d_flags, nb, d_rank, d_tot)) return SZ_NSCS;
+        CU(cudaMemcpyAsync(c.pinned_words, d_tot, 8, cudaMemcpyDeviceToHost, st));      // pinned: the call returns at once
+        return 0;
+    };
+    const bool fit_early = job.quantization_intervals == 0;
+    if (fit_early) {
+        CU(cudaEventRecord(c.ev_fork, c.stream));
+        CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));        // the optimiser below runs on the side stream
+        if (launch_fit(c.stream, 0, 0, (T)0)) return SZ_NSCS;
+    }
+
     // ---- interval optimiser (ref: sz_float.c:6647-6655) ----
     T dense_pos = (T)0;
     if (job.quantization_intervals == 0) {
+        const cudaStream_t so = c.stream2;          // the optimiser's small kernels: high-priority side stream, beside the fit on the main one
         std::vector<uint64_t> pos; sample_positions(c, g, pos);
         const uint32_t cnt = (uint32_t)pos.size();
         uint64_t *d_pos = (uint64_t *)c.get("opt_pos", 8ull * cnt + 8); T *d_vals = (T *)c.get("opt_vals", sizeof(T) * (size_t)cnt + 64);
@@ -671,25 +712,25 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         OptOut *d_out = (OptOut *)((unsigned char *)d_acc + 64); T *d_mean = (T *)((unsigned char *)d_acc + 128);
         void *pin = c.pin(8ull * cnt + 64); if (!pin) return SZ_NSCS;
         memcpy(pin, pos.data(), 8ull * cnt);
-        CU(cudaMemcpyAsync(d_pos, pin, 8ull * cnt, cudaMemcpyHostToDevice, c.stream));
-        CU(cudaMemsetAsync(ob, 0, 4ull * 32768 + 4ull * 8192 + 256, c.stream));
+        CU(cudaMemcpyAsync(d_pos, pin, 8ull * cnt, cudaMemcpyHostToDevice, so));
+        CU(cudaMemsetAsync(ob, 0, 4ull * 32768 + 4ull * 8192 + 256, so));
         {
             const size_t sm = sizeof(T) * (size_t)cnt + 16;
             const int in_smem = sm <= c.smem_optin - 1024 ? 1 : 0;
             if (in_smem) CU(cudaFuncSetAttribute(sample_mean_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-            sample_mean_kernel<T><<<1, 1024, in_smem ? sm : 0, c.stream>>>(d_x, d_pos, cnt, d_vals, d_mean, in_smem); KCHECK();
+            sample_mean_kernel<T><<<1, 1024, in_smem ? sm : 0, so>>>(d_x, d_pos, cnt, d_vals, d_mean, in_smem); KCHECK();
         }
         const uint64_t rows = opt_row_limit(g, (uint32_t)job.sampleDistance);
         if (rows > 0) {
             int grid = (int)std::min<uint64_t>((rows + 255) / 256, (uint64_t)c.sm_count * 8);
-            if (job.dim == 3) opt_sample_kernel<T, 3><<<grid, 256, 0, c.stream>>>(d_x, g, (uint32_t)job.sampleDistance, rows, d_mean, ebw, maxRangeRadius, d_int, d_freq, d_acc);
-            else opt_sample_kernel<T, 2><<<grid, 256, 0, c.stream>>>(d_x, g, (uint32_t)job.sampleDistance, rows, d_mean, ebw, maxRangeRadius, d_int, d_freq, d_acc);
+            if (job.dim == 3) opt_sample_kernel<T, 3><<<grid, 256, 0, so>>>(d_x, g, (uint32_t)job.sampleDistance, rows, d_mean, ebw, maxRangeRadius, d_int, d_freq, d_acc);
+            else opt_sample_kernel<T, 2><<<grid, 256, 0, so>>>(d_x, g, (uint32_t)job.sampleDistance, rows, d_mean, ebw, maxRangeRadius, d_int, d_freq, d_acc);
             KCHECK();
         }
-        opt_finish_kernel<T><<<1, 1024, 0, c.stream>>>(d_int, d_freq, d_acc, d_mean, maxRangeRadius, job.predThreshold, d_out); KCHECK();
+        opt_finish_kernel<T><<<1, 1024, 0, so>>>(d_int, d_freq, d_acc, d_mean, maxRangeRadius, job.predThreshold, d_out); KCHECK();
         OptOut ho;
-        CU(cudaMemcpyAsync(&ho, d_out, sizeof(ho), cudaMemcpyDeviceToHost, c.stream));
-        CU(cudaStreamSynchronize(c.stream));
+        CU(cudaMemcpyAsync(&ho, d_out, sizeof(ho), cudaMemcpyDeviceToHost, so));
+        CU(cudaStreamSynchronize(so));
         // scalar tail of optimize_intervals_* (ref: sz_float.c:6486-6520)
         unsigned int acc = 2 * (ho.first_index + 1);
         unsigned int p2 = round_up_pow2(acc); if (p2 < 32) p2 = 32;
@@ -711,37 +752,13 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     }
     if (mark(ST_MEAN)) return SZ_NSCS;
 
-    // ---- precisions (ref: sz_float.c:6639-6645, 2D :5608-5612) and noise (:6697 / :5674) ----
-    T prec[4] = {0, 0, 0, 0};
-    {
-        const T rel = (job.dim == 3) ? (T)0.025 : (T)(0.15 / 3);
-        const T t = rel * eb;
-        if (job.dim == 3) { prec[0] = t / (T)g.ax[0].late; prec[1] = t / (T)g.ax[1].late; prec[2] = t / (T)g.ax[2].late; prec[3] = t; }
-        else { prec[0] = t / (T)g.ax[1].late; prec[1] = t / (T)g.ax[2].late; prec[2] = t; }
+    // ---- fit + selection: the early run stands unless blocks are predicted from the mean as well ----
+    if (fit_early) CU(cudaStreamSynchronize(c.stream));          // (the optimiser's stream was synchronised for its result)
+    if (!fit_early || use_mean) {
+        if (launch_fit(c.stream, 0, use_mean, mean)) return SZ_NSCS;
+        CU(cudaStreamSynchronize(c.stream));
     }
-    const T noise = (job.dim == 3) ? (T)((double)eb * 1.22) : (T)((double)eb * 0.81);
-
-    // ---- fit + selection ----
-    T *d_reg = (T *)c.get("reg", sizeof(T) * 4ull * nb), *d_regc = (T *)c.get("reg_c", sizeof(T) * 4ull * nb), *d_clast = (T *)c.get("coeff_last", sizeof(T) * 4ull * nb),
-      *d_cunp = (T *)c.get("coeff_unpred", sizeof(T) * 4ull * nb);
-    uint16_t *d_ctype = (uint16_t *)c.get("coeff_type", 2ull * 4 * nb + 64);
-    unsigned char *d_ind = (unsigned char *)c.get("indicator", nb + 64);
-    uint32_t *d_flags = (uint32_t *)c.get("reg_flags", 4ull * nb + 64), *d_list = (uint32_t *)c.get("reg_list", 4ull * nb + 64);
-    unsigned long long *d_rank = (unsigned long long *)c.get("reg_rank", 8ull * nb + 64);
-    unsigned long long *d_tot = (unsigned long long *)c.get("totals", 256);
-    if (!d_reg || !d_regc || !d_clast || !d_cunp || !d_ctype || !d_ind || !d_flags || !d_list || !d_rank || !d_tot) return SZ_NSCS;
-    {
-        int grid = (nb + 127) / 128;
-        if (job.dim == 3) fit_select_kernel<T, 3><<<grid, 128, 0, c.stream>>>(d_x, g, noise, use_mean, mean, d_reg, d_ind);
-        else fit_select_kernel<T, 2><<<grid, 128, 0, c.stream>>>(d_x, g, noise, use_mean, mean, d_reg, d_ind);
-        KCHECK();
-        reg_flag_kernel<<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, nb, d_flags); KCHECK();
-        if (launch_scan(c, c.stream, 0, d_flags, nb, d_rank, d_tot)) return SZ_NSCS;
-    }
-    unsigned long long reg_count_ll = 0;
-    CU(cudaMemcpyAsync(&reg_count_ll, d_tot, 8, cudaMemcpyDeviceToHost, c.stream));
-    CU(cudaStreamSynchronize(c.stream));
-    const uint32_t reg_count = (uint32_t)reg_count_ll;
+    const uint32_t reg_count = (uint32_t)c.pinned_words[0];
     if (mark(ST_FIT)) return SZ_NSCS;
 
     // ---- coefficient chain (its proof stage also counts the codes: the histograms of the four coefficient trees) ----
