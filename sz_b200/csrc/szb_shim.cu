@@ -12,6 +12,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
+#include <condition_variable>
 #include <functional>
 #include <map>
 #include <mutex>
@@ -199,25 +201,62 @@ static int copy_threads() {                                     // host threads 
     if (n == 0) { const char *e = getenv("SZB200_COPY_THREADS"); n = e ? atoi(e) : 4; if (n < 1) n = 1; if (n > 8) n = 8; }
     return n;
 }
-static void memcpy2(void *d, const void *s, size_t n) {          // one chunk, shared by several host threads
-    const int parts = n >= ((size_t)1 << 20) ? copy_threads() : 1;
-    if (parts == 1) { memcpy(d, s, n); return; }
-    const size_t h = (n / (size_t)parts) & ~(size_t)4095;
-    std::thread helpers[7];
-    for (int k = 1; k < parts; k++) {
-        const size_t off = (size_t)k * h, len = (k == parts - 1) ? n - off : h;
-        helpers[k - 1] = std::thread([=] { memcpy((unsigned char *)d + off, (const unsigned char *)s + off, len); });
+// The host side of a bounced copy is a memcpy between pinned and pageable memory that one core cannot do at the DMA's pace: several
+// threads share every chunk.  They are kept (creating them per chunk cost more than the copy: 7 x ~20 us for 8 MB at 20 GB/s), asleep
+// between copies and spinning for the next chunk while one is under way.  One bounced copy uses them at a time; a second one, from
+// another host thread, copies its chunks alone.
+struct CopyPool {
+    std::mutex owner;                                  // held by the bounced copy that uses the pool
+    std::mutex m; std::condition_variable cv;
+    std::vector<std::thread> th;
+    std::atomic<int> active{0};
+    std::atomic<unsigned> gen{0};
+    std::atomic<int> pending{0};
+    unsigned char *d = nullptr; const unsigned char *s = nullptr; size_t part = 0, n = 0; int parts = 0;
+    void worker(int k) {
+        unsigned seen = 0;
+        for (;;) {
+            { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return active.load(std::memory_order_acquire) != 0; }); }
+            while (active.load(std::memory_order_acquire)) {
+                const unsigned g = gen.load(std::memory_order_acquire);
+                if (g == seen) { std::this_thread::yield(); continue; }
+                seen = g;
+                if (k < parts) { const size_t off = (size_t)k * part, len = (k == parts - 1) ? n - off : part; memcpy(d + off, s + off, len); }
+                pending.fetch_sub(1, std::memory_order_release);
+            }
+        }
     }
-    memcpy(d, s, h);
-    for (int k = 1; k < parts; k++) helpers[k - 1].join();
-}
+    void begin() {
+        if (th.empty()) for (int k = 1; k < copy_threads(); k++) { th.emplace_back([this, k] { worker(k); }); th.back().detach(); }
+        { std::lock_guard<std::mutex> l(m); active.store(1, std::memory_order_release); }
+        cv.notify_all();
+    }
+    void end() { active.store(0, std::memory_order_release); }
+    void copy(void *dst, const void *src, size_t bytes) {
+        const int nt = copy_threads();
+        if (bytes < ((size_t)1 << 20) || nt == 1) { memcpy(dst, src, bytes); return; }
+        d = (unsigned char *)dst; s = (const unsigned char *)src; n = bytes; parts = nt; part = (bytes / (size_t)nt) & ~(size_t)4095;
+        pending.store(nt - 1, std::memory_order_relaxed);
+        gen.fetch_add(1, std::memory_order_release);
+        memcpy(d, s, part);                                // part 0 is this thread's
+        while (pending.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+    }
+};
+static CopyPool &g_pool = *new CopyPool;             // never destroyed: its threads outlive static destruction
+struct PoolUse {                                       // scope of one bounced copy
+    bool mine;
+    PoolUse() : mine(copy_threads() > 1 && g_pool.owner.try_lock()) { if (mine) g_pool.begin(); }
+    ~PoolUse() { if (mine) { g_pool.end(); g_pool.owner.unlock(); } }
+    void copy(void *d, const void *s, size_t n) { if (mine) g_pool.copy(d, s, n); else memcpy(d, s, n); }
+};
 static int h2d_bounced(Ctx &c, void *dst, const void *src, size_t bytes) {
     if (ensure_bounce(c)) { CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream)); return 0; }
     const size_t nchunks = (bytes + BOUNCE_CHUNK - 1) / BOUNCE_CHUNK;
+    PoolUse pool;
     for (size_t i = 0; i < nchunks; i++) {
         const size_t off = i * BOUNCE_CHUNK, n = std::min(BOUNCE_CHUNK, bytes - off);
         if (i >= 2) CU(cudaEventSynchronize(c.ev_bounce[i & 1]));       // the DMA that last read this buffer has finished
-        memcpy2(c.bounce + (i & 1) * BOUNCE_CHUNK, (const unsigned char *)src + off, n);
+        pool.copy(c.bounce + (i & 1) * BOUNCE_CHUNK, (const unsigned char *)src + off, n);
         CU(cudaMemcpyAsync((unsigned char *)dst + off, c.bounce + (i & 1) * BOUNCE_CHUNK, n, cudaMemcpyHostToDevice, c.stream));
         CU(cudaEventRecord(c.ev_bounce[i & 1], c.stream));
     }
@@ -238,6 +277,7 @@ static int d2h_bounced(Ctx &c, void *dst, const void *src, size_t bytes) {
     const bool hprof = getenv("SZB200_HOST_PROFILE") != nullptr;
     double t_wait = 0, t_copy = 0;
     auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    PoolUse pool;
     if (issue(0)) return SZ_NSCS;
     for (size_t i = 0; i < nchunks; i++) {
         if (i + 1 < nchunks && issue(i + 1)) return SZ_NSCS;      // buffer (i+1)&1 was drained at step i-1
@@ -247,7 +287,7 @@ static int d2h_bounced(Ctx &c, void *dst, const void *src, size_t bytes) {
         const size_t off = i * BOUNCE_CHUNK, n = std::min(BOUNCE_CHUNK, bytes - off);
         // the host side of the copy is what bounds it (one core writes ~10 GB/s): several threads share every chunk (measured on the
         // 512^3 stream, 38.5 MB: 2.4 ms with two threads, 1.6 ms with four, 1.65 ms with eight)
-        memcpy2((unsigned char *)dst + off, c.bounce + (i & 1) * BOUNCE_CHUNK, n);
+        pool.copy((unsigned char *)dst + off, c.bounce + (i & 1) * BOUNCE_CHUNK, n);
         if (hprof) { t_wait += t1 - t0; t_copy += now() - t1; }
     }
     if (hprof) fprintf(stderr, "[host-prof] D2H of %zu bytes through the bounce buffers: waited for DMA %.2f ms, host copies %.2f ms\n", bytes, t_wait, t_copy);
