@@ -198,7 +198,7 @@ template <typename T>
 __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__restrict__ reg_c /*[ncoef][nb], compacted*/, const uint32_t *__restrict__ reg_list,
                                                                     uint32_t nb, uint32_t reg_count, T p0, T p1, T p2, T p3, int use_div,
                                                                     uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/,
-                                                                    T *__restrict__ coeff_unpred /*[ncoef][nb]*/, LatHist hists, ChainOut *out, int first_mode, float band_scale) {
+                                                                    T *__restrict__ coeff_unpred /*[ncoef][nb]*/, LatHist hists, unsigned int *done_flags /*[ncoef]: set when the coefficient's codes and histogram are final*/, ChainOut *out, int first_mode, float band_scale) {
     typedef typename TT<T>::bits_t bits_t;
     constexpr int W = LAT_W;
     __shared__ LatSlot<T> s_slot[2];
@@ -218,6 +218,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
     uint32_t ucount = 0;
     unsigned int n_ticks = 0, n_redo = 0, n_pair = 0, n_full = 0;
     long long cyc_s = 0, cyc_h = 0; const long long cyc_0 = clock64();
+    unsigned long long dbg_g0; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_g0));
     unsigned int prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // LAT_PROF builds: {count, cycles} of clean words, clean groups, PAIR groups, groups run step by step
     LatWin<T> vw, sw, gw;
     LatPrep<T> P; P.in = false;
@@ -424,7 +425,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
         // ---- what the next tick does (the same decision in every thread) ----
         if (vw.valid) {
             if (fail) {                                    // rerun the failed window from its exact entry value; everything after it is void
-                if (vw.mode >= 2) { if (tid == 0) out->err = 1u; return; }     // the complete formula disagrees with itself: cannot happen
+                if (vw.mode >= 2) { if (tid == 0) { out->err = 1u; if (done_flags) atomicExch(done_flags + e, 1u); } return; }     // the complete formula disagrees with itself: cannot happen
                 gw.p = vw.p; gw.cnt = (int)min((uint32_t)W, reg_count - vw.p); gw.slot = vw.slot; gw.mode = vw.mode + 1; gw.entry = vw.entry; gw.valid = true; gw.fresh = true;
                 vw.valid = false; sw.valid = false; n_redo++;
                 continue;
@@ -456,12 +457,16 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
             gw.p = sw.p + (uint32_t)sw.cnt; gw.cnt = (int)min((uint32_t)W, reg_count - gw.p); gw.slot = sw.slot ^ 1; gw.mode = first_mode; gw.valid = true; gw.fresh = false;
         } else gw.valid = false;
     }
+    __threadfence();                                 // every thread's histogram counts and stores, then the flag
+    __syncthreads();
     if (tid == 0) {
+        if (done_flags) atomicExch(done_flags + e, 1u);
         out->unpred_count[e] = ucount;
         if (e == (int)gridDim.x - 1) {
             out->passes = n_ticks; out->slow_chunks = n_redo; out->kcyc_serial = (unsigned int)(cyc_s >> 10);
             out->kcyc_total = (unsigned int)((clock64() - cyc_0) >> 10);
             for (int i = 0; i < 8; i++) out->prof[i] = prof[i];
+            { unsigned long long g1; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g1)); out->prof[6] = (unsigned int)(dbg_g0 / 1000ull); out->prof[7] = (unsigned int)(g1 / 1000ull); }
         }
     }
     if (e == (int)gridDim.x - 1 && warp >= 1 && lane == 0) { atomicAdd(&out->n_pair, n_pair); atomicAdd(&out->n_full, n_full); if (warp == 1) out->kcyc_helper = (unsigned int)(cyc_h >> 10); }

@@ -88,6 +88,12 @@ struct Ctx {
         CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
         for (auto &e : ev) CU(cudaEventCreate(&e));
         CU(cudaEventCreate(&ev_tree0)); CU(cudaEventCreate(&ev_tree1)); CU(cudaEventCreate(&ev_side0)); CU(cudaEventCreate(&ev_side1));
+        {   // Kernels launched while huff_build_kernel already sits on its SMs waiting for them (compress_impl) are loaded here: with lazy
+            // module loading a kernel's first launch synchronises with the kernels that are running, i.e. with the one that waits for it.
+            cudaFuncAttributes fa;
+            CU(cudaFuncGetAttributes(&fa, coeff_lattice_kernel<float>)); CU(cudaFuncGetAttributes(&fa, coeff_lattice_kernel<double>));
+            CU(cudaFuncGetAttributes(&fa, reg_gather_kernel<float>)); CU(cudaFuncGetAttributes(&fa, reg_gather_kernel<double>));
+        }
         ev_ok = true;
         cudaDeviceProp pr; CU(cudaGetDeviceProperties(&pr, d));
         sm_count = pr.multiProcessorCount; smem_optin = pr.sharedMemPerBlockOptin;
@@ -498,7 +504,7 @@ static int tree_ws(Ctx &c, int idx, uint32_t nbins, TreeWs &w) {
            o_code = take(8ull * nbins), o_clen = take(nbins), o_tree = take(16 + 13ull * cap), o_out = take(64);
     unsigned char *base = (unsigned char *)c.get(name, off); if (!base) return SZ_NSCS;
     w.hist = (uint32_t *)(base + o_hist);
-    w.d.hist = w.hist; w.d.nbins = nbins; w.d.capacity = cap;
+    w.d.hist = w.hist; w.d.nbins = nbins; w.d.capacity = cap; w.d.wait_flag = nullptr;
     w.d.n_left = (uint32_t *)(base + o_left); w.d.n_right = (uint32_t *)(base + o_right); w.d.n_sizeL = (uint32_t *)(base + o_sizeL); w.d.n_sym = (uint32_t *)(base + o_sym);
     w.d.n_pre = (uint32_t *)(base + o_pre); w.d.n_code = (uint64_t *)(base + o_code_n); w.d.n_len = (uint8_t *)(base + o_len_n);
     w.d.frontier = (uint32_t *)(base + o_front); w.d.heap_g = (uint32_t *)(base + o_heap);
@@ -806,23 +812,8 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     const int ntrees = 1 + (reg_count > 0 ? ncoef : 0);
     if (tree_ws(c, 0, intervals, tw[0])) return SZ_NSCS;
     for (int e = 0; e < ntrees - 1; e++) if (tree_ws(c, 1 + e, 65536, tw[1 + e])) return SZ_NSCS;
-    ChainOut *d_chain = (ChainOut *)c.get("chain_out", 128); if (!d_chain) return SZ_NSCS;
-    CU(cudaMemsetAsync(d_chain, 0, 128, c.stream));
-    if (reg_count > 0) {
-        LatHist hists; memset(&hists, 0, sizeof(hists));
-        for (int e = 0; e < ncoef; e++) { hists.h[e] = tw[1 + e].hist; CU(cudaMemsetAsync(tw[1 + e].hist, 0, 4ull * 65536, c.stream)); }
-        reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, ncoef, d_reg, d_regc, d_list); KCHECK();
-        const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
-        // one CTA per coefficient: lattice guess, add chain, exact proof (szb_chain.cuh); SZB200_CHAIN=exact runs every step with the
-        // reference's complete formula (the form a failed window falls back to), for tests and timing
-        static const int chain_mode = [] { const char *e = getenv("SZB200_CHAIN"); return e && !strcmp(e, "exact") ? 2 : 0; }();
-        static const float chain_band = [] { const char *e = getenv("SZB200_LAT_BAND"); return e ? (float)atof(e) : LAT_BAND; }();
-        coeff_lattice_kernel<T><<<ncoef, LAT_THREADS, 0, c.stream>>>(d_regc, d_list, nb, reg_count, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, hists, d_chain, chain_mode, chain_band); KCHECK();
-    }
-    if (mark(ST_CHAIN)) return SZ_NSCS;
-
-    // ---- side branch on stream2 (needs only the chain's output): coefficient histograms, their Huffman trees (exact heap
-    //      emulation, the longest serial stage) and bit lengths run concurrently with the wavefront / main-tree / main-length work ----
+    // everything the side branch needs is allocated, cleared and uploaded here, before the chain is launched: the host then queues the tree
+    // kernel while the chain still runs and the GPU starts it the moment the chain ends
     HuffTreeDesc *d_desc = (HuffTreeDesc *)c.get("tree_desc", sizeof(HuffTreeDesc) * 8); if (!d_desc) return SZ_NSCS;
     const uint32_t heap_cap = (uint32_t)((c.smem_optin - 8192) / 8);
     const size_t heap_sm = 8ull * heap_cap;
@@ -849,14 +840,36 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         d_cstate = (unsigned long long *)c.get("enc_cstate", 8 * (4 * nchunk_c + 8)); if (!d_cstate) return SZ_NSCS;
         CU(cudaMemsetAsync(d_cstate, 0, 8 * (4 * nchunk_c + 8), c.stream));
     }
+    unsigned int *d_done = (unsigned int *)c.get("chain_done", 64); if (!d_done) return SZ_NSCS;
+    CU(cudaMemsetAsync(d_done, 0, 64, c.stream));
+    ChainOut *d_chain = (ChainOut *)c.get("chain_out", 128); if (!d_chain) return SZ_NSCS;
+    CU(cudaMemsetAsync(d_chain, 0, 128, c.stream));
+    for (int e = 0; e < ntrees - 1; e++) CU(cudaMemsetAsync(tw[1 + e].hist, 0, 4ull * 65536, c.stream));      // counted by the chain's proof stage
+    for (int e = 0; e < ntrees - 1; e++) tw[1 + e].d.wait_flag = d_done + e;      // tree e starts when chain e has set its flag
     {
         HuffTreeDesc hd[8];
         for (int i = 0; i < ntrees; i++) hd[i] = tw[i].d;
         CU(cudaMemcpyAsync(d_desc, hd, sizeof(HuffTreeDesc) * ntrees, cudaMemcpyHostToDevice, c.stream));   // pageable: staged before return
     }
-    if (ntrees > 1) {
+    if (ntrees > 1) {                                  // the side stream starts from here: everything above is ready, the chain is not awaited
         CU(cudaEventRecord(c.ev_fork, c.stream));
         CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+    }
+    if (reg_count > 0) {
+        LatHist hists; memset(&hists, 0, sizeof(hists));
+        for (int e = 0; e < ncoef; e++) hists.h[e] = tw[1 + e].hist;
+        reg_gather_kernel<T><<<(nb + 255) / 256, 256, 0, c.stream>>>(d_ind, d_rank, nb, ncoef, d_reg, d_regc, d_list); KCHECK();
+        const int use_div = (sizeof(T) == 4 && !use_mean) ? 1 : 0;     // ref: sz_float.c:7133 vs :6795; double always multiplies
+        // one CTA per coefficient: lattice guess, add chain, exact proof (szb_chain.cuh); SZB200_CHAIN=exact runs every step with the
+        // reference's complete formula (the form a failed window falls back to), for tests and timing
+        static const int chain_mode = [] { const char *e = getenv("SZB200_CHAIN"); return e && !strcmp(e, "exact") ? 2 : 0; }();
+        static const float chain_band = [] { const char *e = getenv("SZB200_LAT_BAND"); return e ? (float)atof(e) : LAT_BAND; }();
+        coeff_lattice_kernel<T><<<ncoef, LAT_THREADS, 0, c.stream>>>(d_regc, d_list, nb, reg_count, prec[0], prec[1], prec[2], prec[3], use_div, d_ctype, d_clast, d_cunp, hists, d_done, d_chain, chain_mode, chain_band); KCHECK();
+    }
+    // ---- side branch on stream2: the coefficient Huffman trees (exact heap emulation, the longest serial stage) and the coefficient bit
+    //      streams, concurrent with the wavefront / main-tree / main-encode work.  The tree kernel does not wait for the chain's end in stream order (it was
+    //      forked before the chain): its CTAs sit on their SMs and wait for the chain's per-coefficient flags ----
+    if (ntrees > 1) {
         CU(cudaEventRecord(c.ev_side0, c.stream2));
         CU(cudaEventRecord(c.ev_tree0, c.stream2));
         CU(launch_huff_build(c.stream2, d_desc + 1, ntrees - 1, heap_sm, heap_cap, std::min<uint64_t>(65536u, reg_count))); KCHECK();
@@ -870,6 +883,8 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
         CU(cudaEventRecord(c.ev_side1, c.stream2));
         CU(cudaEventRecord(c.ev_join, c.stream2));
     }
+
+    if (mark(ST_CHAIN)) return SZ_NSCS;
 
     // ---- wavefront predict + quantise ----
     {
@@ -888,9 +903,9 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     if (launch_scan(c, c.stream, 0, d_cb, nchunk_main, d_cbo, d_tot + 1)) return SZ_NSCS;
     if (launch_scan(c, c.stream, 0, d_cz, nchunk_main, d_czo, d_tot + 2)) return SZ_NSCS;
     // ---- sizes of the main stream (the side branch with the coefficient trees is still running; nothing here waits for it) ----
-    unsigned long long h_tot[8]; uint32_t h_tree[5][8]; ChainOut h_chain;
+    unsigned long long h_tot[8]; uint32_t h_tree[5][16]; ChainOut h_chain;
     CU(cudaMemcpyAsync(h_tot, d_tot, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
-    CU(cudaMemcpyAsync(h_tree[0], tw[0].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaMemcpyAsync(h_tree[0], tw[0].d.out, 64, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
     if (check_wf_err(c)) return SZ_NSCS;
     const uint64_t main_bits = h_tot[1], total_unpred = h_tot[2];
@@ -909,13 +924,13 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     // ---- join the side branch (coefficient trees), then the coefficient bit streams ----
     if (ntrees > 1) { CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0)); if (mark(ST_JOIN)) return SZ_NSCS; }
     CU(cudaMemcpyAsync(h_tot + 3, d_tot + 3, 5 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
-    for (int i = 1; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 32, cudaMemcpyDeviceToHost, c.stream));
+    for (int i = 1; i < ntrees; i++) CU(cudaMemcpyAsync(h_tree[i], tw[i].d.out, 64, cudaMemcpyDeviceToHost, c.stream));
     CU(cudaMemcpyAsync(&h_chain, d_chain, sizeof(h_chain), cudaMemcpyDeviceToHost, c.stream));
     CU(cudaStreamSynchronize(c.stream));
     if (getenv("SZB200_TREE_PROFILE")) fprintf(stderr, "[chain-prof] steps=%u passes=%u (reruns: %u) kcycles: serial thread busy=%u, helper busy=%u, total=%u; last coefficient: pair-form steps=%u, full steps=%u\n", reg_count, h_chain.passes, h_chain.slow_chunks, h_chain.kcyc_serial, h_chain.kcyc_helper, h_chain.kcyc_total, h_chain.n_pair, h_chain.n_full);
     if (getenv("SZB200_TREE_PROFILE") && h_chain.prof[0] + h_chain.prof[2]) fprintf(stderr, "[chain-prof] serial thread {count, cycles}: clean words %u %u, clean groups %u %u, pair groups %u %u, step-by-step groups %u %u\n", h_chain.prof[0], h_chain.prof[1], h_chain.prof[2], h_chain.prof[3], h_chain.prof[4], h_chain.prof[5], h_chain.prof[6], h_chain.prof[7]);
     if (getenv("SZB200_TREE_PROFILE")) for (int i = 0; i < ntrees; i++)
-        fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7]);
+        fprintf(stderr, "[tree-prof] tree %d: leaves=%u kcycles: compaction=%u leaf-inserts=%u inserts+merges=%u level-passes=%u; whole CTA %u kcycles in %u ns, after waiting %u us for its input (the chain ended %d us before that wait did)\n", i, h_tree[i][2], h_tree[i][4], h_tree[i][5], h_tree[i][6], h_tree[i][7], h_tree[i][13], h_tree[i][12], h_tree[i][15] - h_tree[i][14], i ? (int)(h_tree[i][15] - h_chain.prof[7]) : 0);
     if (h_chain.err) { set_err("coefficient chain: a step left its tabulated interval (internal error)"); return SZ_NSCS; }
     for (int i = 0; i < ntrees; i++) if (h_tree[i][3]) { set_err(h_tree[i][3] == 2 ? "Huffman tree build gave up (tree %d)" : "Huffman code longer than 64 bits (tree %d)", i); return SZ_NSCS; }
     uint64_t cbytes[4] = {0, 0, 0, 0};
@@ -953,8 +968,8 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     for (int i = 1; i < evi; i++) { float ms = 0; cudaEventElapsedTime(&ms, c.ev[i - 1], c.ev[i]); st.ms_stage[stage_of_ev[i]] += ms; }
     cudaEventElapsedTime(&st.ms_total, c.ev[0], c.ev[evi - 1]);
     if (ntrees > 1) {
-        cudaEventElapsedTime(&st.ms_stage[14], c.ev_tree0, c.ev_tree1);
-        float a = 0, b = 0; cudaEventElapsedTime(&a, c.ev_side0, c.ev_tree0); cudaEventElapsedTime(&b, c.ev_tree1, c.ev_side1); st.ms_stage[15] = a + b;
+        for (int i = 1; i < ntrees; i++) st.ms_stage[14] = std::max(st.ms_stage[14], (float)h_tree[i][12] * 1e-6f);      // measured inside the kernel, behind its wait for the chain
+        float b = 0; cudaEventElapsedTime(&b, c.ev_tree1, c.ev_side1); st.ms_stage[15] = b;
     }
     c.last = st; c.have_last = true;
     c.dbg_g = g; c.dbg_dtype = job.dtype; c.dbg_intervals = intervals; c.dbg_reg_count = reg_count;
