@@ -472,4 +472,79 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
     if (e == (int)gridDim.x - 1 && warp >= 1 && lane == 0) { atomicAdd(&out->n_pair, n_pair); atomicAdd(&out->n_full, n_full); if (warp == 1) out->kcyc_helper = (unsigned int)(cyc_h >> 10); }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Decoder side (ref: szd_float.c:5809-5819): last = last + 2 (t - R) * prec, or the next stored raw value when t == 0.  The increments
+// (or raw values) and the "is raw" flags come from coeff_dec_prep_kernel; what is left is the add chain itself, run like (S) above: one
+// CTA per coefficient, windows of LAT_W steps, one thread adds 32 increments from registers per word (a word with a raw value in it goes
+// step by step), the helpers fetch the next window and scatter the previous one's results to their block ids.
+template <typename T>
+__global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const T *__restrict__ val /*[ncoef][reg_count]*/, const unsigned char *__restrict__ rst,
+                                                                         uint32_t nb, uint32_t reg_count, const uint32_t *__restrict__ reg_list,
+                                                                         T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
+    constexpr int W = LAT_W;
+    __shared__ __align__(16) T s_val[2][W];
+    __shared__ __align__(16) T s_out[2][W];
+    __shared__ unsigned int s_rm[2][W / 32];              // raw-value flags of a window, one bit per step
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, h = tid - 32;
+    const int e = blockIdx.x;
+    const T *val_e = val + (size_t)e * reg_count;
+    const unsigned char *rst_e = rst + (size_t)e * reg_count;
+    const uint32_t nwin = (reg_count + W - 1) / W;
+    T last = (T)0;
+    if (warp != 0) {                                       // window 0
+        const bool in = (uint32_t)h < reg_count;
+        s_val[0][h] = in ? val_e[h] : (T)0;
+        const unsigned int rm = __ballot_sync(0xffffffffu, in && rst_e[h] != 0);
+        if (lane == 0) s_rm[0][warp - 1] = rm;
+    }
+    __syncthreads();
+    for (uint32_t w = 0; w <= nwin; w++) {
+        if (warp == 0) {
+            if (lane == 0 && w < nwin) {
+                const int sl = (int)(w & 1u);
+                const int cnt = (int)min((uint32_t)W, reg_count - w * W);
+                const int nwords = (cnt + 31) >> 5;
+                T a[32], b[32];
+                lat_ld32(&s_val[sl][0], a);
+                auto word = [&](int j, const T (&v)[32]) {
+                    const unsigned int rm = s_rm[sl][j];
+                    T o[32];
+                    if (rm == 0u) {
+#pragma unroll
+                        for (int t = 0; t < 32; t++) { last = last + v[t]; o[t] = last; }
+                    } else {
+#pragma unroll
+                        for (int t = 0; t < 32; t++) { const T sum = last + v[t]; last = ((rm >> t) & 1u) ? v[t] : sum; o[t] = last; }
+                    }
+#pragma unroll
+                    for (int g = 0; g < 4; g++) lat_st8(&s_out[sl][32 * j + 8 * g], &o[8 * g]);
+                };
+                for (int j = 0; j < nwords; j += 2) {
+                    if (j + 1 < nwords) lat_ld32(&s_val[sl][32 * (j + 1)], b);
+                    word(j, a);
+                    if (j + 1 >= nwords) break;
+                    if (j + 2 < nwords) lat_ld32(&s_val[sl][32 * (j + 2)], a);
+                    word(j + 1, b);
+                }
+            }
+        } else {
+            // the next window's values and flags (loaded first, stored last: the scatter hides their latency)
+            const uint32_t pn = (w + 1) * W + (uint32_t)h;
+            const bool in_n = w + 1 < nwin && pn < reg_count;
+            T vn = (T)0; unsigned char rn = 0;
+            if (in_n) { vn = val_e[pn]; rn = rst_e[pn]; }
+            if (w >= 1) {                                  // the previous window's results to their blocks
+                const uint32_t pp = (w - 1) * W + (uint32_t)h;
+                if (pp < reg_count) coeff_last[(size_t)e * nb + reg_list[pp]] = s_out[(w - 1) & 1u][h];
+            }
+            if (w + 1 < nwin) {
+                s_val[(w + 1) & 1u][h] = vn;
+                const unsigned int rm = __ballot_sync(0xffffffffu, in_n && rn != 0);
+                if (lane == 0) s_rm[(w + 1) & 1u][warp - 1] = rm;
+            }
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace szb

@@ -1405,94 +1405,8 @@ __global__ void __launch_bounds__(1024) coeff_dec_prep_kernel(const uint16_t *__
     }
 }
 
-// step 2 (serial): last = reset ? value : last + increment, one lane per coefficient.  Same three-stage pipeline as the
-// compression-side chain: warp 0 runs the adds of chunk c, helper warps 1,2,3,5 (warp 4 would share warp 0's scheduler)
-// prefetch chunk c+1 and scatter the results of chunk c-1 to their block ids.
-constexpr int DCHAIN_THREADS = 192;
-template <typename T>
-__global__ void __launch_bounds__(DCHAIN_THREADS) coeff_chain_decode_kernel(const T *__restrict__ val, const unsigned char *__restrict__ rst, uint32_t nb,
-                                                                            uint32_t reg_count, int ncoef, const uint32_t *__restrict__ reg_list,
-                                                                            T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
-    constexpr int CH = 256, PER = CH / 128;
-    __shared__ __align__(16) T s_val[3][4][CH];
-    __shared__ __align__(16) unsigned char s_rst[3][4][CH];
-    __shared__ __align__(16) T s_out[2][4][CH];
-    __shared__ uint32_t s_blk[3][CH];
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int eB = warp == 5 ? 3 : ((warp == 4 || warp == 0) ? 99 : warp - 1);
-    const int tB = eB * 32 + lane;                           // index among the 128 helper threads
-    auto load_chunk = [&](uint32_t chunk) {
-        const uint32_t r0 = chunk * CH;
-        if (r0 >= reg_count) return;
-        const int buf = (int)(chunk % 3u);
-        const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-        T v[4][PER]; unsigned char f[4][PER]; uint32_t bl[PER];
-#pragma unroll
-        for (int e = 0; e < 4; e++)
-#pragma unroll
-            for (int q = 0; q < PER; q++) {
-                const int i = tB + q * 128;
-                if (e < ncoef && i < cnt) { v[e][q] = val[(size_t)e * reg_count + r0 + i]; f[e][q] = rst[(size_t)e * reg_count + r0 + i]; }
-            }
-#pragma unroll
-        for (int q = 0; q < PER; q++) { const int i = tB + q * 128; if (i < cnt) bl[q] = reg_list[r0 + i]; }
-#pragma unroll
-        for (int e = 0; e < 4; e++)
-#pragma unroll
-            for (int q = 0; q < PER; q++) {
-                const int i = tB + q * 128;
-                if (e < ncoef && i < cnt) { s_val[buf][e][i] = v[e][q]; s_rst[buf][e][i] = f[e][q]; }
-            }
-#pragma unroll
-        for (int q = 0; q < PER; q++) { const int i = tB + q * 128; if (i < cnt) s_blk[buf][i] = bl[q]; }
-    };
-    if (eB < 4) load_chunk(0);
-    T last = (T)0;
-    const uint32_t nchunks = (reg_count + CH - 1) / CH;
-    __syncthreads();
-    for (uint32_t it = 0; it <= nchunks; it++) {
-        if (warp == 0) {
-            if (it < nchunks && lane < ncoef) {
-                const int e = lane, buf = (int)(it % 3u), lb = (int)(it & 1u);
-                const int cnt = (int)min((uint32_t)CH, reg_count - it * CH);
-                // eight steps at a time: all loads first, then the add chain in registers, then the stores (left to itself the
-                // compiler keeps every step's load behind the previous step's store and the chain pays a shared-memory round trip per step)
-                int i = 0;
-                for (; i + 8 <= cnt; i += 8) {
-                    T v[8], o[8];
-                    const unsigned long long fw = *reinterpret_cast<const unsigned long long *>(&s_rst[buf][e][i]);      // the eight reset flags
-#pragma unroll
-                    for (int q = 0; q < 8; q++) v[q] = s_val[buf][e][i + q];
-                    if (fw == 0ull) {                         // no raw value among the eight (the usual case): a bare add chain
-#pragma unroll
-                        for (int q = 0; q < 8; q++) { last = last + v[q]; o[q] = last; }
-                    } else {
-#pragma unroll
-                        for (int q = 0; q < 8; q++) { const T sum = last + v[q]; last = ((fw >> (8 * q)) & 0xffull) ? v[q] : sum; o[q] = last; }
-                    }
-#pragma unroll
-                    for (int q = 0; q < 8; q++) s_out[lb][e][i + q] = o[q];
-                }
-                for (; i < cnt; i++) {
-                    const T v = s_val[buf][e][i];
-                    const T sum = last + v;
-                    last = s_rst[buf][e][i] ? v : sum;
-                    s_out[lb][e][i] = last;
-                }
-            }
-        } else if (eB < 4) {
-            if (it + 1 < nchunks) load_chunk(it + 1);
-            if (it >= 1) {
-                const uint32_t cb = it - 1, r0 = cb * CH;
-                const int buf = (int)(cb % 3u), lb = (int)(cb & 1u);
-                const int cnt = (int)min((uint32_t)CH, reg_count - r0);
-                for (int e = 0; e < ncoef; e++)
-                    for (int i = tB; i < cnt; i += 128) coeff_last[(size_t)e * nb + s_blk[buf][i]] = s_out[lb][e][i];
-            }
-        }
-        __syncthreads();
-    }
-}
+// step 2 (serial): the add chain itself, coeff_chain_decode_kernel in szb_chain.cuh
+
 
 // indicator bits (MSB-first, 1 = Lorenzo; ref: TypeManager.c:47-71) <-> byte-per-block array
 __global__ void indicator_pack_kernel(const unsigned char *__restrict__ ind, uint32_t nb, unsigned char *out) {
