@@ -275,15 +275,16 @@ def run_ours(args):
     ev0.record(lib_stream)
     for _ in range(args.steps):
         n = step()
-        st = sz_b200.last_stats()
-        launches += st.launches
-        for k, v in st.as_dict()["ms_stage"].items():
-            stage_ms[k] = stage_ms.get(k, 0.0) + v
     # (the gather of an N>1 step is enqueued on torch's current stream after the library's job has finished: the closing event goes
     #  where the last work of the step went)
     ev1.record(lib_stream if world == 1 else torch.cuda.current_stream())
     barrier()
     ms_dev = ev0.elapsed_time(ev1)
+    # launch count and per-stage times: the library's own record of a step, read outside the timed region (every step launches the same)
+    st = sz_b200.last_stats()
+    launches = st.launches * args.steps
+    for k, v in st.as_dict()["ms_stage"].items():
+        stage_ms[k] = v * args.steps
     clocks = sampler.stop() if rank == 0 else None
     ms_step = max_over_ranks(ms_dev) / args.steps
     value = world * nbytes / (ms_step * 1e-3) / 1e9
