@@ -11,14 +11,6 @@ sys.path.insert(0, HERE)
 sys.path.insert(0, os.path.dirname(HERE))
 
 
-def noisy_quadratic(shape, dtype, seed=3):
-    rng = np.random.default_rng(seed)
-    g = np.meshgrid(*[np.linspace(-1, 1, n) for n in shape], indexing="ij")
-    f = sum((i + 1) * x for i, x in enumerate(g)) + 0.7 * sum(x * x for x in g) + np.sin(3 * g[0]) * np.cos(2 * g[-1])
-    f = f + rng.normal(0, 4e-3 * (f.max() - f.min()), size=shape)
-    return np.ascontiguousarray(f.astype(dtype))
-
-
 def main():
     import szref
     import sz_b200
@@ -26,8 +18,8 @@ def main():
     sz_b200.init(cfg)
     orc = szref.Oracle()
     orc.init(cfg)
-    fields = [("noisy quadratic f32 3D", noisy_quadratic((120, 96, 102), np.float32)),      # every block a regression block, ~1500 distinct codes
-              ("noisy quadratic f64 2D", noisy_quadratic((640, 700), np.float64)),
+    fields = [("noisy quadratic f32 3D", szref.noisy_quadratic((120, 96, 102), np.float32)),      # every block a regression block, ~1500 distinct codes
+              ("noisy quadratic f64 2D", szref.noisy_quadratic((640, 700), np.float64)),
               ("blocky f32", szref.blocky_field(120, np.float32)),           # coefficient codes spread over the whole range, unpredictable ones among them
               ("blocky f64", szref.blocky_field(60, np.float64)),
               ("plane f32", szref.plane_field((66, 70, 74), np.float32))]

@@ -330,6 +330,16 @@ def blocky_field(n, dtype, seed=7):
     return np.ascontiguousarray(f.astype(dtype))
 
 
+def noisy_quadratic(shape, dtype=np.float32, seed=3):
+    """a smooth quadratic + oscillation with noise a few error bounds wide (REL 1e-3): every block is a regression block and the quantised
+    coefficients spread over a thousand and more codes -- the field for the coefficient chain, its Huffman trees and their bit streams"""
+    rng = np.random.default_rng(seed)
+    g = np.meshgrid(*[np.linspace(-1, 1, n) for n in shape], indexing="ij")
+    f = sum((i + 1) * x for i, x in enumerate(g)) + 0.7 * sum(x * x for x in g) + np.sin(3 * g[0]) * np.cos(2 * g[-1])
+    f = f + rng.normal(0, 4e-3 * (f.max() - f.min()), size=shape)
+    return np.ascontiguousarray(f.astype(dtype))
+
+
 def ref_compress_file(path, dtype, shape, cfg, mode, abs_eb, rel, want_dec=False):
     """Worker for process pools: run the compiled reference on an array stored as .npy; returns (size, md5, dec_md5 or None,
     seconds inside SZ_compress_args).  The array is memory-mapped, the reference gets a private contiguous copy."""
