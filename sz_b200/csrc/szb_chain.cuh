@@ -375,16 +375,15 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                     // exact threshold: the smallest float d with lat_mag(d) >= aB, looked for among the floats around (2 aB - 1) prec
                     const T d0 = (T)((double)(2 * aB - 1) * (double)prec);
                     bits_t b0; memcpy(&b0, &d0, sizeof(T));
-                    int first = 99;
-#pragma unroll
-                    for (int o = 4; o >= -4; o--) {
-                        const bits_t b = b0 + (bits_t)(long long)o; T d; memcpy(&d, &b, sizeof(T));
-                        if (lat_mag<T>(d, prec, rprec, use_div) >= (int)aB) first = o;
-                    }
-                    bool ok = first != 99 && d0 > (T)0 && b0 >= (bits_t)16;
-                    {   // below the found float the magnitude must be smaller (monotone function: one more evaluation settles it)
-                        const bits_t b = b0 + (bits_t)(long long)(first - 1); T d; memcpy(&d, &b, sizeof(T));
-                        if (ok && lat_mag<T>(d, prec, rprec, use_div) >= (int)aB) ok = false;
+                    // (2 aB - 1) prec itself passes unless the rounding of d0 went below it; the threshold is at most a few floats
+                    // further down (the quotient and the +1 round to nearest): walk from d0 to the first float that fails, or up to the
+                    // first that passes -- two or three evaluations of the monotone function instead of a table of nine
+                    bool ok = d0 > (T)0 && b0 >= (bits_t)16;
+                    int first = 0;
+                    auto passes = [&](int o) { const bits_t b = b0 + (bits_t)(long long)o; T d; memcpy(&d, &b, sizeof(T)); return lat_mag<T>(d, prec, rprec, use_div) >= (int)aB; };
+                    if (ok) {
+                        if (passes(0)) { while (first > -7 && passes(first - 1)) first--; ok = first > -7; }
+                        else { first = 1; while (first < 7 && !passes(first)) first++; ok = first < 7; }
                     }
                     if (ok) {
                         const bits_t b = b0 + (bits_t)(long long)first; memcpy(&P.thr, &b, sizeof(T));
