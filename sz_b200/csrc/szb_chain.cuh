@@ -472,30 +472,44 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Decoder side (ref: szd_float.c:5809-5819): last = last + 2 (t - R) * prec, or the next stored raw value when t == 0.  The increments
-// (or raw values) and the "is raw" flags come from coeff_dec_prep_kernel; what is left is the add chain itself, run like (S) above: one
-// CTA per coefficient, windows of LAT_W steps, one thread adds 32 increments from registers per word (a word with a raw value in it goes
-// step by step), the helpers fetch the next window and scatter the previous one's results to their block ids.
+// Decoder side (ref: szd_float.c:5809-5819): last = last + 2 (t - R) * prec, or the next stored raw value when t == 0.  Run like (S) above:
+// one CTA per coefficient, windows of LAT_W steps; the helpers turn the next window's codes into increments (or raw values, found by
+// the ordered rank of the zero code among the zeros before it) and scatter the previous window's results to their block ids; one
+// thread adds 32 increments from registers per word (a word with a raw value in it goes step by step).
 template <typename T>
-__global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const T *__restrict__ val /*[ncoef][reg_count]*/, const unsigned char *__restrict__ rst,
-                                                                         uint32_t nb, uint32_t reg_count, const uint32_t *__restrict__ reg_list,
-                                                                         T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
+__global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, const T *__restrict__ cu /*[ncoef][nb] raw values in order*/,
+                                                                         uint32_t nb, uint32_t reg_count, T p0, T p1, T p2, T p3, int r0_, int r1_, int r2_, int r3_,
+                                                                         const uint32_t *__restrict__ reg_list, T *__restrict__ coeff_last /*[ncoef][nb] by block id*/) {
     constexpr int W = LAT_W;
     __shared__ __align__(16) T s_val[2][W];
     __shared__ __align__(16) T s_out[2][W];
-    __shared__ unsigned int s_rm[2][W / 32];              // raw-value flags of a window, one bit per step
+    __shared__ unsigned int s_rm[2][W / 32];              // raw-value flags of a window, one bit per step (also: their count per warp)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, h = tid - 32;
     const int e = blockIdx.x;
-    const T *val_e = val + (size_t)e * reg_count;
-    const unsigned char *rst_e = rst + (size_t)e * reg_count;
+    const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
+    const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
+    const uint16_t *ct_e = coeff_type + (size_t)e * nb;
+    const T *cu_e = cu + (size_t)e * nb;
     const uint32_t nwin = (reg_count + W - 1) / W;
     T last = (T)0;
-    if (warp != 0) {                                       // window 0
-        const bool in = (uint32_t)h < reg_count;
-        s_val[0][h] = in ? val_e[h] : (T)0;
-        const unsigned int rm = __ballot_sync(0xffffffffu, in && rst_e[h] != 0);
-        if (lane == 0) s_rm[0][warp - 1] = rm;
-    }
+    unsigned int zrun = 0;                                 // helpers: raw values consumed by the windows prepared so far
+    // helpers: codes of window `win` -> s_val / s_rm of slot win & 1 (tc: this thread's code, loaded by the caller ahead of time)
+    auto prepare = [&](uint32_t win, int tc, bool in) {
+        const int sl = (int)(win & 1u);
+        const bool z = in && tc == 0;
+        const unsigned int zm = __ballot_sync(0xffffffffu, z);
+        if (lane == 0) s_rm[sl][warp - 1] = zm;
+        lat_helper_bar();
+        unsigned int before = 0, tot = 0;
+#pragma unroll
+        for (int q = 0; q < W / 32; q++) { const unsigned int c = __popc(s_rm[sl][q]); before += q < warp - 1 ? c : 0u; tot += c; }
+        T v = (T)0;
+        if (z) v = cu_e[zrun + before + __popc(zm & ((1u << lane) - 1u))];
+        else if (in) { const T dq = (T)(2 * (tc - rad)); v = dq * prec; }
+        s_val[sl][h] = v;
+        zrun += tot;
+    };
+    if (warp != 0) { const bool in = (uint32_t)h < reg_count; prepare(0u, in ? (int)ct_e[h] : 1, in); }
     __syncthreads();
     for (uint32_t w = 0; w <= nwin; w++) {
         if (warp == 0) {
@@ -527,20 +541,16 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const T
                 }
             }
         } else {
-            // the next window's values and flags (loaded first, stored last: the scatter hides their latency)
+            // the next window's codes (loaded first, used last: the scatter hides their latency)
             const uint32_t pn = (w + 1) * W + (uint32_t)h;
             const bool in_n = w + 1 < nwin && pn < reg_count;
-            T vn = (T)0; unsigned char rn = 0;
-            if (in_n) { vn = val_e[pn]; rn = rst_e[pn]; }
+            int tn = 1;
+            if (in_n) tn = (int)ct_e[pn];
             if (w >= 1) {                                  // the previous window's results to their blocks
                 const uint32_t pp = (w - 1) * W + (uint32_t)h;
                 if (pp < reg_count) coeff_last[(size_t)e * nb + reg_list[pp]] = s_out[(w - 1) & 1u][h];
             }
-            if (w + 1 < nwin) {
-                s_val[(w + 1) & 1u][h] = vn;
-                const unsigned int rm = __ballot_sync(0xffffffffu, in_n && rn != 0);
-                if (lane == 0) s_rm[(w + 1) & 1u][warp - 1] = rm;
-            }
+            if (w + 1 < nwin) prepare(w + 1, tn, in_n);
         }
         __syncthreads();
     }

@@ -1296,12 +1296,18 @@ __global__ void __launch_bounds__(DECW_TB) dec_write_bm_kernel(const uint32_t *_
         const uint64_t limit = total_bits + 64;
         if (hi > limit) hi = limit;
         BitReader br; br.init(words, start_used[sidx]);
-        BMIter it; it.init(g, p);
+        // The raster position is only needed where an unpredictable value goes (code 0, rare): the block-major walk is not advanced
+        // per symbol but caught up there -- stepped when the previous zero is near, set up anew otherwise.
+        BMIter it; uint64_t it_p = ~0ull;
         while (br.pos < hi && p < n) {
             const uint32_t sym = dec_symbol(br, s_lut, tr);
             if (staged) ss[p - wbase] = (uint16_t)sym; else codes_bm[p] = (uint16_t)sym;
-            if (sym == 0 && field_out) { if (zr < unpred_count) field_out[it.raster] = unpred[zr]; zr++; }
-            it.next(g);
+            if (sym == 0 && field_out) {
+                if (it_p == ~0ull || p - it_p > 48u) it.init(g, p); else for (uint64_t q = it_p; q < p; q++) it.next(g);
+                it_p = p;
+                if (zr < unpred_count) field_out[it.raster] = unpred[zr];
+                zr++;
+            }
             p++;
         }
     }
@@ -1364,48 +1370,7 @@ __global__ void fill_u16_kernel(uint16_t *out, uint64_t n, uint16_t v) {
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) out[i] = v;
 }
 
-// coefficient chain decode (S1, decoder side; ref: szd_float.c:5809-5819): last = last + 2(t-R)*prec, or the next stored raw
-// value when t == 0.  Only the running float addition is serial; everything else is prepared by a parallel kernel first.
-// step 1 (parallel, one CTA per coefficient): every regression block's increment 2*(code-radius)*precision, or -- for an
-// unpredictable coefficient (code 0) -- its raw value, found by the ordered rank of the zero among the zeros before it
-template <typename T>
-__global__ void __launch_bounds__(1024) coeff_dec_prep_kernel(const uint16_t *__restrict__ coeff_type /*[ncoef][nb]*/, uint32_t nb, uint32_t reg_count,
-                                                              T p0, T p1, T p2, T p3, int r0_, int r1_, int r2_, int r3_,
-                                                              const T *__restrict__ cu /*[ncoef][nb] raw values in order*/,
-                                                              T *__restrict__ val /*[ncoef][reg_count]*/, unsigned char *__restrict__ rst /*[ncoef][reg_count]*/) {
-    const int e = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
-    const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
-    const T *cue = cu + (size_t)e * nb;
-    __shared__ unsigned int s_w[32];
-    __shared__ unsigned int s_run;
-    if (tid == 0) s_run = 0;
-    __syncthreads();
-    for (uint32_t base = 0; base < reg_count; base += 1024) {
-        const uint32_t i = base + tid;
-        const int tcode = (i < reg_count) ? (int)coeff_type[(size_t)e * nb + i] : 1;
-        const bool z = tcode == 0;
-        const unsigned int zm = __ballot_sync(0xffffffffu, z);
-        if (lane == 0) s_w[warp] = __popc(zm);
-        __syncthreads();
-        unsigned int before = 0, tot = 0;
-#pragma unroll
-        for (int w2 = 0; w2 < 32; w2++) { const unsigned int c = s_w[w2]; before += (w2 < warp) ? c : 0u; tot += c; }
-        const unsigned int run = s_run;
-        if (i < reg_count) {
-            T v;
-            if (z) v = cue[run + before + __popc(zm & ((1u << lane) - 1u))];
-            else { T dq = (T)(2 * (tcode - rad)); v = dq * prec; }
-            val[(size_t)e * reg_count + i] = v;
-            rst[(size_t)e * reg_count + i] = z ? 1 : 0;
-        }
-        __syncthreads();
-        if (tid == 0) s_run = run + tot;
-        __syncthreads();
-    }
-}
-
-// step 2 (serial): the add chain itself, coeff_chain_decode_kernel in szb_chain.cuh
+// coefficient chain decode (S1, decoder side; ref: szd_float.c:5809-5819): coeff_chain_decode_kernel in szb_chain.cuh
 
 
 // indicator bits (MSB-first, 1 = Lorenzo; ref: TypeManager.c:47-71) <-> byte-per-block array

@@ -1289,11 +1289,11 @@ static int decompress_impl(Ctx &c, const szb200_job &job, const void *body, size
     unsigned long long *d_dec_totals = nullptr; uint64_t dec_expect[5] = {0, 0, 0, 0, 0};
     auto chain_tail = [&](cudaStream_t st) -> int {
         if (reg_count == 0) return 0;
-        T *d_dval = (T *)c.get("dchain_val", sizeof(T) * 4ull * reg_count + 64);
-        unsigned char *d_drst = (unsigned char *)c.get("dchain_rst", 4ull * reg_count + 64);
-        if (!d_dval || !d_drst) return SZ_NSCS;
-        coeff_dec_prep_kernel<T><<<ncoef, 1024, 0, st>>>(d_ctype, nb, reg_count, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3], d_cu, d_dval, d_drst); KCHECK();
-        coeff_chain_decode_kernel<T><<<ncoef, LAT_THREADS, 0, st>>>(d_dval, d_drst, nb, reg_count, d_list, d_clast); KCHECK();
+        // The serial chains run beside the main write pass.  They ask for shared memory they do not use, so that at most one CTA of that
+        // pass fits on an SM next to a chain: the chain's speed is the issue rate its one thread gets.
+        const int chain_pad = (int)std::min<size_t>(c.smem_optin > 80 * 1024 ? c.smem_optin - 80 * 1024 : 0, 150 * 1024);
+        CU(cudaFuncSetAttribute(coeff_chain_decode_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, chain_pad));
+        coeff_chain_decode_kernel<T><<<ncoef, LAT_THREADS, chain_pad, st>>>(d_ctype, d_cu, nb, reg_count, prec[0], prec[1], prec[2], prec[3], crad[0], crad[1], crad[2], crad[3], d_list, d_clast); KCHECK();
         return 0;
     };
     {
