@@ -509,7 +509,13 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const u
         s_val[sl][h] = v;
         zrun += tot;
     };
-    if (warp != 0) { const bool in = (uint32_t)h < reg_count; prepare(0u, in ? (int)ct_e[h] : 1, in); }
+    int t_ahead = 1;                                       // helpers: this thread's code of the window after the next one, loaded a tick early
+    if (warp != 0) {
+        const bool in = (uint32_t)h < reg_count;
+        prepare(0u, in ? (int)ct_e[h] : 1, in);
+        const uint32_t p1 = (uint32_t)W + (uint32_t)h;
+        if (p1 < reg_count) t_ahead = (int)ct_e[p1];
+    }
     __syncthreads();
     for (uint32_t w = 0; w <= nwin; w++) {
         if (warp == 0) {
@@ -541,11 +547,11 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const u
                 }
             }
         } else {
-            // the next window's codes (loaded first, used last: the scatter hides their latency)
+            // the next window's codes were loaded a tick ago; the ones after it are requested now
             const uint32_t pn = (w + 1) * W + (uint32_t)h;
             const bool in_n = w + 1 < nwin && pn < reg_count;
-            int tn = 1;
-            if (in_n) tn = (int)ct_e[pn];
+            const int tn = t_ahead;
+            { const uint32_t p2 = (w + 2) * W + (uint32_t)h; t_ahead = p2 < reg_count ? (int)ct_e[p2] : 1; }
             if (w >= 1) {                                  // the previous window's results to their blocks
                 const uint32_t pp = (w - 1) * W + (uint32_t)h;
                 if (pp < reg_count) coeff_last[(size_t)e * nb + reg_list[pp]] = s_out[(w - 1) & 1u][h];

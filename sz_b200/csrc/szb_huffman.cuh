@@ -997,10 +997,19 @@ struct DecTree { const uint32_t *L, *R, *C; const uint8_t *leaf; uint32_t nodeCo
 
 // lut[v], v = the next DEC_K stream bits (MSB first): a codeword of length <= DEC_K that prefixes v -> LEAF | len << 16 | symbol;
 // otherwise the index of the internal node reached after DEC_K bits (the walk continues from there bit by bit).
+// Behind it, two tables of ALL the codewords that lie completely inside the window (short codes: several symbols per look-up):
+//   lutS[v] (u32, at lut + 2^K):   bits consumed | start mask << 4 | zero-symbol start mask << 15   (bit j of a mask: a symbol starts at
+//                                  window offset j); 0 when not even the first codeword fits.  For the synchronisation rounds, which
+//                                  only need positions and counts.
+//   lutW[v] (u64, at lut + 2^(K+1)): k | bits of the first k symbols << 3 | "a zero among them" << 7 | symbols, 8 bits each, from bit 8;
+//                                  k <= 6 leading symbols that are all below 256; k = 0: none.  For the write pass.
+constexpr int DEC_LUT_WORDS = (1 << DEC_K) * 4;                // u32 words of the three tables together
 __global__ void dec_lut_kernel(const uint32_t *__restrict__ L, const uint32_t *__restrict__ R, const uint32_t *__restrict__ C,
                                const uint8_t *__restrict__ leaf, uint32_t *__restrict__ lut) {
     const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= (1u << DEC_K)) return;
+    uint32_t *lutS = lut + (1u << DEC_K);
+    unsigned long long *lutW = reinterpret_cast<unsigned long long *>(lut + (2u << DEC_K));
     uint32_t node = 0, e = 0;
     bool done = false;
     for (int d = 0; d < DEC_K; d++) {
@@ -1010,6 +1019,27 @@ __global__ void dec_lut_kernel(const uint32_t *__restrict__ L, const uint32_t *_
         if ((nx & DEC_CHILD_LEAF) || node == 0) { e = DEC_LEAF | ((uint32_t)(d + 1) << 16) | (C[node] & 0xffffu); done = true; break; }
     }
     lut[v] = done ? e : node;
+    // every codeword inside the window, greedily from offset 0
+    uint32_t smask = 0, zmask = 0, used = 0, kw = 0, usedw = 0, zw = 0;
+    unsigned long long symsw = 0;
+    bool wopen = true;
+    for (uint32_t off = 0; off < (uint32_t)DEC_K;) {
+        uint32_t nd = 0, len = 0; bool hit = false;
+        for (uint32_t d = off; d < (uint32_t)DEC_K; d++) {
+            const uint32_t bit = (v >> (DEC_K - 1 - d)) & 1u;
+            const uint32_t nx = bit ? R[nd] : L[nd];
+            nd = nx & ~DEC_CHILD_LEAF;
+            if ((nx & DEC_CHILD_LEAF) || nd == 0) { len = d + 1 - off; hit = true; break; }
+        }
+        if (!hit) break;
+        const uint32_t sym = C[nd];
+        smask |= 1u << off; if (sym == 0) zmask |= 1u << off;
+        used = off + len;
+        if (wopen && kw < 6 && sym < 256u) { symsw |= (unsigned long long)sym << (8 * kw); kw++; usedw = used; if (sym == 0) zw = 1; } else wopen = false;
+        off += len;
+    }
+    lutS[v] = smask ? (used | (smask << 4) | (zmask << 15)) : 0u;
+    lutW[v] = kw ? ((unsigned long long)kw | ((unsigned long long)usedw << 3) | ((unsigned long long)zw << 7) | (symsw << 8)) : 0ull;
 }
 
 // MSB-first bit reader over the 4-byte aligned, zero-padded copy of the payload (big-endian words)
@@ -1155,10 +1185,10 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const DecJobList *__restr
     // of the symbol starts of its latest decode and one of the starts of zero symbols (shared memory).  A re-decode stops at the
     // first position whose old bit is set: from there on everything is known, and the counts follow from the masks.  The masks
     // only live inside one launch; a thread's first decode in a launch always runs to the end.
-    __shared__ uint32_t s_lut[1 << DEC_K];
+    __shared__ uint32_t s_lut[1 << DEC_K], s_lutS[1 << DEC_K];
     __shared__ unsigned long long s_end[256];
     __shared__ uint32_t s_bm[256][9], s_zm[256][9];            // 8 words + 1 of padding (bank spread)
-    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
+    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) { s_lut[q] = tr.lut[q]; s_lutS[q] = tr.lut[(1 << DEC_K) + q]; }
     const int tid = threadIdx.x;
     const uint64_t sidx = (uint64_t)block * blockDim.x + tid;
     const bool active = sidx < nsub;
@@ -1189,17 +1219,33 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const DecJobList *__restr
                 cnt = 0; zc = 0;
 #pragma unroll
                 for (int w = 0; w < 8; w++) { bm[w] = 0u; zm[w] = 0u; }
-                uint32_t accb = 0, accz = 0; int curw = 0;
+                // two words of start bits at a time (a look-up covers DEC_K positions and may straddle a word)
+                unsigned long long accb = 0, accz = 0; int curw = 0;
                 while (br.pos < hi) {
                     const uint32_t off = (uint32_t)(br.pos - lo);
                     const int w = (int)(off >> 5);
-                    if (w != curw) { bm[curw] = accb; zm[curw] = accz; accb = 0; accz = 0; curw = w; }
-                    const uint32_t sym = dec_symbol(br, s_lut, tr);
-                    accb |= 1u << (off & 31u);
-                    if (sym == 0) { accz |= 1u << (off & 31u); zc++; }
-                    cnt++;
+                    while (curw < w) { bm[curw] = (uint32_t)accb; zm[curw] = (uint32_t)accz; accb >>= 32; accz >>= 32; curw++; }
+                    br.refill();
+                    const uint32_t e = s_lutS[(uint32_t)(br.buf >> (64 - DEC_K))];
+                    const uint32_t sm = (e >> 4) & ((1u << DEC_K) - 1u);
+                    if (sm) {
+                        // all the code words inside the window at once; those that start at or behind `hi` belong to the next sub-sequence
+                        const unsigned long long room = hi - br.pos;
+                        const uint32_t m = room < (unsigned long long)DEC_K ? (sm & ((1u << (uint32_t)room) - 1u)) : sm;
+                        const uint32_t z = (e >> 15) & m;
+                        cnt += __popc(m); zc += __popc(z);
+                        accb |= (unsigned long long)m << (off & 31u); accz |= (unsigned long long)z << (off & 31u);
+                        const uint32_t rest = sm & ~m;
+                        br.consume(rest ? (__ffs((int)rest) - 1) : (int)(e & 15u));
+                    } else {
+                        const uint32_t sym = dec_symbol(br, s_lut, tr);
+                        accb |= 1ull << (off & 31u);
+                        if (sym == 0) { accz |= 1ull << (off & 31u); zc++; }
+                        cnt++;
+                    }
                 }
-                bm[curw] = accb; zm[curw] = accz;
+                bm[curw] = (uint32_t)accb; zm[curw] = (uint32_t)accz;
+                if (curw + 1 < 8) { bm[curw + 1] = (uint32_t)(accb >> 32); zm[curw + 1] = (uint32_t)(accz >> 32); }
                 my_end = br.pos;
                 have_mask = true;
             } else {
@@ -1259,6 +1305,7 @@ __global__ void __launch_bounds__(256) dec_sync_kernel(const DecJobList *__restr
 // its own symbols one by one touches a different 32-byte sector per lane and per symbol: ~0.7 ms of sector traffic at 512^3).
 // Unpredictable values (code 0, rare) are pre-placed into the output field at their raster position.
 constexpr int DECW_TB = 128, DECW_CAP = 4096;               // symbols a warp can stage; a longer run (codes < 2 bits on average) is stored directly
+constexpr size_t DECW_SMEM = 8u * (1u << DEC_K) + (size_t)(DECW_TB / 32) * DECW_CAP * 2u;   // dynamic shared memory of dec_write_bm_kernel
 // A main tree that is one leaf with symbol 0 (ref: Huffman.c:316-321 fills the type array with the root's symbol whatever it is):
 // every point is unpredictable, the list of raw values IS the field in block-major order -- each thread places 16 of them.
 template <typename T>
@@ -1277,8 +1324,13 @@ __global__ void __launch_bounds__(DECW_TB) dec_write_bm_kernel(const uint32_t *_
                                                               uint64_t n, Geom g, uint16_t *__restrict__ codes_bm, const T *__restrict__ unpred,
                                                               uint64_t unpred_count, T *field_out) {
     __shared__ uint32_t s_lut[1 << DEC_K];
-    __shared__ uint16_t s_sym[DECW_TB / 32][DECW_CAP];
-    for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) s_lut[q] = tr.lut[q];
+    extern __shared__ __align__(16) unsigned char s_dyn_w[];    // DECW_SMEM bytes: the multi-symbol table, then the warps' staging areas
+    unsigned long long *s_lutW = reinterpret_cast<unsigned long long *>(s_dyn_w);
+    uint16_t (*s_sym)[DECW_CAP] = reinterpret_cast<uint16_t (*)[DECW_CAP]>(s_dyn_w + 8u * (1u << DEC_K));
+    {
+        const unsigned long long *gW = reinterpret_cast<const unsigned long long *>(tr.lut + (2u << DEC_K));
+        for (int q = threadIdx.x; q < (1 << DEC_K); q += blockDim.x) { s_lut[q] = tr.lut[q]; s_lutW[q] = gW[q]; }
+    }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t sidx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1300,6 +1352,19 @@ __global__ void __launch_bounds__(DECW_TB) dec_write_bm_kernel(const uint32_t *_
         // per symbol but caught up there -- stepped when the previous zero is near, set up anew otherwise.
         BMIter it; uint64_t it_p = ~0ull;
         while (br.pos < hi && p < n) {
+            br.refill();
+            const unsigned long long e = s_lutW[(uint32_t)(br.buf >> (64 - DEC_K))];
+            const uint32_t k = (uint32_t)e & 7u;
+            if (k != 0u && !(e & 0x80ull) && br.pos + (uint64_t)DEC_K <= hi && p + k <= n) {
+                // up to six short code words in one look-up (none of them the zero code, all of them inside this sub-sequence)
+#pragma unroll
+                for (uint32_t j = 0; j < 6; j++) {
+                    if (j < k) { const uint16_t sy = (uint16_t)((e >> (8u + 8u * j)) & 0xffull); if (staged) ss[p - wbase + j] = sy; else codes_bm[p + j] = sy; }
+                }
+                p += k;
+                br.consume((int)((e >> 3) & 15ull));
+                continue;
+            }
             const uint32_t sym = dec_symbol(br, s_lut, tr);
             if (staged) ss[p - wbase] = (uint16_t)sym; else codes_bm[p] = (uint16_t)sym;
             if (sym == 0 && field_out) {

@@ -117,6 +117,10 @@ struct Ctx {
         }
         return pinned;
     }
+    int need_pinned_words() {
+        if (!pinned_words && cudaMallocHost((void **)&pinned_words, 256) != cudaSuccess) { pinned_words = nullptr; cudaGetLastError(); set_err("pinned alloc failed"); return SZ_NSCS; }
+        return 0;
+    }
     void release() {
         for (auto &kv : bufs) if (kv.second.p) cudaFree(kv.second.p);
         bufs.clear();
@@ -727,7 +731,7 @@ static int compress_impl(Ctx &c, const szb200_job &job, const T *d_x, void *dst,
     unsigned long long *d_rank = (unsigned long long *)c.get("reg_rank", 8ull * nb + 64);
     unsigned long long *d_tot = (unsigned long long *)c.get("totals", 256);
     if (!d_reg || !d_regc || !d_clast || !d_cunp || !d_ctype || !d_ind || !d_flags || !d_list || !d_rank || !d_tot) return SZ_NSCS;
-    if (!c.pinned_words && cudaMallocHost((void **)&c.pinned_words, 256) != cudaSuccess) { c.pinned_words = nullptr; cudaGetLastError(); set_err("pinned alloc failed"); return SZ_NSCS; }
+    if (c.need_pinned_words()) return SZ_NSCS;
     auto launch_fit = [&](cudaStream_t st, int scan_slot, int um, T mn) -> int {
         int grid = (nb + 127) / 128;
         if (job.dim == 3) fit_select_kernel<T, 3><<<grid, 128, 0, st>>>(d_x, g, noise, um, mn, d_reg, d_ind);
@@ -1010,8 +1014,9 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
     for (int j = 0; j < njobs; j++) {
         DecJob &J = jobs[j];
         snprintf(nm, sizeof(nm), "dec_tree%d", J.slot);
-        unsigned char *tb = (unsigned char *)c.get(nm, 16ull * J.nodeCount + 1024 + 4ull * (1u << DEC_K)); if (!tb) return SZ_NSCS;
-        J.lut = (uint32_t *)tb; J.L = J.lut + (1u << DEC_K); J.R = J.L + J.nodeCount; J.C = J.R + J.nodeCount; J.leaf = (uint8_t *)(J.C + J.nodeCount);
+        unsigned char *tb = (unsigned char *)c.get(nm, 16ull * J.nodeCount + 1024 + 4ull * DEC_LUT_WORDS); if (!tb) return SZ_NSCS;
+        // the three look-up tables (dec_lut_kernel), then the unpacked tree
+        J.lut = (uint32_t *)tb; J.L = J.lut + DEC_LUT_WORDS; J.R = J.L + J.nodeCount; J.C = J.R + J.nodeCount; J.leaf = (uint8_t *)(J.C + J.nodeCount);
         dec_tree_unpack_kernel<<<(J.nodeCount + 255) / 256, 256, 0, c.stream>>>(J.d_tree, J.nodeCount, J.L, J.R, J.C, J.leaf); KCHECK();
         // a tree whose root is a leaf has exactly one node (ref: Huffman.c:316-321); only then is the root's symbol needed on the host
         roots[j].leaf = J.nodeCount == 1 ? 1 : 0; roots[j].sym = 0;
@@ -1045,49 +1050,17 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         J.count = (uint32_t *)(J.zero_off + J.nsub + 1); J.zcount = J.count + J.nsub + 1;
     }
     pmark();
-    // Jacobi rounds: round 0 is the speculative decode; a job has converged when a whole round moved no start position.
-    // One launch per round covers every job that has not converged yet.
-    DecJobList *d_list = (DecJobList *)c.get("dec_joblist", sizeof(DecJobList) + 64); if (!d_list) return SZ_NSCS;
-    for (int round = 0;; round++) {
-        DecJobList L; memset(&L, 0, sizeof(L));
-        uint32_t ctas = 0; bool any = false;
-        for (int j = 0; j < njobs; j++) {
-            DecJob &J = jobs[j];
-            DecJobDev &D = L.j[j];
-            D.cta_begin = ctas; D.active = 0;
-            if (J.single_leaf) continue;
-            D.words = J.words; D.total_bits = J.total_bits; D.nsub = J.nsub; D.tr = DecTree{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
-            D.end_prev = J.ep; D.end_cur = J.ec; D.start_used = J.start_used; D.count = J.count; D.zcount = J.zcount; D.changed = d_changed + j;
-            ctas += (uint32_t)((J.nsub + 255) / 256);
-            if (J.converged) continue;
-            D.active = 1; any = true;
-            std::swap(J.ep, J.ec);
-        }
-        L.n = njobs;
-        if (!any) break;
-        CU(cudaMemsetAsync(d_changed, 0, 4 * 8, c.stream));
-        CU(cudaMemcpyAsync(d_list, &L, sizeof(L), cudaMemcpyHostToDevice, c.stream));       // pageable source: staged before the call returns
-        dec_sync_kernel<<<ctas, 256, 0, c.stream>>>(d_list, round == 0 ? 1 : 0); KCHECK();
-        if (round == 0) continue;                                // the first round always changes something
-        unsigned int ch[8];
-        CU(cudaMemcpyAsync(ch, d_changed, 4 * njobs, cudaMemcpyDeviceToHost, c.stream));
-        CU(cudaStreamSynchronize(c.stream));
-        for (int j = 0; j < njobs; j++) if (!jobs[j].converged && !ch[j]) jobs[j].converged = true;
-        if (round > 100000) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
-    }
-    pmark();
     // the prefix sums also give the number of symbols every stream really holds; the caller compares them with the counts the
     // header promises once the job is done (a truncated stream otherwise decodes "successfully" into too few symbols)
     unsigned long long *d_dtot = (unsigned long long *)c.get("dec_totals", 64); if (!d_dtot) return SZ_NSCS;
     CU(cudaMemsetAsync(d_dtot, 0, 64, c.stream));
     *d_totals_out = d_dtot;
     for (int j = 0; j < 5; j++) expect[j] = (j < njobs && !jobs[j].single_leaf) ? jobs[j].nsym : 0;
-    // prefix sums and the write pass: the main stream on the context's stream; all coefficient streams beside it on the second
-    // one, with one launch for their prefix sums and one for their write passes
-    CU(cudaEventRecord(c.ev_fork, c.stream));
-    CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+    // The coefficient streams' prefix sums and write passes (one launch each for all of them) and the work that only needs the
+    // coefficient codes (the coefficient chain) go to the second stream, forked from the main one where this is called.
     bool side_used = false;
-    {
+    auto launch_side = [&](bool fork) -> int {
+        if (fork) { CU(cudaEventRecord(c.ev_fork, c.stream)); CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0)); }
         DecJobList L; memset(&L, 0, sizeof(L));
         uint32_t ctas = 0;
         for (int j = 0; j < njobs; j++) {
@@ -1106,7 +1079,91 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
             dec_coef_write_kernel<<<ctas, 256, 0, c.stream2>>>(d_clist); KCHECK();
             side_used = true;
         }
+        if (side_tail) { if (side_tail(c.stream2)) return SZ_NSCS; side_used = true; }
+        return 0;
+    };
+    // Jacobi rounds: round 0 is the speculative decode; a job has converged when a whole round moved no start position.
+    // One launch per round covers every job that has not converged yet.  Round 0 starts every CTA's first sub-sequence at a guess, round 1
+    // hands the true starts across the CTA boundaries and is nearly always the last one: the coefficient streams' side branch is queued
+    // right behind it, before its verdict is read back, and queued again only if the verdict asks for another round on one of them.
+    if (c.need_pinned_words()) return SZ_NSCS;
+    DecJobList *d_list = (DecJobList *)c.get("dec_joblist", sizeof(DecJobList) + 64), *d_list2 = (DecJobList *)c.get("dec_joblist2", sizeof(DecJobList) + 64);
+    if (!d_list || !d_list2) return SZ_NSCS;
+    unsigned int *d_changed2 = d_changed + 16;
+    // one round for the jobs `take` selects (not yet converged ones), on stream `st`
+    auto launch_round = [&](cudaStream_t st, const std::function<bool(const DecJob &)> &take, bool first, DecJobList *d_l, unsigned int *d_ch, bool &any) -> int {
+        DecJobList L; memset(&L, 0, sizeof(L));
+        uint32_t ctas = 0; any = false;
+        for (int j = 0; j < njobs; j++) {
+            DecJob &J = jobs[j];
+            DecJobDev &D = L.j[j];
+            D.cta_begin = ctas; D.active = 0;
+            if (J.single_leaf || !take(J)) continue;
+            D.words = J.words; D.total_bits = J.total_bits; D.nsub = J.nsub; D.tr = DecTree{J.L, J.R, J.C, J.leaf, J.nodeCount, J.lut};
+            D.end_prev = J.ep; D.end_cur = J.ec; D.start_used = J.start_used; D.count = J.count; D.zcount = J.zcount; D.changed = d_ch + j;
+            ctas += (uint32_t)((J.nsub + 255) / 256);
+            if (J.converged) continue;
+            D.active = 1; any = true;
+            std::swap(J.ep, J.ec);
+        }
+        L.n = njobs;
+        if (!any) return 0;
+        CU(cudaMemsetAsync(d_ch, 0, 4 * 8, st));
+        CU(cudaMemcpyAsync(d_l, &L, sizeof(L), cudaMemcpyHostToDevice, st));       // pageable source: staged before the call returns
+        dec_sync_kernel<<<ctas, 256, 0, st>>>(d_l, first ? 1 : 0); KCHECK();
+        return 0;
+    };
+    auto is_coef = [](const DecJob &J) { return !J.blockmajor; };
+    auto is_main = [](const DecJob &J) { return J.blockmajor; };
+    auto is_any = [](const DecJob &) { return true; };
+    // The coefficient streams (a few CTAs each) go through their two rounds, their prefix sums, write passes and the coefficient chain on
+    // the second stream, from the start, beside the main stream's rounds.  Round 1's verdict on them is read back when the main
+    // stream is done; should it ask for another round (not seen), the rounds go on below and the side branch is queued once more.
+    bool side_early = false, coef_moved = false;
+    {
+        bool have_coef = false;
+        for (int j = 0; j < njobs; j++) if (!jobs[j].single_leaf && !jobs[j].blockmajor) have_coef = true;
+        if (have_coef) {
+            bool any = false;
+            CU(cudaEventRecord(c.ev_fork, c.stream));
+            CU(cudaStreamWaitEvent(c.stream2, c.ev_fork, 0));
+            if (launch_round(c.stream2, is_coef, true, d_list2, d_changed2, any)) return SZ_NSCS;
+            if (launch_round(c.stream2, is_coef, false, d_list2, d_changed2, any)) return SZ_NSCS;
+            CU(cudaMemcpyAsync(c.pinned_words + 8, d_changed2, 4 * 8, cudaMemcpyDeviceToHost, c.stream2));
+            CU(cudaEventRecord(c.ev_side0, c.stream2));
+            if (launch_side(false)) return SZ_NSCS;
+            side_early = true;
+        }
     }
+    for (int round = 0;; round++) {
+        bool any = false;
+        if (launch_round(c.stream, side_early ? std::function<bool(const DecJob &)>(is_main) : std::function<bool(const DecJob &)>(is_any), round == 0, d_list, d_changed, any)) return SZ_NSCS;
+        if (!any) break;
+        if (round == 0) continue;                                // the first round always changes something
+        unsigned int ch[8];
+        CU(cudaMemcpyAsync(ch, d_changed, 4 * njobs, cudaMemcpyDeviceToHost, c.stream));
+        CU(cudaStreamSynchronize(c.stream));
+        for (int j = 0; j < njobs; j++) if ((!side_early || jobs[j].blockmajor) && !jobs[j].converged && !ch[j]) jobs[j].converged = true;
+        if (round > 100000) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
+    }
+    if (side_early) {
+        CU(cudaEventSynchronize(c.ev_side0));
+        const unsigned int *ch2 = reinterpret_cast<const unsigned int *>(c.pinned_words + 8);
+        for (int j = 0; j < njobs; j++) if (!jobs[j].single_leaf && !jobs[j].blockmajor) { if (ch2[j]) coef_moved = true; else jobs[j].converged = true; }
+        for (int round = 2; coef_moved; round++) {               // more rounds for the coefficient streams (on the main stream, in order behind the side branch)
+            bool any = false;
+            CU(cudaEventRecord(c.ev_join, c.stream2)); CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
+            if (launch_round(c.stream, is_coef, false, d_list, d_changed, any)) return SZ_NSCS;
+            if (!any) break;
+            unsigned int ch[8];
+            CU(cudaMemcpyAsync(ch, d_changed, 4 * njobs, cudaMemcpyDeviceToHost, c.stream));
+            CU(cudaStreamSynchronize(c.stream));
+            for (int j = 0; j < njobs; j++) if (!jobs[j].blockmajor && !jobs[j].converged && !ch[j]) jobs[j].converged = true;
+            if (round > 100000) { set_err("Huffman decode failed to synchronise"); return SZ_NSCS; }
+        }
+    }
+    pmark();
+    if (!side_early || coef_moved) { if (launch_side(true)) return SZ_NSCS; }     // (again: the coefficient streams needed more rounds)
     for (int j = 0; j < njobs; j++) {
         DecJob &J = jobs[j];
         if (J.single_leaf || !J.blockmajor) continue;
@@ -1114,11 +1171,10 @@ static int huff_decode_all(Ctx &c, DecJob *jobs, int njobs, const Geom &g, const
         if (launch_scan(c, c.stream, 0, J.count, J.nsub, J.sym_off, d_dtot + j)) return SZ_NSCS;
         if (launch_scan(c, c.stream, 0, J.zcount, J.nsub, J.zero_off, nullptr)) return SZ_NSCS;
         const unsigned grid = (unsigned)((J.nsub + DECW_TB - 1) / DECW_TB);
-        dec_write_bm_kernel<T><<<grid, DECW_TB, 0, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
+        CU(cudaFuncSetAttribute(dec_write_bm_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DECW_SMEM));
+        dec_write_bm_kernel<T><<<grid, DECW_TB, DECW_SMEM, c.stream>>>(J.words, J.total_bits, J.nsub, tr, J.start_used, J.sym_off, J.zero_off, J.nsym, g, J.d_out, d_unpred, unpred_count, d_field);
         KCHECK();
     }
-    // work that only needs the coefficient codes (the coefficient chain) continues on the second stream, beside the main write pass
-    if (side_tail) { if (side_tail(c.stream2)) return SZ_NSCS; side_used = true; }
     pmark();
     if (side_used) { CU(cudaEventRecord(c.ev_join, c.stream2)); CU(cudaStreamWaitEvent(c.stream, c.ev_join, 0)); }
     pmark();
