@@ -33,7 +33,7 @@
 namespace szb {
 
 constexpr int LAT_W = 256;                    // steps per window = helper threads
-constexpr int LAT_THREADS = LAT_W + 32;       // warp 0: the serial thread; warps 1..8: helpers
+constexpr int LAT_THREADS = 11 * 32;           // warp 0: the serial thread; warps 1-3, 5-7, 9, 10: helpers; warps 4 and 8 share warp 0's scheduler and stay idle
 constexpr float LAT_BAND = 0.35f;             // drift band in units of mag eps sqrt(steps), see (G1)
 template <typename T> struct LatEps;
 template <> struct LatEps<float> { static constexpr double eps = 1.0 / 8388608.0; };              // 2^-23: ulp(x) <= eps |x|
@@ -206,7 +206,9 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
     __shared__ unsigned char s_tie[W];            // (G1) bit 0: may be at a midpoint, bit 1: cur above its lattice point, bit 2: PAIR data ready; (G2) bit 3: at a midpoint
     __shared__ float s_wmag[W / 32];
     __shared__ unsigned int s_wcnt[2][W / 32];    // by tick parity: read after the tick's barrier, written again one tick later
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, h = tid - 32;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const bool helper = warp != 0 && warp != 4 && warp != 8;          // the serial thread keeps its scheduler to itself
+    const int hw = warp - 1 - (warp > 4 ? 1 : 0) - (warp > 8 ? 1 : 0), h = hw * 32 + lane;
     const int e = blockIdx.x;
     const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
     const T rprec = (T)1 / prec;
@@ -227,7 +229,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
     while (vw.valid || sw.valid || gw.valid) {
         // ======================== (G2): the window (S) runs in this tick gets its final table ========================
         if (sw.valid) {
-            if (warp != 0) {
+            if (helper) {
                 LatSlot<T> &L = s_slot[sw.slot];
                 // measured drift: where the exact `last` entering the window lies relative to the lattice the guess used
                 const double y = ((double)sw.entry - P.base) * inv2p, yk = rint(y), rho = y - yk;
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                 else if (pairform) { inc = P.fincA; incB = P.fincB; thr = P.fthr; q = P.fqA; qB = P.fqB; }
                 if (full || !P.in) { inc = (T)0; q = 0; }
                 const unsigned int hm = __ballot_sync(0xffffffffu, pairform), xm = __ballot_sync(0xffffffffu, full);
-                if (lane == 0) { L.hm[warp - 1] = hm; L.xm[warp - 1] = xm; }
+                if (lane == 0) { L.hm[hw] = hm; L.xm[hw] = xm; }
                 L.inc[h] = inc; L.incB[h] = incB; L.thr[h] = thr; L.q[h] = q; L.qB[h] = qB;
                 n_pair += __popc(hm); n_full += __popc(xm);
             }
@@ -275,7 +277,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                 L.exit = L.out[wend - 1];
                 cyc_s += clock64() - c0;
             }
-        } else {
+        } else if (helper) {
             const long long c0 = clock64();
             // global loads of this tick first: their latency hides behind (V)
             T cur_g = (T)0; uint32_t blk_v = 0;
@@ -297,7 +299,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                     v_ct = ct;
                 }
                 zmask = __ballot_sync(0xffffffffu, h < vw.cnt && ct == 0);
-                if (lane == 0) s_wcnt[n_ticks & 1u][warp - 1] = __popc(zmask);
+                if (lane == 0) s_wcnt[n_ticks & 1u][hw] = __popc(zmask);
             }
             lat_helper_bar();
             if (vw.valid && h < vw.cnt) {            // written before the verdict: a failed window is rerun and writes the same places again
@@ -305,7 +307,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                 coeff_last[(size_t)e * nb + blk_v] = lout;
                 if (ct == 0) {
                     unsigned int before = 0;
-                    for (int w = 0; w < warp - 1; w++) before += s_wcnt[n_ticks & 1u][w];
+                    for (int w = 0; w < hw; w++) before += s_wcnt[n_ticks & 1u][w];
                     coeff_unpred[(size_t)e * nb + ucount + before + __popc(zmask & ((1u << lane) - 1u))] = vcur;
                 }
             }
@@ -328,7 +330,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                     if (!(m <= 3.0e38f)) m = 3.0e38f;
 #pragma unroll
                     for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-                    if (lane == 0) s_wmag[warp - 1] = m;
+                    if (lane == 0) s_wmag[hw] = m;
                 }
                 // the step before the window (pipelined windows only): its lattice index under the same base
                 int kprev0 = 0; bool valid_prev0 = true;
@@ -468,7 +470,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
             { unsigned long long g1; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g1)); out->prof[6] = (unsigned int)(dbg_g0 / 1000ull); out->prof[7] = (unsigned int)(g1 / 1000ull); }
         }
     }
-    if (e == (int)gridDim.x - 1 && warp >= 1 && lane == 0) { atomicAdd(&out->n_pair, n_pair); atomicAdd(&out->n_full, n_full); if (warp == 1) out->kcyc_helper = (unsigned int)(cyc_h >> 10); }
+    if (e == (int)gridDim.x - 1 && helper && lane == 0) { atomicAdd(&out->n_pair, n_pair); atomicAdd(&out->n_full, n_full); if (hw == 0) out->kcyc_helper = (unsigned int)(cyc_h >> 10); }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -484,7 +486,9 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const u
     __shared__ __align__(16) T s_val[2][W];
     __shared__ __align__(16) T s_out[2][W];
     __shared__ unsigned int s_rm[2][W / 32];              // raw-value flags of a window, one bit per step (also: their count per warp)
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, h = tid - 32;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const bool helper = warp != 0 && warp != 4 && warp != 8;          // the serial thread keeps its scheduler to itself
+    const int hw = warp - 1 - (warp > 4 ? 1 : 0) - (warp > 8 ? 1 : 0), h = hw * 32 + lane;
     const int e = blockIdx.x;
     const T prec = e == 0 ? p0 : e == 1 ? p1 : e == 2 ? p2 : p3;
     const int rad = e == 0 ? r0_ : e == 1 ? r1_ : e == 2 ? r2_ : r3_;
@@ -498,11 +502,11 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const u
         const int sl = (int)(win & 1u);
         const bool z = in && tc == 0;
         const unsigned int zm = __ballot_sync(0xffffffffu, z);
-        if (lane == 0) s_rm[sl][warp - 1] = zm;
+        if (lane == 0) s_rm[sl][hw] = zm;
         lat_helper_bar();
         unsigned int before = 0, tot = 0;
 #pragma unroll
-        for (int q = 0; q < W / 32; q++) { const unsigned int c = __popc(s_rm[sl][q]); before += q < warp - 1 ? c : 0u; tot += c; }
+        for (int q = 0; q < W / 32; q++) { const unsigned int c = __popc(s_rm[sl][q]); before += q < hw ? c : 0u; tot += c; }
         T v = (T)0;
         if (z) v = cu_e[zrun + before + __popc(zm & ((1u << lane) - 1u))];
         else if (in) { const T dq = (T)(2 * (tc - rad)); v = dq * prec; }
@@ -510,7 +514,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const u
         zrun += tot;
     };
     int t_ahead = 1;                                       // helpers: this thread's code of the window after the next one, loaded a tick early
-    if (warp != 0) {
+    if (helper) {
         const bool in = (uint32_t)h < reg_count;
         prepare(0u, in ? (int)ct_e[h] : 1, in);
         const uint32_t p1 = (uint32_t)W + (uint32_t)h;
@@ -546,7 +550,7 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_chain_decode_kernel(const u
                     word(j + 1, b);
                 }
             }
-        } else {
+        } else if (helper) {
             // the next window's codes were loaded a tick ago; the ones after it are requested now
             const uint32_t pn = (w + 1) * W + (uint32_t)h;
             const bool in_n = w + 1 < nwin && pn < reg_count;
