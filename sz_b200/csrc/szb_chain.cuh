@@ -9,7 +9,7 @@
 // k_i = round((cur_i - base) / (2 prec)) has a closed form and code_i = k_i - k_{i-1} + 32768.  Floating point only moves `last`
 // off the lattice by a few ulps; that matters for the code when cur_i lies within this drift of the midpoint of two lattice
 // points, and it always matters for the bits of last_i.  One CTA per coefficient, windows of LAT_W steps, three stages that run
-// side by side on consecutive windows (one __syncthreads per window):
+// side by side on consecutive windows (two __syncthreads per window):
 //   (G1) helper thread h guesses the code of step h of the NEXT window from the closed form (double arithmetic, relative to the exact
 //       `last` that entered the window (S) is running) and prepares the step in up to three forms: SURE (one increment
 //       fl(2 dk * prec)); PAIR when cur_h may lie within the drift band of a midpoint -- two candidate codes of magnitudes n, n+1,
