@@ -246,24 +246,44 @@ def run_ours(args):
     recon = torch.empty_like(x)
 
     # N > 1: the gather of step i (NCCL, its own stream) runs beside the compress of step i + 1; stream and gather buffers alternate,
-    # and a buffer is reused only after the gather that read it has finished (the library orders itself after torch's current stream)
+    # and a buffer is reused only after the gather that read it has finished (the library orders itself after torch's current stream).
+    # The gather's host side (one read-back of the sizes, N broadcast launches) runs on a helper thread while the main thread is inside
+    # the next compress call (ctypes releases the interpreter lock there); all collectives are issued by that one thread, in step order.
     stream_bufs = [stream_buf, torch.empty(cap, dtype=torch.uint8, device="cuda")] if world > 1 else [stream_buf]
     gather_bufs = [torch.empty(world * (cap // 8), dtype=torch.uint8, device="cuda") for _ in range(2)] if world > 1 else None
     comm_stream = torch.cuda.Stream() if world > 1 else None
     gather_done = [None, None]
+    gather_fut = [None, None]
     step_no = [0]
+    pool = None
+    if world > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        pool = ThreadPoolExecutor(max_workers=1)
+
+    def gather_job(b, n):
+        torch.cuda.set_device(local)
+        with torch.cuda.stream(comm_stream):
+            slabs.gather_streams(stream_bufs[b], n, out=gather_bufs[b])
+            ev = torch.cuda.Event()
+            ev.record(comm_stream)
+        gather_done[b] = ev
+
+    def drain():
+        for b in range(2):
+            if gather_fut[b] is not None:
+                gather_fut[b].result()
+                gather_fut[b] = None
 
     def step():
         b = step_no[0] & 1 if world > 1 else 0
         step_no[0] += 1
-        if world > 1 and gather_done[b] is not None:
-            torch.cuda.current_stream().wait_event(gather_done[b])
+        if world > 1 and gather_fut[b] is not None:
+            gather_fut[b].result()                                  # the gather that last read this buffer has been queued ...
+            gather_fut[b] = None
+            torch.cuda.current_stream().wait_event(gather_done[b])   # ... and the library waits for it on the device
         n = sz_b200.compress_device(x, stream_bufs[b], sz_b200.REL, 1e-4, REL_BOUND)        # returns when the stream is complete
         if world > 1:
-            with torch.cuda.stream(comm_stream):
-                slabs.gather_streams(stream_bufs[b], n, out=gather_bufs[b])
-                gather_done[b] = torch.cuda.Event()
-                gather_done[b].record(comm_stream)
+            gather_fut[b] = pool.submit(gather_job, b, n)
         return n
 
     def barrier():
@@ -279,6 +299,7 @@ def run_ours(args):
 
     for _ in range(args.warmup):
         n = step()
+    drain()
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -288,6 +309,7 @@ def run_ours(args):
     ev0.record(lib_stream)
     for _ in range(args.steps):
         n = step()
+    drain()                                                         # every gather is queued: the closing event goes behind the last one
     # (the gather of an N>1 step is enqueued on the communication stream after the library's job has finished: the closing event goes
     #  where the last work of the last step went)
     ev1.record(lib_stream if world == 1 else comm_stream)
