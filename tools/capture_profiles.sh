@@ -11,4 +11,4 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:huff
 ncu -i gpurun_out/lat_full.ncu-rep --page raw --csv > gpurun_out/lat_full_raw.csv 2>/dev/null
 ncu -i gpurun_out/huff_full.ncu-rep --page raw --csv > gpurun_out/huff_full_raw.csv 2>/dev/null
 ls -la gpurun_out | tail -15
-tail -2 gpurun_out/ncu1.log gpurun_out/ncu2.log gpurun_out/ncu3.log
+for f in gpurun_out/ncu1.log gpurun_out/ncu2.log gpurun_out/ncu3.log; do tail -n 2 "$f"; done
