@@ -432,10 +432,12 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
                 continue;
             }
             if (v_ct >= 0) atomicAdd(hist_e + v_ct, 1u);   // the window has passed: its codes are final
-            unsigned int tot = 0;
+            if (helper) {                                  // (the count of unpredictable coefficients is the helpers' business)
+                unsigned int tot = 0;
 #pragma unroll
-            for (int w = 0; w < W / 32; w++) tot += s_wcnt[par][w];
-            ucount += tot;
+                for (int w = 0; w < W / 32; w++) tot += s_wcnt[par][w];
+                ucount += tot;
+            }
         }
         if (sw.valid) {
             const int wend = (int)s_slot[sw.slot].wend;
@@ -460,9 +462,9 @@ __global__ void __launch_bounds__(LAT_THREADS) coeff_lattice_kernel(const T *__r
     }
     __threadfence();                                 // every thread's histogram counts and stores, then the flag
     __syncthreads();
+    if (tid == 32) out->unpred_count[e] = ucount;          // (helper 0: the serial thread's warp does not keep the count)
     if (tid == 0) {
         if (done_flags) atomicExch(done_flags + e, 1u);
-        out->unpred_count[e] = ucount;
         if (e == (int)gridDim.x - 1) {
             out->passes = n_ticks; out->slow_chunks = n_redo; out->kcyc_serial = (unsigned int)(cyc_s >> 10);
             out->kcyc_total = (unsigned int)((clock64() - cyc_0) >> 10);
