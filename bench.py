@@ -410,7 +410,11 @@ def run_ours(args):
                          "traffic": traffic, "traffic_all_launches_of_one_step": traffic_step,
                          "traffic_over_algorithmic": None if not traffic_step else traffic_step / float(algo_bytes),
                          "traffic_source": traffic_src, "peak_source": peak_src,
-                         "algorithmic_bytes": algo_bytes, "kernel_ms": dom_ms, "job_frac": algo_bytes / (ms_step * 1e-3) / 1e9 / peak,
+                         "algorithmic_bytes": algo_bytes, "kernel_ms": dom_ms,
+                         "kernel_ms_source": ("the library's per-stage record: CUDA events on the launching stream; the coefficient-tree kernel is queued before the chain "
+                                              "kernel and waits on its SMs for the chain's flags, so its duration is read with %globaltimer inside the kernel, behind "
+                                              "that wait (events around the launch would add the chain's 1 ms)"),
+                         "job_frac": algo_bytes / (ms_step * 1e-3) / 1e9 / peak,
                          "note": "the dominant kernel is a serial dependency chain of the stream format (exact heap order decides the Huffman "
                                  "tree), bound by instruction latency on a few SMs, not by HBM: its fraction measures how far the step is from "
                                  "the bandwidth bound, not how well it uses bandwidth"},
